@@ -1,0 +1,65 @@
+/* pace_b200 — C ABI of the B200-native FV3 dycore hot path.
+ *
+ * This is the drop-in boundary: plain pointers and sizes, no torch / C++ types.
+ * The host-side mirror of the reference classes (pace_b200/dycore.py) binds these with ctypes; the
+ * reference-side binding a maintainer would add is shown in INTEGRATION.md.
+ *
+ * Conventions
+ *   - every call returns 0 on success, non-zero on failure; pace_b200_last_error() gives the text.
+ *   - all arrays are DEVICE pointers to fp64, owned by the caller (PyTorch), laid out
+ *       3-D: f[t][k][j][i]  (t = subdomain on this GPU, k in [0,npz], j in [0,ny+7), i in [0,sj))
+ *       2-D: f[t][j][i],  K-only: f[k]
+ *     with the reference's index convention: 3-cell halo, origin (3,3,0) (NDSL sizer.py:131-154).
+ *   - fields are registered once by name (the reference's own attribute names, e.g. "delp",
+ *     "ad.gz" for AcousticDynamics._gz, "grid.rarea" for GridData.rarea); module calls then take
+ *     only scalars, like the reference's __call__ signatures minus the arrays.
+ *   - calls are asynchronous on the stream given to pace_b200_set_stream (default stream 0).
+ */
+#ifndef PACE_B200_H
+#define PACE_B200_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* Subset of pyFV3.DynamicalCoreConfig (pyFV3/_config.py:143-281) read on the hot path, plus the
+ * subdomain geometry of NDSL SubtileGridSizer (sizer.py:20-154). */
+typedef struct pace_b200_config {
+  int npx, npy, npz;
+  int nx, ny;          /* compute cells per subdomain */
+  int n_tiles_local;   /* subdomains resident on this GPU */
+  int n_split, k_split;
+  int hord_dp, hord_mt, hord_tm, hord_tr, hord_vt;
+  int kord_mt, kord_tm, kord_tr, kord_wz;
+  int nord, n_sponge, nf_omega;
+  int grid_type;
+  int do_sat_adj, do_vort_damp, rf_fast, hydrostatic, convert_ke, fill, adiabatic, do_qa;
+  int use_old_omega, do_f3d, inline_q, nwat;
+  double dt_atmos;
+  double a_imp, beta, p_fac, d_con, d2_bg, d2_bg_k1, d2_bg_k2, d4_bg, dddmp, delt_max, ke_bg;
+  double rf_cutoff, tau, vtdm4, d_ext, consv_te;
+  double ptop, da_min, da_min_c;
+  int ks;
+} pace_b200_config;
+
+/* Row stride (elements) the library expects for a subdomain of nx compute cells. */
+int pace_b200_row_stride(int nx);
+
+/* Create a dycore instance for `cfg->n_tiles_local` subdomains on the current CUDA device.
+ * edge_flags[t]: bit0 west, bit1 east, bit2 south, bit3 north — whether subdomain t touches that
+ * edge of its cube tile (GridIndexing.west_edge..., NDSL dsl/stencil.py:560-620). */
+int pace_b200_create(const pace_b200_config* cfg, const unsigned char* edge_flags, void** handle);
+int pace_b200_destroy(void* handle);
+const char* pace_b200_last_error(void* handle);
+int pace_b200_set_stream(void* handle, void* cuda_stream);
+/* Register a caller-owned device array under the reference's attribute name. */
+int pace_b200_set_field(void* handle, const char* name, double* device_ptr);
+
+/* NonhydrostaticVerticalSolverCGrid.__call__ (pyFV3/stencils/riem_solver_c.py:200-278).
+ * in: csw.delpc csw.ptc ad.cappa q_con omga(w3) ad.ws3 phis(hs) ad.gz   out: ad.gz ad.pkc(pef) */
+int pace_b200_riem_solver_c(void* handle, double dt2);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

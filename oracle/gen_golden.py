@@ -1,0 +1,79 @@
+"""TEST INFRASTRUCTURE ONLY — generate the golden fixtures under tests/golden/ by running the
+UNMODIFIED reference (pyFV3 numpy backend, /root/reference) on 6 ranks in this container.
+
+    python oracle/gen_golden.py [--raw /tmp/pace_golden_raw] [--n-split 1]
+
+Writes
+  tests/golden/c12_rank0_stages[_ns<N>].npz : rank 0, one dycore step, C12 L79, config of
+        tests/main/fv3core/test_dycore_call.py:28-78 (== driver/examples/configs/baroclinic_c12.yaml):
+        initial contents of every watched array + for each module call the arrays it changed
+        (full arrays incl. halos).  Keys "<seq>:<name>", JSON label list in "__labels__".
+  tests/golden/c12_rank0_grid.npz           : metric terms / damping coefficients of rank 0
+  tests/golden/c12_6rank_grid.npz, c12_6rank_init.npz, c12_6rank_final.npz :
+        all six ranks (grid full arrays; state = compute domain only, halos are exchanged by the code
+        under test), for end-to-end parity of one full step with real halo exchange.
+The transcendentals of the oracle are pinned to glibc libm (see refshim/bootstrap.py).
+"""
+import argparse
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+from oracle.refshim.bootstrap import bootstrap  # noqa: E402
+
+bootstrap()
+import numpy as np  # noqa: E402
+
+from oracle.refshim.proc_comm import run_ranks  # noqa: E402
+from oracle.refshim.run_reference import default_config_kwargs, rank_main  # noqa: E402
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--raw", default="/tmp/pace_golden_raw")
+    ap.add_argument("--n-split", type=int, default=1)
+    ap.add_argument("--npx", type=int, default=13)
+    ap.add_argument("--steps", type=int, default=1)
+    ap.add_argument("--skip-run", action="store_true")
+    ap.add_argument("--stages-only", action="store_true")
+    args = ap.parse_args()
+    tag = "c%d" % (args.npx - 1)
+    suffix = "" if args.n_split == 1 else "_ns%d" % args.n_split
+    raw = args.raw + suffix
+    if not args.skip_run:
+        cfg = default_config_kwargs(npx=args.npx, n_split=args.n_split)
+        res = run_ranks(6, rank_main, (cfg, args.steps, (0,), raw), timeout=7200)
+        for r in res:
+            print(r)
+    out = os.path.join(ROOT, "tests", "golden")
+    os.makedirs(out, exist_ok=True)
+    st = np.load(os.path.join(raw, "rank0_stages.npz"))
+    np.savez_compressed(os.path.join(out, "%s_rank0_stages%s.npz" % (tag, suffix)), **{k: st[k] for k in st.files})
+    labels = json.loads(bytes(st["__labels__"]).decode())
+    for n, (label, changed) in enumerate(labels):
+        print(n, label, changed if n else "(%d arrays)" % len(changed))
+    if args.stages_only:
+        return
+    g0 = np.load(os.path.join(raw, "rank0_grid.npz"))
+    np.savez_compressed(os.path.join(out, "%s_rank0_grid.npz" % tag), **{k: g0[k] for k in g0.files})
+    grid, init, final = {}, {}, {}
+    for r in range(6):
+        g = np.load(os.path.join(raw, "rank%d_grid.npz" % r))
+        for k in g.files:
+            grid["%d:%s" % (r, k)] = g[k]
+        for src, dst in (("init", init), ("final", final)):
+            s = np.load(os.path.join(raw, "rank%d_%s.npz" % (r, src)))
+            for k in s.files:
+                a = s[k]
+                # compute domain (+1 for interface dims is kept: slice 3:-3 of the (n+7) allocation)
+                dst["%d:%s" % (r, k)] = a[3:-3, 3:-3] if a.ndim >= 2 else a
+    np.savez_compressed(os.path.join(out, "%s_6rank_grid.npz" % tag), **grid)
+    np.savez_compressed(os.path.join(out, "%s_6rank_init%s.npz" % (tag, suffix)), **init)
+    np.savez_compressed(os.path.join(out, "%s_6rank_final%s.npz" % (tag, suffix)), **final)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,75 @@
+"""ctypes binding of libpace_b200.so (C ABI in include/pace_b200.h).
+
+The CUDA library is the only compute path: if it is missing this module raises — there is no CPU or
+PyTorch fallback.
+"""
+import ctypes
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libpace_b200.so")
+
+_I = ctypes.c_int
+_D = ctypes.c_double
+
+
+class Config(ctypes.Structure):
+    """Mirror of `pace_b200_config` (include/pace_b200.h)."""
+
+    _fields_ = (
+        [(n, _I) for n in ("npx", "npy", "npz", "nx", "ny", "n_tiles_local", "n_split", "k_split")]
+        + [(n, _I) for n in ("hord_dp", "hord_mt", "hord_tm", "hord_tr", "hord_vt")]
+        + [(n, _I) for n in ("kord_mt", "kord_tm", "kord_tr", "kord_wz")]
+        + [(n, _I) for n in ("nord", "n_sponge", "nf_omega", "grid_type")]
+        + [(n, _I) for n in ("do_sat_adj", "do_vort_damp", "rf_fast", "hydrostatic", "convert_ke", "fill",
+                             "adiabatic", "do_qa", "use_old_omega", "do_f3d", "inline_q", "nwat")]
+        + [("dt_atmos", _D)]
+        + [(n, _D) for n in ("a_imp", "beta", "p_fac", "d_con", "d2_bg", "d2_bg_k1", "d2_bg_k2", "d4_bg", "dddmp",
+                             "delt_max", "ke_bg", "rf_cutoff", "tau", "vtdm4", "d_ext", "consv_te")]
+        + [(n, _D) for n in ("ptop", "da_min", "da_min_c")]
+        + [("ks", _I)]
+    )
+
+
+_lib = None
+
+
+def load():
+    """Load the shared library (raises if it has not been built)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            "pace_b200: %s is missing — build it with `python -m pace_b200.build`; "
+            "there is no CPU fallback" % LIB_PATH
+        )
+    _lib = bind(ctypes.CDLL(LIB_PATH))
+    return _lib
+
+
+def bind(lib):
+    """Declare argument/return types of every entry point of include/pace_b200.h."""
+    vp = ctypes.c_void_p
+    lib.pace_b200_row_stride.argtypes = [_I]
+    lib.pace_b200_row_stride.restype = _I
+    lib.pace_b200_create.argtypes = [ctypes.POINTER(Config), ctypes.c_char_p, ctypes.POINTER(vp)]
+    lib.pace_b200_destroy.argtypes = [vp]
+    lib.pace_b200_last_error.argtypes = [vp]
+    lib.pace_b200_last_error.restype = ctypes.c_char_p
+    lib.pace_b200_set_stream.argtypes = [vp, vp]
+    lib.pace_b200_set_field.argtypes = [vp, ctypes.c_char_p, vp]
+    for name, extra in MODULE_CALLS.items():
+        fn = getattr(lib, "pace_b200_" + name)
+        fn.argtypes = [vp] + extra
+        fn.restype = _I
+    return lib
+
+
+# module entry points: name -> scalar argument types after the handle
+MODULE_CALLS = {
+    "riem_solver_c": [_D],
+}
+
+EXPORTS = ["pace_b200_row_stride", "pace_b200_create", "pace_b200_destroy", "pace_b200_last_error",
+           "pace_b200_set_stream", "pace_b200_set_field"] + ["pace_b200_" + n for n in MODULE_CALLS]

@@ -1,0 +1,180 @@
+// pace_b200 — shared device/host helpers for the FV3 dycore kernels (sm_100a).
+//
+// Memory layout (all 3-D fields of all subdomains resident on this GPU):
+//     f[t][k][j][i]   i fastest, row stride sj (>= nx+7, padded), plane stride sk = sj*(ny+7),
+//                     subdomain ("tile") stride st3 = sk*(nz+1).
+// Index convention equals the reference's storage indices (NDSL sizer.py:131-154): 3-cell halo,
+// compute cells i in [3, 3+nx), interface dims one more.  2-D fields are f[t][j][i] (stride sk).
+//
+// Parity rule: every kernel keeps the reference's per-element expression tree and evaluation
+// order (GT4Py numpy semantics); the library is compiled with -fmad=false so nothing is contracted.
+#pragma once
+#ifdef PACE_HOST_EMU
+// Test-only host emulation (tests/hostemu.py): the SAME kernel source compiled by g++ with the launch
+// helpers turned into loops, so kernel logic can be debugged against the golden fixtures on a machine
+// without a GPU.  Never built or loaded by the product package.
+#include "host_emu.hpp"
+#else
+#include <cuda_runtime.h>
+#endif
+#include <cmath>
+#include <cstdint>
+#include <cstdio>
+
+namespace pace {
+
+constexpr int MAX_TILES = 32;
+constexpr int HALO = 3;
+
+enum EdgeBits : unsigned char { EDGE_W = 1, EDGE_E = 2, EDGE_S = 4, EDGE_N = 8 };
+
+// GFS constant set (reference NDSL/ndsl/constants.py:91-153, PACE_CONSTANTS default)
+constexpr double GRAV = 9.80665;
+constexpr double RDGAS = 287.05;
+constexpr double RVGAS = 461.50;
+constexpr double CP_AIR = 1004.6;
+constexpr double KAPPA = RDGAS / CP_AIR;
+constexpr double CV_AIR = CP_AIR - RDGAS;
+constexpr double RDG = -RDGAS / GRAV;
+constexpr double K1K = RDGAS / CV_AIR;
+constexpr double ZVIR = RVGAS / RDGAS - 1;
+constexpr double CV_VAP = 3.0 * RVGAS;
+constexpr double CP_VAP = 4.0 * RVGAS;
+constexpr double C_ICE = 1972.0;
+constexpr double C_LIQ = 4.1855e3;
+constexpr double TICE = 273.16;
+constexpr double DZ_MIN = 2.0;
+constexpr double HUGE_R = 1.0e40;
+
+struct Geo {
+  int nx, ny, nz, nt;   // compute cells per subdomain, number of subdomains on this GPU
+  int sj, sk;           // row / plane strides (elements)
+  long long st3;        // subdomain stride of 3-D fields
+  int is, ie, js, je;   // first/last compute cell (3, nx+2, 3, ny+2)
+  unsigned char edge[MAX_TILES];  // EdgeBits per subdomain: does it touch the tile edge?
+};
+
+// One grid point handed to a stencil body.
+struct Pt {
+  long long o;   // linear offset of (t,k,j,i) in 3-D fields
+  int o2;        // linear offset of (t,j,i) in 2-D fields
+  int i, j, k, t;
+  int sj, sk;
+  bool W, E, S, N;  // subdomain touches west/east/south/north tile edge
+};
+
+__device__ __forceinline__ Pt make_pt(const Geo& g, int t, int i, int j, int k) {
+  Pt p;
+  p.i = i; p.j = j; p.k = k; p.t = t;
+  p.sj = g.sj; p.sk = g.sk;
+  p.o2 = t * g.sk + j * g.sj + i;
+  p.o = (long long)t * g.st3 + (long long)k * g.sk + j * g.sj + i;
+  unsigned char e = g.edge[t];
+  p.W = e & EDGE_W; p.E = e & EDGE_E; p.S = e & EDGE_S; p.N = e & EDGE_N;
+  return p;
+}
+
+// field access relative to the current point `p`
+#define A(f, di, dj, dk) (f)[p.o + (di) + (dj) * p.sj + (long long)(dk) * p.sk]
+#define A0(f) (f)[p.o]
+#define A2(f, di, dj) (f)[p.o2 + (di) + (dj) * p.sj]
+#define A20(f) (f)[p.o2]
+
+struct Box {
+  int i0, j0, k0, ni, nj, nk;
+};
+
+#ifndef PACE_HOST_EMU
+template <class F>
+__global__ void __launch_bounds__(256) k_ijk(Geo g, Box b, F f) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  int j = blockIdx.y * blockDim.y + threadIdx.y;
+  if (i >= b.ni || j >= b.nj) return;
+  int k = blockIdx.z % b.nk, t = blockIdx.z / b.nk;
+  Pt p = make_pt(g, t, b.i0 + i, b.j0 + j, b.k0 + k);
+  f(p);
+}
+
+// column kernels: one thread per (t,j,i); the body loops over k itself (p.k = b.k0)
+template <class F>
+__global__ void __launch_bounds__(128) k_ij(Geo g, Box b, F f) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  int j = blockIdx.y * blockDim.y + threadIdx.y;
+  if (i >= b.ni || j >= b.nj) return;
+  int t = blockIdx.z;
+  Pt p = make_pt(g, t, b.i0 + i, b.j0 + j, b.k0);
+  f(p);
+}
+
+template <class F>
+inline void launch_ijk(cudaStream_t s, const Geo& g, Box b, F f) {
+  if (b.ni <= 0 || b.nj <= 0 || b.nk <= 0) return;
+  dim3 blk(32, 8, 1);
+  dim3 grd((b.ni + 31) / 32, (b.nj + 7) / 8, b.nk * g.nt);
+  k_ijk<<<grd, blk, 0, s>>>(g, b, f);
+}
+
+template <class F>
+inline void launch_ij(cudaStream_t s, const Geo& g, Box b, F f) {
+  if (b.ni <= 0 || b.nj <= 0) return;
+  dim3 blk(32, 4, 1);
+  dim3 grd((b.ni + 31) / 32, (b.nj + 3) / 4, g.nt);
+  k_ij<<<grd, blk, 0, s>>>(g, b, f);
+}
+
+#else   // PACE_HOST_EMU: plain loops, same iteration space
+template <class F>
+inline void launch_ijk(cudaStream_t, const Geo& g, Box b, F f) {
+  for (int t = 0; t < g.nt; ++t)
+    for (int k = 0; k < b.nk; ++k)
+      for (int j = 0; j < b.nj; ++j)
+        for (int i = 0; i < b.ni; ++i) f(make_pt(g, t, b.i0 + i, b.j0 + j, b.k0 + k));
+}
+template <class F>
+inline void launch_ij(cudaStream_t, const Geo& g, Box b, F f) {
+  for (int t = 0; t < g.nt; ++t)
+    for (int j = 0; j < b.nj; ++j)
+      for (int i = 0; i < b.ni; ++i) f(make_pt(g, t, b.i0 + i, b.j0 + j, b.k0));
+}
+#endif
+
+// ---- boxes in the reference's vocabulary (GridIndexing.get_origin_domain, stencil.py:768-788) -----
+// compute domain of a staggering, grown by halos; xi/yi/zi = interface dims (+1 extent)
+inline Box box_dims(const Geo& g, bool xi, bool yi, bool zi, int hx = 0, int hy = 0) {
+  Box b;
+  b.i0 = HALO - hx; b.j0 = HALO - hy; b.k0 = 0;
+  b.ni = g.nx + (xi ? 1 : 0) + 2 * hx;
+  b.nj = g.ny + (yi ? 1 : 0) + 2 * hy;
+  b.nk = g.nz + (zi ? 1 : 0);
+  return b;
+}
+inline Box box_full(const Geo& g, int addk = 0) {  // origin_full / domain_full(add=(0,0,addk))
+  return Box{0, 0, 0, g.nx + 2 * HALO, g.ny + 2 * HALO, g.nz + addk};
+}
+inline Box box_compute(const Geo& g, int oi = 0, int oj = 0, int ai = 0, int aj = 0, int ak = 0) {
+  return Box{HALO + oi, HALO + oj, 0, g.nx + ai, g.ny + aj, g.nz + ak};
+}
+
+// ---- math: single point of definition for the transcendentals (parity) -------------
+__device__ __forceinline__ double fv_exp(double x) { return exp(x); }
+__device__ __forceinline__ double fv_log(double x) { return log(x); }
+__device__ __forceinline__ double fv_pow(double x, double y) { return pow(x, y); }
+__device__ __forceinline__ double fv_sqrt(double x) { return sqrt(x); }
+__device__ __forceinline__ double fv_abs(double x) { return fabs(x); }
+// gtscript min/max/sign as the numpy backend evaluates them (np.minimum/np.maximum semantics on
+// non-NaN data; sign(a,b) = |a| if b>=0 else -|a|, basic_operations.py:32-45)
+__device__ __forceinline__ double fv_min(double a, double b) { return a < b ? a : b; }
+__device__ __forceinline__ double fv_max(double a, double b) { return a > b ? a : b; }
+
+#define CUDA_CHECK_RET(call)                                                              \
+  do {                                                                                    \
+    cudaError_t e_ = (call);                                                              \
+    if (e_ != cudaSuccess) {                                                              \
+      ::pace::set_error("%s:%d: %s: %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); \
+      return 1;                                                                           \
+    }                                                                                     \
+  } while (0)
+
+void set_error(const char* fmt, ...);
+
+}  // namespace pace

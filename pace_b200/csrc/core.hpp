@@ -1,0 +1,52 @@
+// pace_b200 — host-side state of one dycore instance (all subdomains resident on one GPU).
+#pragma once
+#include <map>
+#include <string>
+#include <vector>
+
+#include "common.cuh"
+
+namespace pace {
+
+// Mirrors the subset of pyFV3.DynamicalCoreConfig (_config.py:143-281) the hot path reads.
+struct Config {
+  int npx, npy, npz;       // tile size + 1, levels
+  int nx, ny;              // subdomain compute size
+  int n_tiles_local;       // subdomains on this GPU
+  int n_split, k_split;
+  int hord_dp, hord_mt, hord_tm, hord_tr, hord_vt;
+  int kord_mt, kord_tm, kord_tr, kord_wz;
+  int nord, n_sponge, nf_omega;
+  int grid_type;
+  int do_sat_adj, do_vort_damp, rf_fast, hydrostatic, convert_ke, fill, adiabatic, do_qa;
+  int use_old_omega, do_f3d, inline_q, nwat;
+  double dt_atmos;
+  double a_imp, beta, p_fac, d_con, d2_bg, d2_bg_k1, d2_bg_k2, d4_bg, dddmp, delt_max, ke_bg;
+  double rf_cutoff, tau, vtdm4, d_ext, consv_te;
+  double ptop, da_min, da_min_c;
+  int ks;
+};
+
+struct Core {
+  Config cfg;
+  Geo g;
+  cudaStream_t stream = 0;
+  std::map<std::string, double*> fields;    // caller-owned device arrays (state, grid, temporaries)
+  std::map<std::string, double*> scratch;   // library-owned 3-D scratch, allocated on first use
+  std::vector<void*> owned;
+  std::string err;
+
+  double* F(const char* name);              // caller-registered field, error if missing
+  double* S(const char* name);              // zero-initialised library scratch field [nt][nz+1][ny+7][sj]
+  bool has(const char* name) const { return fields.count(name) != 0; }
+  size_t field_elems() const { return (size_t)g.st3 * g.nt; }
+  ~Core();
+};
+
+// ---- module entry points (one per reference class / stencil group) -------------------------------
+int riem_solver_c(Core& c, double dt2);
+int c_sw(Core& c, double dt2);
+int update_dz_c(Core& c, double dt2);
+int p_grad_c(Core& c, double dt2);
+
+}  // namespace pace

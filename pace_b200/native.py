@@ -1,0 +1,127 @@
+"""NativeCore: owns the device buffers (PyTorch tensors) of all subdomains resident on one GPU and
+drives libpace_b200 through the C ABI.
+
+Layout (see csrc/common.cuh): 3-D fields are torch tensors of shape (nt, npz+1, ny+7, sj), fp64,
+i fastest, i.e. the transpose of the reference's numpy-backend (i, j, k) storage
+(gt4py storage/cartesian/layout.py:143-149) padded to the library's row stride.
+"""
+import ctypes
+
+import numpy as np
+import torch
+
+from . import _lib
+
+DEFAULTS = dict(
+    n_split=1, k_split=1, hord_dp=6, hord_mt=6, hord_tm=6, hord_tr=8, hord_vt=6, kord_mt=9, kord_tm=-9,
+    kord_tr=9, kord_wz=9, nord=3, n_sponge=48, nf_omega=1, grid_type=0, do_sat_adj=1, do_vort_damp=1, rf_fast=1,
+    hydrostatic=0, convert_ke=0, fill=1, adiabatic=0, do_qa=1, use_old_omega=1, do_f3d=0, inline_q=0, nwat=6,
+    dt_atmos=225.0, a_imp=1.0, beta=0.0, p_fac=0.05, d_con=1.0, d2_bg=0.0, d2_bg_k1=0.2, d2_bg_k2=0.1,
+    d4_bg=0.15, dddmp=0.5, delt_max=0.002, ke_bg=0.0, rf_cutoff=3000.0, tau=10.0, vtdm4=0.06, d_ext=0.0,
+    consv_te=0.0, ptop=300.0, da_min=0.0, da_min_c=0.0, ks=18,
+)
+
+
+class NativeError(RuntimeError):
+    pass
+
+
+class NativeCore:
+    def __init__(self, nx, ny, npz, n_tiles=1, edge_flags=None, device="cuda:0", _lib_handle=None, **cfg):
+        # _lib_handle: dependency injection for tests/hostemu.py only (kernel sources compiled for the
+        # host to debug logic without a GPU); the product always loads the CUDA library.
+        self.lib = _lib_handle if _lib_handle is not None else _lib.load()
+        self.device = torch.device(device)
+        if _lib_handle is None:
+            if not torch.cuda.is_available() or self.device.type != "cuda":
+                raise NativeError("pace_b200 needs a CUDA device (there is no CPU fallback)")
+            torch.cuda.set_device(self.device)
+        self.nx, self.ny, self.npz, self.nt = nx, ny, npz, n_tiles
+        self.sj = self.lib.pace_b200_row_stride(nx)
+        self.nj = ny + 7
+        c = _lib.Config()
+        vals = dict(DEFAULTS)
+        vals.update(cfg)
+        vals.update(nx=nx, ny=ny, npz=npz, n_tiles_local=n_tiles)
+        vals.setdefault("npx", nx + 1)
+        vals.setdefault("npy", ny + 1)
+        for name, ctype in _lib.Config._fields_:
+            v = vals[name]
+            setattr(c, name, int(v) if ctype is ctypes.c_int else float(v))
+        self.cfg = vals
+        flags = bytes(edge_flags if edge_flags is not None else [15] * n_tiles)
+        self.handle = ctypes.c_void_p()
+        rc = self.lib.pace_b200_create(ctypes.byref(c), flags, ctypes.byref(self.handle))
+        if rc != 0:
+            raise NativeError(self.lib.pace_b200_last_error(None).decode())
+        self.t = {}  # name -> torch tensor
+        if self.device.type == "cuda":
+            self.lib.pace_b200_set_stream(self.handle, ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
+
+    def __del__(self):
+        h = getattr(self, "handle", None)
+        if h:
+            self.lib.pace_b200_destroy(h)
+            self.handle = None
+
+    # -- buffers ---------------------------------------------------------------------------------
+    def _register(self, name, tensor):
+        self.t[name] = tensor
+        self.lib.pace_b200_set_field(self.handle, name.encode(), ctypes.c_void_p(tensor.data_ptr()))
+        return tensor
+
+    def alloc3(self, name, fill=0.0):
+        return self._register(
+            name, torch.full((self.nt, self.npz + 1, self.nj, self.sj), fill, dtype=torch.float64, device=self.device)
+        )
+
+    def alloc2(self, name):
+        return self._register(name, torch.zeros((self.nt, self.nj, self.sj), dtype=torch.float64, device=self.device))
+
+    def allock(self, name, n=None):
+        return self._register(name, torch.zeros((n or self.npz + 1,), dtype=torch.float64, device=self.device))
+
+    def put(self, name, arrays):
+        """arrays: per-subdomain list of reference-layout numpy arrays (i,j,k) / (i,j) / (k,)."""
+        a0 = np.asarray(arrays[0])
+        if a0.ndim == 1:
+            t = self.t.get(name)
+            if t is None:
+                t = self.allock(name, a0.shape[0])
+            t.copy_(torch.from_numpy(np.ascontiguousarray(a0, dtype=np.float64)))
+            return t
+        t = self.t.get(name)
+        if t is None:
+            t = self.alloc3(name) if a0.ndim == 3 else self.alloc2(name)
+        host = np.zeros(tuple(t.shape), dtype=np.float64)
+        for n, a in enumerate(arrays):
+            a = np.asarray(a, dtype=np.float64)
+            if a.ndim == 3:
+                ni, nj, nk = a.shape
+                host[n, :nk, :nj, :ni] = a.transpose(2, 1, 0)
+            else:
+                ni, nj = a.shape
+                host[n, :nj, :ni] = a.T
+        t.copy_(torch.from_numpy(host))
+        return t
+
+    def get(self, name):
+        """Back to the reference layout: list over subdomains of (i,j,k) / (i,j) arrays."""
+        t = self.t[name].cpu().numpy()
+        ni = self.nx + 7
+        if t.ndim == 4:
+            return [np.ascontiguousarray(t[n, :, :, :ni].transpose(2, 1, 0)) for n in range(self.nt)]
+        if t.ndim == 3:
+            return [np.ascontiguousarray(t[n, :, :ni].T) for n in range(self.nt)]
+        return [t]
+
+    # -- calls -----------------------------------------------------------------------------------
+    def call(self, name, *scalars):
+        fn = getattr(self.lib, "pace_b200_" + name)
+        rc = fn(self.handle, *scalars)
+        if rc != 0:
+            raise NativeError("%s: %s" % (name, self.lib.pace_b200_last_error(self.handle).decode()))
+
+    def sync(self):
+        if self.device.type == "cuda":
+            torch.cuda.synchronize(self.device)

@@ -1,0 +1,58 @@
+"""Run one module entry point of the C ABI on the state the reference had just before the same call
+(golden stage log) and compare everything it changed — and that it changed nothing else."""
+import numpy as np
+
+from tests.golden_util import report
+
+DT_ATMOS = 225.0
+DT = DT_ATMOS  # k_split = n_split = 1 in the golden config
+DT2 = 0.5 * DT
+
+
+def make_core(backend, nx=12, ny=12, npz=79, **kw):
+    from pace_b200.native import NativeCore
+
+    if backend == "hostemu":
+        from tests import hostemu
+
+        return NativeCore(nx, ny, npz, device="cpu", _lib_handle=hostemu.load(), **kw)
+    return NativeCore(nx, ny, npz, device="cuda:0", **kw)
+
+
+def load_state(core, state, grid):
+    for name, arr in state.items():
+        core.put(name, [arr])
+    for name, arr in grid.items():
+        if np.ndim(arr) > 0:
+            core.put(name, [arr])
+
+
+def check_module(backend, golden, grid, stage, call, args, tol=0.0, near_zero=0.0, cfg=None, skip=()):
+    cfg = dict(cfg or {})
+    cfg.setdefault("ptop", float(grid["grid.ptop"]))
+    cfg.setdefault("da_min", float(grid["damp.da_min"]))
+    cfg.setdefault("da_min_c", float(grid["damp.da_min_c"]))
+    core = make_core(backend, **cfg)
+    before = golden.before(stage)
+    load_state(core, before, grid)
+    core.call(call, *args)
+    core.sync()
+    after = golden.after(stage)
+    changed = golden.changed_by(stage)
+    results = {}
+    worst = 0.0
+    for name in before:
+        if name in skip:
+            continue
+        got = core.get(name)[0]
+        want = after[name]
+        err, nbad = report(name, got, want, near_zero)
+        results[name] = (err, nbad, name in changed)
+        worst = max(worst, err)
+    msg = "\n".join(
+        "  %-16s %s max_rel=%.3e non-identical=%d" % (n, "out" if c else "   ", e, b)
+        for n, (e, b, c) in sorted(results.items()) if c or b
+    )
+    print("[%s/%s]\n%s" % (backend, stage, msg))
+    assert worst <= tol, "parity failed for %s (tol %g):\n%s" % (stage, tol, msg)
+    return results
