@@ -59,6 +59,18 @@ int pace_b200_set_field(void* handle, const char* name, double* device_ptr);
  * in: csw.delpc csw.ptc ad.cappa q_con omga(w3) ad.ws3 phis(hs) ad.gz   out: ad.gz ad.pkc(pef) */
 int pace_b200_riem_solver_c(void* handle, double dt2);
 
+/* CGridShallowWaterDynamics.__call__ (pyFV3/stencils/c_sw.py:644-807) incl. DGrid2AGrid2CGridVectors
+ * (d2a2c_vect.py:588-699).  in: delp pt u v w   out: uc vc ua va ad.ut ad.vt ad.divgd omga csw.delpc
+ * csw.ptc (and the halo corners of delp, pt, w, as in the reference) */
+int pace_b200_c_sw(void* handle, double dt2);
+
+/* UpdateGeopotentialHeightOnCGrid.__call__ (pyFV3/stencils/updatedzc.py:185-226).
+ * in: ad.zs ad.ut ad.vt ad.gz grid.area grid.dp_ref   out: ad.gz ad.ws3 */
+int pace_b200_update_dz_c(void* handle, double dt2);
+
+/* p_grad_c_stencil (pyFV3/stencils/dyn_core.py:122-173).  in: csw.delpc ad.pkc ad.gz   inout: uc vc */
+int pace_b200_p_grad_c(void* handle, double dt2);
+
 #ifdef __cplusplus
 }
 #endif

@@ -69,6 +69,9 @@ def bind(lib):
 # module entry points: name -> scalar argument types after the handle
 MODULE_CALLS = {
     "riem_solver_c": [_D],
+    "c_sw": [_D],
+    "update_dz_c": [_D],
+    "p_grad_c": [_D],
 }
 
 EXPORTS = ["pace_b200_row_stride", "pace_b200_create", "pace_b200_destroy", "pace_b200_last_error",

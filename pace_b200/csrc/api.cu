@@ -112,5 +112,8 @@ int pace_b200_set_field(void* h, const char* name, double* p) {
   return finish(c, (call));
 
 int pace_b200_riem_solver_c(void* h, double dt2) { ENTRY(riem_solver_c(*c, dt2)) }
+int pace_b200_c_sw(void* h, double dt2) { ENTRY(c_sw(*c, dt2)) }
+int pace_b200_update_dz_c(void* h, double dt2) { ENTRY(update_dz_c(*c, dt2)) }
+int pace_b200_p_grad_c(void* h, double dt2) { ENTRY(p_grad_c(*c, dt2)) }
 
 }  // extern "C"

@@ -3,5 +3,8 @@
 from tests.module_harness import DT, DT2
 
 CASES = {
+    "c_sw": dict(stage="c_sw", call="c_sw", args=(DT2,), tol=0.0),
+    "updatedzc": dict(stage="updatedzc", call="update_dz_c", args=(DT2,), tol=0.0),
+    "p_grad_c": dict(stage="p_grad_c", call="p_grad_c", args=(DT2,), tol=0.0),
     "riem_solver_c": dict(stage="riem_solver_c", call="riem_solver_c", args=(DT2,), tol=1e-11, tol_host=0.0),
 }
