@@ -55,6 +55,11 @@ int pace_b200_set_stream(void* handle, void* cuda_stream);
 /* Register a caller-owned device array under the reference's attribute name. */
 int pace_b200_set_field(void* handle, const char* name, double* device_ptr);
 
+/* Set a small per-level (K) column from HOST memory, e.g. the column namelist of d_sw
+ * (pyFV3/stencils/d_sw.py:647-691: "col.nord", "col.nord_v", "col.damp_vt", ...) or the delnflux damping
+ * columns (delnflux.py:22-38).  The library keeps a host copy and a device copy under `name`. */
+int pace_b200_set_column(void* handle, const char* name, const double* host_values, int n);
+
 /* NonhydrostaticVerticalSolverCGrid.__call__ (pyFV3/stencils/riem_solver_c.py:200-278).
  * in: csw.delpc csw.ptc ad.cappa q_con omga(w3) ad.ws3 phis(hs) ad.gz   out: ad.gz ad.pkc(pef) */
 int pace_b200_riem_solver_c(void* handle, double dt2);
@@ -70,6 +75,33 @@ int pace_b200_update_dz_c(void* handle, double dt2);
 
 /* p_grad_c_stencil (pyFV3/stencils/dyn_core.py:122-173).  in: csw.delpc ad.pkc ad.gz   inout: uc vc */
 int pace_b200_p_grad_c(void* handle, double dt2);
+
+/* FiniteVolumeFluxPrep.__call__ (pyFV3/stencils/fxadv.py:590-691).
+ * in: uc vc   out: ad.crx ad.cry ad.xfx ad.yfx dsw.uc_contra dsw.vc_contra */
+int pace_b200_fv_prep(void* handle, double dt);
+
+/* DGridShallowWaterLagrangianDynamics.__call__ (pyFV3/stencils/d_sw.py:997-1303).
+ * inout: delp pt u v w uc vc q_con mfxd mfyd cxd cyd ad.heat_source diss_estd ad.divgd ad.vt(delpc)
+ * in: ua va ad.zh   out: ad.crx ad.cry ad.xfx ad.yfx */
+int pace_b200_d_sw(void* handle, double dt);
+
+/* FiniteVolumeTransport.__call__ (pyFV3/stencils/fvtp2d.py:251-368) on registered fields; optional
+ * arguments are "" (or NULL).  nord_col/damp select the DelnFlux damping (fvtp2d.py:168-180). */
+int pace_b200_fvtp2d(void* handle, const char* q, const char* crx, const char* cry, const char* xfx,
+                     const char* yfx, const char* fx, const char* fy, const char* x_mass_flux,
+                     const char* y_mass_flux, const char* mass, int hord, const char* nord_col,
+                     const char* damp, int nk);
+
+/* DelnFluxNoSG.__call__ (pyFV3/stencils/delnflux.py:1243-1278). */
+int pace_b200_delnflux_nosg(void* handle, const char* q, const char* fx2, const char* fy2, const char* damp,
+                            const char* d2, const char* nord_col, int nk);
+
+/* AGrid2BGridFourthOrder.__call__ (pyFV3/stencils/a2b_ord4.py:715-808) on levels [k0, k0+nk). */
+int pace_b200_a2b_ord4(void* handle, const char* qin, const char* qout, int k0, int nk, int replace);
+
+/* DivergenceDamping.__call__ (pyFV3/stencils/divergence_damping.py:549-713). */
+int pace_b200_divergence_damping(void* handle, const char* vort_b, const char* delpc, const char* ke,
+                                 const char* vort_a, double dt);
 
 #ifdef __cplusplus
 }

@@ -39,13 +39,16 @@ def main():
     ap.add_argument("--steps", type=int, default=1)
     ap.add_argument("--skip-run", action="store_true")
     ap.add_argument("--stages-only", action="store_true")
+    ap.add_argument("--deep", action="store_true", help="also hook d_sw/updatedzd/nh_p_grad internals (dev only)")
     args = ap.parse_args()
     tag = "c%d" % (args.npx - 1)
     suffix = "" if args.n_split == 1 else "_ns%d" % args.n_split
+    if args.deep:
+        suffix += "_deep"
     raw = args.raw + suffix
     if not args.skip_run:
         cfg = default_config_kwargs(npx=args.npx, n_split=args.n_split)
-        res = run_ranks(6, rank_main, (cfg, args.steps, (0,), raw), timeout=7200)
+        res = run_ranks(6, rank_main, (cfg, args.steps, (0,), raw, 0, args.deep), timeout=7200)
         for r in res:
             print(r)
     out = os.path.join(ROOT, "tests", "golden")

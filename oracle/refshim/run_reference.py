@@ -141,11 +141,47 @@ def state_arrays(state):
     return out
 
 
-def instrument(dycore, state):
+def instrument_deep(dycore, state, rec_watch, wrap):
+    """Finer-grained hooks inside d_sw / updatedzd / nh_p_grad (development + sub-module fixtures)."""
+    ad = dycore.acoustic_dynamics
+    dsw = ad.dgrid_shallow_water_lagrangian_dynamics
+    for n in ("_tmp_heat_s", "_tmp_diss_e", "_vort_x_delta", "_vort_y_delta", "_dt_kinetic_energy_on_cell_corners",
+              "_abs_vorticity_agrid", "_damped_rel_vorticity_agrid", "_uc_contra", "_vc_contra", "_tmp_ut", "_tmp_vt",
+              "_tmp_fx", "_tmp_fy", "_tmp_gx", "_tmp_gy", "_tmp_dw", "_tmp_wk", "_vorticity_agrid",
+              "_vorticity_bgrid_damped", "_tmp_fx2", "_tmp_fy2"):
+        rec_watch["dsw." + n.lstrip("_")] = getattr(dsw, n)
+    for n in ("fv_prep", "fvtp2d_dp", "_flux_capacitor_stencil", "delnflux_nosg_w", "_heat_diss_stencil",
+              "fvtp2d_vt_nodelnflux", "_apply_fluxes", "fvtp2d_dp_t", "fvtp2d_tm", "_apply_pt_delp_fluxes",
+              "_adjust_w_and_qcon_stencil", "_compute_kinetic_energy", "_compute_vorticity_stencil",
+              "divergence_damping", "_rel_vorticity_to_abs", "_u_and_v_from_ke_stencil", "delnflux_nosg_v",
+              "_vort_differencing_stencil", "_heat_source_from_vorticity_damping_stencil",
+              "_accumulate_heat_source_and_dissipation_estimate_stencil", "_update_u_and_v_stencil"):
+        wrap(dsw, n, "dsw." + n.lstrip("_"))
+    dd = dsw.divergence_damping
+    for n in dir(dd):
+        v = getattr(dd, n, None)
+        if n.startswith("_") and not n.startswith("__") and hasattr(v, "data") and hasattr(v, "dims") and len(v.dims) == 3:
+            rec_watch["dd." + n.lstrip("_")] = v
+    dzd = ad.update_height_on_d_grid
+    for n in dir(dzd):
+        v = getattr(dzd, n, None)
+        if n.startswith("_") and not n.startswith("__") and hasattr(v, "data") and hasattr(v, "dims") and len(v.dims) >= 2:
+            rec_watch["dzd." + n.lstrip("_")] = v
+    nh = ad.nonhydrostatic_pressure_gradient
+    for n in dir(nh):
+        v = getattr(nh, n, None)
+        if n.startswith("_") and not n.startswith("__") and hasattr(v, "data") and hasattr(v, "dims") and len(v.dims) == 3:
+            rec_watch["nh." + n.lstrip("_")] = v
+
+
+def instrument(dycore, state, deep=False):
     """Wrap the module-level callables of one dycore and return the Recorder."""
     ad = dycore.acoustic_dynamics
     csw = ad.cgrid_shallow_water_lagrangian_dynamics
     watch = dict(state_arrays(state))
+    pending = []
+    if deep:
+        instrument_deep(dycore, state, watch, lambda parent, attr, label: pending.append((parent, attr, label)))
     for n in ("_ut", "_vt", "_gz", "_zh", "_pkc", "_pk3", "_pem", "_divgd", "_heat_source", "_crx", "_cry", "_xfx",
               "_yfx", "_ws3", "cappa"):
         watch["ad." + n.lstrip("_")] = getattr(ad, n)
@@ -160,6 +196,8 @@ def instrument(dycore, state):
     def wrap(parent, attr, label):
         setattr(parent, attr, _Wrapped(getattr(parent, attr), label, rec))
 
+    for parent, attr, label in pending:
+        wrap(parent, attr, label)
     wrap(dycore, "_fv_setup_stencil", "fv_setup")
     wrap(dycore, "_pt_to_potential_density_pt", "pt_to_potential_density_pt")
     wrap(dycore, "acoustic_dynamics", "acoustic_dynamics")
@@ -190,7 +228,7 @@ def instrument(dycore, state):
     return rec
 
 
-def rank_main(mpi_comm, cfg_kwargs, n_steps=1, record_ranks=(0,), out_dir=None, time_steps=0):
+def rank_main(mpi_comm, cfg_kwargs, n_steps=1, record_ranks=(0,), out_dir=None, time_steps=0, deep=False):
     """Body of one rank. Returns a dict of small results; large data goes to out_dir/*.npz."""
     import os
 
@@ -205,7 +243,7 @@ def rank_main(mpi_comm, cfg_kwargs, n_steps=1, record_ranks=(0,), out_dir=None, 
     t_build = time.time() - t0
     res = {"rank": rank, "build_s": t_build}
     init = {k: v.copy() for k, v in state_arrays(state).items()}
-    rec = instrument(dycore, state) if rank in record_ranks else None
+    rec = instrument(dycore, state, deep) if rank in record_ranks else None
     step_s = []
     for s in range(n_steps):
         t0 = time.time()

@@ -11,6 +11,7 @@ LIB_PATH = os.path.join(HERE, "libpace_b200.so")
 
 _I = ctypes.c_int
 _D = ctypes.c_double
+_S = ctypes.c_char_p
 
 
 class Config(ctypes.Structure):
@@ -59,6 +60,7 @@ def bind(lib):
     lib.pace_b200_last_error.restype = ctypes.c_char_p
     lib.pace_b200_set_stream.argtypes = [vp, vp]
     lib.pace_b200_set_field.argtypes = [vp, ctypes.c_char_p, vp]
+    lib.pace_b200_set_column.argtypes = [vp, ctypes.c_char_p, ctypes.POINTER(ctypes.c_double), _I]
     for name, extra in MODULE_CALLS.items():
         fn = getattr(lib, "pace_b200_" + name)
         fn.argtypes = [vp] + extra
@@ -72,7 +74,13 @@ MODULE_CALLS = {
     "c_sw": [_D],
     "update_dz_c": [_D],
     "p_grad_c": [_D],
+    "fv_prep": [_D],
+    "d_sw": [_D],
+    "fvtp2d": [_S] * 10 + [_I, _S, _S, _I],
+    "delnflux_nosg": [_S] * 6 + [_I],
+    "a2b_ord4": [_S, _S, _I, _I, _I],
+    "divergence_damping": [_S, _S, _S, _S, _D],
 }
 
 EXPORTS = ["pace_b200_row_stride", "pace_b200_create", "pace_b200_destroy", "pace_b200_last_error",
-           "pace_b200_set_stream", "pace_b200_set_field"] + ["pace_b200_" + n for n in MODULE_CALLS]
+           "pace_b200_set_stream", "pace_b200_set_field", "pace_b200_set_column"] + ["pace_b200_" + n for n in MODULE_CALLS]

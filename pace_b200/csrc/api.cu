@@ -4,6 +4,7 @@
 
 #include "../../include/pace_b200.h"
 #include "core.hpp"
+#include "transport.hpp"
 
 namespace pace {
 
@@ -41,6 +42,23 @@ double* Core::S(const char* name) {
   owned.push_back(ptr);
   scratch[name] = (double*)ptr;
   return (double*)ptr;
+}
+
+const std::vector<double>* Core::H(const char* name) {
+  auto it = hcol.find(name);
+  if (it == hcol.end()) {
+    if (err.empty()) err = std::string("column not set: ") + name;
+    return nullptr;
+  }
+  return &it->second;
+}
+
+int Core::col_max(const char* name) {
+  const std::vector<double>* v = H(name);
+  if (!v) return 0;
+  double m = 0;
+  for (int k = 0; k < g.nz && k < (int)v->size(); ++k) m = (*v)[k] > m ? (*v)[k] : m;
+  return (int)m;
 }
 
 Core::~Core() {
@@ -106,6 +124,34 @@ int pace_b200_set_field(void* h, const char* name, double* p) {
   return 0;
 }
 
+int pace_b200_set_column(void* h, const char* name, const double* host_values, int n) {
+  Core* c = (Core*)h;
+  c->err.clear();
+  c->hcol[name] = std::vector<double>(host_values, host_values + n);
+  double* dev = nullptr;
+  auto it = c->fields.find(name);
+  if (it != c->fields.end() && c->colsize[name] >= n) {
+    dev = it->second;
+  } else {
+    void* ptr = nullptr;
+    if (cudaMalloc(&ptr, sizeof(double) * n) != cudaSuccess) {
+      c->err = "cudaMalloc failed for column";
+      return 1;
+    }
+    c->owned.push_back(ptr);
+    dev = (double*)ptr;
+    c->fields[name] = dev;
+    c->colsize[name] = n;
+  }
+  if (cudaMemcpy(dev, host_values, sizeof(double) * n, cudaMemcpyHostToDevice) != cudaSuccess) {
+    c->err = "cudaMemcpy failed for column";
+    return 1;
+  }
+  return 0;
+}
+
+static double* opt_field(Core* c, const char* name) { return (name && name[0]) ? c->F(name) : nullptr; }
+
 #define ENTRY(call)          \
   Core* c = (Core*)h;        \
   c->err.clear();            \
@@ -115,5 +161,52 @@ int pace_b200_riem_solver_c(void* h, double dt2) { ENTRY(riem_solver_c(*c, dt2))
 int pace_b200_c_sw(void* h, double dt2) { ENTRY(c_sw(*c, dt2)) }
 int pace_b200_update_dz_c(void* h, double dt2) { ENTRY(update_dz_c(*c, dt2)) }
 int pace_b200_p_grad_c(void* h, double dt2) { ENTRY(p_grad_c(*c, dt2)) }
+int pace_b200_fv_prep(void* h, double dt) { ENTRY(fv_prep(*c, dt)) }
+int pace_b200_d_sw(void* h, double dt) { ENTRY(d_sw(*c, dt)) }
+
+int pace_b200_fvtp2d(void* h, const char* q, const char* crx, const char* cry, const char* xfx, const char* yfx,
+                     const char* fx, const char* fy, const char* x_mass_flux, const char* y_mass_flux,
+                     const char* mass, int hord, const char* nord_col, const char* damp, int nk) {
+  Core* c = (Core*)h;
+  c->err.clear();
+  Fvtp2dArgs a;
+  a.q = c->F(q); a.crx = c->F(crx); a.cry = c->F(cry); a.xfx = c->F(xfx); a.yfx = c->F(yfx);
+  a.fx = c->F(fx); a.fy = c->F(fy);
+  a.x_mass_flux = opt_field(c, x_mass_flux); a.y_mass_flux = opt_field(c, y_mass_flux); a.mass = opt_field(c, mass);
+  a.hord = hord; a.nk = nk;
+  if (nord_col && nord_col[0]) {
+    a.nord_col = c->F(nord_col); a.damp = c->F(damp); a.nmax = c->col_max(nord_col);
+  }
+  if (!c->err.empty()) return 1;
+  return finish(c, fvtp2d(*c, a));
+}
+
+int pace_b200_delnflux_nosg(void* h, const char* q, const char* fx2, const char* fy2, const char* damp,
+                            const char* d2, const char* nord_col, int nk) {
+  Core* c = (Core*)h;
+  c->err.clear();
+  DelnArgs d;
+  d.q = c->F(q); d.fx = c->F(fx2); d.fy = c->F(fy2); d.damp = c->F(damp); d.d2 = opt_field(c, d2);
+  d.nord_col = c->F(nord_col); d.nmax = c->col_max(nord_col); d.nk = nk; d.accumulate = false;
+  if (!c->err.empty()) return 1;
+  return finish(c, delnflux(*c, d));
+}
+
+int pace_b200_a2b_ord4(void* h, const char* qin, const char* qout, int k0, int nk, int replace) {
+  Core* c = (Core*)h;
+  c->err.clear();
+  double *a = c->F(qin), *b = c->F(qout);
+  if (!c->err.empty()) return 1;
+  return finish(c, a2b_ord4(*c, a, b, k0, nk, replace != 0));
+}
+
+int pace_b200_divergence_damping(void* h, const char* vort_b, const char* delpc, const char* ke,
+                                 const char* vort_a, double dt) {
+  Core* c = (Core*)h;
+  c->err.clear();
+  double *a = c->F(vort_b), *b = c->F(delpc), *k = c->F(ke), *va = c->F(vort_a);
+  if (!c->err.empty()) return 1;
+  return finish(c, divergence_damping(*c, a, b, k, va, dt));
+}
 
 }  // extern "C"

@@ -33,12 +33,17 @@ struct Core {
   cudaStream_t stream = 0;
   std::map<std::string, double*> fields;    // caller-owned device arrays (state, grid, temporaries)
   std::map<std::string, double*> scratch;   // library-owned 3-D scratch, allocated on first use
+  std::map<std::string, std::vector<double>> hcol;  // host copies of K-columns set via pace_b200_set_column
+  std::map<std::string, int> colsize;
   std::vector<void*> owned;
   std::string err;
 
   double* F(const char* name);              // caller-registered field, error if missing
   double* S(const char* name);              // zero-initialised library scratch field [nt][nz+1][ny+7][sj]
+  double* FS(const char* name) { return fields.count(name) ? fields[name] : S(name); }  // registered, else scratch
   bool has(const char* name) const { return fields.count(name) != 0; }
+  const std::vector<double>* H(const char* name);  // host copy of a K-column, error if missing
+  int col_max(const char* name);                    // int(max) of a K-column (e.g. nmax of a nord column)
   size_t field_elems() const { return (size_t)g.st3 * g.nt; }
   ~Core();
 };
@@ -48,5 +53,9 @@ int riem_solver_c(Core& c, double dt2);
 int c_sw(Core& c, double dt2);
 int update_dz_c(Core& c, double dt2);
 int p_grad_c(Core& c, double dt2);
+int fv_prep(Core& c, double dt);
+int d_sw(Core& c, double dt);
+int a2b_ord4(Core& c, const double* qin, double* qout, int k0, int nk, bool replace);
+int divergence_damping(Core& c, double* vort_b, double* delpc, double* ke, const double* vort_a, double dt);
 
 }  // namespace pace

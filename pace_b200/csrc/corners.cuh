@@ -106,3 +106,46 @@ __device__ __forceinline__ void yfill_src(const EdgeInfo& e, int nc, int& i, int
   }
 }
 }  // namespace pace
+
+namespace pace {
+// copy_corners_x / copy_corners_y (corners.py:307-424; same tables in delnflux.py copy_corners_*_nord):
+// each 3x3 corner block of the halo is overwritten with the rotated neighbouring halo strip.  In
+// absolute indices, with a = distance from the tile edge in x (1..3), b = distance in y (1..3):
+//   x-copy:  (is-a, js-b) <- (is-b, js-1+a)    (ie+a, js-b) <- (ie+b, js-1+a)
+//            (is-a, je+b) <- (is-b, je+1-a)    (ie+a, je+b) <- (ie+b, je+1-a)
+//   y-copy:  (is-a, js-b) <- (is-1+b, js-a)    (ie+a, js-b) <- (ie+1-b, js-a)
+//            (is-a, je+b) <- (is-1+b, je+a)    (ie+a, je+b) <- (ie+1-b, je+a)
+// Sources are never corner cells, so a consumer may equally read "as if copied" (virtual copy).
+__device__ __forceinline__ void copyx_src(const EdgeInfo& e, int& i, int& j) {
+  if (e.S && j < e.js) {
+    if (e.W && i < e.is) { int a = e.is - i, b = e.js - j; i = e.is - b; j = e.js - 1 + a; }
+    else if (e.E && i > e.ie) { int a = i - e.ie, b = e.js - j; i = e.ie + b; j = e.js - 1 + a; }
+  } else if (e.N && j > e.je) {
+    if (e.W && i < e.is) { int a = e.is - i, b = j - e.je; i = e.is - b; j = e.je + 1 - a; }
+    else if (e.E && i > e.ie) { int a = i - e.ie, b = j - e.je; i = e.ie + b; j = e.je + 1 - a; }
+  }
+}
+__device__ __forceinline__ void copyy_src(const EdgeInfo& e, int& i, int& j) {
+  if (e.S && j < e.js) {
+    if (e.W && i < e.is) { int a = e.is - i, b = e.js - j; i = e.is - 1 + b; j = e.js - a; }
+    else if (e.E && i > e.ie) { int a = i - e.ie, b = e.js - j; i = e.ie + 1 - b; j = e.js - a; }
+  } else if (e.N && j > e.je) {
+    if (e.W && i < e.is) { int a = e.is - i, b = j - e.je; i = e.is - 1 + b; j = e.je + a; }
+    else if (e.E && i > e.ie) { int a = i - e.ie, b = j - e.je; i = e.ie + 1 - b; j = e.je + a; }
+  }
+}
+// value of f at (p.i+di, p.j+dj, p.k) as seen after copy_corners_x / _y
+__device__ __forceinline__ double rd_cx(const double* f, const Pt& p, const EdgeInfo& e, int di, int dj) {
+  int i = p.i + di, j = p.j + dj;
+  copyx_src(e, i, j);
+  return f[p.o + (i - p.i) + (j - p.j) * p.sj];
+}
+__device__ __forceinline__ double rd_cy(const double* f, const Pt& p, const EdgeInfo& e, int di, int dj) {
+  int i = p.i + di, j = p.j + dj;
+  copyy_src(e, i, j);
+  return f[p.o + (i - p.i) + (j - p.j) * p.sj];
+}
+
+// materialised copy_corners_x / _y of `q` in place, levels [0,nk)
+void copy_corners(Core& c, double* q, bool ydir, int nk);
+}  // namespace pace

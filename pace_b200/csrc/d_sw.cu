@@ -1,0 +1,267 @@
+// D-grid shallow-water Lagrangian dynamics (Fortran d_sw): the full-step update of delp, pt, w, q_con, u, v.
+//
+// Reference: pyFV3/stencils/d_sw.py:34-741 (stencils), :997-1303 (__call__ order);
+//            pyFV3/stencils/xtp_u.py:8-95, ytp_v.py:8-94 (PPM advection of u, v inside the KE stencil).
+// 178 reference launches; the transport operators are in transport.cu, the flux prep in fxadv.cu, the
+// divergence damping in divergence_damping.cu, the rest is grouped here (comments name the reference
+// stencil each kernel covers).
+#include "ppm.cuh"
+#include "transport.hpp"
+
+namespace pace {
+
+int divergence_damping(Core& c, double* vort_b, double* delpc, double* ke, const double* vort_a, double dt);
+int fv_prep(Core& c, double dt);
+
+namespace {
+// bl/br of xtp_u.get_bl_br / ytp_v.get_bl_br for iord < 8, cell offset d along the sweep direction.
+// zero_lo/zero_hi: cell index ranges {lo-1,lo} / {hi,hi+1} get bl = br = 0 on the rows (columns) that
+// touch the tile edge in the OTHER direction (xtp_u.py:46-54).
+template <class QF, class DF>
+__device__ __forceinline__ void adv_blbr(QF Q, DF D, int pos, int lo, int hi, bool elo, bool ehi, bool zero_row,
+                                         int d, double& bl, double& br) {
+  double al0 = ppm_al(Q, D, pos, lo, hi, elo, ehi, d);
+  double al1 = ppm_al(Q, D, pos, lo, hi, elo, ehi, d + 1);
+  bl = al0 - Q(d);
+  br = al1 - Q(d);
+  const int x = pos + d;
+  if (zero_row && ((elo && (x == lo - 1 || x == lo)) || (ehi && (x == hi || x == hi + 1)))) {
+    bl = 0.0;
+    br = 0.0;
+  }
+}
+// advect_u_along_x / advect_v_along_y (xtp_u.py:57-95) for iord < 8
+template <class QF, class DF>
+__device__ __forceinline__ double adv_along(QF Q, DF D, double ub, double cfl, int pos, int lo, int hi, bool elo,
+                                            bool ehi, bool zero_row, int mord) {
+  double bl, br, blm, brm;
+  adv_blbr(Q, D, pos, lo, hi, elo, ehi, zero_row, 0, bl, br);
+  adv_blbr(Q, D, pos, lo, hi, elo, ehi, zero_row, -1, blm, brm);
+  double b0 = bl + br, b0m = blm + brm;
+  double fx0 = cfl > 0.0 ? (1.0 - cfl) * (brm - cfl * b0m) : (1.0 + cfl) * (bl + cfl * b0);
+  bool s0, sm;
+  if (mord == 5) {
+    s0 = bl * br < 0;
+    sm = blm * brm < 0;
+  } else {
+    s0 = (3.0 * fabs(b0)) < fabs(bl - br);
+    sm = (3.0 * fabs(b0m)) < fabs(blm - brm);
+  }
+  double mask = (sm || s0) ? 1.0 : 0.0;
+  return ub > 0.0 ? Q(-1) + fx0 * mask : Q(0) + fx0 * mask;
+}
+}  // namespace
+
+int d_sw(Core& c, double dt) {
+  const Geo g = c.g;
+  cudaStream_t st = c.stream;
+  const Config& cf = c.cfg;
+  if (cf.inline_q) { c.err = "D-Grid Shallow Water Lagrangian Dynamics (D_SW): inline_q not implemented."; return 1; }
+  if (cf.d_ext > 0) { c.err = "D-Grid Shallow Water Lagrangian Dynamics (D_SW): untested d_ext > 0. need to call a2b_ord2, not implemented."; return 1; }
+  if (cf.hydrostatic) { c.err = "D-Grid Shallow Water Lagrangian Dynamics (D_SW): Hydrostatic is not implemented"; return 1; }
+  if (cf.do_f3d) { c.err = "do_f3d is not implemented"; return 1; }
+  if (cf.hord_mt >= 8 || cf.hord_mt < 0) { c.err = "d_sw: hord_mt >= 8 (xtp_u/ytp_v ord-8 branch) is not implemented"; return 1; }
+
+  double *delpc = c.F("ad.vt");  // the reference passes AcousticDynamics._vt as d_sw's delpc (dyn_core.py:867-868)
+  double *delp = c.F("delp"), *pt = c.F("pt"), *u = c.F("u"), *v = c.F("v"), *w = c.F("w"), *uc = c.F("uc"),
+         *vc = c.F("vc"), *q_con = c.F("q_con"), *mfx = c.F("mfxd"), *mfy = c.F("mfyd"), *cx = c.F("cxd"),
+         *cy = c.F("cyd"), *crx = c.F("ad.crx"), *cry = c.F("ad.cry"), *xfx = c.F("ad.xfx"), *yfx = c.F("ad.yfx"),
+         *heat_source = c.F("ad.heat_source"), *diss_est = c.F("diss_estd");
+  double *ucc = c.FS("dsw.uc_contra"), *vcc = c.FS("dsw.vc_contra");
+  const double *rarea = c.F("grid.rarea"), *dx = c.F("grid.dx"), *dy = c.F("grid.dy"), *rdx = c.F("grid.rdx"),
+               *rdy = c.F("grid.rdy"), *cosa = c.F("grid.cosa"), *rsina = c.F("grid.rsina"), *f0 = c.F("grid.fC_agrid"),
+               *rsin2 = c.F("grid.rsin2"), *cosa_s = c.F("grid.cosa_s");
+  const double *col_nord_v = c.F("col.nord_v"), *col_nord_w = c.F("col.nord_w"), *col_nord_t = c.F("col.nord_t"),
+               *col_damp_vt = c.F("col.damp_vt"), *col_damp_w = c.F("col.damp_w"), *col_d_con = c.F("col.d_con"),
+               *col_ke_bg = c.F("col.ke_bg"), *damp_vt_fv = c.F("col.delnflux_damp_vt_fv"),
+               *damp_t_fv = c.F("col.delnflux_damp_t_fv"), *damp_vt_c = c.F("col.delnflux_damp_vt"),
+               *damp_w_c = c.F("col.delnflux_damp_w");
+  double *tfx = c.FS("dsw.tmp_fx"), *tfy = c.FS("dsw.tmp_fy"), *gx = c.FS("dsw.tmp_gx"), *gy = c.FS("dsw.tmp_gy"),
+         *fx2 = c.FS("dsw.tmp_fx2"), *fy2 = c.FS("dsw.tmp_fy2"), *dw = c.FS("dsw.tmp_dw"), *wk = c.FS("dsw.tmp_wk"),
+         *heat_s = c.FS("dsw.tmp_heat_s"), *diss_e = c.FS("dsw.tmp_diss_e"), *ke = c.FS("dsw.dt_kinetic_energy_on_cell_corners"),
+         *vort_a = c.FS("dsw.vorticity_agrid"), *vort_b = c.FS("dsw.vorticity_bgrid_damped"),
+         *abs_vort = c.FS("dsw.abs_vorticity_agrid"), *tut = c.FS("dsw.tmp_ut"), *tvt = c.FS("dsw.tmp_vt"),
+         *damped_vort = c.FS("dsw.damped_rel_vorticity_agrid"), *vxd = c.FS("dsw.vort_x_delta"), *vyd = c.FS("dsw.vort_y_delta");
+  if (!c.err.empty()) return 1;
+  const int is = g.is, ie = g.ie, js = g.js, je = g.je, nz = g.nz;
+  const int nmax_v = c.col_max("col.nord_v"), nmax_w = c.col_max("col.nord_w"), nmax_t = c.col_max("col.nord_t");
+  if (!c.err.empty()) return 1;
+
+  // 1. fv_prep
+  if (fv_prep(c, dt)) return 1;
+  // 2. fvtp2d_dp(delp) with delnflux(nord_v, damp_vt)
+  Fvtp2dArgs a;
+  a.crx = crx; a.cry = cry; a.xfx = xfx; a.yfx = yfx; a.nk = nz;
+  a.q = delp; a.fx = tfx; a.fy = tfy; a.hord = cf.hord_dp; a.nord_col = col_nord_v; a.damp = damp_vt_fv; a.nmax = nmax_v;
+  if (fvtp2d(c, a)) return 1;
+  // 3. flux_capacitor (compute + 3 halo)
+  launch_ijk(st, g, box_dims(g, 0, 0, 0, 3, 3), [=] __device__(const Pt& p) {
+    A0(cx) = A0(cx) + A0(crx);
+    A0(cy) = A0(cy) + A0(cry);
+    A0(mfx) = A0(mfx) + A0(tfx);
+    A0(mfy) = A0(mfy) + A0(tfy);
+  });
+  // 4. delnflux_nosg_w(w)
+  {
+    DelnArgs d;
+    d.q = w; d.fx = fx2; d.fy = fy2; d.nord_col = col_nord_w; d.damp = damp_w_c; d.d2 = wk; d.nmax = nmax_w; d.nk = nz;
+    if (delnflux(c, d)) return 1;
+  }
+  // 5. heat_diss
+  launch_ijk(st, g, box_dims(g, 0, 0, 0), [=] __device__(const Pt& p) {
+    double hs = 0.0;
+    if (col_damp_w[p.k] > 1e-5) {
+      double dd8 = col_ke_bg[p.k] * fabs(dt);
+      double dwv = (A0(fx2) - A(fx2, 1, 0, 0) + A0(fy2) - A(fy2, 0, 1, 0)) * A20(rarea);
+      A0(dw) = dwv;
+      hs = dd8 - dwv * (A0(w) + 0.5 * dwv);
+    }
+    A0(heat_s) = hs;
+    A0(diss_e) = hs;
+  });
+  // 6./7. fvtp2d_vt_nodelnflux(w, mass fluxes) ; apply_fluxes(w)
+  a = Fvtp2dArgs();
+  a.crx = crx; a.cry = cry; a.xfx = xfx; a.yfx = yfx; a.nk = nz;
+  a.q = w; a.fx = gx; a.fy = gy; a.hord = cf.hord_vt; a.x_mass_flux = tfx; a.y_mass_flux = tfy;
+  if (fvtp2d(c, a)) return 1;
+  launch_ijk(st, g, box_dims(g, 0, 0, 0), [=] __device__(const Pt& p) {
+    A0(w) = A0(w) * A0(delp) + (A0(gx) - A(gx, 1, 0, 0) + A0(gy) - A(gy, 0, 1, 0)) * A20(rarea);
+  });
+  // 8./9. fvtp2d_dp_t(q_con, mass=delp) ; apply_fluxes(q_con)
+  a.q = q_con; a.hord = cf.hord_dp; a.mass = delp; a.nord_col = col_nord_t; a.damp = damp_t_fv; a.nmax = nmax_t;
+  if (fvtp2d(c, a)) return 1;
+  launch_ijk(st, g, box_dims(g, 0, 0, 0), [=] __device__(const Pt& p) {
+    A0(q_con) = A0(q_con) * A0(delp) + (A0(gx) - A(gx, 1, 0, 0) + A0(gy) - A(gy, 0, 1, 0)) * A20(rarea);
+  });
+  // 10. fvtp2d_tm(pt, mass=delp)
+  a.q = pt; a.hord = cf.hord_tm; a.nord_col = col_nord_v; a.damp = damp_vt_fv; a.nmax = nmax_v;
+  if (fvtp2d(c, a)) return 1;
+  // 11./12. apply_pt_delp_fluxes ; adjust_w_and_qcon
+  launch_ijk(st, g, box_dims(g, 0, 0, 0), [=] __device__(const Pt& p) {
+    double ptv = A0(pt) * A0(delp) + (A0(gx) - A(gx, 1, 0, 0) + A0(gy) - A(gy, 0, 1, 0)) * A20(rarea);
+    double dp = A0(delp) + (A0(tfx) - A(tfx, 1, 0, 0) + A0(tfy) - A(tfy, 0, 1, 0)) * A20(rarea);
+    A0(delp) = dp;
+    A0(pt) = ptv / dp;
+    double wv = A0(w) / dp;
+    wv = col_damp_w[p.k] > 1e-5 ? wv + A0(dw) : wv;
+    A0(w) = wv;
+    A0(q_con) = A0(q_con) / dp;
+  });
+  // 13. compute_kinetic_energy on the corner compute domain
+  const int mord_mt = cf.hord_mt < 0 ? -cf.hord_mt : cf.hord_mt;
+  const double *dxa = c.F("grid.dxa"), *dya = c.F("grid.dya");
+  (void)dxa; (void)dya;
+  launch_ijk(st, g, box_dims(g, 1, 1, 0), [=] __device__(const Pt& p) {
+    const int i = p.i, j = p.j;
+    const bool iW = p.W && i == is, iE = p.E && i == ie + 1, jS = p.S && j == js, jN = p.N && j == je + 1;
+    // interpolate_uc_vc_to_cell_corners (d_sw.py:694-741)
+    double ub_cov = 0.5 * (A(uc, 0, -1, 0) + A0(uc));
+    double vb_cov = 0.5 * (A(vc, -1, 0, 0) + A0(vc));
+    double ub = (ub_cov - vb_cov * A20(cosa)) * A20(rsina);
+    double vb = (vb_cov - ub_cov * A20(cosa)) * A20(rsina);
+    if (jS || jN) ub = 0.25 * (-A(ucc, 0, -2, 0) + 3.0 * (A(ucc, 0, -1, 0) + A0(ucc)) - A(ucc, 0, 1, 0));
+    if (iW || iE) ub = 0.5 * (A(ucc, 0, -1, 0) + A0(ucc));
+    if (iW || iE) vb = 0.25 * (-A(vcc, -2, 0, 0) + 3.0 * (A(vcc, -1, 0, 0) + A0(vcc)) - A(vcc, 1, 0, 0));
+    if (jS || jN) vb = 0.5 * (A(vcc, -1, 0, 0) + A0(vcc));
+    // advect_v_along_y(v, vb, rdy, dy, dya, dt): zero corners on columns i == is / ie+1
+    double adv_v, adv_u;
+    {
+      auto Q = [&](int d) { return A(v, 0, d, 0); };
+      auto D = [&](int d) { return A2(dy, 0, d); };
+      double cfl = vb > 0 ? vb * dt * A2(rdy, 0, -1) : vb * dt * A20(rdy);
+      adv_v = adv_along(Q, D, vb, cfl, j, js, je, p.S, p.N, iW || iE, mord_mt);
+    }
+    {
+      auto Q = [&](int d) { return A(u, d, 0, 0); };
+      auto D = [&](int d) { return A2(dx, d, 0); };
+      double cfl = ub > 0 ? ub * dt * A2(rdx, -1, 0) : ub * dt * A20(rdx);
+      adv_u = adv_along(Q, D, ub, cfl, i, is, ie, p.W, p.E, jS || jN, mord_mt);
+    }
+    double kev = 0.5 * dt * (ub * adv_u + vb * adv_v);
+    // all_corners_ke (d_sw.py:266-305)
+    if ((iW || iE) && (jS || jN)) {
+      int io1, jo1, io2;
+      double vsign;
+      if (iW && jS) { io1 = 0; jo1 = 0; io2 = -1; vsign = 1; }
+      else if (iE && jS) { io1 = -1; jo1 = 0; io2 = 0; vsign = -1; }
+      else if (iE && jN) { io1 = -1; jo1 = -1; io2 = 0; vsign = 1; }
+      else { io1 = 0; jo1 = -1; io2 = -1; vsign = -1; }
+      double dt6 = dt / 6.0;
+      kev = dt6 * ((A0(ucc) + A(ucc, 0, -1, 0)) * ((io1 + 1) * A0(u) - (io1 * A(u, -1, 0, 0))) +
+                   (A0(vcc) + A(vcc, -1, 0, 0)) * ((jo1 + 1) * A0(v) - (jo1 * A(v, 0, -1, 0))) +
+                   (((jo1 + 1) * A0(ucc) - (jo1 * A(ucc, 0, -1, 0))) +
+                    vsign * ((io1 + 1) * A0(vcc) - (io1 * A(vcc, -1, 0, 0)))) *
+                       ((io2 + 1) * A0(u) - (io2 * A(u, -1, 0, 0))));
+    }
+    A0(ke) = kev;
+  });
+  // 14. compute_vorticity (compute + 3 halo)
+  launch_ijk(st, g, box_dims(g, 0, 0, 0, 3, 3), [=] __device__(const Pt& p) {
+    double rdy_tmp = A20(rarea) * A20(dx);
+    double rdx_tmp = A20(rarea) * A20(dy);
+    A0(vort_a) = (A0(u) - A(u, 0, 1, 0) * A2(dx, 0, 1) / A20(dx)) * rdy_tmp +
+                 (A(v, 1, 0, 0) * A2(dy, 1, 0) / A20(dy) - A0(v)) * rdx_tmp;
+  });
+  // 15. divergence_damping
+  if (divergence_damping(c, vort_b, delpc, ke, vort_a, dt)) return 1;
+  // 16. rel_vorticity_to_abs (compute + 3 halo)
+  launch_ijk(st, g, box_dims(g, 0, 0, 0, 3, 3), [=] __device__(const Pt& p) { A0(abs_vort) = A0(vort_a) + A20(f0); });
+  // 17. fvtp2d_vt_nodelnflux(abs vorticity) -> tmp_fx, tmp_fy
+  a = Fvtp2dArgs();
+  a.crx = crx; a.cry = cry; a.xfx = xfx; a.yfx = yfx; a.nk = nz;
+  a.q = abs_vort; a.fx = tfx; a.fy = tfy; a.hord = cf.hord_vt;
+  if (fvtp2d(c, a)) return 1;
+  // 18. u_and_v_from_ke
+  launch_ijk(st, g, box_dims(g, 1, 1, 0), [=] __device__(const Pt& p) {
+    if (p.i <= ie) A0(u) = A0(u) * A20(dx) + A0(ke) - A(ke, 1, 0, 0) + A0(tfy);
+    if (p.j <= je) A0(v) = A0(v) * A20(dy) + A0(ke) - A(ke, 0, 1, 0) - A0(tfx);
+  });
+  // 19. delnflux_nosg_v(vorticity_agrid) -> tmp_ut, tmp_vt
+  {
+    DelnArgs d;
+    d.q = vort_a; d.fx = tut; d.fy = tvt; d.nord_col = col_nord_v; d.damp = damp_vt_c; d.d2 = damped_vort; d.nmax = nmax_v; d.nk = nz;
+    if (delnflux(c, d)) return 1;
+  }
+  // 20. vort_differencing
+  launch_ijk(st, g, box_dims(g, 1, 1, 0), [=] __device__(const Pt& p) {
+    if (col_d_con[p.k] > 1e-5) {
+      if (p.i <= ie) A0(vxd) = A0(vort_b) - A(vort_b, 1, 0, 0);
+      if (p.j <= je) A0(vyd) = A0(vort_b) - A(vort_b, 0, 1, 0);
+    }
+  });
+  // 21./22. heat_source_from_vorticity_damping + accumulate_heat_source_and_dissipation_estimate (compute domain)
+  const bool do_accum = cf.d_con > 1.0e-5;
+  launch_ijk(st, g, box_dims(g, 0, 0, 0), [=] __device__(const Pt& p) {
+    double hs = A0(heat_s);
+    const double frac = col_d_con[p.k];
+    if (frac > 1e-5) {
+      auto ubt = [&](int dj) { return (A(vxd, 0, dj, 0) + A(tvt, 0, dj, 0)) * A2(rdx, 0, dj); };
+      auto fyf = [&](int dj) { return A(u, 0, dj, 0) * A2(rdx, 0, dj); };
+      auto vbt = [&](int di) { return (A(vyd, di, 0, 0) - A(tut, di, 0, 0)) * A2(rdy, di, 0); };
+      auto fxf = [&](int di) { return A(v, di, 0, 0) * A2(rdy, di, 0); };
+      double ub0 = ubt(0), ub1 = ubt(1), fy0 = fyf(0), fy1 = fyf(1);
+      double vb0 = vbt(0), vb1 = vbt(1), fx0 = fxf(0), fx1 = fxf(1);
+      double gy0 = fy0 * ub0, gy1 = fy1 * ub1, gx0 = fx0 * vb0, gx1 = fx1 * vb1;
+      double u2 = fy0 + fy1, du2 = ub0 + ub1, v2 = fx0 + fx1, dv2 = vb0 + vb1;
+      double dampterm = A20(rsin2) * 0.25 *
+                        ((ub0 * ub0 + ub1 * ub1 + vb0 * vb0 + vb1 * vb1) + 2.0 * (gy0 + gy1 + gx0 + gx1) -
+                         A20(cosa_s) * (u2 * dv2 + v2 * du2 + du2 * dv2));
+      hs = A0(delp) * (hs - frac * dampterm);
+      A0(heat_s) = hs;
+    }
+    if (do_accum) {
+      A0(heat_source) = A0(heat_source) + hs;
+      A0(diss_est) = A0(diss_est) + A0(diss_e);
+    }
+  });
+  // 23. update_u_and_v
+  launch_ijk(st, g, box_dims(g, 1, 1, 0), [=] __device__(const Pt& p) {
+    if (col_damp_vt[p.k] > 1e-5) {
+      if (p.i <= ie) A0(u) = A0(u) + A0(tvt);
+      if (p.j <= je) A0(v) = A0(v) - A0(tut);
+    }
+  });
+  return 0;
+}
+
+}  // namespace pace

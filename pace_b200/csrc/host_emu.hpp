@@ -15,3 +15,5 @@ inline cudaError_t cudaFree(void* p) { free(p); return 0; }
 inline cudaError_t cudaMemsetAsync(void* p, int v, size_t n, cudaStream_t) { memset(p, v, n); return 0; }
 inline cudaError_t cudaPeekAtLastError() { return 0; }
 inline const char* cudaGetErrorString(cudaError_t) { return "host-emu error"; }
+enum { cudaMemcpyHostToDevice = 1 };
+inline cudaError_t cudaMemcpy(void* d, const void* s, size_t n, int) { memcpy(d, s, n); return 0; }

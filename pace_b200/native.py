@@ -14,7 +14,7 @@ from . import _lib
 
 DEFAULTS = dict(
     n_split=1, k_split=1, hord_dp=6, hord_mt=6, hord_tm=6, hord_tr=8, hord_vt=6, kord_mt=9, kord_tm=-9,
-    kord_tr=9, kord_wz=9, nord=3, n_sponge=48, nf_omega=1, grid_type=0, do_sat_adj=1, do_vort_damp=1, rf_fast=1,
+    kord_tr=9, kord_wz=9, nord=3, n_sponge=1, nf_omega=1, grid_type=0, do_sat_adj=1, do_vort_damp=1, rf_fast=1,
     hydrostatic=0, convert_ke=0, fill=1, adiabatic=0, do_qa=1, use_old_omega=1, do_f3d=0, inline_q=0, nwat=6,
     dt_atmos=225.0, a_imp=1.0, beta=0.0, p_fac=0.05, d_con=1.0, d2_bg=0.0, d2_bg_k1=0.2, d2_bg_k2=0.1,
     d4_bg=0.15, dddmp=0.5, delt_max=0.002, ke_bg=0.0, rf_cutoff=3000.0, tau=10.0, vtdm4=0.06, d_ext=0.0,
@@ -115,9 +115,41 @@ class NativeCore:
             return [np.ascontiguousarray(t[n, :, :ni].T) for n in range(self.nt)]
         return [t]
 
+    def set_column(self, name, values):
+        """Small per-level column (host values; the library keeps host + device copies)."""
+        v = np.ascontiguousarray(values, dtype=np.float64)
+        rc = self.lib.pace_b200_set_column(self.handle, name.encode(), v.ctypes.data_as(ctypes.POINTER(ctypes.c_double)), v.size)
+        if rc != 0:
+            raise NativeError("set_column %s: %s" % (name, self.lib.pace_b200_last_error(self.handle).decode()))
+
+    def set_columns_from_config(self):
+        from .hostprep import all_columns
+
+        for name, v in all_columns(self.cfg, self.npz, self.cfg["da_min"], self.cfg["da_min_c"]).items():
+            self.set_column(name, v)
+
+    def put_grid(self, grids):
+        """grids: list over subdomains of dict name -> reference-layout array ("grid.*", "damp.*")."""
+        from .hostprep import derived_grid_fields
+
+        g0 = grids[0]
+        for name in g0:
+            if np.ndim(g0[name]) == 0 or name in ("grid.edge_s", "grid.edge_n"):
+                continue
+            if np.ndim(g0[name]) == 1:
+                self.set_column(name, g0[name])
+            elif np.ndim(g0[name]) == 2:
+                self.put(name, [g[name] for g in grids])
+        for name, arrs in derived_grid_fields(grids, self.nx, self.ny).items():
+            if name == "grid.a2b_corner_coef":
+                self.set_column(name, arrs[0])
+            else:
+                self.put(name, arrs)
+
     # -- calls -----------------------------------------------------------------------------------
     def call(self, name, *scalars):
         fn = getattr(self.lib, "pace_b200_" + name)
+        scalars = [a.encode() if isinstance(a, str) else a for a in scalars]
         rc = fn(self.handle, *scalars)
         if rc != 0:
             raise NativeError("%s: %s" % (name, self.lib.pace_b200_last_error(self.handle).decode()))

@@ -24,3 +24,11 @@ def grid0():
     from tests.golden_util import load_grid
 
     return load_grid("c12_rank0_grid.npz")
+
+
+@pytest.fixture(scope="session")
+def golden_deep():
+    """Finer-grained stage log (d_sw / updatedzd / nh_p_grad internals); same run as `golden`."""
+    from tests.golden_util import Stages
+
+    return Stages("c12_rank0_stages_deep.npz")

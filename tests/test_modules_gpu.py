@@ -9,7 +9,7 @@ pytestmark = pytest.mark.gpu
 
 
 @pytest.mark.parametrize("case", sorted(CASES))
-def test_module_gpu(case, golden, grid0):
+def test_module_gpu(case, golden, golden_deep, grid0):
     c = CASES[case]
-    check_module("cuda", golden, grid0, c["stage"], c["call"], c["args"], tol=c.get("tol", 0.0),
-                 near_zero=c.get("near_zero", 0.0), skip=c.get("skip", ()))
+    check_module("cuda", golden_deep if c.get("deep") else golden, grid0, c["stage"], c["call"], c["args"], tol=c.get("tol", 0.0),
+                 near_zero=c.get("near_zero", 0.0), skip=c.get("skip", ()), begin=c.get("begin"), region=c.get("region"))

@@ -7,7 +7,7 @@ from tests.module_harness import check_module
 
 
 @pytest.mark.parametrize("case", sorted(CASES))
-def test_module_hostemu(case, golden, grid0):
+def test_module_hostemu(case, golden, golden_deep, grid0):
     c = CASES[case]
-    check_module("hostemu", golden, grid0, c["stage"], c["call"], c["args"], tol=c.get("tol_host", 0.0),
-                 near_zero=c.get("near_zero", 0.0), skip=c.get("skip", ()))
+    check_module("hostemu", golden_deep if c.get("deep") else golden, grid0, c["stage"], c["call"], c["args"], tol=c.get("tol_host", 0.0),
+                 near_zero=c.get("near_zero", 0.0), skip=c.get("skip", ()), begin=c.get("begin"), region=c.get("region"))
