@@ -85,6 +85,38 @@ int pace_b200_fv_prep(void* handle, double dt);
  * in: ua va ad.zh   out: ad.crx ad.cry ad.xfx ad.yfx */
 int pace_b200_d_sw(void* handle, double dt);
 
+/* NonhydrostaticVerticalSolver.__call__ (pyFV3/stencils/riem_solver3.py:225-339).
+ * in: delp ad.cappa q_con pt ad.zs ad.wsd  inout: pe ad.zh w delz  out: ad.pkc ad.pk3 (+ pk peln if last_call) */
+int pace_b200_riem_solver3(void* handle, double dt, int last_call);
+
+/* UpdateHeightOnDGrid.__call__ (pyFV3/stencils/updatedzd.py:316-389).
+ * in: ad.zs ad.crx ad.cry ad.xfx ad.yfx  inout: ad.zh  out: ad.wsd */
+int pace_b200_update_dz_d(void* handle, double dt);
+
+/* Helper stencils of AcousticDynamics (pyFV3/stencils/dyn_core.py:53-119, 603-607). */
+int pace_b200_zero_data(void* handle, int first_timestep);
+int pace_b200_gz_from_zs_delz(void* handle);
+int pace_b200_pem_from_delp(void* handle);
+int pace_b200_copy_full(void* handle, const char* src, const char* dst);
+int pace_b200_compute_geopotential(void* handle);
+
+/* edge_pe (pyFV3/stencils/pe_halo.py:6-34) and PK3Halo.__call__ (pk3_halo.py:11-73). */
+int pace_b200_edge_pe(void* handle);
+int pace_b200_pk3_halo(void* handle);
+
+/* NonHydrostaticPressureGradient.__call__ (pyFV3/stencils/nh_p_grad.py:201-265).
+ * inout: u v ad.pkc(pp) ad.gz ad.pk3   in: delp */
+int pace_b200_nh_p_grad(void* handle, double dt);
+
+/* RayleighDamping.__call__ (pyFV3/stencils/ray_fast.py:49-206).  inout: u v w */
+int pace_b200_ray_fast(void* handle, double dt);
+
+/* HyperdiffusionDamping.__call__ (pyFV3/stencils/del2cubed.py:163-202) on the registered field q. */
+int pace_b200_del2cubed(void* handle, const char* q, double cd, int nmax);
+
+/* apply_diffusive_heating (pyFV3/stencils/temperature_adjust.py:8-42) on levels [0, nk). */
+int pace_b200_apply_diffusive_heating(void* handle, double delt_time_factor, int nk);
+
 /* FiniteVolumeTransport.__call__ (pyFV3/stencils/fvtp2d.py:251-368) on registered fields; optional
  * arguments are "" (or NULL).  nord_col/damp select the DelnFlux damping (fvtp2d.py:168-180). */
 int pace_b200_fvtp2d(void* handle, const char* q, const char* crx, const char* cry, const char* xfx,

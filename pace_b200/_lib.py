@@ -76,6 +76,19 @@ MODULE_CALLS = {
     "p_grad_c": [_D],
     "fv_prep": [_D],
     "d_sw": [_D],
+    "riem_solver3": [_D, _I],
+    "update_dz_d": [_D],
+    "zero_data": [_I],
+    "gz_from_zs_delz": [],
+    "pem_from_delp": [],
+    "copy_full": [_S, _S],
+    "compute_geopotential": [],
+    "edge_pe": [],
+    "pk3_halo": [],
+    "nh_p_grad": [_D],
+    "ray_fast": [_D],
+    "del2cubed": [_S, _D, _I],
+    "apply_diffusive_heating": [_D, _I],
     "fvtp2d": [_S] * 10 + [_I, _S, _S, _I],
     "delnflux_nosg": [_S] * 6 + [_I],
     "a2b_ord4": [_S, _S, _I, _I, _I],

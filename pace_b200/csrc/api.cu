@@ -61,6 +61,31 @@ int Core::col_max(const char* name) {
   return (int)m;
 }
 
+int set_column(Core& c, const char* name, const double* host_values, int n) {
+  c.hcol[name] = std::vector<double>(host_values, host_values + n);
+  double* dev = nullptr;
+  auto it = c.fields.find(name);
+  if (it != c.fields.end() && c.colsize.count(name) && c.colsize[name] >= n) {
+    dev = it->second;
+  } else {
+    void* ptr = nullptr;
+    if (cudaMalloc(&ptr, sizeof(double) * n) != cudaSuccess) {
+      c.err = "cudaMalloc failed for column";
+      return 1;
+    }
+    c.owned.push_back(ptr);
+    dev = (double*)ptr;
+    c.fields[name] = dev;
+    c.colsize[name] = n;
+  }
+  // stream-ordered so a column rewritten between calls (e.g. col.rf) cannot overtake queued kernels
+  if (cudaMemcpyAsync(dev, c.hcol[name].data(), sizeof(double) * n, cudaMemcpyHostToDevice, c.stream) != cudaSuccess) {
+    c.err = "cudaMemcpy failed for column";
+    return 1;
+  }
+  return 0;
+}
+
 Core::~Core() {
   for (void* p : owned) cudaFree(p);
 }
@@ -127,27 +152,7 @@ int pace_b200_set_field(void* h, const char* name, double* p) {
 int pace_b200_set_column(void* h, const char* name, const double* host_values, int n) {
   Core* c = (Core*)h;
   c->err.clear();
-  c->hcol[name] = std::vector<double>(host_values, host_values + n);
-  double* dev = nullptr;
-  auto it = c->fields.find(name);
-  if (it != c->fields.end() && c->colsize[name] >= n) {
-    dev = it->second;
-  } else {
-    void* ptr = nullptr;
-    if (cudaMalloc(&ptr, sizeof(double) * n) != cudaSuccess) {
-      c->err = "cudaMalloc failed for column";
-      return 1;
-    }
-    c->owned.push_back(ptr);
-    dev = (double*)ptr;
-    c->fields[name] = dev;
-    c->colsize[name] = n;
-  }
-  if (cudaMemcpy(dev, host_values, sizeof(double) * n, cudaMemcpyHostToDevice) != cudaSuccess) {
-    c->err = "cudaMemcpy failed for column";
-    return 1;
-  }
-  return 0;
+  return set_column(*c, name, host_values, n);
 }
 
 static double* opt_field(Core* c, const char* name) { return (name && name[0]) ? c->F(name) : nullptr; }
@@ -162,6 +167,27 @@ int pace_b200_c_sw(void* h, double dt2) { ENTRY(c_sw(*c, dt2)) }
 int pace_b200_update_dz_c(void* h, double dt2) { ENTRY(update_dz_c(*c, dt2)) }
 int pace_b200_p_grad_c(void* h, double dt2) { ENTRY(p_grad_c(*c, dt2)) }
 int pace_b200_fv_prep(void* h, double dt) { ENTRY(fv_prep(*c, dt)) }
+int pace_b200_riem_solver3(void* h, double dt, int last_call) { ENTRY(riem_solver3(*c, dt, last_call)) }
+int pace_b200_update_dz_d(void* h, double dt) { ENTRY(update_dz_d(*c, dt)) }
+int pace_b200_zero_data(void* h, int first_timestep) { ENTRY(zero_data(*c, first_timestep)) }
+int pace_b200_gz_from_zs_delz(void* h) { ENTRY(gz_from_zs_delz(*c)) }
+int pace_b200_pem_from_delp(void* h) { ENTRY(pem_from_delp(*c)) }
+int pace_b200_copy_full(void* h, const char* src, const char* dst) { ENTRY(copy_full(*c, src, dst)) }
+int pace_b200_edge_pe(void* h) { ENTRY(edge_pe(*c)) }
+int pace_b200_pk3_halo(void* h) { ENTRY(pk3_halo(*c)) }
+int pace_b200_compute_geopotential(void* h) { ENTRY(compute_geopotential(*c)) }
+int pace_b200_nh_p_grad(void* h, double dt) { ENTRY(nh_p_grad(*c, dt)) }
+int pace_b200_ray_fast(void* h, double dt) { ENTRY(ray_fast(*c, dt)) }
+int pace_b200_del2cubed(void* h, const char* q, double cd, int nmax) {
+  Core* c = (Core*)h;
+  c->err.clear();
+  double* qp = c->F(q);
+  if (!c->err.empty()) return 1;
+  return finish(c, del2cubed(*c, qp, cd, nmax));
+}
+int pace_b200_apply_diffusive_heating(void* h, double delt_time_factor, int nk) {
+  ENTRY(apply_diffusive_heating(*c, delt_time_factor, nk))
+}
 int pace_b200_d_sw(void* h, double dt) { ENTRY(d_sw(*c, dt)) }
 
 int pace_b200_fvtp2d(void* h, const char* q, const char* crx, const char* cry, const char* xfx, const char* yfx,

@@ -53,7 +53,21 @@ int riem_solver_c(Core& c, double dt2);
 int c_sw(Core& c, double dt2);
 int update_dz_c(Core& c, double dt2);
 int p_grad_c(Core& c, double dt2);
+int set_column(Core& c, const char* name, const double* host_values, int n);
 int fv_prep(Core& c, double dt);
+int riem_solver3(Core& c, double dt, int last_call);
+int update_dz_d(Core& c, double dt);
+int zero_data(Core& c, int first_timestep);
+int gz_from_zs_delz(Core& c);
+int pem_from_delp(Core& c);
+int copy_full(Core& c, const char* src_name, const char* dst_name);
+int edge_pe(Core& c);
+int pk3_halo(Core& c);
+int compute_geopotential(Core& c);
+int nh_p_grad(Core& c, double dt);
+int ray_fast(Core& c, double dt);
+int del2cubed(Core& c, double* q, double cd, int nmax);
+int apply_diffusive_heating(Core& c, double delt_time_factor, int nk);
 int d_sw(Core& c, double dt);
 int a2b_ord4(Core& c, const double* qin, double* qout, int k0, int nk, bool replace);
 int divergence_damping(Core& c, double* vort_b, double* delpc, double* ke, const double* vort_a, double dt);

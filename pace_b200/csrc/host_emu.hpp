@@ -17,3 +17,4 @@ inline cudaError_t cudaPeekAtLastError() { return 0; }
 inline const char* cudaGetErrorString(cudaError_t) { return "host-emu error"; }
 enum { cudaMemcpyHostToDevice = 1 };
 inline cudaError_t cudaMemcpy(void* d, const void* s, size_t n, int) { memcpy(d, s, n); return 0; }
+inline cudaError_t cudaMemcpyAsync(void* d, const void* s, size_t n, int, cudaStream_t) { memcpy(d, s, n); return 0; }

@@ -156,3 +156,72 @@ int riem_solver_c(Core& c, double dt2) {
 }
 
 }  // namespace pace
+
+namespace pace {
+
+// NonhydrostaticVerticalSolver.__call__ (riem_solver3.py:225-339): precompute + sim1_solver + finalize
+// in one column kernel.  in: delp cappa pe ad.zh q_con pt w delz ad.wsd ad.zs
+// out: w delz ad.zh pe ad.pkc(ppe) ad.pk3 (+ pk, peln when last_call)
+int riem_solver3(Core& c, double dt, int last_call) {
+  const Geo g = c.g;
+  const int km = g.nz;
+  if (c.cfg.a_imp <= 0.999) { c.err = "a_imp <= 0.999 is not implemented"; return 1; }
+  const double *delp = c.F("delp"), *cappa = c.F("ad.cappa"), *q_con = c.F("q_con"), *pt = c.F("pt"),
+               *zs = c.F("ad.zs"), *ws = c.F("ad.wsd");
+  double *pe = c.F("pe"), *zh = c.F("ad.zh"), *w = c.F("w"), *delz = c.F("delz"), *ppe = c.F("ad.pkc"),
+         *pk3 = c.F("ad.pk3"), *pk = c.F("pk"), *peln = c.F("peln");
+  double *dm = c.S("riem3.dm"), *pe_init = c.S("riem3.pe_init"), *p_int = c.S("riem3.p_interface"),
+         *logp = c.S("riem3.log_p_interface"), *gm = c.S("riem3.gamma"), *p_gas = c.S("riem3.p_gas"),
+         *pg = c.S("riem3.pg"), *logpg = c.S("riem3.logpg");
+  Sim1Work s = sim1_work(c);
+  if (!c.err.empty()) return 1;
+  const double ptop = c.cfg.ptop, p_fac = c.cfg.p_fac;
+  const double t1g = 2.0 * dt * dt, rdt = 1.0 / dt;
+  const double peln1 = std::log(ptop);            // math.log(ptop)           (riem_solver3.py:287)
+  const double ptk = std::exp(KAPPA * peln1);     // math.exp(KAPPA * peln1)  (riem_solver3.py:288)
+  constexpr double RGRAV = 1.0 / GRAV;
+  const bool beta_neg = c.cfg.beta < -0.1;
+  launch_ij(c.stream, g, box_compute(g, 0, 0, 0, 0, 1), [=] __device__(const Pt& p) {
+    // precompute (riem_solver3.py:26-90)
+    for (int k = 0; k <= km; ++k) {
+      K_(dm, k) = K_(delp, k);
+      K_(pe_init, k) = K_(pe, k);
+    }
+    K_(p_int, 0) = ptop; K_(logp, 0) = peln1; K_(pk3, 0) = ptk; K_(pg, 0) = ptop; K_(logpg, 0) = peln1;
+    for (int k = 1; k <= km; ++k) {
+      double pi = K_(p_int, k - 1) + K_(dm, k - 1);
+      K_(p_int, k) = pi;
+      double lp = fv_log(pi);
+      K_(logp, k) = lp;
+      double pgk = K_(pg, k - 1) + K_(dm, k - 1) * (1.0 - K_(q_con, k - 1));
+      K_(pg, k) = pgk;
+      K_(logpg, k) = fv_log(pgk);
+      K_(pk3, k) = fv_exp(KAPPA * lp);
+    }
+    for (int k = 0; k <= km; ++k) {
+      K_(gm, k) = 1.0 / (1.0 - K_(cappa, k));
+      K_(dm, k) = K_(dm, k) * RGRAV;
+    }
+    for (int k = 0; k < km; ++k) {
+      K_(p_gas, k) = (K_(pg, k + 1) - K_(pg, k)) / (K_(logpg, k + 1) - K_(logpg, k));
+      K_(delz, k) = K_(zh, k + 1) - K_(zh, k);
+    }
+    sim1_column(p, km, w, dm, gm, delz, pt, p_gas, pe, p_int, A20(ws), cappa, dt, t1g, rdt, p_fac, s);
+    // finalize (riem_solver3.py:93-146)
+    for (int k = 0; k <= km; ++k) {
+      K_(ppe, k) = beta_neg ? K_(pe, k) + K_(p_int, k) : K_(pe, k);
+      if (last_call) {
+        K_(peln, k) = K_(logp, k);
+        K_(pk, k) = K_(pk3, k);
+        K_(pe, k) = K_(p_int, k);
+      } else {
+        K_(pe, k) = K_(pe_init, k);
+      }
+    }
+    K_(zh, km) = A20(zs);
+    for (int k = km - 1; k >= 0; --k) K_(zh, k) = K_(zh, k + 1) - K_(delz, k);
+  });
+  return 0;
+}
+
+}  // namespace pace

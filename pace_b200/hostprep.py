@@ -52,7 +52,7 @@ def column_namelist(cfg, npz):
 
 def calc_damp(damp_c, da_min, nord):
     """pyFV3/stencils/delnflux.py:22-38: (damp_c * da_min) ** (nord + 1), per level."""
-    return np.array([math.pow(float(d) * float(da_min), float(n) + 1.0) for d, n in zip(damp_c, nord)])
+    return np.array([math.pow(float(d) * float(da_min), float(n) + 1.0) for d, n in zip(damp_c, nord)] + [0.0])
 
 
 def all_columns(cfg, npz, da_min, da_min_c):
@@ -61,12 +61,30 @@ def all_columns(cfg, npz, da_min, da_min_c):
     # DelnFluxNoSG rounds its nord column in place (delnflux.py:1069)
     for n in ("nord_v", "nord_w", "nord_t"):
         col[n] = np.round(col[n])
-    out = {"col." + k: v for k, v in col.items()}
+    # [Z_DIM] quantities are allocated with npz+1 entries (NDSL sizer.py:141-154); stencils that run over
+    # npz+1 levels (updatedzd's delnflux) read the trailing 0
+    out = {"col." + k: np.concatenate([v, [0.0]]) for k, v in col.items()}
     out["col.delnflux_damp_vt"] = calc_damp(col["damp_vt"], da_min_c, col["nord_v"])  # d_sw.py:980-984
     out["col.delnflux_damp_w"] = calc_damp(col["damp_w"], da_min_c, col["nord_w"])    # d_sw.py:985-989
     out["col.delnflux_damp_vt_fv"] = calc_damp(col["damp_vt"], da_min, col["nord_v"])  # DelnFlux in fvtp2d_dp / _tm
     out["col.delnflux_damp_t_fv"] = calc_damp(col["damp_t"], da_min, col["nord_t"])    # DelnFlux in fvtp2d_dp_t
     return out
+
+
+def cubic_spline_constants(dp_ref, npz):
+    """pyFV3/stencils/updatedzd.py:130-167 cubic_spline_interpolation_constants."""
+    dp0 = np.asarray(dp_ref, dtype=np.float64)[:npz]
+    gk = np.zeros(npz + 1)
+    beta = np.zeros(npz + 1)
+    gamma = np.zeros(npz + 1)
+    gk[0] = dp0[1] / dp0[0]
+    beta[0] = gk[0] * (gk[0] + 0.5)
+    gamma[0] = (1.0 + gk[0] * (gk[0] + 1.5)) / beta[0]
+    gk[1:npz] = dp0[:-1] / dp0[1:]
+    for i in range(1, npz):
+        beta[i] = 2.0 + 2.0 * gk[i] - gamma[i - 1]
+        gamma[i] = gk[i] / beta[i]
+    return {"col.dzd_gk": gk, "col.dzd_beta": beta, "col.dzd_gamma": gamma}
 
 
 def _great_circle_dist(p1a, p1b, p2a, p2b):

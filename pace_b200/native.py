@@ -130,7 +130,10 @@ class NativeCore:
 
     def put_grid(self, grids):
         """grids: list over subdomains of dict name -> reference-layout array ("grid.*", "damp.*")."""
-        from .hostprep import derived_grid_fields
+        from .hostprep import cubic_spline_constants, derived_grid_fields
+
+        for name, v in cubic_spline_constants(grids[0]["grid.dp_ref"], self.npz).items():
+            self.set_column(name, v)
 
         g0 = grids[0]
         for name in g0:
