@@ -76,6 +76,31 @@ int pace_b200_update_dz_c(void* handle, double dt2);
 /* p_grad_c_stencil (pyFV3/stencils/dyn_core.py:122-173).  in: csw.delpc ad.pkc ad.gz   inout: uc vc */
 int pace_b200_p_grad_c(void* handle, double dt2);
 
+/* Pointwise stencils of DynamicalCore._compute: fv_setup (pyFV3/stencils/moist_cv.py:201-234),
+ * pt_to_potential_density_pt and omega_from_w (fv_dynamics.py:33-58), copy_defn on npz levels. */
+int pace_b200_fv_setup(void* handle);
+int pace_b200_pt_to_potential_density_pt(void* handle);
+int pace_b200_omega_from_w(void* handle);
+int pace_b200_copy_levels(void* handle, const char* src, const char* dst);
+
+/* One region of a halo update: the destination box (array indices) of subdomain dst_t is filled from
+ * subdomain src_t at index (aii*i + aij*j + bi, aji*i + ajj*j + bj); comp/src_comp select the x (0) or y (1)
+ * array of a vector pair, sign its sign.  Replaces Boundary + rotate_*_data + the pack/unpack index arrays of
+ * NDSL (comm/boundary.py:10-120, halo/rotate.py:4-50, halo/data_transformer.py:54-99). */
+typedef struct pace_b200_halo_op {
+  int dst_t, src_t, comp, src_comp;
+  double sign;
+  int i0, j0, ni, nj;
+  int aii, aij, bi, aji, ajj, bj;
+} pace_b200_halo_op;
+
+/* Upload a plan (list of ops between subdomains of this GPU) under plan_id in [0,16). */
+int pace_b200_halo_plan_set(void* handle, int plan_id, const void* ops, int n_ops);
+/* HaloUpdater.update() for up to 8 fields (or vector pairs when y_names != NULL) sharing one plan
+ * (NDSL/ndsl/halo/updater.py:150-303), levels [0, nk). */
+int pace_b200_halo_update(void* handle, int plan_id, const char* const* x_names, const char* const* y_names,
+                          int n, int nk);
+
 /* FiniteVolumeFluxPrep.__call__ (pyFV3/stencils/fxadv.py:590-691).
  * in: uc vc   out: ad.crx ad.cry ad.xfx ad.yfx dsw.uc_contra dsw.vc_contra */
 int pace_b200_fv_prep(void* handle, double dt);

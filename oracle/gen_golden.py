@@ -72,7 +72,8 @@ def main():
             for k in s.files:
                 a = s[k]
                 # compute domain (+1 for interface dims is kept: slice 3:-3 of the (n+7) allocation)
-                dst["%d:%s" % (r, k)] = a[3:-3, 3:-3] if a.ndim >= 2 else a
+                # 3-D: compute domain only; 2-D (phis, ps): full array — phis is read in the halo
+                dst["%d:%s" % (r, k)] = a[3:-3, 3:-3] if a.ndim == 3 else a
     np.savez_compressed(os.path.join(out, "%s_6rank_grid.npz" % tag), **grid)
     np.savez_compressed(os.path.join(out, "%s_6rank_init%s.npz" % (tag, suffix)), **init)
     np.savez_compressed(os.path.join(out, "%s_6rank_final%s.npz" % (tag, suffix)), **final)

@@ -32,6 +32,13 @@ class Config(ctypes.Structure):
     )
 
 
+class HaloOp(ctypes.Structure):
+    """Mirror of `pace_b200_halo_op`."""
+
+    _fields_ = [(n, _I) for n in ("dst_t", "src_t", "comp", "src_comp")] + [("sign", _D)] + [
+        (n, _I) for n in ("i0", "j0", "ni", "nj", "aii", "aij", "bi", "aji", "ajj", "bj")]
+
+
 _lib = None
 
 
@@ -61,6 +68,8 @@ def bind(lib):
     lib.pace_b200_set_stream.argtypes = [vp, vp]
     lib.pace_b200_set_field.argtypes = [vp, ctypes.c_char_p, vp]
     lib.pace_b200_set_column.argtypes = [vp, ctypes.c_char_p, ctypes.POINTER(ctypes.c_double), _I]
+    lib.pace_b200_halo_plan_set.argtypes = [vp, _I, vp, _I]
+    lib.pace_b200_halo_update.argtypes = [vp, _I, ctypes.POINTER(_S), ctypes.POINTER(_S), _I, _I]
     for name, extra in MODULE_CALLS.items():
         fn = getattr(lib, "pace_b200_" + name)
         fn.argtypes = [vp] + extra
@@ -76,6 +85,10 @@ MODULE_CALLS = {
     "p_grad_c": [_D],
     "fv_prep": [_D],
     "d_sw": [_D],
+    "fv_setup": [],
+    "pt_to_potential_density_pt": [],
+    "omega_from_w": [],
+    "copy_levels": [_S, _S],
     "riem_solver3": [_D, _I],
     "update_dz_d": [_D],
     "zero_data": [_I],
@@ -96,4 +109,4 @@ MODULE_CALLS = {
 }
 
 EXPORTS = ["pace_b200_row_stride", "pace_b200_create", "pace_b200_destroy", "pace_b200_last_error",
-           "pace_b200_set_stream", "pace_b200_set_field", "pace_b200_set_column"] + ["pace_b200_" + n for n in MODULE_CALLS]
+           "pace_b200_set_stream", "pace_b200_set_field", "pace_b200_set_column", "pace_b200_halo_plan_set", "pace_b200_halo_update"] + ["pace_b200_" + n for n in MODULE_CALLS]

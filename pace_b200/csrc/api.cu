@@ -167,6 +167,14 @@ int pace_b200_c_sw(void* h, double dt2) { ENTRY(c_sw(*c, dt2)) }
 int pace_b200_update_dz_c(void* h, double dt2) { ENTRY(update_dz_c(*c, dt2)) }
 int pace_b200_p_grad_c(void* h, double dt2) { ENTRY(p_grad_c(*c, dt2)) }
 int pace_b200_fv_prep(void* h, double dt) { ENTRY(fv_prep(*c, dt)) }
+int pace_b200_fv_setup(void* h) { ENTRY(fv_setup(*c)) }
+int pace_b200_pt_to_potential_density_pt(void* h) { ENTRY(pt_to_potential_density_pt(*c)) }
+int pace_b200_omega_from_w(void* h) { ENTRY(omega_from_w(*c)) }
+int pace_b200_copy_levels(void* h, const char* src, const char* dst) { ENTRY(copy_levels(*c, src, dst)) }
+int pace_b200_halo_plan_set(void* h, int plan_id, const void* ops, int n_ops) { ENTRY(halo_plan_set(*c, plan_id, ops, n_ops)) }
+int pace_b200_halo_update(void* h, int plan_id, const char* const* x_names, const char* const* y_names, int n, int nk) {
+  ENTRY(halo_update(*c, plan_id, x_names, y_names, n, nk))
+}
 int pace_b200_riem_solver3(void* h, double dt, int last_call) { ENTRY(riem_solver3(*c, dt, last_call)) }
 int pace_b200_update_dz_d(void* h, double dt) { ENTRY(update_dz_d(*c, dt)) }
 int pace_b200_zero_data(void* h, int first_timestep) { ENTRY(zero_data(*c, first_timestep)) }

@@ -35,6 +35,8 @@ struct Core {
   std::map<std::string, double*> scratch;   // library-owned 3-D scratch, allocated on first use
   std::map<std::string, std::vector<double>> hcol;  // host copies of K-columns set via pace_b200_set_column
   std::map<std::string, int> colsize;
+  void* halo_ops[16] = {nullptr};               // device copies of halo plans (pace_b200_halo_plan_set)
+  int halo_nops[16] = {0};
   std::vector<void*> owned;
   std::string err;
 
@@ -54,6 +56,12 @@ int c_sw(Core& c, double dt2);
 int update_dz_c(Core& c, double dt2);
 int p_grad_c(Core& c, double dt2);
 int set_column(Core& c, const char* name, const double* host_values, int n);
+int halo_plan_set(Core& c, int plan_id, const void* host_ops, int n_ops);
+int halo_update(Core& c, int plan_id, const char* const* x_names, const char* const* y_names, int n, int nk);
+int fv_setup(Core& c);
+int pt_to_potential_density_pt(Core& c);
+int omega_from_w(Core& c);
+int copy_levels(Core& c, const char* src_name, const char* dst_name);
 int fv_prep(Core& c, double dt);
 int riem_solver3(Core& c, double dt, int last_call);
 int update_dz_d(Core& c, double dt);

@@ -1,0 +1,176 @@
+"""DycoreEngine: the call sequences of the reference's AcousticDynamics.__call__ and DynamicalCore._compute
+(pyFV3/stencils/dyn_core.py:714-1013, fv_dynamics.py:513-655) over ALL subdomains resident on one GPU.
+
+The numerics are the CUDA kernels behind the C ABI (include/pace_b200.h); this file only orders the module calls
+and the halo updates, like the reference's Python classes do.  Where the reference starts a halo update early and
+waits later (HaloUpdater.start / wait), the fields are not modified in between, so the exchange is issued once at
+the wait point on the same stream.
+"""
+import numpy as np
+
+from .halo import HaloPlanner
+from .native import NativeCore
+
+GRAV = 9.80665
+HUGE_R = 1.0e40
+CNST_0P20 = 0.2
+
+# halo plan ids
+A3, A2, B3, D3, C3, SYNC = 0, 1, 2, 3, 4, 5
+
+STATE_3D = [
+    "u", "v", "w", "ua", "va", "uc", "vc", "delp", "delz", "pe", "pt", "peln", "pk", "pkz", "qvapor", "qliquid",
+    "qice", "qrain", "qsnow", "qgraupel", "qo3mr", "qsgs_tke", "qcld", "q_con", "omga", "mfxd", "mfyd", "cxd", "cyd",
+    "diss_estd",
+]
+STATE_2D = ["ps", "phis"]
+ACOUSTIC_TEMPORARIES = ["ad.ut", "ad.vt", "ad.gz", "ad.zh", "ad.pem", "ad.pkc", "ad.pk3", "ad.heat_source", "ad.cappa",
+                        "ad.divgd", "ad.crx", "ad.cry", "ad.xfx", "ad.yfx", "csw.delpc", "csw.ptc", "dyn.dp1", "dyn.cvm"]
+TEMPORARIES_2D = ["ad.ws3", "ad.wsd", "ad.zs"]
+
+
+def nk_heat_dissipation(cfg, npz):
+    """pyFV3/stencils/dyn_core.py:176-191 get_nk_heat_dissipation."""
+    if cfg["convert_ke"] or cfg["vtdm4"] > 1.0e-4:
+        return npz
+    if cfg["d2_bg_k1"] < 1.0e-3:
+        return 0
+    if cfg["d2_bg_k2"] < 1.0e-3:
+        return 1
+    return 2
+
+
+class DycoreEngine:
+    def __init__(self, n_tile, layout, npz, grids, ranks=None, device="cuda:0", _lib_handle=None, **cfg):
+        """grids: list (one per resident subdomain) of dicts with the reference's GridData / DampingCoefficients
+        arrays ("grid.*", "damp.*", reference layout).  ranks: cube ranks of those subdomains (default: all)."""
+        self.planner = HaloPlanner(n_tile, layout)
+        self.ranks = list(range(self.planner.total_ranks)) if ranks is None else list(ranks)
+        if len(self.ranks) != self.planner.total_ranks:
+            raise NotImplementedError("multi-GPU placement goes through pace_b200.distributed")
+        n = self.planner.n
+        g0 = grids[0]
+        cfg = dict(cfg)
+        cfg.setdefault("ptop", float(g0["grid.ptop"]))
+        cfg.setdefault("da_min", float(g0["damp.da_min"]))
+        cfg.setdefault("da_min_c", float(g0["damp.da_min_c"]))
+        self.core = NativeCore(n, n, npz, n_tiles=len(self.ranks), device=device, _lib_handle=_lib_handle,
+                               edge_flags=[self.planner.edge_flags(r) for r in self.ranks], npx=n_tile + 1,
+                               npy=n_tile + 1, **cfg)
+        self.cfg = self.core.cfg
+        self.npz = npz
+        core = self.core
+        for name in STATE_3D + ACOUSTIC_TEMPORARIES:
+            core.alloc3(name)
+        for name in STATE_2D + TEMPORARIES_2D:
+            core.alloc2(name)
+        core.t["ad.pk3"].fill_(HUGE_R)  # dyn_core.py:476-477
+        core.put_grid(grids)
+        core.set_columns_from_config()
+        local = {r: n for n, r in enumerate(self.ranks)}
+        pl = self.planner
+        core.set_halo_plan(A3, pl.scalar_plan(False, False, 3, self.ranks), local)
+        core.set_halo_plan(A2, pl.scalar_plan(False, False, 2, self.ranks), local)
+        core.set_halo_plan(B3, pl.scalar_plan(True, True, 3, self.ranks), local)
+        core.set_halo_plan(D3, pl.vector_plan("d", 3, self.ranks), local)
+        core.set_halo_plan(C3, pl.vector_plan("c", 3, self.ranks), local)
+        core.set_halo_plan(SYNC, pl.interface_sync_plan(self.ranks), local)
+        self._nk_heat = nk_heat_dissipation(self.cfg, npz)
+        self._do_del2cubed = self._nk_heat != 0 and self.cfg["d_con"] > 1.0e-5
+        self._check_config()
+
+    def _check_config(self):
+        """Unimplemented-option guards of the reference, same messages (fv_dynamics.py:178-203, 462-499;
+        dyn_core.py:434-439)."""
+        c = self.cfg
+        if c["dt_atmos"] == 0:
+            raise RuntimeError("Bad dynamical core configuration: the atmospheric timestep is 0 seconds!")
+        if c["nwat"] != 6:
+            raise NotImplementedError("Dynamical core (fv_dynamics): nwat==%d is not implemented."
+                                      " Only nwat=6 has been implemented." % c["nwat"])
+        if c["d_ext"] != 0:
+            raise RuntimeError("Acoustics (dyn_core): d_ext != 0 is not implemented")
+        if c["beta"] != 0:
+            raise RuntimeError("Acoustics (dyn_core): beta != 0 is not implemented")
+        if c["hydrostatic"]:
+            raise NotImplementedError("Hydrostatic is not implemented")
+        if c["consv_te"] > 0:
+            raise NotImplementedError("Dynamical Core (fv_dynamics): compute total energy is not implemented")
+        if (not c["rf_fast"]) and c["tau"] != 0:
+            raise NotImplementedError("Dynamical Core (fv_dynamics): Rayleigh_Super,"
+                                      " called when rf_fast=False and tau !=0, is not implemented")
+        if c["inline_q"]:
+            raise NotImplementedError("Dynamical core (fv_dynamics):tracer_2d not implemented. z_tracer available")
+
+    # -- state ingest / egress -----------------------------------------------------------------------------------
+    def set_state(self, states):
+        """states: list over resident subdomains of dict name -> reference-layout array (DycoreState fields)."""
+        for name in STATE_3D + STATE_2D:
+            if name in states[0]:
+                self.core.put(name, [s[name] for s in states])
+        # AcousticDynamics.__init__: zs = phis / GRAV (dyn_core.py:489-496)
+        self.core.put("ad.zs", [np.asarray(s["phis"], dtype=np.float64) / GRAV for s in states])
+
+    def get_state(self, names=None):
+        names = names or (STATE_3D + STATE_2D)
+        out = [dict() for _ in self.ranks]
+        for name in names:
+            for n, a in enumerate(self.core.get(name)):
+                out[n][name] = a
+        return out
+
+    # -- AcousticDynamics.__call__ (dyn_core.py:714-1013) ------------------------------------------------------
+    def acoustic_dynamics(self, timestep, n_map=1):
+        core, c, npz = self.core, self.cfg, self.npz
+        n_split = int(c["n_split"])
+        end_step = n_map == int(c["k_split"])
+        dt = timestep / n_split
+        dt2 = 0.5 * dt
+        core.halo_update(A3, ["q_con", "ad.cappa"])
+        core.call("zero_data", int(n_map == 1))
+        for it in range(n_split):
+            remap_step = it == n_split - 1
+            if it == 0:
+                core.call("gz_from_zs_delz")
+                core.halo_update(A3, ["delp", "pt"])
+            if it == n_split - 1 and end_step and c["use_old_omega"]:
+                core.call("pem_from_delp")
+            core.halo_update(D3, ["u"], ["v"])
+            core.halo_update(A3, ["w"])
+            core.call("c_sw", dt2)
+            if c["nord"] > 0:
+                core.halo_update(B3, ["ad.divgd"])
+            if it == 0:
+                core.halo_update(A3, ["ad.gz"], nk=npz + 1)
+                core.call("copy_full", "ad.gz", "ad.zh")
+            else:
+                core.call("copy_full", "ad.zh", "ad.gz")
+            core.call("update_dz_c", dt2)
+            core.call("riem_solver_c", dt2)
+            core.call("p_grad_c", dt2)
+            core.halo_update(C3, ["uc"], ["vc"])
+            core.call("d_sw", dt)
+            core.halo_update(A3, ["delp", "pt", "q_con"])
+            core.call("update_dz_d", dt)
+            core.call("riem_solver3", dt, int(remap_step))
+            core.halo_update(A3, ["ad.zh"], nk=npz + 1)
+            core.halo_update(A2, ["ad.pkc"], nk=npz + 1)
+            if remap_step:
+                core.call("edge_pe")
+            core.call("pk3_halo")
+            core.call("compute_geopotential")
+            core.call("nh_p_grad", dt)
+            if c["rf_fast"]:
+                core.call("ray_fast", dt)
+            if it == n_split - 1 and c["grid_type"] < 4:
+                core.halo_update(SYNC, ["u"], ["v"])
+        if self._do_del2cubed:
+            core.halo_update(A3, ["ad.heat_source"])
+            cd = CNST_0P20 * c["da_min"]
+            core.call("del2cubed", "ad.heat_source", cd, min(3, int(c["nord"]) + 1))
+            core.call("apply_diffusive_heating", abs(dt * c["delt_max"]), self._nk_heat)
+
+    # -- DynamicalCore.compute_preamble (fv_dynamics.py:461-508) -------------------------------------------------
+    def compute_preamble(self):
+        self.core.call("fv_setup")
+        self.core.call("pt_to_potential_density_pt")

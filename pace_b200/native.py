@@ -149,6 +149,25 @@ class NativeCore:
             else:
                 self.put(name, arrs)
 
+    # -- halo exchange ---------------------------------------------------------------------------
+    def set_halo_plan(self, plan_id, ops, rank_to_local):
+        """ops: list of pace_b200.halo.HaloOp whose dst and src subdomains are both resident here."""
+        arr = (_lib.HaloOp * max(1, len(ops)))()
+        for n, o in enumerate(ops):
+            arr[n] = _lib.HaloOp(rank_to_local[o.dst_rank], rank_to_local[o.src_rank], o.comp, o.src_comp, o.sign,
+                                 o.i0, o.j0, o.ni, o.nj, o.aii, o.aij, o.bi, o.aji, o.ajj, o.bj)
+        rc = self.lib.pace_b200_halo_plan_set(self.handle, plan_id, ctypes.cast(arr, ctypes.c_void_p), len(ops))
+        if rc != 0:
+            raise NativeError("halo_plan_set: %s" % self.lib.pace_b200_last_error(self.handle).decode())
+
+    def halo_update(self, plan_id, x_names, y_names=None, nk=None):
+        n = len(x_names)
+        xs = (ctypes.c_char_p * n)(*[s.encode() for s in x_names])
+        ys = (ctypes.c_char_p * n)(*[s.encode() for s in y_names]) if y_names else None
+        rc = self.lib.pace_b200_halo_update(self.handle, plan_id, xs, ys, n, self.npz if nk is None else nk)
+        if rc != 0:
+            raise NativeError("halo_update: %s" % self.lib.pace_b200_last_error(self.handle).decode())
+
     # -- calls -----------------------------------------------------------------------------------
     def call(self, name, *scalars):
         fn = getattr(self.lib, "pace_b200_" + name)

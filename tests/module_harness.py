@@ -9,14 +9,15 @@ DT = DT_ATMOS  # k_split = n_split = 1 in the golden config
 DT2 = 0.5 * DT
 
 
-def make_core(backend, nx=12, ny=12, npz=79, **kw):
+def make_core(backend, nx=12, ny=12, npz=79, n_tiles=1, edge_flags=None, **kw):
     from pace_b200.native import NativeCore
 
     if backend == "hostemu":
         from tests import hostemu
 
-        return NativeCore(nx, ny, npz, device="cpu", _lib_handle=hostemu.load(), **kw)
-    return NativeCore(nx, ny, npz, device="cuda:0", **kw)
+        return NativeCore(nx, ny, npz, n_tiles=n_tiles, edge_flags=edge_flags, device="cpu",
+                          _lib_handle=hostemu.load(), **kw)
+    return NativeCore(nx, ny, npz, n_tiles=n_tiles, edge_flags=edge_flags, device="cuda:0", **kw)
 
 
 def load_state(core, state, grid):
