@@ -83,6 +83,18 @@ int pace_b200_pt_to_potential_density_pt(void* handle);
 int pace_b200_omega_from_w(void* handle);
 int pace_b200_copy_levels(void* handle, const char* src, const char* dst);
 
+/* TracerAdvection.__call__ (pyFV3/stencils/tracer_2d_1l.py:289-417) in the three pieces between which the
+ * reference updates the tracer halos: flux_compute + divide_fluxes_by_n_substeps; one sub-cycle
+ * (apply_mass_flux, then fvtp2d + apply_tracer_flux per tracer); swap_dp.
+ * inout: the nq tracers (qvapor, qliquid, qrain, qice, qsnow, qgraupel, qo3mr, qsgs_tke), dyn.dp1, cxd cyd mfxd mfyd */
+int pace_b200_tracer_flux_prep(void* handle, int n_split);
+int pace_b200_tracer_substep(void* handle, int nq);
+int pace_b200_tracer_swap_dp(void* handle);
+
+/* Test hook: the kernels' exp / log / pow (csrc/libm_port.cuh, bit-identical to the oracle's host libm)
+ * evaluated elementwise on device arrays.  op 0: exp(x), 1: log(x), 2: pow(x, y). */
+int pace_b200_math_eval(void* handle, int op, int n, const double* x, const double* y, double* out);
+
 /* One region of a halo update: the destination box (array indices) of subdomain dst_t is filled from
  * subdomain src_t at index (aii*i + aij*j + bi, aji*i + ajj*j + bj); comp/src_comp select the x (0) or y (1)
  * array of a vector pair, sign its sign.  Replaces Boundary + rotate_*_data + the pack/unpack index arrays of

@@ -70,6 +70,7 @@ def bind(lib):
     lib.pace_b200_set_column.argtypes = [vp, ctypes.c_char_p, ctypes.POINTER(ctypes.c_double), _I]
     lib.pace_b200_halo_plan_set.argtypes = [vp, _I, vp, _I]
     lib.pace_b200_halo_update.argtypes = [vp, _I, ctypes.POINTER(_S), ctypes.POINTER(_S), _I, _I]
+    lib.pace_b200_math_eval.argtypes = [vp, _I, _I, vp, vp, vp]
     for name, extra in MODULE_CALLS.items():
         fn = getattr(lib, "pace_b200_" + name)
         fn.argtypes = [vp] + extra
@@ -86,6 +87,9 @@ MODULE_CALLS = {
     "fv_prep": [_D],
     "d_sw": [_D],
     "fv_setup": [],
+    "tracer_flux_prep": [_I],
+    "tracer_substep": [_I],
+    "tracer_swap_dp": [],
     "pt_to_potential_density_pt": [],
     "omega_from_w": [],
     "copy_levels": [_S, _S],
@@ -109,4 +113,4 @@ MODULE_CALLS = {
 }
 
 EXPORTS = ["pace_b200_row_stride", "pace_b200_create", "pace_b200_destroy", "pace_b200_last_error",
-           "pace_b200_set_stream", "pace_b200_set_field", "pace_b200_set_column", "pace_b200_halo_plan_set", "pace_b200_halo_update"] + ["pace_b200_" + n for n in MODULE_CALLS]
+           "pace_b200_set_stream", "pace_b200_set_field", "pace_b200_set_column", "pace_b200_halo_plan_set", "pace_b200_halo_update", "pace_b200_math_eval"] + ["pace_b200_" + n for n in MODULE_CALLS]

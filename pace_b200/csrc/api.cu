@@ -168,6 +168,12 @@ int pace_b200_update_dz_c(void* h, double dt2) { ENTRY(update_dz_c(*c, dt2)) }
 int pace_b200_p_grad_c(void* h, double dt2) { ENTRY(p_grad_c(*c, dt2)) }
 int pace_b200_fv_prep(void* h, double dt) { ENTRY(fv_prep(*c, dt)) }
 int pace_b200_fv_setup(void* h) { ENTRY(fv_setup(*c)) }
+int pace_b200_math_eval(void* h, int op, int n, const double* x, const double* y, double* out) {
+  ENTRY(math_eval(*c, op, n, x, y, out))
+}
+int pace_b200_tracer_flux_prep(void* h, int n_split) { ENTRY(tracer_flux_prep(*c, n_split)) }
+int pace_b200_tracer_substep(void* h, int nq) { ENTRY(tracer_substep(*c, nq)) }
+int pace_b200_tracer_swap_dp(void* h) { ENTRY(tracer_swap_dp(*c)) }
 int pace_b200_pt_to_potential_density_pt(void* h) { ENTRY(pt_to_potential_density_pt(*c)) }
 int pace_b200_omega_from_w(void* h) { ENTRY(omega_from_w(*c)) }
 int pace_b200_copy_levels(void* h, const char* src, const char* dst) { ENTRY(copy_levels(*c, src, dst)) }

@@ -156,9 +156,12 @@ inline Box box_compute(const Geo& g, int oi = 0, int oj = 0, int ai = 0, int aj 
 }
 
 // ---- math: single point of definition for the transcendentals (parity) -------------
-__device__ __forceinline__ double fv_exp(double x) { return exp(x); }
-__device__ __forceinline__ double fv_log(double x) { return log(x); }
-__device__ __forceinline__ double fv_pow(double x, double y) { return pow(x, y); }
+}  // namespace pace
+#include "libm_port.cuh"
+namespace pace {
+__device__ __forceinline__ double fv_exp(double x) { return libm::exp_(x); }
+__device__ __forceinline__ double fv_log(double x) { return libm::log_(x); }
+__device__ __forceinline__ double fv_pow(double x, double y) { return libm::pow_(x, y); }
 __device__ __forceinline__ double fv_sqrt(double x) { return sqrt(x); }
 __device__ __forceinline__ double fv_abs(double x) { return fabs(x); }
 // gtscript min/max/sign as the numpy backend evaluates them (np.minimum/np.maximum semantics on

@@ -58,6 +58,10 @@ int p_grad_c(Core& c, double dt2);
 int set_column(Core& c, const char* name, const double* host_values, int n);
 int halo_plan_set(Core& c, int plan_id, const void* host_ops, int n_ops);
 int halo_update(Core& c, int plan_id, const char* const* x_names, const char* const* y_names, int n, int nk);
+int tracer_flux_prep(Core& c, int n_split);
+int tracer_substep(Core& c, int nq);
+int tracer_swap_dp(Core& c);
+int math_eval(Core& c, int op, int n, const double* x, const double* y, double* out);
 int fv_setup(Core& c);
 int pt_to_potential_density_pt(Core& c);
 int omega_from_w(Core& c);

@@ -2,6 +2,7 @@
 #pragma once
 #include <cstdlib>
 #include <cstring>
+#include <cmath>
 #define __device__
 #define __host__
 #define __global__

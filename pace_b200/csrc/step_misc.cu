@@ -64,3 +64,17 @@ int copy_levels(Core& c, const char* src_name, const char* dst_name) {
 }
 
 }  // namespace pace
+
+namespace pace {
+// Test hook: evaluate the transcendentals used by the kernels (csrc/libm_port.cuh) elementwise on device
+// arrays, so tests can compare them bit-for-bit with the host libm.  op 0: exp(x), 1: log(x), 2: pow(x, y).
+int math_eval(Core& c, int op, int n, const double* x, const double* y, double* out) {
+  Geo g = c.g;
+  g.nt = 1;
+  launch_ijk(c.stream, g, Box{0, 0, 0, n, 1, 1}, [=] __device__(const Pt& p) {
+    const int i = p.i;
+    out[i] = op == 0 ? fv_exp(x[i]) : (op == 1 ? fv_log(x[i]) : fv_pow(x[i], y[i]));
+  });
+  return 0;
+}
+}  // namespace pace

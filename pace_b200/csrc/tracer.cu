@@ -1,0 +1,87 @@
+// Tracer advection (Fortran tracer_2d_1L): sub-cycled fvtp2d transport of the NQ tracers with the mass
+// fluxes / Courant numbers accumulated over the acoustic substeps.
+//
+// Reference: pyFV3/stencils/tracer_2d_1l.py:25-176 (stencils), :289-417 (__call__).  The halo updates between
+// sub-cycles are issued by the caller (engine.py), exactly where the reference calls its HaloUpdater.
+#include "transport.hpp"
+
+namespace pace {
+
+static const char* TRACER_NAMES[9] = {"qvapor", "qliquid", "qrain", "qice", "qsnow", "qgraupel", "qo3mr", "qsgs_tke", "qcld"};
+const char* tracer_name(int n) { return TRACER_NAMES[n]; }  // ndsl/dsl/gt4py_utils.py:28-38
+
+// flux_compute + divide_fluxes_by_n_substeps (tracer_2d_1l.py:47-108)
+int tracer_flux_prep(Core& c, int n_split) {
+  const Geo g = c.g;
+  double *cx = c.F("cxd"), *cy = c.F("cyd"), *mfx = c.F("mfxd"), *mfy = c.F("mfyd");
+  double *xfx = c.FS("tr.x_area_flux"), *yfx = c.FS("tr.y_area_flux");
+  const double *dxa = c.F("grid.dxa"), *dya = c.F("grid.dya"), *dx = c.F("grid.dx"), *dy = c.F("grid.dy"),
+               *sin_sg1 = c.F("grid.sin_sg1"), *sin_sg2 = c.F("grid.sin_sg2"), *sin_sg3 = c.F("grid.sin_sg3"),
+               *sin_sg4 = c.F("grid.sin_sg4");
+  if (!c.err.empty()) return 1;
+  const int is = g.is, ie = g.ie, js = g.js, je = g.je;
+  const double frac = 1.0 / n_split;
+  // origin_full, domain_full(add=(1,1,0)): the whole (nx+7) x (ny+7) allocation
+  launch_ijk(c.stream, g, Box{0, 0, 0, g.nx + 7, g.ny + 7, g.nz}, [=] __device__(const Pt& p) {
+    double xv = A0(xfx), yv = A0(yfx);
+    if (p.i >= is && p.i <= ie + 1 && p.j >= js - 3 && p.j <= je + 3) {
+      double cxv = A0(cx);
+      xv = cxv > 0 ? cxv * A2(dxa, -1, 0) * A20(dy) * A2(sin_sg3, -1, 0) : cxv * A20(dxa) * A20(dy) * A20(sin_sg1);
+    }
+    if (p.i >= is - 3 && p.i <= ie + 3 && p.j >= js && p.j <= je + 1) {
+      double cyv = A0(cy);
+      yv = cyv > 0 ? cyv * A2(dya, 0, -1) * A20(dx) * A2(sin_sg4, 0, -1) : cyv * A20(dya) * A20(dx) * A20(sin_sg2);
+    }
+    if (n_split > 1) {
+      A0(cx) = A0(cx) * frac;
+      xv = xv * frac;
+      A0(mfx) = A0(mfx) * frac;
+      A0(cy) = A0(cy) * frac;
+      yv = yv * frac;
+      A0(mfy) = A0(mfy) * frac;
+    }
+    A0(xfx) = xv;
+    A0(yfx) = yv;
+  });
+  return 0;
+}
+
+// one sub-cycle: apply_mass_flux, then fvtp2d + apply_tracer_flux for each tracer (tracer_2d_1l.py:381-411)
+int tracer_substep(Core& c, int nq) {
+  const Geo g = c.g;
+  cudaStream_t st = c.stream;
+  double *dp1 = c.F("dyn.dp1"), *dp2 = c.FS("tr.tmp_dp");
+  const double *cx = c.F("cxd"), *cy = c.F("cyd"), *mfx = c.F("mfxd"), *mfy = c.F("mfyd"), *rarea = c.F("grid.rarea");
+  double *xfx = c.FS("tr.x_area_flux"), *yfx = c.FS("tr.y_area_flux"), *fx = c.FS("tr.x_flux"), *fy = c.FS("tr.y_flux");
+  if (!c.err.empty()) return 1;
+  launch_ijk(st, g, box_compute(g), [=] __device__(const Pt& p) {
+    A0(dp2) = A0(dp1) + (A0(mfx) - A(mfx, 1, 0, 0) + A0(mfy) - A(mfy, 0, 1, 0)) * A20(rarea);
+  });
+  for (int n = 0; n < nq; ++n) {
+    double* q = c.F(TRACER_NAMES[n]);
+    if (!c.err.empty()) return 1;
+    Fvtp2dArgs a;
+    a.q = q; a.crx = cx; a.cry = cy; a.xfx = xfx; a.yfx = yfx; a.fx = fx; a.fy = fy;
+    a.x_mass_flux = mfx; a.y_mass_flux = mfy; a.hord = c.cfg.hord_tr; a.nk = g.nz;
+    if (fvtp2d(c, a)) return 1;
+    launch_ijk(st, g, box_compute(g), [=] __device__(const Pt& p) {
+      A0(q) = (A0(q) * A0(dp1) + (A0(fx) - A(fx, 1, 0, 0) + A0(fy) - A(fy, 0, 1, 0)) * A20(rarea)) / A0(dp2);
+    });
+  }
+  return 0;
+}
+
+// swap_dp (tracer_2d_1l.py:171-176), compute domain
+int tracer_swap_dp(Core& c) {
+  const Geo g = c.g;
+  double *dp1 = c.F("dyn.dp1"), *dp2 = c.FS("tr.tmp_dp");
+  if (!c.err.empty()) return 1;
+  launch_ijk(c.stream, g, box_compute(g), [=] __device__(const Pt& p) {
+    double tmp = A0(dp1);
+    A0(dp1) = A0(dp2);
+    A0(dp2) = tmp;
+  });
+  return 0;
+}
+
+}  // namespace pace

@@ -170,6 +170,21 @@ class DycoreEngine:
             core.call("del2cubed", "ad.heat_source", cd, min(3, int(c["nord"]) + 1))
             core.call("apply_diffusive_heating", abs(dt * c["delt_max"]), self._nk_heat)
 
+    # -- TracerAdvection.__call__ (tracer_2d_1l.py:289-417) ----------------------------------------------------
+    TRACERS = ["qvapor", "qliquid", "qrain", "qice", "qsnow", "qgraupel", "qo3mr", "qsgs_tke"]  # NQ = 8 (GFS)
+
+    def tracer_advection(self):
+        core = self.core
+        cmax_max_all_ranks = 2.0  # the reference hard-codes this in place of an allreduce (tracer_2d_1l.py:337-364)
+        n_split = int(np.floor(1.0 + cmax_max_all_ranks))
+        core.call("tracer_flux_prep", n_split)
+        core.halo_update(A3, self.TRACERS)
+        for it in range(n_split):
+            core.call("tracer_substep", len(self.TRACERS))
+            if it != n_split - 1:
+                core.halo_update(A3, self.TRACERS)
+                core.call("tracer_swap_dp")
+
     # -- DynamicalCore.compute_preamble (fv_dynamics.py:461-508) -------------------------------------------------
     def compute_preamble(self):
         self.core.call("fv_setup")

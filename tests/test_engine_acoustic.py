@@ -79,3 +79,26 @@ def test_acoustic_six_tiles_gpu(golden):
     # libdevice exp/log/pow differ from the oracle's glibc by <= 1 ulp; through the p' = p_full - p_hydrostatic
     # cancellation of the Riemann solves that becomes ~1e-11 relative after one acoustic call
     run("cuda", golden, 1e-9)
+
+
+TRACER_OUT = ["qvapor", "qliquid", "qrain", "qice", "qsnow", "qgraupel", "qo3mr", "qsgs_tke", "cxd", "cyd", "mfxd",
+              "mfyd", "dyn.dp1"]
+
+
+def run_tracer(backend, golden, tol):
+    eng = make_engine(backend)
+    eng.compute_preamble()
+    eng.core.call("copy_levels", "delp", "dyn.dp1")
+    eng.acoustic_dynamics(225.0, n_map=1)
+    eng.tracer_advection()
+    eng.core.sync()
+    compare_rank0(eng, golden.after("tracer_advection"), TRACER_OUT, tol)
+
+
+def test_tracer_six_tiles_hostemu(golden):
+    run_tracer("hostemu", golden, 0.0)
+
+
+@pytest.mark.gpu
+def test_tracer_six_tiles_gpu(golden):
+    run_tracer("cuda", golden, 1e-9)
