@@ -95,6 +95,18 @@ int pace_b200_tracer_swap_dp(void* handle);
  * evaluated elementwise on device arrays.  op 0: exp(x), 1: log(x), 2: pow(x, y). */
 int pace_b200_math_eval(void* handle, int op, int n, const double* x, const double* y, double* out);
 
+/* MapSingle.__call__ (pyFV3/stencils/map_single.py:155-208; Fortran map_single / map_scalar / map1_ppm):
+ * conservative PPM remap of q from source interfaces pe1 to target interfaces pe2, per column.
+ * iv: -2 (w), -1 (winds), 0 (positive-definite tracers), 1 (others); kord <= 10; qs: optional bottom value (iv -2). */
+int pace_b200_map_single(void* handle, const char* q, const char* pe1, const char* pe2, const char* qs, int iv,
+                         int kord, int x_interface, int y_interface, double qmin);
+
+/* LagrangianToEulerian.__call__ (pyFV3/stencils/remapping.py:522-731) in two pieces around the saturation
+ * adjustment: remap_main = init_pe .. copy_from_below (13 MapSingle + fillz); remap_finish = moist_pt_last_step
+ * (last_step) or pt /= pkz. */
+int pace_b200_remap_main(void* handle, int nq);
+int pace_b200_remap_finish(void* handle, int last_step);
+
 /* One region of a halo update: the destination box (array indices) of subdomain dst_t is filled from
  * subdomain src_t at index (aii*i + aij*j + bi, aji*i + ajj*j + bj); comp/src_comp select the x (0) or y (1)
  * array of a vector pair, sign its sign.  Replaces Boundary + rotate_*_data + the pack/unpack index arrays of

@@ -167,6 +167,14 @@ def instrument_deep(dycore, state, rec_watch, wrap):
         v = getattr(dzd, n, None)
         if n.startswith("_") and not n.startswith("__") and hasattr(v, "data") and hasattr(v, "dims") and len(v.dims) >= 2:
             rec_watch["dzd." + n.lstrip("_")] = v
+    rm = dycore._lagrangian_to_eulerian_obj
+    for n in ("_pe1", "_pe2", "_pe3", "_dp2", "_pn2", "_pe0", "_gz", "_cvm"):
+        rec_watch["rm." + n.lstrip("_")] = getattr(rm, n)
+    for n in ("_init_pe", "_moist_cv_pt_pressure", "_pn2_pk_delp", "_map_single_pt", "_mapn_tracer", "_map_single_w",
+              "_map_single_delz", "_undo_delz_adjust_and_copy_peln", "_moist_cv_pkz", "_pressures_mapu",
+              "_map_single_u", "_pressures_mapv", "_map_single_v", "_update_ua", "_copy_from_below_stencil",
+              "_saturation_adjustment", "_moist_cv_last_step_stencil", "_basic_adjust_divide_stencil"):
+        wrap(rm, n, "rm." + n.lstrip("_"))
     nh = ad.nonhydrostatic_pressure_gradient
     for n in dir(nh):
         v = getattr(nh, n, None)

@@ -87,6 +87,9 @@ MODULE_CALLS = {
     "fv_prep": [_D],
     "d_sw": [_D],
     "fv_setup": [],
+    "remap_main": [_I],
+    "remap_finish": [_I],
+    "map_single": [_S, _S, _S, _S, _I, _I, _I, _I, _D],
     "tracer_flux_prep": [_I],
     "tracer_substep": [_I],
     "tracer_swap_dp": [],

@@ -168,6 +168,16 @@ int pace_b200_update_dz_c(void* h, double dt2) { ENTRY(update_dz_c(*c, dt2)) }
 int pace_b200_p_grad_c(void* h, double dt2) { ENTRY(p_grad_c(*c, dt2)) }
 int pace_b200_fv_prep(void* h, double dt) { ENTRY(fv_prep(*c, dt)) }
 int pace_b200_fv_setup(void* h) { ENTRY(fv_setup(*c)) }
+int pace_b200_remap_main(void* h, int nq) { ENTRY(remap_main(*c, nq)) }
+int pace_b200_remap_finish(void* h, int last_step) { ENTRY(remap_finish(*c, last_step)) }
+int pace_b200_map_single(void* h, const char* q, const char* pe1, const char* pe2, const char* qs, int iv, int kord,
+                         int x_interface, int y_interface, double qmin) {
+  Core* c = (Core*)h;
+  c->err.clear();
+  double *qp = c->F(q), *p1 = c->F(pe1), *p2 = c->F(pe2), *qsp = opt_field(c, qs);
+  if (!c->err.empty()) return 1;
+  return finish(c, map_single(*c, qp, p1, p2, qsp, iv, kord, x_interface != 0, y_interface != 0, qmin));
+}
 int pace_b200_math_eval(void* h, int op, int n, const double* x, const double* y, double* out) {
   ENTRY(math_eval(*c, op, n, x, y, out))
 }

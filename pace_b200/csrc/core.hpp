@@ -62,6 +62,10 @@ int tracer_flux_prep(Core& c, int n_split);
 int tracer_substep(Core& c, int nq);
 int tracer_swap_dp(Core& c);
 int math_eval(Core& c, int op, int n, const double* x, const double* y, double* out);
+int map_single(Core& c, double* q, const double* pe1, const double* pe2, const double* qs, int iv, int kord, bool xi,
+               bool yi, double qmin);
+int remap_main(Core& c, int nq);
+int remap_finish(Core& c, int last_step);
 int fv_setup(Core& c);
 int pt_to_potential_density_pt(Core& c);
 int omega_from_w(Core& c);

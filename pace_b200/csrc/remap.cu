@@ -1,0 +1,530 @@
+// Lagrangian-to-Eulerian vertical remapping: MapSingle (Fortran map_single / map_scalar / map1_ppm), the PPM
+// profile reconstruction (remap_profile, kord <= 10), MapNTracer + fillz, and the pointwise stencils of
+// LagrangianToEulerian.__call__.
+//
+// Reference: pyFV3/stencils/map_single.py:14-81,155-208; remap_profile.py:20-147 (constraints), :150-250
+// (set_initial_vals), :253-337 (apply_constraints), :340-563 (set_interpolation_coefficients);
+// mapn_tracer.py:14-87; fillz.py:16-172; remapping.py:43-284 (stencils), :522-731 (__call__);
+// moist_cv.py:15-199.
+//
+// One MapSingle = 7 reference launches through 9 full-size temporaries; here it is ONE column kernel: a thread
+// owns a column, the profile (q, gam, a4_1..4, extm) lives in thread-local arrays, pe1/pe2/q are read once and q
+// written once.  i is the fastest thread index, so every level access is a coalesced row segment.
+#include "core.hpp"
+
+namespace pace {
+
+namespace {
+
+constexpr int KMAX = 96;  // thread-local column length (npz + 1 <= KMAX; 79 and 91 level configurations)
+
+struct Col {
+  double q[KMAX + 1], gam[KMAX + 1], a1[KMAX], a2[KMAX], a3[KMAX], a4[KMAX], dp[KMAX];
+  bool extm[KMAX], ext5[KMAX], ext6[KMAX];
+};
+
+__device__ __forceinline__ void a4_from(double a1, double a2, double a3, double& a4) { a4 = 3.0 * (2.0 * a1 - (a2 + a3)); }
+
+// remap_profile.py:88-111 posdef_constraint_iv1
+__device__ __forceinline__ void posdef_iv1(double& a1, double& a2, double& a3, double& a4) {
+  double da1 = a3 - a2, da2 = da1 * da1, a6da = a4 * da1;
+  if (((a1 - a2) * (a1 - a3)) >= 0.0) { a2 = a1; a3 = a1; a4 = 0.0; }
+  else if (a6da < -1.0 * da2) { a4 = 3.0 * (a2 - a1); a3 = a2 - a4; }
+  else if (a6da > da2) { a4 = 3.0 * (a3 - a1); a2 = a3 - a4; }
+}
+// remap_profile.py:56-85 posdef_constraint_iv0
+__device__ __forceinline__ void posdef_iv0(double& a1, double& a2, double& a3, double& a4) {
+  if (a1 <= 0.0) { a2 = a1; a3 = a1; a4 = 0.0; }
+  else if (fabs(a3 - a2) < -a4 && (a1 + 0.25 * ((a3 - a2) * (a3 - a2)) / a4 + a4 * (1.0 / 12.0)) < 0.0) {
+    if (a1 < a3 && a1 < a2) { a3 = a1; a2 = a1; a4 = 0.0; }
+    else if (a3 > a2) { a4 = 3.0 * (a2 - a1); a3 = a2 - a4; }
+    else { a4 = 3.0 * (a3 - a1); a2 = a3 - a4; }
+  }
+}
+// remap_profile.py:114-135 remap_constraint
+__device__ __forceinline__ void remap_constraint(double& a1, double& a2, double& a3, double& a4, bool extm) {
+  double da1 = a3 - a2, da2 = da1 * da1, a6da = a4 * da1;
+  if (extm) { a2 = a1; a3 = a1; a4 = 0.0; }
+  else if (a6da < -da2) { a4 = 3.0 * (a2 - a1); a3 = a2 - a4; }
+  else if (a6da > da2) { a4 = 3.0 * (a3 - a1); a2 = a3 - a4; }
+}
+__device__ __forceinline__ double lim3_min(double a, double b, double c) {  // a if a<b and a<c else b if b<c else c
+  return (a < b && a < c) ? a : (b < c ? b : c);
+}
+__device__ __forceinline__ double lim3_max(double a, double b, double c) {
+  return (a > b && a > c) ? a : (b > c ? b : c);
+}
+
+// RemapProfile.__call__ (remap_profile.py:644-697) on one column.  in: c.a1 (cell means), c.dp; out: c.a2..a4
+__device__ void remap_profile(Col& c, int km, int iv, int kord, double qs, double qmin) {
+  double* q = c.q;
+  double* gam = c.gam;
+  const double *a1 = c.a1, *delp = c.dp;
+  // ---- set_initial_vals (domain: km+1 interface levels) ----
+  if (iv != -2) {
+    double gr = delp[1] / delp[0];
+    double bet = gr * (gr + 0.5);
+    q[0] = ((gr + gr) * (gr + 1.0) * a1[0] + a1[1]) / bet;
+    gam[0] = (1.0 + gr * (gr + 1.5)) / bet;
+    for (int k = 1; k < km; ++k) {
+      double d4 = delp[k - 1] / delp[k];
+      bet = 2.0 + d4 + d4 - gam[k - 1];
+      q[k] = (3.0 * (a1[k - 1] + d4 * a1[k]) - q[k - 1]) / bet;
+      gam[k] = d4 / bet;
+    }
+    {
+      double d4 = delp[km - 2] / delp[km - 1];
+      double a_bot = 1.0 + d4 * (d4 + 1.5);
+      q[km] = (2.0 * d4 * (d4 + 1.0) * a1[km - 1] + a1[km - 2] - a_bot * q[km - 1]) / (d4 * (d4 + 0.5) - a_bot * gam[km - 1]);
+    }
+    for (int k = km - 1; k >= 0; --k) q[k] = q[k] - gam[k] * q[k + 1];
+  } else {
+    q[0] = 1.5 * a1[0];
+    gam[1] = 0.5;
+    {
+      double gr = delp[0] / delp[1];
+      double bet = 2.0 + gr + gr - gam[1];
+      q[1] = (3.0 * (a1[0] + a1[1]) - q[0]) / bet;
+    }
+    for (int k = 2; k < km; ++k) {
+      double old_gr = delp[k - 2] / delp[k - 1];
+      double old_bet = 2.0 + old_gr + old_gr - gam[k - 1];
+      gam[k] = old_gr / old_bet;
+    }
+    for (int k = 2; k < km - 1; ++k) {
+      double gr = delp[k - 1] / delp[k];
+      double bet = 2.0 + gr + gr - gam[k];
+      q[k] = (3.0 * (a1[k - 1] + a1[k]) - q[k - 1]) / bet;
+    }
+    {
+      int k = km - 1;
+      double gr = delp[k - 1] / delp[k];
+      q[k] = (3.0 * (a1[k - 1] + a1[k]) - gr * qs - q[k - 1]) / (2.0 + gr + gr - gam[k]);
+    }
+    q[km] = qs;
+    for (int k = km - 2; k >= 0; --k) q[k] = q[k] - gam[k + 1] * q[k + 1];
+  }
+  // ---- apply_constraints (domain: km levels) ----
+  // gam[k] = a1[k] - a1[k-1] for k >= 1 (gam[0] keeps its set_initial_vals value)
+  for (int k = 1; k < km; ++k) gam[k] = a1[k] - a1[k - 1];
+  auto tmpmax = [&](int k) { return a1[k - 1] > a1[k] ? a1[k - 1] : a1[k]; };
+  auto tmpmin = [&](int k) { return a1[k - 1] < a1[k] ? a1[k - 1] : a1[k]; };
+  {
+    int k = 1;
+    if (q[k] >= tmpmax(k)) q[k] = tmpmax(k);
+    if (q[k] <= tmpmin(k)) q[k] = tmpmin(k);
+  }
+  for (int k = 2; k < km - 1; ++k) {
+    double tmp = tmpmax(k), tmp2 = tmpmin(k);
+    if ((gam[k - 1] * gam[k + 1]) > 0) {
+      if (q[k] >= tmp) q[k] = tmp;
+      if (q[k] <= tmp2) q[k] = tmp2;
+    } else if (gam[k - 1] > 0) {
+      if (q[k] <= tmp2) q[k] = tmp2;
+    } else {
+      if (q[k] >= tmp) q[k] = tmp;
+      if (iv == 0 && q[k] < 0.0) q[k] = 0.0;
+    }
+  }
+  {
+    int k = km - 1;
+    if (q[k] >= tmpmax(k)) q[k] = tmpmax(k);
+    if (q[k] <= tmpmin(k)) q[k] = tmpmin(k);
+  }
+  double *a2 = c.a2, *a3 = c.a3, *a4 = c.a4;
+  for (int k = 0; k < km; ++k) { a2[k] = q[k]; a3[k] = q[k + 1]; }
+  c.extm[0] = (a2[0] - a1[0]) * (a3[0] - a1[0]) > 0.0;
+  for (int k = 1; k < km - 1; ++k) c.extm[k] = gam[k] * gam[k + 1] < 0.0;
+  c.extm[km - 1] = (a2[km - 1] - a1[km - 1]) * (a3[km - 1] - a1[km - 1]) > 0.0;
+  if (kord > 9) {
+    for (int k = 0; k < km; ++k) {
+      double x0 = 2.0 * a1[k] - (a2[k] + a3[k]);
+      double x1 = fabs(a2[k] - a3[k]);
+      a4[k] = 3.0 * x0;
+      c.ext5[k] = fabs(x0) > x1;
+      c.ext6[k] = fabs(a4[k]) > x1;
+    }
+  }
+  // ---- set_interpolation_coefficients (domain: km levels); a1 is modified only formally (returned unchanged) ----
+  double* a1w = c.a1;
+  if (iv == 0) {
+    if (a2[0] < 0.0) a2[0] = 0.0;
+    a4_from(a1[0], a2[0], a3[0], a4[0]);
+    a4_from(a1[1], a2[1], a3[1], a4[1]);
+  }
+  if (iv == -1) {
+    if (a2[0] * a1[0] <= 0.0) a2[0] = 0.0;
+    a4_from(a1[0], a2[0], a3[0], a4[0]);
+    a4_from(a1[1], a2[1], a3[1], a4[1]);
+  }
+  if (iv == 2) {
+    a2[0] = a1[0]; a3[0] = a1[0]; a4[0] = 0.0;
+    a4_from(a1[1], a2[1], a3[1], a4[1]);
+  }
+  if (iv < -1 || iv == 1 || iv > 2) {
+    a4_from(a1[0], a2[0], a3[0], a4[0]);
+    a4_from(a1[1], a2[1], a3[1], a4[1]);
+  }
+  if (iv != 2) posdef_iv1(a1w[0], a2[0], a3[0], a4[0]);
+  remap_constraint(a1w[1], a2[1], a3[1], a4[1], c.extm[1]);
+  for (int k = 2; k < km - 2; ++k) {
+    if (kord < 9) {
+      double pmp_1 = a1[k] - gam[k + 1];
+      double lac_1 = pmp_1 + 1.5 * gam[k + 2];
+      double tmp_min = lim3_min(a1[k], pmp_1, lac_1);
+      double tmp_max0 = a2[k] > tmp_min ? a2[k] : tmp_min;
+      double tmp_max = lim3_max(a1[k], pmp_1, lac_1);
+      a2[k] = tmp_max0 < tmp_max ? tmp_max0 : tmp_max;
+      double pmp_2 = a1[k] + 2.0 * gam[k + 1];
+      double lac_2 = pmp_2 - 1.5 * gam[k - 1];
+      tmp_min = lim3_min(a1[k], pmp_2, lac_2);
+      tmp_max0 = a3[k] > tmp_min ? a3[k] : tmp_min;
+      tmp_max = lim3_max(a1[k], pmp_2, lac_2);
+      a3[k] = tmp_max0 < tmp_max ? tmp_max0 : tmp_max;
+      a4_from(a1[k], a2[k], a3[k], a4[k]);
+    } else if (kord == 9) {
+      double pmp_1 = a1[k] - 2.0 * gam[k + 1];
+      double lac_1 = pmp_1 + 1.5 * gam[k + 2];
+      double pmp_2 = a1[k] + 2.0 * gam[k];
+      double lac_2 = pmp_2 - 1.5 * gam[k - 1];
+      if ((c.extm[k] && c.extm[k - 1]) || (c.extm[k] && c.extm[k + 1]) || (c.extm[k] && (qmin > 0.0 && a1[k] < qmin))) {
+        a2[k] = a1[k]; a3[k] = a1[k]; a4[k] = 0.0;
+      } else {
+        a4[k] = 6.0 * a1[k] - 3.0 * (a2[k] + a3[k]);
+        if (fabs(a4[k]) > fabs(a2[k] - a3[k])) {
+          double tmp_min = lim3_min(a1[k], pmp_1, lac_1);
+          double tmp_max0 = a2[k] > tmp_min ? a2[k] : tmp_min;
+          double tmp_max = lim3_max(a1[k], pmp_1, lac_1);
+          a2[k] = tmp_max0 < tmp_max ? tmp_max0 : tmp_max;
+          tmp_min = lim3_min(a1[k], pmp_2, lac_2);
+          tmp_max0 = a3[k] > tmp_min ? a3[k] : tmp_min;
+          tmp_max = lim3_max(a1[k], pmp_2, lac_2);
+          a3[k] = tmp_max0 < tmp_max ? tmp_max0 : tmp_max;
+          a4[k] = 6.0 * a1[k] - 3.0 * (a2[k] + a3[k]);
+        }
+      }
+    } else {  // kord == 10
+      double pmp_1 = a1[k] - 2.0 * gam[k + 1];
+      double lac_1 = pmp_1 + 1.5 * gam[k + 2];
+      double pmp_2 = a1[k] + 2.0 * gam[k];
+      double lac_2 = pmp_2 - 1.5 * gam[k - 1];
+      double tmp_min2 = lim3_min(a1[k], pmp_1, lac_1);
+      double tmp_max2 = lim3_max(a1[k], pmp_1, lac_1);
+      double tmp2 = a2[k] > tmp_min2 ? a2[k] : tmp_min2;
+      double tmp_min3 = a1[k] < pmp_2 ? a1[k] : pmp_2;
+      tmp_min3 = lac_2 < tmp_min3 ? lac_2 : tmp_min3;
+      double tmp_max3 = a1[k] > pmp_2 ? a1[k] : pmp_2;
+      tmp_max3 = lac_2 > tmp_max3 ? lac_2 : tmp_max3;
+      double tmp3 = a3[k] > tmp_min3 ? a3[k] : tmp_min3;
+      bool n5 = c.ext5[k - 1] || c.ext5[k + 1], n6 = c.ext6[k - 1] || c.ext6[k + 1];
+      if (c.ext5[k]) {
+        if (n5) { a2[k] = a1[k]; a3[k] = a1[k]; }
+        else if (n6) { a2[k] = tmp2 < tmp_max2 ? tmp2 : tmp_max2; a3[k] = tmp3 < tmp_max3 ? tmp3 : tmp_max3; }
+      } else if (c.ext6[k]) {
+        if (n5) { a2[k] = tmp2 < tmp_max2 ? tmp2 : tmp_max2; a3[k] = tmp3 < tmp_max3 ? tmp3 : tmp_max3; }
+      }
+      a4_from(a1[k], a2[k], a3[k], a4[k]);
+    }
+    if (iv == 0) posdef_iv0(a1w[k], a2[k], a3[k], a4[k]);
+  }
+  if (iv == 0 && a3[km - 1] < 0.0) a3[km - 1] = 0.0;
+  if (iv == -1 && a3[km - 1] * a1[km - 1] <= 0.0) a3[km - 1] = 0.0;
+  a4_from(a1[km - 2], a2[km - 2], a3[km - 2], a4[km - 2]);
+  a4_from(a1[km - 1], a2[km - 1], a3[km - 1], a4[km - 1]);
+  remap_constraint(a1w[km - 2], a2[km - 2], a3[km - 2], a4[km - 2], c.extm[km - 2]);
+  posdef_iv1(a1w[km - 1], a2[km - 1], a3[km - 1], a4[km - 1]);
+}
+
+// MapSingle.__call__ on one column: q (in/out, km levels) from source interfaces pe1 to target interfaces pe2
+__device__ void map_single_column(const Pt& p, Col& c, int km, double* q, const double* pe1, const double* pe2, int iv,
+                                  int kord, double qs, double qmin) {
+  for (int k = 0; k < km; ++k) {
+    c.a1[k] = A(q, 0, 0, k);
+    c.dp[k] = A(pe1, 0, 0, k + 1) - A(pe1, 0, 0, k);
+  }
+  remap_profile(c, km, iv, kord, qs, qmin);
+  // lagrangian_contributions (map_single.py:21-81); L = k + lev is the absolute source layer.  Variable-k reads
+  // are clipped to the allocated levels [0, km] like the numpy backend does.
+  auto P1 = [&](int L) { return A(pe1, 0, 0, L > km ? km : L); };
+  auto cl = [&](int L) { return L > km - 1 ? km - 1 : L; };  // layer arrays: km entries meaningful
+  int L = 0;
+  for (int k = 0; k < km; ++k) {
+    const double pe2k = A(pe2, 0, 0, k), pe2k1 = A(pe2, 0, 0, k + 1);
+    int Lc = cl(L);
+    double pl = (pe2k - P1(L)) / c.dp[Lc];
+    double qv;
+    if (pe2k1 <= P1(L + 1)) {
+      double pr = (pe2k1 - P1(L)) / c.dp[Lc];
+      qv = c.a2[Lc] + 0.5 * (c.a4[Lc] + c.a3[Lc] - c.a2[Lc]) * (pr + pl) - c.a4[Lc] * 1.0 / 3.0 * (pr * (pr + pl) + pl * pl);
+    } else {
+      double qsum = (P1(L + 1) - pe2k) *
+                    (c.a2[Lc] + 0.5 * (c.a4[Lc] + c.a3[Lc] - c.a2[Lc]) * (1.0 + pl) - c.a4[Lc] * 1.0 / 3.0 * (1.0 + pl * (1.0 + pl)));
+      L = L + 1;
+      while (L < km && P1(L + 1) < pe2k1) {
+        qsum += c.dp[cl(L)] * c.a1[cl(L)];
+        L = L + 1;
+      }
+      Lc = cl(L);
+      double dp = pe2k1 - P1(L);
+      double esl = dp / c.dp[Lc];
+      qsum += dp * (c.a2[Lc] + 0.5 * esl * (c.a3[Lc] - c.a2[Lc] + c.a4[Lc] * (1.0 - (2.0 / 3.0) * esl)));
+      qv = qsum / (pe2k1 - pe2k);
+    }
+    A(q, 0, 0, k) = qv;
+  }
+}
+
+// fix_tracer (fillz.py:16-107) on one column
+__device__ void fillz_column(const Pt& p, Col& c, int km, double* q, const double* dp) {
+  double* lower = c.a2;   // reuse thread-local arrays
+  double* upper = c.a3;
+  double* dm = c.a4;
+  double* dmp = c.gam;
+  double* qq = c.a1;
+  double* d = c.dp;
+  for (int k = 0; k < km; ++k) { qq[k] = A(q, 0, 0, k); d[k] = A(dp, 0, 0, k); lower[k] = 0.0; upper[k] = 0.0; dm[k] = 0.0; dmp[k] = 0.0; }
+  int zfix = 0;
+  double sum0 = 0.0, sum1 = 0.0;
+  if (qq[0] < 0.0) qq[1] = qq[1] + qq[0] * d[0] / d[1];
+  if (qq[0] < 0) qq[0] = 0;
+  dm[0] = qq[0] * d[0];
+  for (int k = 1; k < km - 1; ++k) {
+    if (lower[k - 1] != 0.0) qq[k] = qq[k] - (lower[k - 1] / d[k]);
+    if (qq[k] < 0.0) {
+      zfix += 1;
+      if (qq[k - 1] > 0.0) {
+        double dq = qq[k - 1] * d[k - 1] < -(qq[k] * d[k]) ? qq[k - 1] * d[k - 1] : -(qq[k] * d[k]);
+        qq[k] = qq[k] + dq / d[k];
+        upper[k] = dq;
+      }
+      if (qq[k] < 0.0 && qq[k + 1] > 0.0) {
+        double dq = qq[k + 1] * d[k + 1] < -(qq[k] * d[k]) ? qq[k + 1] * d[k + 1] : -(qq[k] * d[k]);
+        qq[k] = qq[k] + dq / d[k];
+        lower[k] = dq;
+      }
+    }
+  }
+  for (int k = 0; k < km - 1; ++k) {
+    if (upper[k + 1] != 0.0) qq[k] = qq[k] - upper[k + 1] / d[k];
+    dm[k] = qq[k] * d[k];
+    dmp[k] = dm[k] > 0.0 ? dm[k] : 0.0;
+  }
+  {
+    int k = km - 1;
+    if (lower[k - 1] != 0.0) qq[k] = qq[k] - (lower[k - 1] / d[k]);
+    double qup = qq[k - 1] * d[k - 1];
+    double qly = -qq[k] * d[k];
+    double dup = qup < qly ? qup : qly;
+    if (qq[k] < 0.0 && qq[k - 1] > 0.0) {
+      zfix += 1;
+      qq[k] = qq[k] + (dup / d[k]);
+      upper[k] = dup;
+    }
+    dm[k] = qq[k] * d[k];
+    dmp[k] = dm[k] > 0.0 ? dm[k] : 0.0;
+  }
+  {
+    int k = km - 2;
+    if (upper[k + 1] != 0.0) {
+      qq[k] = qq[k] - (upper[k + 1] / d[k]);
+      dm[k] = qq[k] * d[k];
+      dmp[k] = dm[k] > 0.0 ? dm[k] : 0.0;
+    }
+  }
+  for (int k = 1; k < km; ++k) { sum0 += dm[k]; sum1 += dmp[k]; }
+  double fac = sum0 > 0.0 ? sum0 / sum1 : 0.0;
+  if (zfix > 0 && fac > 0.0)
+    for (int k = 1; k < km; ++k) qq[k] = fac * dm[k] / d[k] > 0.0 ? fac * dm[k] / d[k] : 0.0;
+  for (int k = 0; k < km; ++k) A(q, 0, 0, k) = qq[k];
+}
+
+#ifndef PACE_HOST_EMU
+#define COL_DECL Col col
+#else
+#define COL_DECL static thread_local Col col
+#endif
+
+}  // namespace
+
+const char* tracer_name(int n);
+
+// MapSingle.__call__ exposed on registered fields (also used by the test-suite on synthetic columns).
+// xi / yi: the field's horizontal staggering (dims [X(_INTERFACE), Y(_INTERFACE), Z]).
+int map_single(Core& c, double* q, const double* pe1, const double* pe2, const double* qs, int iv, int kord, bool xi,
+               bool yi, double qmin) {
+  const Geo g = c.g;
+  const int km = g.nz;
+  if (km + 1 > KMAX) { c.err = "map_single: npz + 1 exceeds the thread-local column length (96)"; return 1; }
+  if (kord > 10) { c.err = "Remap Profile: kord > 10 not implemented. kord <= 10 available."; return 1; }
+  launch_ij(c.stream, g, box_dims(g, xi, yi, false), [=] __device__(const Pt& p) {
+    COL_DECL;
+    map_single_column(p, col, km, q, pe1, pe2, iv, kord, qs ? A20(qs) : 0.0, qmin);
+  });
+  return 0;
+}
+
+// LagrangianToEulerian.__call__ up to (not including) the saturation adjustment (remapping.py:590-668)
+int remap_main(Core& c, int nq) {
+  const Geo g = c.g;
+  cudaStream_t st = c.stream;
+  const Config& cf = c.cfg;
+  if (cf.kord_tm >= 0) { c.err = "map ppm, untested mode where kord_tm >= 0"; return 1; }
+  if (cf.hydrostatic) { c.err = "Hydrostatic is not implemented"; return 1; }
+  const int km = g.nz;
+  if (km + 1 > KMAX) { c.err = "remapping: npz + 1 exceeds the thread-local column length (96)"; return 1; }
+  double *pt = c.F("pt"), *delp = c.F("delp"), *delz = c.F("delz"), *peln = c.F("peln"), *u = c.F("u"), *v = c.F("v"),
+         *w = c.F("w"), *cappa = c.F("ad.cappa"), *q_con = c.F("q_con"), *pkz = c.F("pkz"), *pk = c.F("pk"),
+         *pe = c.F("pe"), *ps = c.F("ps");
+  const double *wsd = c.F("ad.wsd"), *ak = c.F("grid.ak"), *bk = c.F("grid.bk");
+  const double *qvapor = c.F("qvapor"), *qliquid = c.F("qliquid"), *qrain = c.F("qrain"), *qsnow = c.F("qsnow"),
+               *qice = c.F("qice"), *qgraupel = c.F("qgraupel");
+  double *pe1 = c.FS("rm.pe1"), *pe2 = c.FS("rm.pe2"), *pe3 = c.FS("rm.pe3"), *dp2 = c.FS("rm.dp2"), *pn2 = c.FS("rm.pn2"),
+         *pe0 = c.FS("rm.pe0"), *gz = c.FS("rm.gz"), *cvm = c.FS("rm.cvm");
+  if (!c.err.empty()) return 1;
+  const int is = g.is, ie = g.ie, js = g.js, je = g.je;
+  const int kord_tm = cf.kord_tm < 0 ? -cf.kord_tm : cf.kord_tm;
+  const int kord_tr = cf.kord_tr < 0 ? -cf.kord_tr : cf.kord_tr;
+  const int kord_wz = cf.kord_wz, kord_mt = cf.kord_mt;
+  const double r_vir = ZVIR, akap = KAPPA, ptop = cf.ptop, t_min = 184.0;
+
+  // init_pe (domain nx, ny+1, km+1) + moist_cv_pt_pressure + pn2_pk_delp (compute domain)
+  launch_ij(st, g, Box{is, js, 0, g.nx, g.ny + 1, 1}, [=] __device__(const Pt& p) {
+    for (int k = 0; k <= km; ++k) A(pe1, 0, 0, k) = A(pe, 0, 0, k);
+    A(pe2, 0, 0, 0) = ptop;
+    A(pe2, 0, 0, km) = A(pe, 0, 0, km);
+    if (p.j > je) return;
+    for (int k = 0; k < km; ++k) {
+      // moist_pt_func (moist_cv.py:62-86)
+      double ql = A(qliquid, 0, 0, k) + A(qrain, 0, 0, k);
+      double qs_ = A(qice, 0, 0, k) + A(qsnow, 0, 0, k) + A(qgraupel, 0, 0, k);
+      double gzv = ql + qs_;
+      double qv = A(qvapor, 0, 0, k);
+      double cv = (1.0 - (qv + gzv)) * CV_AIR + qv * CV_VAP + ql * C_LIQ + qs_ * C_ICE;
+      A(q_con, 0, 0, k) = gzv;
+      double cap = RDGAS / (RDGAS + cv / (1.0 + r_vir * qv));
+      A(cappa, 0, 0, k) = cap;
+      double ptv = A(pt, 0, 0, k), dpv = A(delp, 0, 0, k), dzv = A(delz, 0, 0, k);
+      A(pt, 0, 0, k) = ptv * fv_exp(cap / (1.0 - cap) * fv_log(RDG * dpv / dzv * ptv));
+      A(delz, 0, 0, k) = -dzv / dpv;
+    }
+    double psv = A(pe, 0, 0, km);
+    A20(ps) = psv;
+    A(pn2, 0, 0, 0) = A(peln, 0, 0, 0);
+    for (int k = 1; k < km; ++k) A(pe2, 0, 0, k) = ak[k] + bk[k] * psv;
+    A(pn2, 0, 0, km) = A(peln, 0, 0, km);
+    for (int k = km - 1; k >= 0; --k) {
+      double d = A(pe2, 0, 0, k + 1) - A(pe2, 0, 0, k);
+      A(dp2, 0, 0, k) = d;
+      A(delp, 0, 0, k) = d;
+    }
+    // pn2_pk_delp (km levels)
+    for (int k = 0; k < km; ++k) {
+      double l = fv_log(A(pe2, 0, 0, k));
+      A(pn2, 0, 0, k) = l;
+      A(pk, 0, 0, k) = fv_exp(akap * l);
+    }
+  });
+  // map_single_pt (iv 1, log-p coordinates), MapNTracer (iv 0) + fillz, map_single_w (iv -2, qs = wsd),
+  // map_single_delz (iv 1): all on the compute domain -> one column kernel
+  double* tr[9];
+  for (int n = 0; n < nq; ++n) tr[n] = c.F(tracer_name(n));
+  if (!c.err.empty()) return 1;
+  struct TrPtrs { double* p[9]; } trp;
+  for (int n = 0; n < 9; ++n) trp.p[n] = n < nq ? tr[n] : nullptr;
+  const bool fill = cf.fill != 0;
+  launch_ij(st, g, box_compute(g), [=] __device__(const Pt& p) {
+    COL_DECL;
+    map_single_column(p, col, km, pt, peln, pn2, 1, kord_tm, 0.0, t_min);
+    for (int n = 0; n < nq; ++n) {
+      // mapn_tracer.py:40-41: every tracer uses kord_tr, entry 5 is forced to 9
+      int kord = n == 5 ? 9 : kord_tr;
+      map_single_column(p, col, km, trp.p[n], pe1, pe2, 0, kord, 0.0, 0.0);
+    }
+    if (fill)
+      for (int n = 0; n < nq; ++n) fillz_column(p, col, km, trp.p[n], dp2);
+    map_single_column(p, col, km, w, pe1, pe2, -2, kord_wz, A20(wsd), 0.0);
+    map_single_column(p, col, km, delz, pe1, pe2, 1, kord_wz, 0.0, 0.0);
+    // undo_delz_adjust_and_copy_peln
+    for (int k = 0; k < km; ++k) A(delz, 0, 0, k) = -A(delz, 0, 0, k) * A(delp, 0, 0, k);
+    for (int k = 0; k <= km; ++k) {
+      A(pe0, 0, 0, k) = A(peln, 0, 0, k);
+      A(peln, 0, 0, k) = A(pn2, 0, 0, k);
+    }
+    // moist_pkz (moist_cv.py:170-198)
+    for (int k = 0; k < km; ++k) {
+      double ql = A(qliquid, 0, 0, k) + A(qrain, 0, 0, k);
+      double qs_ = A(qice, 0, 0, k) + A(qsnow, 0, 0, k) + A(qgraupel, 0, 0, k);
+      double gzv = ql + qs_;
+      double qv = A(qvapor, 0, 0, k);
+      double cv = (1.0 - (qv + gzv)) * CV_AIR + qv * CV_VAP + ql * C_LIQ + qs_ * C_ICE;
+      A(cvm, 0, 0, k) = cv;
+      A(gz, 0, 0, k) = gzv;
+      A(q_con, 0, 0, k) = gzv;
+      double cap = RDGAS / (RDGAS + cv / (1.0 + r_vir * qv));
+      A(cappa, 0, 0, k) = cap;
+      A(pkz, 0, 0, k) = fv_exp(cap * fv_log(RDG * A(delp, 0, 0, k) / A(delz, 0, 0, k) * A(pt, 0, 0, k)));
+    }
+  });
+  // pressures_mapu + map_single_u on [is..ie] x [js..je+1]
+  launch_ij(st, g, Box{is, js, 0, g.nx, g.ny + 1, 1}, [=] __device__(const Pt& p) {
+    COL_DECL;
+    double pe_bottom_m = A(pe, 0, -1, km), pe1_bottom = A(pe, 0, 0, km);
+    A(pe0, 0, 0, 0) = A(pe, 0, 0, 0);
+    for (int k = 1; k <= km; ++k) A(pe0, 0, 0, k) = 0.5 * (A(pe, 0, -1, k) + A(pe1, 0, 0, k));
+    for (int k = 0; k <= km; ++k) {
+      double bkh = 0.5 * bk[k];
+      A(pe3, 0, 0, k) = ak[k] + bkh * (pe_bottom_m + pe1_bottom);
+    }
+    map_single_column(p, col, km, u, pe0, pe3, -1, kord_mt, 0.0, 0.0);
+  });
+  // pressures_mapv + map_single_v on [is..ie+1] x [js..je]
+  launch_ij(st, g, Box{is, js, 0, g.nx + 1, g.ny, 1}, [=] __device__(const Pt& p) {
+    COL_DECL;
+    double pe_bottom_m = A(pe, -1, 0, km), pe_bottom = A(pe, 0, 0, km);
+    A(pe3, 0, 0, 0) = ak[0];
+    A(pe0, 0, 0, 0) = A(pe, 0, 0, 0);
+    for (int k = 1; k <= km; ++k) {
+      double bkh = 0.5 * bk[k];
+      A(pe0, 0, 0, k) = 0.5 * (A(pe, -1, 0, k) + A(pe, 0, 0, k));
+      A(pe3, 0, 0, k) = ak[k] + bkh * (pe_bottom_m + pe_bottom);
+    }
+    map_single_column(p, col, km, v, pe0, pe3, -1, kord_mt, 0.0, 0.0);
+  });
+  // update_ua(pe2, pe3) on [is..ie] x [js..je+1], then copy_from_below(pe3 -> pe) on the compute domain
+  launch_ij(st, g, Box{is, js, 0, g.nx, g.ny + 1, 1}, [=] __device__(const Pt& p) {
+    for (int k = 0; k < km; ++k) {
+      double val = A(pe2, 0, 0, k + 1);
+      if (k < km - 1 && p.j == je + 1) val = A(pe2, 0, -1, k + 1);
+      A(pe3, 0, 0, k) = val;
+    }
+    if (p.j <= je)
+      for (int k = 1; k < km; ++k) A(pe, 0, 0, k) = A(pe3, 0, 0, k - 1);
+  });
+  return 0;
+}
+
+// the tail of LagrangianToEulerian.__call__ after the saturation adjustment (remapping.py:715-731)
+int remap_finish(Core& c, int last_step) {
+  const Geo g = c.g;
+  const int km = g.nz;
+  double *pt = c.F("pt"), *gz = c.FS("rm.gz");
+  const double *pkz = c.F("pkz"), *qvapor = c.F("qvapor"), *qliquid = c.F("qliquid"), *qrain = c.F("qrain"),
+               *qsnow = c.F("qsnow"), *qice = c.F("qice"), *qgraupel = c.F("qgraupel");
+  if (!c.err.empty()) return 1;
+  const double dtmp = 0.0, r_vir = ZVIR;
+  if (last_step) {
+    if (c.cfg.consv_te > 0.001) { c.err = "We do not support consv_te > 0.001 because that would trigger an allReduce"; return 1; }
+    // moist_pt_last_step (moist_cv.py:101-117); the reference's domain has km+1 levels, the extra one is not meaningful
+    launch_ijk(c.stream, g, box_compute(g), [=] __device__(const Pt& p) {
+      double gzv = A0(qliquid) + A0(qrain) + A0(qice) + A0(qsnow) + A0(qgraupel);
+      A0(gz) = gzv;
+      A0(pt) = (A0(pt) + dtmp * A0(pkz)) / ((1.0 + r_vir * A0(qvapor)) * (1.0 - gzv));
+    });
+  } else {
+    launch_ijk(c.stream, g, box_compute(g), [=] __device__(const Pt& p) { A0(pt) = A0(pt) / A0(pkz); });
+  }
+  (void)km;
+  return 0;
+}
+
+}  // namespace pace

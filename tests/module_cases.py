@@ -8,6 +8,9 @@ CASES = {
     "fv_setup": dict(stage="fv_setup", call="fv_setup", args=(), tol=1e-14, tol_host=0.0),
     "pt_to_potential_density_pt": dict(stage="pt_to_potential_density_pt", call="pt_to_potential_density_pt", args=(), tol=0.0),
     "omega_from_w": dict(stage="omega_from_w", call="omega_from_w", args=(), tol=0.0),
+    "remap_main": dict(stage="rm.copy_from_below_stencil", begin="pre:rm.init_pe", call="remap_main", args=(8,), tol=0.0,
+                       deep=True),
+    "remap_finish": dict(stage="rm.moist_cv_last_step_stencil", call="remap_finish", args=(1,), tol=0.0, deep=True),
     "zero_data": dict(stage="zero_data", call="zero_data", args=(1,), tol=0.0),
     "gz_from_zs_delz": dict(stage="gz_from_zs_delz", call="gz_from_zs_delz", args=(), tol=0.0),
     "copy_gz_zh": dict(stage="copy_gz_zh", call="copy_full", args=("ad.gz", "ad.zh"), tol=0.0),
