@@ -107,6 +107,17 @@ int pace_b200_map_single(void* handle, const char* q, const char* pe1, const cha
 int pace_b200_remap_main(void* handle, int nq);
 int pace_b200_remap_finish(void* handle, int last_step);
 
+/* SatAdjustConfig (pyFV3/_config.py:15-66) as read by SatAdjust3d. */
+typedef struct pace_b200_satadj_config {
+  int rad_snow, rad_rain, rad_graupel, tintqs, icloud_f, do_qa;
+  double sat_adj0, ql_gen, qs_mlt, ql0_max, t_sub, qi_gen, qi_lim, qi0_max, dw_ocean, dw_land, cld_min;
+  double tau_i2s, tau_v2l, tau_r2g, tau_l2r, tau_l2v, tau_imlt, tau_smlt;
+} pace_b200_satadj_config;
+
+/* SatAdjust3d.__call__ (pyFV3/stencils/saturation_adjustment.py:982-1108) on levels [kmp, npz).
+ * inout: qvapor qliquid qice qrain qsnow qgraupel pt ad.cappa   out: qcld q_con pkz   in: delp delz phis grid.area_64 */
+int pace_b200_sat_adjust(void* handle, const pace_b200_satadj_config* cfg, double mdt, int last_step, int kmp);
+
 /* One region of a halo update: the destination box (array indices) of subdomain dst_t is filled from
  * subdomain src_t at index (aii*i + aij*j + bi, aji*i + ajj*j + bj); comp/src_comp select the x (0) or y (1)
  * array of a vector pair, sign its sign.  Replaces Boundary + rotate_*_data + the pack/unpack index arrays of

@@ -32,6 +32,25 @@ class Config(ctypes.Structure):
     )
 
 
+class SatAdjConfig(ctypes.Structure):
+    """Mirror of `pace_b200_satadj_config`; defaults = NDSL NamelistDefaults (ndsl/namelist.py:26-57)."""
+
+    _fields_ = [(n, _I) for n in ("rad_snow", "rad_rain", "rad_graupel", "tintqs", "icloud_f", "do_qa")] + [
+        (n, _D) for n in ("sat_adj0", "ql_gen", "qs_mlt", "ql0_max", "t_sub", "qi_gen", "qi_lim", "qi0_max", "dw_ocean",
+                          "dw_land", "cld_min", "tau_i2s", "tau_v2l", "tau_r2g", "tau_l2r", "tau_l2v", "tau_imlt",
+                          "tau_smlt")]
+    DEFAULTS = dict(rad_snow=1, rad_rain=1, rad_graupel=1, tintqs=0, icloud_f=0, do_qa=1, sat_adj0=0.90, ql_gen=1.0e-3,
+                    qs_mlt=1.0e-6, ql0_max=2.0e-3, t_sub=184.0, qi_gen=1.82e-6, qi_lim=1.0, qi0_max=1.0e-4,
+                    dw_ocean=0.10, dw_land=0.15, cld_min=0.05, tau_i2s=1000.0, tau_v2l=90.0, tau_r2g=900.0,
+                    tau_l2r=900.0, tau_l2v=300.0, tau_imlt=600.0, tau_smlt=900.0)
+
+    @classmethod
+    def make(cls, **over):
+        vals = dict(cls.DEFAULTS)
+        vals.update(over)
+        return cls(**vals)
+
+
 class HaloOp(ctypes.Structure):
     """Mirror of `pace_b200_halo_op`."""
 
@@ -71,6 +90,7 @@ def bind(lib):
     lib.pace_b200_halo_plan_set.argtypes = [vp, _I, vp, _I]
     lib.pace_b200_halo_update.argtypes = [vp, _I, ctypes.POINTER(_S), ctypes.POINTER(_S), _I, _I]
     lib.pace_b200_math_eval.argtypes = [vp, _I, _I, vp, vp, vp]
+    lib.pace_b200_sat_adjust.argtypes = [vp, ctypes.POINTER(SatAdjConfig), _D, _I, _I]
     for name, extra in MODULE_CALLS.items():
         fn = getattr(lib, "pace_b200_" + name)
         fn.argtypes = [vp] + extra
@@ -116,4 +136,4 @@ MODULE_CALLS = {
 }
 
 EXPORTS = ["pace_b200_row_stride", "pace_b200_create", "pace_b200_destroy", "pace_b200_last_error",
-           "pace_b200_set_stream", "pace_b200_set_field", "pace_b200_set_column", "pace_b200_halo_plan_set", "pace_b200_halo_update", "pace_b200_math_eval"] + ["pace_b200_" + n for n in MODULE_CALLS]
+           "pace_b200_set_stream", "pace_b200_set_field", "pace_b200_set_column", "pace_b200_halo_plan_set", "pace_b200_halo_update", "pace_b200_math_eval", "pace_b200_sat_adjust"] + ["pace_b200_" + n for n in MODULE_CALLS]

@@ -7,6 +7,11 @@
 #include "transport.hpp"
 
 namespace pace {
+struct SatCfg {
+  int rad_snow, rad_rain, rad_graupel, tintqs, icloud_f, do_qa;
+  double sat_adj0, ql_gen, qs_mlt, ql0_max, t_sub, qi_gen, qi_lim, qi0_max, dw_ocean, dw_land, cld_min;
+  double tau_i2s, tau_v2l, tau_r2g, tau_l2r, tau_l2v, tau_imlt, tau_smlt;
+};
 
 static thread_local std::string g_err;
 
@@ -168,6 +173,10 @@ int pace_b200_update_dz_c(void* h, double dt2) { ENTRY(update_dz_c(*c, dt2)) }
 int pace_b200_p_grad_c(void* h, double dt2) { ENTRY(p_grad_c(*c, dt2)) }
 int pace_b200_fv_prep(void* h, double dt) { ENTRY(fv_prep(*c, dt)) }
 int pace_b200_fv_setup(void* h) { ENTRY(fv_setup(*c)) }
+int pace_b200_sat_adjust(void* h, const pace_b200_satadj_config* cfg, double mdt, int last_step, int kmp) {
+  static_assert(sizeof(pace_b200_satadj_config) == sizeof(SatCfg), "satadj config mirror out of sync");
+  ENTRY(sat_adjust(*c, *(const SatCfg*)cfg, mdt, last_step, kmp))
+}
 int pace_b200_remap_main(void* h, int nq) { ENTRY(remap_main(*c, nq)) }
 int pace_b200_remap_finish(void* h, int last_step) { ENTRY(remap_finish(*c, last_step)) }
 int pace_b200_map_single(void* h, const char* q, const char* pe1, const char* pe2, const char* qs, int iv, int kord,

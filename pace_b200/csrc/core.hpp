@@ -66,6 +66,8 @@ int map_single(Core& c, double* q, const double* pe1, const double* pe2, const d
                bool yi, double qmin);
 int remap_main(Core& c, int nq);
 int remap_finish(Core& c, int last_step);
+struct SatCfg;
+int sat_adjust(Core& c, const SatCfg& sc, double mdt, int last_step, int kmp);
 int fv_setup(Core& c);
 int pt_to_potential_density_pt(Core& c);
 int omega_from_w(Core& c);

@@ -168,6 +168,12 @@ class NativeCore:
         if rc != 0:
             raise NativeError("halo_update: %s" % self.lib.pace_b200_last_error(self.handle).decode())
 
+    def sat_adjust(self, mdt, last_step, kmp, **over):
+        cfg = _lib.SatAdjConfig.make(**over)
+        rc = self.lib.pace_b200_sat_adjust(self.handle, ctypes.byref(cfg), float(mdt), int(last_step), int(kmp))
+        if rc != 0:
+            raise NativeError("sat_adjust: %s" % self.lib.pace_b200_last_error(self.handle).decode())
+
     # -- calls -----------------------------------------------------------------------------------
     def call(self, name, *scalars):
         fn = getattr(self.lib, "pace_b200_" + name)
