@@ -118,6 +118,13 @@ typedef struct pace_b200_satadj_config {
  * inout: qvapor qliquid qice qrain qsnow qgraupel pt ad.cappa   out: qcld q_con pkz   in: delp delz phis grid.area_64 */
 int pace_b200_sat_adjust(void* handle, const pace_b200_satadj_config* cfg, double mdt, int last_step, int kmp);
 
+/* AdjustNegativeTracerMixingRatio.__call__ (pyFV3/stencils/neg_adj3.py:385-431).
+ * inout: qvapor qliquid qrain qsnow qice qgraupel qcld pt   in: delp */
+int pace_b200_neg_adj3(void* handle);
+/* CubedToLatLon ord4_transform (NDSL/ndsl/stencils/c2l_ord.py:110-157); the u/v halo update that precedes it
+ * in CubedToLatLon.__call__ is issued by the caller.  in: u v   out: ua va */
+int pace_b200_c2l_ord4(void* handle);
+
 /* One region of a halo update: the destination box (array indices) of subdomain dst_t is filled from
  * subdomain src_t at index (aii*i + aij*j + bi, aji*i + ajj*j + bj); comp/src_comp select the x (0) or y (1)
  * array of a vector pair, sign its sign.  Replaces Boundary + rotate_*_data + the pack/unpack index arrays of

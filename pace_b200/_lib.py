@@ -107,6 +107,8 @@ MODULE_CALLS = {
     "fv_prep": [_D],
     "d_sw": [_D],
     "fv_setup": [],
+    "neg_adj3": [],
+    "c2l_ord4": [],
     "remap_main": [_I],
     "remap_finish": [_I],
     "map_single": [_S, _S, _S, _S, _I, _I, _I, _I, _D],

@@ -173,6 +173,8 @@ int pace_b200_update_dz_c(void* h, double dt2) { ENTRY(update_dz_c(*c, dt2)) }
 int pace_b200_p_grad_c(void* h, double dt2) { ENTRY(p_grad_c(*c, dt2)) }
 int pace_b200_fv_prep(void* h, double dt) { ENTRY(fv_prep(*c, dt)) }
 int pace_b200_fv_setup(void* h) { ENTRY(fv_setup(*c)) }
+int pace_b200_neg_adj3(void* h) { ENTRY(neg_adj3(*c)) }
+int pace_b200_c2l_ord4(void* h) { ENTRY(c2l_ord4(*c)) }
 int pace_b200_sat_adjust(void* h, const pace_b200_satadj_config* cfg, double mdt, int last_step, int kmp) {
   static_assert(sizeof(pace_b200_satadj_config) == sizeof(SatCfg), "satadj config mirror out of sync");
   ENTRY(sat_adjust(*c, *(const SatCfg*)cfg, mdt, last_step, kmp))

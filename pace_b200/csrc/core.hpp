@@ -68,6 +68,8 @@ int remap_main(Core& c, int nq);
 int remap_finish(Core& c, int last_step);
 struct SatCfg;
 int sat_adjust(Core& c, const SatCfg& sc, double mdt, int last_step, int kmp);
+int neg_adj3(Core& c);
+int c2l_ord4(Core& c);
 int fv_setup(Core& c);
 int pt_to_potential_density_pt(Core& c);
 int omega_from_w(Core& c);

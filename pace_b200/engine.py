@@ -77,6 +77,13 @@ class DycoreEngine:
         core.set_halo_plan(SYNC, pl.interface_sync_plan(self.ranks), local)
         self._nk_heat = nk_heat_dissipation(self.cfg, npz)
         self._do_del2cubed = self._nk_heat != 0 and self.cfg["d_con"] > 1.0e-5
+        # LagrangianToEulerian.__init__ (remapping.py:347-351): first level with pfull > 10 hPa
+        pfull = np.asarray(g0["grid.p"])
+        self._kmp = npz - 1
+        for k in range(npz):
+            if pfull[k] > 10.0e2:
+                self._kmp = k
+                break
         self._check_config()
 
     def _check_config(self):
@@ -184,6 +191,36 @@ class DycoreEngine:
             if it != n_split - 1:
                 core.halo_update(A3, self.TRACERS)
                 core.call("tracer_swap_dp")
+
+    # -- LagrangianToEulerian.__call__ (remapping.py:522-731) --------------------------------------------------
+    def remapping(self, last_step, mdt):
+        core = self.core
+        core.call("remap_main", len(self.TRACERS))
+        if self.cfg["do_sat_adj"]:
+            core.sat_adjust(mdt, last_step, self._kmp)
+        core.call("remap_finish", int(last_step))
+
+    # -- DynamicalCore.step_dynamics / _compute (fv_dynamics.py:445-655) ----------------------------------------
+    def step_dynamics(self):
+        core, c = self.core, self.cfg
+        k_split = int(c["k_split"])
+        self.compute_preamble()
+        for k in range(k_split):
+            n_map = k + 1
+            last_step = k == k_split - 1
+            core.call("copy_levels", "delp", "dyn.dp1")
+            self.acoustic_dynamics(c["dt_atmos"] / k_split, n_map=n_map)
+            self.tracer_advection()
+            if self.npz > 4:
+                self.remapping(last_step, c["dt_atmos"] / k_split)
+                if last_step:
+                    core.call("omega_from_w")
+                    if c["nf_omega"] > 0:
+                        core.halo_update(A3, ["omga"])
+                        core.call("del2cubed", "omga", 0.18 * c["da_min"], int(c["nf_omega"]))
+        core.call("neg_adj3")
+        core.halo_update(D3, ["u"], ["v"])
+        core.call("c2l_ord4")
 
     # -- DynamicalCore.compute_preamble (fv_dynamics.py:461-508) -------------------------------------------------
     def compute_preamble(self):
