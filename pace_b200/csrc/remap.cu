@@ -338,6 +338,8 @@ __device__ void fillz_column(const Pt& p, Col& c, int km, double* q, const doubl
   for (int k = 0; k < km; ++k) A(q, 0, 0, k) = qq[k];
 }
 
+struct TrPtrs { double* p[9]; };
+
 #ifndef PACE_HOST_EMU
 #define COL_DECL Col col
 #else
@@ -429,7 +431,7 @@ int remap_main(Core& c, int nq) {
   double* tr[9];
   for (int n = 0; n < nq; ++n) tr[n] = c.F(tracer_name(n));
   if (!c.err.empty()) return 1;
-  struct TrPtrs { double* p[9]; } trp;
+  TrPtrs trp;
   for (int n = 0; n < 9; ++n) trp.p[n] = n < nq ? tr[n] : nullptr;
   const bool fill = cf.fill != 0;
   launch_ij(st, g, box_compute(g), [=] __device__(const Pt& p) {
