@@ -1,0 +1,244 @@
+#!/usr/bin/env python
+"""bench.py — FV3 dycore step throughput of the B200-native hot path (pace_b200) and of the CPU baseline.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c384|c128|c48] [--impl reference]
+
+One "step" = one DynamicalCore.step_dynamics (k_split=1, n_split=6: 6 acoustic substeps + tracer advection +
+vertical remap) on synthetic inputs of the named shape (pace_b200/synthetic.py).  Metric: simulated-days/day =
+dt_atmos / wall-seconds-per-step (NDSL/ndsl/performance/report.py:116-129 without the /365).
+Prints ONE JSON line (rank 0).
+"""
+import argparse
+import ctypes
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: (tile size, layout, description)
+    "c384": (384, 2, "Baroclinic-shaped C384 L79 fp64, 6 tiles x 2x2 = 24 subdomains of 192x192x79, k_split=1 n_split=6"),
+    "c128": (128, 1, "Baroclinic-shaped C128 L79 fp64, 6 subdomains of 128x128x79, k_split=1 n_split=6"),
+    "c48": (48, 1, "Baroclinic-shaped C48 L79 fp64, 6 subdomains, k_split=1 n_split=6"),
+    "c24": (24, 1, "Baroclinic-shaped C24 L79 fp64, 6 subdomains, k_split=1 n_split=6"),
+}
+DT_ATMOS = 225.0
+N_SPLIT = 6
+NPZ = 79
+# algorithmic (compulsory) bytes per cell: SURVEY.md section 8(d) / DESIGN.md section 5
+BYTES_PER_CELL_FVTP2D_INNER = 4 * 8  # inner PPM sweeps: read q, crx, cry ; write 2 fluxes -> counted 3R + 2W, see DESIGN
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return json.load(open(p)), "measured"
+    return {"hbm_gbs": 6650.0}, "fallback"
+
+
+class ClockSampler(threading.Thread):
+    def __init__(self, index=0):
+        super().__init__(daemon=True)
+        self.index = index
+        self.samples = []
+        self.stop_flag = False
+
+    def run(self):
+        q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + q, "--format=csv,noheader,nounits"],
+                                     capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.samples.append([x.strip() for x in out.split(",")])
+            except Exception:
+                pass
+            time.sleep(0.2)
+
+    def summary(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unavailable"]}
+        sm = sorted(int(s[0]) for s in self.samples if s[0].isdigit())
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(s[2 + i].lower().startswith("active") for s in self.samples)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": int(self.samples[0][1]), "reasons": reasons,
+                "samples": len(self.samples)}
+
+
+def cpu_port_rate(n_tile, threads, steps=1):
+    """simulated-days/day of the CPU port (oracle/cpu_port.py: the kernel sources compiled for the host, verified
+    bit-exact against the reference's golden vectors) on a bounded sample."""
+    from oracle import cpu_port
+    from pace_b200.synthetic import make_engine
+
+    os.environ["OMP_NUM_THREADS"] = str(threads)
+    lib = cpu_port.load(openmp=True)
+    eng = make_engine(n_tile, 1, npz=NPZ, device="cpu", _lib_handle=lib, n_split=N_SPLIT, k_split=1, dt_atmos=DT_ATMOS)
+    eng.step_dynamics()  # warm-up
+    t0 = time.time()
+    for _ in range(steps):
+        eng.step_dynamics()
+    dt = (time.time() - t0) / steps
+    return DT_ATMOS / dt, dt
+
+
+def run_reference(args):
+    """--impl reference: the CPU implementation of the path on the box's host cores.  The reference itself is
+    Python (GT4Py numpy backend) and cannot travel to the GPU box, so this arm times the CPU port."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    n_tile, layout, desc = WORKLOADS[args.workload]
+    sample_tile = 48
+    times = []
+    for _ in range(max(1, min(args.steps, 3))):
+        rate, dt = cpu_port_rate(sample_tile, cores, steps=1)
+        times.append(dt)
+    dt = sum(times) / len(times)
+    # a step costs time proportional to the number of cells: scale the sample to the workload
+    scale = (n_tile / sample_tile) ** 2
+    ms = dt * scale * 1000.0
+    value = DT_ATMOS / (ms / 1000.0)
+    line = {
+        "impl": "reference", "metric": "dycore simulated-days/day", "value": value, "unit": "simulated days / day",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": desc},
+        "cpu_baseline": {"value": value, "unit": "simulated days / day", "cores": cores, "kind": "port",
+                         "sample": "one dycore step at C%d L79 (6 subdomains) timed on the host, scaled by cell count "
+                                   "(x%.0f) to the workload" % (sample_tile, scale)},
+        "e2e": {"value": value, "unit": "simulated days / day", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--workload", default=None)
+    ap.add_argument("--impl", default="pace_b200")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    args = ap.parse_args()
+    if args.workload is None:
+        args.workload = "c384"
+    if args.impl == "reference":
+        return run_reference(args)
+
+    import torch
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1:
+        raise SystemExit("multi-GPU placement is not wired into bench.py yet")
+    from pace_b200 import _lib
+    from pace_b200.synthetic import make_engine
+
+    torch.cuda.set_device(local_rank)
+    n_tile, layout, desc = WORKLOADS[args.workload]
+    eng = make_engine(n_tile, layout, npz=NPZ, device="cuda:%d" % local_rank, n_split=N_SPLIT, k_split=1, dt_atmos=DT_ATMOS)
+    core = eng.core
+    lib = core.lib
+    n_sub = 6 * layout * layout
+    n = n_tile // layout
+    cells = n_sub * n * n * NPZ
+
+    for _ in range(args.warmup):
+        eng.step_dynamics()
+    torch.cuda.synchronize()
+
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    lib.pace_b200_profile_enable(1)
+    l0 = lib.pace_b200_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(args.steps):
+        eng.step_dynamics()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / args.steps
+    launches = (lib.pace_b200_launch_count() - l0) // args.steps
+    lib.pace_b200_profile_enable(0)
+    buf = ctypes.create_string_buffer(65536)
+    lib.pace_b200_profile_report(buf, 65536)
+    prof = {}
+    for ln in buf.value.decode().splitlines():
+        label, cnt, tot = ln.split()
+        prof[label] = (int(cnt), float(tot))
+    sampler.stop_flag = True
+    sampler.join(timeout=2)
+    value = DT_ATMOS / (ms / 1000.0)
+
+    # roofline of the dominant labelled kernel
+    pk, pk_kind = peaks()
+    roof = None
+    if prof:
+        top = max(prof, key=lambda k: prof[k][1])
+        cnt, tot = prof[top]
+        per_launch_ms = tot / cnt
+        bytes_per_cell = {"fvtp2d_inner_ppm": 5 * 8, "fvtp2d_qi_qj": 7 * 8, "fvtp2d_outer_ppm": 10 * 8,
+                          "riem_solver_c": 8 * 8, "riem_solver3": 15 * 8, "remap_scalars_column": 40 * 8}.get(top, 8 * 8)
+        alg_bytes = cells * bytes_per_cell
+        achieved = alg_bytes / (per_launch_ms / 1000.0) / 1e9
+        roof = {"kernel": top, "bound": "hbm", "achieved": achieved, "peak": pk["hbm_gbs"], "peak_source": pk_kind,
+                "unit": "GB/s", "frac": achieved / pk["hbm_gbs"], "traffic": None, "launches_timed": cnt,
+                "ms_per_launch": per_launch_ms, "share_of_step": tot / args.steps / ms,
+                "labelled_kernels_ms_per_step": {k: v[1] / args.steps for k, v in sorted(prof.items())}}
+
+    # end-to-end: prognostic state from pinned host memory -> device, step, result back to the host
+    e2e = None
+    if not args.no_e2e:
+        names = ["u", "v", "w", "delp", "pt", "delz", "qvapor", "qliquid", "qrain", "qice", "qsnow", "qgraupel",
+                 "qo3mr", "qsgs_tke", "qcld"]
+        host = {k: torch.empty(core.t[k].shape, dtype=torch.float64).pin_memory() for k in names}
+        for k in names:
+            host[k].copy_(core.t[k])
+        nbytes = sum(h.numel() * 8 for h in host.values())
+        k_e2e = max(1, min(args.steps, 2))
+        torch.cuda.synchronize()
+        t0 = time.time()
+        for _ in range(k_e2e):
+            for k in names:
+                core.t[k].copy_(host[k], non_blocking=True)
+            eng.step_dynamics()
+            for k in names:
+                host[k].copy_(core.t[k], non_blocking=True)
+            torch.cuda.synchronize()
+        e2e_ms = (time.time() - t0) / k_e2e * 1000.0
+        e2e = {"value": DT_ATMOS / (e2e_ms / 1000.0), "unit": "simulated days / day", "ms_per_step": e2e_ms,
+               "h2d_bytes_per_step": nbytes, "d2h_bytes_per_step": nbytes, "steps": k_e2e}
+        del host
+
+    cpu = None
+    if not args.no_cpu_baseline:
+        cores = os.cpu_count() or 1
+        sample_tile = 48
+        rate, dt = cpu_port_rate(sample_tile, cores, steps=1)
+        scale = (n_tile / sample_tile) ** 2
+        cpu = {"value": DT_ATMOS / (dt * scale), "unit": "simulated days / day", "cores": cores, "kind": "port",
+               "sample": "one dycore step at C%d L79 (%.1f s on the host), scaled by cell count (x%.0f)" % (sample_tile, dt, scale)}
+
+    line = {
+        "metric": "dycore simulated-days/day", "value": value, "unit": "simulated days / day", "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic (C12 reference fixture resampled, see pace_b200/synthetic.py)",
+        "config": {"workload": desc, "cells": cells, "l2": "working set (%.0f GB) >> L2, no flush needed" % (cells * 8 * 130 / 1e9)},
+        "gpu_launches": int(launches), "clocks": sampler.summary(), "roofline": roof, "cpu_baseline": cpu, "e2e": e2e,
+    }
+    print(json.dumps(line))
+
+
+if __name__ == "__main__":
+    main()

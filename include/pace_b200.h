@@ -55,6 +55,12 @@ int pace_b200_set_stream(void* handle, void* cuda_stream);
 /* Register a caller-owned device array under the reference's attribute name. */
 int pace_b200_set_field(void* handle, const char* name, double* device_ptr);
 
+/* Measurement hooks (bench.py): number of kernels launched by this library so far; CUDA-event timing of the
+ * kernels that carry a label (enable, run, then report "label count total_ms" lines and clear). */
+long long pace_b200_launch_count(void);
+int pace_b200_profile_enable(int on);
+int pace_b200_profile_report(char* buf, int n);
+
 /* Set a small per-level (K) column from HOST memory, e.g. the column namelist of d_sw
  * (pyFV3/stencils/d_sw.py:647-691: "col.nord", "col.nord_v", "col.damp_vt", ...) or the delnflux damping
  * columns (delnflux.py:22-38).  The library keeps a host copy and a device copy under `name`. */

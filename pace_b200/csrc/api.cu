@@ -15,6 +15,33 @@ struct SatCfg {
 
 static thread_local std::string g_err;
 
+// ---- launch accounting ------------------------------------------------------------------------------------
+static long long g_launches = 0;
+long long& launch_counter() { return g_launches; }
+#ifndef PACE_HOST_EMU
+struct ProfEntry { const char* label; cudaEvent_t a, b; };
+static bool g_prof_on = false;
+static std::vector<ProfEntry> g_prof;
+static std::vector<cudaEvent_t> g_event_pool;
+static cudaEvent_t get_event() {
+  if (!g_event_pool.empty()) { cudaEvent_t e = g_event_pool.back(); g_event_pool.pop_back(); return e; }
+  cudaEvent_t e;
+  cudaEventCreate(&e);
+  return e;
+}
+bool prof_enabled() { return g_prof_on; }
+void prof_begin(cudaStream_t s, const char* label) {
+  ProfEntry p{label, get_event(), get_event()};
+  cudaEventRecord(p.a, s);
+  g_prof.push_back(p);
+}
+void prof_end(cudaStream_t s) { cudaEventRecord(g_prof.back().b, s); }
+#else
+bool prof_enabled() { return false; }
+void prof_begin(cudaStream_t, const char*) {}
+void prof_end(cudaStream_t) {}
+#endif
+
 void set_error(const char* fmt, ...) {
   char buf[1024];
   va_list ap;
@@ -161,6 +188,44 @@ int pace_b200_set_column(void* h, const char* name, const double* host_values, i
 }
 
 static double* opt_field(Core* c, const char* name) { return (name && name[0]) ? c->F(name) : nullptr; }
+
+long long pace_b200_launch_count(void) { return launch_counter(); }
+
+int pace_b200_profile_enable(int on) {
+#ifndef PACE_HOST_EMU
+  g_prof_on = on != 0;
+#endif
+  return 0;
+}
+
+// Writes "label count total_ms\n" lines for every labelled kernel timed since the last report; clears the record.
+int pace_b200_profile_report(char* buf, int n) {
+  std::string out;
+#ifndef PACE_HOST_EMU
+  cudaDeviceSynchronize();
+  std::map<std::string, std::pair<long long, double>> acc;
+  for (auto& p : g_prof) {
+    float ms = 0;
+    cudaEventElapsedTime(&ms, p.a, p.b);
+    auto& e = acc[p.label];
+    e.first += 1;
+    e.second += ms;
+    g_event_pool.push_back(p.a);
+    g_event_pool.push_back(p.b);
+  }
+  g_prof.clear();
+  char line[256];
+  for (auto& kv : acc) {
+    snprintf(line, sizeof line, "%s %lld %.6f\n", kv.first.c_str(), kv.second.first, kv.second.second);
+    out += line;
+  }
+#endif
+  if (n > 0) {
+    strncpy(buf, out.c_str(), n - 1);
+    buf[n - 1] = 0;
+  }
+  return 0;
+}
 
 #define ENTRY(call)          \
   Core* c = (Core*)h;        \

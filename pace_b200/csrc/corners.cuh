@@ -63,6 +63,7 @@ static __global__ void k_corner_ops(Geo g, CornerOps ops) {
   corner_fill_cell(g, ops.op[io], t, k, c, n);
 }
 inline void run_corner_ops(cudaStream_t s, const Geo& g, const CornerOps& ops) {
+  ++launch_counter();
   k_corner_ops<<<ops.nk * g.nt, 96, 0, s>>>(g, ops);
 }
 #else

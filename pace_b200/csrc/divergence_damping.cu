@@ -109,6 +109,7 @@ __global__ void k_dgrid_fill(Geo g, double* x, double* y, double mysign, int k0,
 
 void bgrid_fill(Core& c, double* q, bool ydir, int k0, int nk) {
 #ifndef PACE_HOST_EMU
+  ++launch_counter();
   k_bgrid_fill<<<nk * c.g.nt, 64, 0, c.stream>>>(c.g, q, ydir, k0, nk);
 #else
   for (int t = 0; t < c.g.nt; ++t)
@@ -118,6 +119,7 @@ void bgrid_fill(Core& c, double* q, bool ydir, int k0, int nk) {
 }
 void dgrid_fill(Core& c, double* x, double* y, double mysign, int k0, int nk) {
 #ifndef PACE_HOST_EMU
+  ++launch_counter();
   k_dgrid_fill<<<nk * c.g.nt, 96, 0, c.stream>>>(c.g, x, y, mysign, k0, nk);
 #else
   for (int t = 0; t < c.g.nt; ++t)

@@ -69,6 +69,7 @@ int halo_update(Core& c, int plan_id, const char* const* x_names, const char* co
   if (n_ops == 0) return 0;
   const HaloOpDev* ops = (const HaloOpDev*)c.halo_ops[plan_id];
 #ifndef PACE_HOST_EMU
+  LaunchScope scope(c.stream, "halo_update");
   k_halo<<<dim3(n_ops, nk), 128, 0, c.stream>>>(c.g, ops, f, nk);
 #else
   for (int o = 0; o < n_ops; ++o)

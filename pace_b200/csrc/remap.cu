@@ -466,7 +466,7 @@ int remap_main(Core& c, int nq) {
       A(cappa, 0, 0, k) = cap;
       A(pkz, 0, 0, k) = fv_exp(cap * fv_log(RDG * A(delp, 0, 0, k) / A(delz, 0, 0, k) * A(pt, 0, 0, k)));
     }
-  });
+  }, "remap_scalars_column");
   // pressures_mapu + map_single_u on [is..ie] x [js..je+1]
   launch_ij(st, g, Box{is, js, 0, g.nx, g.ny + 1, 1}, [=] __device__(const Pt& p) {
     COL_DECL;

@@ -151,7 +151,7 @@ int riem_solver_c(Core& c, double dt2) {
     for (int k = 1; k <= km; ++k) K_(pef, k) = K_(pe, k) + K_(pem, k);
     K_(gz, km) = A20(hs);
     for (int k = km - 1; k >= 0; --k) K_(gz, k) = K_(gz, k + 1) - K_(dz, k) * GRAV;
-  });
+  }, "riem_solver_c");
   return 0;
 }
 
@@ -220,7 +220,7 @@ int riem_solver3(Core& c, double dt, int last_call) {
     }
     K_(zh, km) = A20(zs);
     for (int k = km - 1; k >= 0; --k) K_(zh, k) = K_(zh, k + 1) - K_(delz, k);
-  });
+  }, "riem_solver3");
   return 0;
 }
 

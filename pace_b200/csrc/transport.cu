@@ -44,6 +44,7 @@ static __global__ void k_copy_corners(Geo g, double* q, bool ydir, int nk) {
 #endif
 void copy_corners(Core& c, double* q, bool ydir, int nk) {
 #ifndef PACE_HOST_EMU
+  ++launch_counter();
   k_copy_corners<<<nk * c.g.nt, 64, 0, c.stream>>>(c.g, q, ydir, nk);
 #else
   for (int t = 0; t < c.g.nt; ++t)
@@ -85,7 +86,7 @@ int fvtp2d(Core& c, const Fvtp2dArgs& a) {
       auto D = [&](int d) { return A2(dxa, d, 0); };
       A0(fx_in) = ppm_flux(Q, D, A0(crx), p.i, is, ie, p.W, p.E, ord_inner);
     }
-  });
+  }, "fvtp2d_inner_ppm");
   // K2: q_i on [is-3..ie+3]x[js..je], q_j on [is..ie]x[js-3..je+3]   (fvtp2d.py:34-77)
   launch_ijk(st, g, Box{0, 0, 0, g.nx + 6, g.ny + 6, nk}, [=] __device__(const Pt& p) {
     if (p.j >= js && p.j <= je) {
@@ -97,7 +98,7 @@ int fvtp2d(Core& c, const Fvtp2dArgs& a) {
       double area_with_x_flux = A20(area) + A0(xfx) - A(xfx, 1, 0, 0);
       A0(q_j) = (A0(q) * A20(area) + fx10 - fx11) / area_with_x_flux;
     }
-  });
+  }, "fvtp2d_qi_qj");
   // K3: outer sweeps + final_fluxes (fvtp2d.py:80-119)
   launch_ijk(st, g, Box{is, js, 0, g.nx + 1, g.ny + 1, nk}, [=] __device__(const Pt& p) {
     if (p.j <= je) {
@@ -112,7 +113,7 @@ int fvtp2d(Core& c, const Fvtp2dArgs& a) {
       double outer = ppm_flux(Q, D, A0(cry), p.j, js, je, p.S, p.N, ord_outer);
       A0(fy) = 0.5 * (outer + A0(fy_in)) * A0(yunit);
     }
-  });
+  }, "fvtp2d_outer_ppm");
   if (a.nord_col) {
     DelnArgs d;
     d.q = q; d.fx = fx; d.fy = fy; d.mass = a.mass; d.nord_col = a.nord_col; d.damp = a.damp; d.nk = nk;

@@ -114,7 +114,7 @@ def a2b_corner_coefficients(lon, lat, lon_agrid, lat_agrid, nx, ny):
         for (a, b) in pairs:
             x1 = _great_circle_dist(float(lon_agrid[ci + a[0], cj + a[1]]), float(lat_agrid[ci + a[0], cj + a[1]]), p0a, p0b)
             x2 = _great_circle_dist(float(lon_agrid[ci + b[0], cj + b[1]]), float(lat_agrid[ci + b[0], cj + b[1]]), p0a, p0b)
-            out[n] = x1 / (x2 - x1)
+            out[n] = x1 / (x2 - x1) if x2 != x1 else 0.0
             n += 1
     return out
 
