@@ -163,11 +163,13 @@ def main():
     l0 = lib.pace_b200_launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     torch.cuda.synchronize()
+    torch.cuda.profiler.start()  # lets `ncu --profile-from-start off` capture exactly the timed steps
     e0.record()
     for _ in range(args.steps):
         eng.step_dynamics()
     e1.record()
     torch.cuda.synchronize()
+    torch.cuda.profiler.stop()
     ms = e0.elapsed_time(e1) / args.steps
     launches = (lib.pace_b200_launch_count() - l0) // args.steps
     lib.pace_b200_profile_enable(0)
