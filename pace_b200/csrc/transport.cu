@@ -13,7 +13,12 @@
 #include "corners.cuh"
 #include "ppm.cuh"
 
+#include <cstdlib>
+#include <string>
+
 namespace pace {
+
+int fvtp2d_fused_launch(Core& c, const Fvtp2dArgs& a);
 
 // ---- materialised copy_corners ---------------------------------------------------------------------
 __device__ __forceinline__ void copy_corner_cell(const Geo& g, double* q, bool ydir, int t, int k, int c, int a, int b) {
@@ -71,6 +76,22 @@ int fvtp2d(Core& c, const Fvtp2dArgs& a) {
 
   // copy_corners_x(q): final observable corner state of q (the y-copied view is read virtually below)
   copy_corners(c, q, false, nk);
+
+#ifndef PACE_HOST_EMU
+  // production path: one fused shared-memory kernel (fvtp2d_fused.cu); PACE_B200_FVTP2D=unfused selects the
+  // three-kernel version below (same arithmetic) for A/B measurements
+  static const bool unfused = [] { const char* v = getenv("PACE_B200_FVTP2D"); return v && std::string(v) == "unfused"; }();
+  if (!unfused) {
+    if (fvtp2d_fused_launch(c, a)) return 1;
+    if (a.nord_col) {
+      DelnArgs d;
+      d.q = q; d.fx = fx; d.fy = fy; d.mass = a.mass; d.nord_col = a.nord_col; d.damp = a.damp; d.nk = nk;
+      d.accumulate = true; d.d2 = nullptr; d.nmax = a.nmax;
+      return delnflux(c, d);
+    }
+    return 0;
+  }
+#endif
 
   // K1: inner sweeps.  q_y_advected_mean on [is-3..ie+3]x[js..je+1] (y-PPM of y-copied q, courant cry),
   //                    q_x_advected_mean on [is..ie+1]x[js-3..je+3] (x-PPM of x-copied q, courant crx)
