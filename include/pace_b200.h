@@ -79,6 +79,19 @@ int pace_b200_c_sw(void* handle, double dt2);
  * in: ad.zs ad.ut ad.vt ad.gz grid.area grid.dp_ref   out: ad.gz ad.ws3 */
 int pace_b200_update_dz_c(void* handle, double dt2);
 
+/* No counterpart in the reference.  Same computation, inputs, outputs and results as pace_b200_update_dz_c, for
+ * callers that cannot let a library allocate device memory: a host model whose own pool took the whole GPU at
+ * start-up, or a time-critical loop that cannot afford the device-wide synchronisation cudaMalloc implies.  Its one
+ * work array (a copy of ad.gz) is a fixed array of PACE_B200_STATIC_SCRATCH_DOUBLES doubles inside the library image
+ * (every GPU that loads the library holds those 16 MiB until the process exits); no allocation routine is called.
+ * Returns non-zero, with a message in pace_b200_last_error, when the handle's fields (subdomains x (npz+1) x (ny+7)
+ * x row stride doubles) exceed that size.  The first call on each device resolves the array's device address: make
+ * it before starting any stream capture on that device.  All handles share the array and it keeps the last call's
+ * contents (each call overwrites everything it reads, nothing needs clearing); calls that can overlap on one GPU
+ * race on it, so order them on one stream or with events. */
+#define PACE_B200_STATIC_SCRATCH_DOUBLES 2097152
+int pace_b200_update_dz_c_static(void* handle, double dt2);
+
 /* p_grad_c_stencil (pyFV3/stencils/dyn_core.py:122-173).  in: csw.delpc ad.pkc ad.gz   inout: uc vc */
 int pace_b200_p_grad_c(void* handle, double dt2);
 

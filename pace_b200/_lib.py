@@ -107,6 +107,7 @@ MODULE_CALLS = {
     "riem_solver_c": [_D],
     "c_sw": [_D],
     "update_dz_c": [_D],
+    "update_dz_c_static": [_D],
     "p_grad_c": [_D],
     "fv_prep": [_D],
     "d_sw": [_D],
