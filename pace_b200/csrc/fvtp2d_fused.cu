@@ -29,7 +29,10 @@ struct FusedArgs {
   int ord_inner, ord_outer, nk;
 };
 
+// OIN / OOUT: |ord| of the inner / outer sweeps as compile-time constants (0 = read it from the arguments)
+template <int OIN, int OOUT>
 __global__ void __launch_bounds__(TX* TY) k_fvtp2d_fused(Geo g, FusedArgs a) {
+  const int ord_in = OIN ? OIN : a.ord_inner, ord_out = OOUT ? OOUT : a.ord_outer;
   __shared__ double qx[QH][QW];          // q seen through copy_corners_x
   __shared__ double qy[QH][QW];          // q seen through copy_corners_y
   __shared__ double fyi[TY + 1][TX + 6]; // inner y flux at (i0-3+ii, j0+jj)
@@ -76,7 +79,7 @@ __global__ void __launch_bounds__(TX* TY) k_fvtp2d_fused(Geo g, FusedArgs a) {
     if (i <= ie + 3 && j <= je + 1) {
       auto Q = [&](int d) { return qy[lj + 3 + d][li]; };
       auto D = [&](int d) { return G2(a.dya, i, j + d); };
-      v = ppm_flux(Q, D, G3(a.cry, i, j), j, js, je, S, N, a.ord_inner);
+      v = ppm_flux_fast(Q, D, G3(a.cry, i, j), j, js, je, S, N, ord_in);
     }
     fyi[lj][li] = v;
   }
@@ -87,7 +90,7 @@ __global__ void __launch_bounds__(TX* TY) k_fvtp2d_fused(Geo g, FusedArgs a) {
     if (i <= ie + 1 && j <= je + 3) {
       auto Q = [&](int d) { return qx[lj][li + 3 + d]; };
       auto D = [&](int d) { return G2(a.dxa, i + d, j); };
-      v = ppm_flux(Q, D, G3(a.crx, i, j), i, is, ie, W, E, a.ord_inner);
+      v = ppm_flux_fast(Q, D, G3(a.crx, i, j), i, is, ie, W, E, ord_in);
     }
     fxi[lj][li] = v;
   }
@@ -126,13 +129,13 @@ __global__ void __launch_bounds__(TX* TY) k_fvtp2d_fused(Geo g, FusedArgs a) {
     if (i <= ie + 1 && j <= je) {
       auto Q = [&](int d) { return qi[lj][li + 3 + d]; };
       auto D = [&](int d) { return G2(a.dxa, i + d, j); };
-      const double outer = ppm_flux(Q, D, G3(a.crx, i, j), i, is, ie, W, E, a.ord_outer);
+      const double outer = ppm_flux_fast(Q, D, G3(a.crx, i, j), i, is, ie, W, E, ord_out);
       a.fx[base3 + j * g.sj + i] = 0.5 * (outer + fxi[lj + 3][li]) * G3(a.xunit, i, j);
     }
     if (i <= ie && j <= je + 1) {
       auto Q = [&](int d) { return qj[lj + 3 + d][li]; };
       auto D = [&](int d) { return G2(a.dya, i, j + d); };
-      const double outer = ppm_flux(Q, D, G3(a.cry, i, j), j, js, je, S, N, a.ord_outer);
+      const double outer = ppm_flux_fast(Q, D, G3(a.cry, i, j), j, js, je, S, N, ord_out);
       a.fy[base3 + j * g.sj + i] = 0.5 * (outer + fyi[lj][li + 3]) * G3(a.yunit, i, j);
     }
   }
@@ -155,7 +158,12 @@ int fvtp2d_fused_launch(Core& c, const Fvtp2dArgs& a) {
   // the fx / fy output domains are (nx+1) x ny and nx x (ny+1): tile the (nx+1) x (ny+1) point set
   dim3 grd((g.nx + 1 + TX - 1) / TX, (g.ny + 1 + TY - 1) / TY, a.nk * g.nt);
   LaunchScope scope(c.stream, "fvtp2d_fused");
-  k_fvtp2d_fused<<<grd, blk, 0, c.stream>>>(g, f);
+  const int oi = f.ord_inner < 0 ? -f.ord_inner : f.ord_inner, oo = f.ord_outer < 0 ? -f.ord_outer : f.ord_outer;
+  if (oi == 5 && oo == 5) k_fvtp2d_fused<5, 5><<<grd, blk, 0, c.stream>>>(g, f);
+  else if (oi == 6 && oo == 6) k_fvtp2d_fused<6, 6><<<grd, blk, 0, c.stream>>>(g, f);
+  else if (oi == 8 && oo == 8) k_fvtp2d_fused<8, 8><<<grd, blk, 0, c.stream>>>(g, f);
+  else if (oi == 8 && oo == 10) k_fvtp2d_fused<8, 10><<<grd, blk, 0, c.stream>>>(g, f);
+  else k_fvtp2d_fused<0, 0><<<grd, blk, 0, c.stream>>>(g, f);
   return 0;
 }
 
