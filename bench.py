@@ -191,7 +191,7 @@ def main():
         cnt, tot = prof[top]
         per_launch_ms = tot / cnt
         bytes_per_cell = {"fvtp2d_inner_ppm": 5 * 8, "fvtp2d_qi_qj": 7 * 8, "fvtp2d_outer_ppm": 10 * 8,
-                          "fvtp2d_fused": 8.4 * 8, "riem_solver_c": 8 * 8, "riem_solver3": 15 * 8, "remap_scalars_column": 40 * 8}.get(top, 8 * 8)
+                          "fvtp2d_fused": 8.4 * 8, "fvtp2d_march": 8.4 * 8, "riem_solver_c": 8 * 8, "riem_solver3": 15 * 8, "remap_scalars_column": 40 * 8}.get(top, 8 * 8)
         alg_bytes = cells * bytes_per_cell
         achieved = alg_bytes / (per_launch_ms / 1000.0) / 1e9
         roof = {"kernel": top, "bound": "hbm", "achieved": achieved, "peak": pk["hbm_gbs"], "peak_source": pk_kind,

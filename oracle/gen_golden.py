@@ -39,6 +39,7 @@ def main():
     ap.add_argument("--steps", type=int, default=1)
     ap.add_argument("--skip-run", action="store_true")
     ap.add_argument("--stages-only", action="store_true")
+    ap.add_argument("--layout", type=int, default=1, help="layout x layout subdomains per tile (no stage log if > 1)")
     ap.add_argument("--deep", action="store_true", help="also hook d_sw/updatedzd/nh_p_grad internals (dev only)")
     args = ap.parse_args()
     tag = "c%d" % (args.npx - 1)
@@ -46,6 +47,8 @@ def main():
     if args.deep:
         suffix += "_deep"
     raw = args.raw + suffix
+    if args.layout > 1:
+        return multi_layout(args, tag, raw + "_l%d" % args.layout)
     if not args.skip_run:
         cfg = default_config_kwargs(npx=args.npx, n_split=args.n_split)
         res = run_ranks(6, rank_main, (cfg, args.steps, (0,), raw, 0, args.deep), timeout=7200)
@@ -77,6 +80,28 @@ def main():
     np.savez_compressed(os.path.join(out, "%s_6rank_grid.npz" % tag), **grid)
     np.savez_compressed(os.path.join(out, "%s_6rank_init%s.npz" % (tag, suffix)), **init)
     np.savez_compressed(os.path.join(out, "%s_6rank_final%s.npz" % (tag, suffix)), **final)
+
+
+def multi_layout(args, tag, raw):
+    """6 * layout^2 ranks: inputs and the state after the step(s) of every rank (no per-stage log)."""
+    n = 6 * args.layout * args.layout
+    if not args.skip_run:
+        cfg = default_config_kwargs(npx=args.npx, n_split=args.n_split, layout=(args.layout, args.layout))
+        for r in run_ranks(n, rank_main, (cfg, args.steps, (), raw, 0, False), timeout=7200):
+            print(r)
+    grid, init, final = {}, {}, {}
+    for r in range(n):
+        g = np.load(os.path.join(raw, "rank%d_grid.npz" % r))
+        for k in g.files:
+            grid["%d:%s" % (r, k)] = g[k]
+        for src, dst in (("init", init), ("final", final)):
+            s = np.load(os.path.join(raw, "rank%d_%s.npz" % (r, src)))
+            for k in s.files:
+                a = s[k]
+                dst["%d:%s" % (r, k)] = a[3:-3, 3:-3] if a.ndim == 3 else a
+    out = os.path.join(ROOT, "tests", "golden")
+    for name, d in (("grid", grid), ("init", init), ("final", final)):
+        np.savez_compressed(os.path.join(out, "%s_%drank_%s.npz" % (tag, n, name)), **d)
 
 
 if __name__ == "__main__":

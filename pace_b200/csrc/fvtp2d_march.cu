@@ -1,0 +1,381 @@
+// Row-marching fvtp2d for sm_100a: one kernel per FiniteVolumeTransport call, all intermediate fields in registers,
+// warp shuffles and warp-private shared-memory rows.
+//
+// A WARP owns one level of one subdomain, a strip of 26 columns (lane <-> i, with a 3-column apron each side) and a
+// chunk of rows, and marches over the rows R = j_lo-3 .. j_hi+3 without any CTA-wide barrier.  Per step it
+//   1. reads row R of q (seen through copy_corners_x and copy_corners_y where they differ: corner blocks only),
+//   2. x-direction, row R:   inner x-PPM flux (edge values / slopes exchanged by shuffles), q_j(i, R) (fvtp2d.py:57-77)
+//   3. y-direction, column i: the inner sweep on q and the outer sweep on q_j advance by one row; PPM edge values /
+//      limited slopes are carried in registers, so each is computed once per cell                 (yppm.py)
+//      -> inner y flux and final fy at interface R-2, q_i(i, R-3)                                  (fvtp2d.py:34-54)
+//   4. x-direction, row R-3: outer x-PPM flux on q_i -> final fx                                   (fvtp2d.py:80-119)
+// Input rows are staged global -> shared two steps ahead with cp.async.  Every field is read once and written once
+// (DRAM traffic = the 7 / 9 algorithmic passes + 6 warm-up rows per chunk; the column aprons hit in L1/L2).  All expressions are those of ppm.cuh / transport.cu, evaluated per element in the same order: results
+// are bit-identical to the three-kernel version and to the reference.
+#include "corners.cuh"
+#include "ppm.cuh"
+#include "transport.hpp"
+
+namespace pace {
+
+#ifndef PACE_HOST_EMU
+
+namespace {
+
+struct MarchArgs {
+  const double *q, *crx, *cry, *xfx, *yfx, *xunit, *yunit, *area, *dxa, *dya;
+  double *fx, *fy;
+  int nk, rows, nstrips, nchunks;  // levels; rows per chunk; column strips; row chunks
+  long long items;                 // nstrips * nchunks * nk * subdomains
+};
+
+// State of one PPM sweep that advances along its own direction one cell per step.
+template <int MORD>
+struct March {
+  double w[5];        // transported scalar at rows R-4 .. R; the cell being completed is w[2]
+  double al_lo;       // MORD < 8: edge value at the lower interface of w[2]
+  double dm_m, dm_0;  // MORD >= 8: limited slopes of w[1], w[2]
+  double pq, pbl, pbr;  // previous cell: value and PPM perturbations
+  bool ps;
+  __device__ __forceinline__ void push(double v) {
+    w[0] = w[1]; w[1] = w[2]; w[2] = w[3]; w[3] = w[4]; w[4] = v;
+  }
+};
+
+// bl, br (and the smoothness flag of the mord < 8 schemes) of the cell in the middle of the window; `pos` is its
+// index along the sweep, `first` = nothing carried yet, `near` = an edge formula may apply (general code path).
+template <int MORD, class DF>
+__device__ __forceinline__ void march_cell(March<MORD>& m, int pos, bool first, bool near, DF D, int lo, int hi,
+                                           bool elo, bool ehi, double& bl, double& br, bool& s) {
+  auto Q = [&](int d) { return m.w[2 + d]; };
+  if (MORD < 8) {
+    using namespace ppmc;
+    double al_hi;
+    if (near) {
+      if (first) m.al_lo = ppm_al(Q, D, pos, lo, hi, elo, ehi, 0);
+      al_hi = ppm_al(Q, D, pos, lo, hi, elo, ehi, 1);
+    } else {
+      if (first) m.al_lo = p1 * (m.w[1] + m.w[2]) + p2 * (m.w[0] + m.w[3]);
+      al_hi = p1 * (m.w[2] + m.w[3]) + p2 * (m.w[1] + m.w[4]);
+    }
+    bl = m.al_lo - m.w[2];
+    br = al_hi - m.w[2];
+    const double b0 = bl + br;
+    s = MORD == 5 ? (bl * br < 0) : ((3.0 * fabs(b0)) < fabs(bl - br));
+    m.al_lo = al_hi;
+  } else {
+    if (first) {
+      m.dm_m = ppm_dm8_v(m.w[0], m.w[1], m.w[2]);
+      m.dm_0 = ppm_dm8_v(m.w[1], m.w[2], m.w[3]);
+    }
+    const double dm_p = ppm_dm8_v(m.w[2], m.w[3], m.w[4]);
+    if (near) {
+      ppm_blbr8(Q, D, pos, lo, hi, elo, ehi, 0, bl, br);
+    } else {
+      const double al_lo = 0.5 * (m.w[1] + m.w[2]) + 1.0 / 3.0 * (m.dm_m - m.dm_0);
+      const double al_hi = 0.5 * (m.w[2] + m.w[3]) + 1.0 / 3.0 * (m.dm_0 - dm_p);
+      const double xt = 2.0 * m.dm_0;
+      bl = -1.0 * fv_sign(fv_min(fabs(xt), fabs(al_lo - m.w[2])), xt);
+      br = fv_sign(fv_min(fabs(xt), fabs(al_hi - m.w[2])), xt);
+    }
+    s = false;
+    m.dm_m = m.dm_0;
+    m.dm_0 = dm_p;
+  }
+}
+
+// flux through the interface between the previous cell (m) and the current one (0) for Courant number c
+template <int MORD>
+__device__ __forceinline__ double cells_flux(double c, double qm, double blm, double brm, bool sm, double q0,
+                                             double bl, double br, bool s0) {
+  if (MORD < 8) {
+    const double b0 = bl + br, b0m = blm + brm;
+    const double mask = (sm || s0) ? 1.0 : 0.0;
+    const double fx1 = c > 0.0 ? (1.0 - c) * (brm - c * b0m) : (1.0 + c) * (bl + c * b0);
+    return c > 0.0 ? qm + fx1 * mask : q0 + fx1 * mask;
+  }
+  if (c > 0.0) {
+    const double b0 = blm + brm;
+    return qm + (1.0 - c) * (brm - c * b0) * 1.0;
+  }
+  const double b0 = bl + br;
+  return q0 + (1.0 + c) * (bl + c * b0) * 1.0;
+}
+
+constexpr int NSLOT = 3, NSTREAM = 10;
+constexpr int SW = 26;         // cells per warp strip (32 lanes - 2 x 3 apron)
+constexpr int WPB = 4;         // warps per CTA (independent work items)
+constexpr int PITCH = 34;      // doubles per staged row
+constexpr int WARP_SMEM = (NSTREAM * NSLOT + 1) * PITCH;  // doubles per warp
+constexpr unsigned FULL = 0xffffffffu;
+
+__device__ __forceinline__ void cp_async8(double* smem_dst, const double* gmem_src) {
+  const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;\n" ::"r"(d), "l"(gmem_src) : "memory");
+}
+
+// PPM flux through the left interface of lane L's cell, sweep along the lanes.  `row` holds the transported scalar of
+// the 32 columns of the strip; `i` is the lane's column, D(d) the grid spacing at column i+d.  Each lane computes the
+// edge value (MORD < 8) or the limited slope and bl/br (MORD >= 8) of its own interface / cell once; neighbours get
+// them by shuffle.  Must be called by all 32 lanes; the result is meaningful for lanes 3..29.
+template <int MORD, class DF>
+__device__ __forceinline__ double xsweep_flux(const double* row, int L, int i, double c, DF D, int is, int ie, bool W,
+                                              bool E) {
+  auto Q = [&](int d) { return row[L + d]; };
+  if (MORD < 8) {
+    using namespace ppmc;
+    double al = 0.0;
+    if (L >= 2 && L <= 30) {
+      const bool special = (W && i >= is - 1 && i <= is + 1) || (E && i >= ie && i <= ie + 2);
+      if (special) al = ppm_al(Q, D, i, is, ie, W, E, 0);
+      else al = p1 * (row[L - 1] + row[L]) + p2 * (row[L - 2] + row[L + 1]);
+    }
+    const double alm = __shfl_up_sync(FULL, al, 1), alp = __shfl_down_sync(FULL, al, 1);
+    const double q0 = row[L], qm = row[L > 0 ? L - 1 : 0];
+    const double bl = al - q0, br = alp - q0, b0 = bl + br;
+    const double blm = alm - qm, brm = al - qm, b0m = blm + brm;
+    bool s0, sm;
+    if (MORD == 5) {
+      s0 = bl * br < 0;
+      sm = blm * brm < 0;
+    } else {
+      s0 = (3.0 * fabs(b0)) < fabs(bl - br);
+      sm = (3.0 * fabs(b0m)) < fabs(blm - brm);
+    }
+    const double mask = (sm || s0) ? 1.0 : 0.0;
+    const double fx1 = c > 0.0 ? (1.0 - c) * (brm - c * b0m) : (1.0 + c) * (bl + c * b0);
+    return c > 0.0 ? qm + fx1 * mask : q0 + fx1 * mask;
+  } else {
+    double dm = 0.0;
+    if (L >= 1 && L <= 30) dm = ppm_dm8_v(row[L - 1], row[L], row[L + 1]);
+    const double dm_m = __shfl_up_sync(FULL, dm, 1), dm_p = __shfl_down_sync(FULL, dm, 1);
+    const double q = row[L];
+    double bl = 0.0, br = 0.0;
+    if (L >= 2 && L <= 29) {
+      const bool special = (W && i >= is - 1 && i <= is + 1) || (E && i >= ie - 1 && i <= ie + 1);
+      if (special) {
+        ppm_blbr8(Q, D, i, is, ie, W, E, 0, bl, br);
+      } else {
+        const double al_lo = 0.5 * (row[L - 1] + q) + 1.0 / 3.0 * (dm_m - dm);
+        const double al_hi = 0.5 * (q + row[L + 1]) + 1.0 / 3.0 * (dm - dm_p);
+        const double xt = 2.0 * dm;
+        bl = -1.0 * fv_sign(fv_min(fabs(xt), fabs(al_lo - q)), xt);
+        br = fv_sign(fv_min(fabs(xt), fabs(al_hi - q)), xt);
+      }
+    }
+    const double blm = __shfl_up_sync(FULL, bl, 1), brm = __shfl_up_sync(FULL, br, 1);
+    const double qm = row[L > 0 ? L - 1 : 0];
+    return cells_flux<8>(c, qm, blm, brm, false, q, bl, br, false);
+  }
+}
+
+template <int OIN, int OOUT>
+__global__ void __launch_bounds__(WPB * 32, 4) k_fvtp2d_march(Geo g, MarchArgs a) {
+  extern __shared__ double smem[];
+  const int L = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  // work item of this warp: (strip, row chunk, level, subdomain)
+  long long item = (long long)blockIdx.x * WPB + wid;
+  if (item >= a.items) return;  // whole warp; no CTA-wide barrier is used anywhere below
+  const int strip = (int)(item % a.nstrips);
+  item /= a.nstrips;
+  const int chunk = (int)(item % a.nchunks);
+  item /= a.nchunks;
+  const int k = (int)(item % a.nk), t = (int)(item / a.nk);
+
+  double* bufC = smem + wid * WARP_SMEM;  // q_i row
+  double* rings = bufC + PITCH;           // NSTREAM x NSLOT staged input rows
+
+  const int is = g.is, ie = g.ie, js = g.js, je = g.je, sj = g.sj;
+  const unsigned char ed = g.edge[t];
+  const bool W = ed & EDGE_W, E = ed & EDGE_E, S = ed & EDGE_S, N = ed & EDGE_N;
+  const EdgeInfo e{is, ie, js, je, W, E, S, N};
+  const int i0 = is + strip * SW;                     // first cell / interface this strip writes
+  const int i = i0 - 3 + L;                           // my column
+  const int i_out_hi = min(i0 + SW - 1, ie);          // last cell this strip writes
+  const bool col_ok = i <= ie + 3;                    // column exists (halo included)
+  const bool cell_out = i >= i0 && i <= i_out_hi;     // fy, q_j owner
+  const bool xface_out = i >= i0 && (i <= i_out_hi || (i == ie + 1 && i_out_hi == ie));  // fx owner
+  const int j_lo = js + chunk * a.rows, j_hi = min(j_lo + a.rows - 1, je);
+  const bool last_chunk = j_hi == je;
+
+  const long long base3 = (long long)t * g.st3 + (long long)k * g.sk;
+  const double *q = a.q + base3, *crx = a.crx + base3, *cry = a.cry + base3, *xfx = a.xfx + base3,
+               *yfx = a.yfx + base3, *xunit = a.xunit + base3, *yunit = a.yunit + base3;
+  double *fx = a.fx + base3, *fy = a.fy + base3;
+  const int base2 = t * g.sk;
+  const double *area = a.area + base2, *dxa = a.dxa + base2, *dya = a.dya + base2;
+
+  constexpr int MI = OIN < 8 ? OIN : 8, MO = OOUT < 8 ? OOUT : 8;
+  March<MI> mi;  // inner y sweep on q
+  March<MO> mo;  // outer y sweep on q_j
+#pragma unroll
+  for (int n = 0; n < 5; ++n) mi.w[n] = mo.w[n] = 0.0;
+  mi.al_lo = mo.al_lo = mi.dm_m = mi.dm_0 = mo.dm_m = mo.dm_0 = 0.0;
+  mi.pq = mi.pbl = mi.pbr = mo.pq = mo.pbl = mo.pbr = 0.0;
+  mi.ps = mo.ps = false;
+  double fxq0 = 0.0, fxq1 = 0.0, fxq2 = 0.0, fxq3 = 0.0;  // inner x flux of rows R, R-1, R-2, R-3
+  double fyin_prev = 0.0;                                 // inner y flux at interface R-3
+  double yfx_prev = 0.0;                                  // yfx(i, R-3)
+
+  // Asynchronous staging: every input row is copied global -> shared two steps ahead of its use (cp.async, no
+  // registers held), in a ring of NSLOT slots per stream.  Streams and the row they carry at step R:
+  //   0 q(R)  1 crx(R)  2 xfx(R)  3 area(R)  4 cry(R-2)  5 yunit(R-2)  6 yfx(R-2)  7 area(R-3)  8 crx(R-3)  9 xunit(R-3)
+  auto ring = [&](int stream, int slot) { return rings + (stream * NSLOT + slot) * PITCH; };
+  auto issue = [&](int sn) {
+    const int Rn = j_lo - 3 + sn;
+    if (col_ok && Rn <= j_hi + 3) {
+      const int slot = sn % NSLOT;
+      const int on = Rn * sj + i;
+      cp_async8(ring(0, slot) + L, q + on);
+      cp_async8(ring(1, slot) + L, crx + on);
+      cp_async8(ring(2, slot) + L, xfx + on);
+      cp_async8(ring(3, slot) + L, area + on);
+      if (Rn >= 2) {
+        const int o2 = on - 2 * sj;
+        cp_async8(ring(4, slot) + L, cry + o2);
+        cp_async8(ring(5, slot) + L, yunit + o2);
+        cp_async8(ring(6, slot) + L, yfx + o2);
+      }
+      if (Rn >= 3) {
+        const int o3 = on - 3 * sj;
+        cp_async8(ring(7, slot) + L, area + o3);
+        cp_async8(ring(8, slot) + L, crx + o3);
+        cp_async8(ring(9, slot) + L, xunit + o3);
+      }
+    }
+    asm volatile("cp.async.commit_group;\n" ::: "memory");
+  };
+  issue(0);
+  issue(1);
+
+  for (int R = j_lo - 3, s = 0; R <= j_hi + 3; ++R, ++s) {
+    const int o = R * sj + i;
+    const int slot = s % NSLOT;
+    asm volatile("cp.async.wait_group 1;\n" ::: "memory");
+    __syncwarp();  // row R has landed for every lane; every lane is done with the slot refilled next
+    issue(s + 2);
+    double* qrow = ring(0, slot);
+    // 1. row R of q; the corner blocks differ between the x and the y view
+    double qx = 0.0, qy = 0.0;
+    if (col_ok) qx = qy = qrow[L];
+    if ((S && R < js) || (N && R > je)) {  // row-uniform
+      if (col_ok && ((W && i < is) || (E && i > ie))) {
+        int xi = i, xj = R, yi = i, yj = R;
+        copyx_src(e, xi, xj);
+        copyy_src(e, yi, yj);
+        qx = q[xj * sj + xi];
+        qy = q[yj * sj + yi];
+        qrow[L] = qx;
+      }
+      __syncwarp();
+    }
+    // 2. inner x flux and q_j on row R
+    double fxin;
+    {
+      auto D = [&](int d) { return dxa[o + d]; };
+      fxin = xsweep_flux<MI>(qrow, L, i, ring(1, slot)[L], D, is, ie, W, E);
+    }
+    const double fxin_p = __shfl_down_sync(FULL, fxin, 1);
+    double qj = 0.0;
+    if (cell_out) {
+      const double xf0 = ring(2, slot)[L], xf1 = ring(2, slot)[L + 1], ar = ring(3, slot)[L];
+      const double fx10 = xf0 * fxin, fx11 = xf1 * fxin_p;
+      const double area_with_x_flux = ar + xf0 - xf1;
+      qj = (qx * ar + fx10 - fx11) / area_with_x_flux;
+    }
+    fxq3 = fxq2; fxq2 = fxq1; fxq1 = fxq0; fxq0 = fxin;
+    // 3. y sweeps: cell jc = R-2 is complete
+    mi.push(qy);
+    mo.push(qj);
+    double qi = 0.0;
+    if (s >= 4) {
+      const int jc = R - 2, oc = o - 2 * sj;
+      const bool first = s == 4;
+      const bool near = (S && jc <= js + 1) || (N && jc >= je - 1);
+      auto D = [&](int d) { return dya[oc + d * sj]; };
+      double bli = 0.0, bri = 0.0, blo = 0.0, bro = 0.0;
+      bool si = false, so = false;
+      if (col_ok) march_cell<MI>(mi, jc, first, near, D, js, je, S, N, bli, bri, si);
+      if (cell_out) march_cell<MO>(mo, jc, first, near, D, js, je, S, N, blo, bro, so);
+      if (s >= 5) {  // interface jc, between cells jc-1 and jc
+        double fyin = 0.0;
+        if (col_ok) {
+          const double cy = ring(4, slot)[L];
+          fyin = cells_flux<MI>(cy, mi.pq, mi.pbl, mi.pbr, mi.ps, mi.w[2], bli, bri, si);
+          if (cell_out && (jc <= j_hi || last_chunk)) {
+            const double outer = cells_flux<MO>(cy, mo.pq, mo.pbl, mo.pbr, mo.ps, mo.w[2], blo, bro, so);
+            fy[oc] = 0.5 * (outer + fyin) * ring(5, slot)[L];
+          }
+          const double yf1 = ring(6, slot)[L];
+          if (s >= 6) {  // q_i on row R-3
+            const double yf0 = yfx_prev, ar = ring(7, slot)[L];
+            const double fyy0 = yf0 * fyin_prev, fyy1 = yf1 * fyin;
+            qi = (mi.w[1] * ar + fyy0 - fyy1) / (ar + yf0 - yf1);
+          }
+          yfx_prev = yf1;
+        }
+        fyin_prev = fyin;
+      }
+      mi.pq = mi.w[2]; mi.pbl = bli; mi.pbr = bri; mi.ps = si;
+      mo.pq = mo.w[2]; mo.pbl = blo; mo.pbr = bro; mo.ps = so;
+    }
+    // 4. outer x flux on row R-3
+    if (s >= 6) {
+      bufC[L] = qi;
+      __syncwarp();
+      const int orow = o - 3 * sj;
+      auto D = [&](int d) { return dxa[orow + d]; };
+      const double outer = xsweep_flux<MO>(bufC, L, i, ring(8, slot)[L], D, is, ie, W, E);
+      if (xface_out) fx[orow] = 0.5 * (outer + fxq3) * ring(9, slot)[L];
+      __syncwarp();  // bufC is rewritten in the next step
+    }
+  }
+  asm volatile("cp.async.wait_group 0;\n" ::: "memory");
+}
+
+template <int OIN, int OOUT>
+void launch(int blocks, size_t smem, cudaStream_t st, const Geo& g, const MarchArgs& f) {
+  static bool attr_set = false;  // opt in to > 48 KB of dynamic shared memory once per instantiation
+  if (!attr_set) {
+    cudaFuncSetAttribute(k_fvtp2d_march<OIN, OOUT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    attr_set = true;
+  }
+  k_fvtp2d_march<OIN, OOUT><<<blocks, WPB * 32, smem, st>>>(g, f);
+}
+}  // namespace
+
+int fvtp2d_march_launch(Core& c, const Fvtp2dArgs& a) {
+  const Geo g = c.g;
+  MarchArgs f;
+  f.q = a.q; f.crx = a.crx; f.cry = a.cry; f.xfx = a.xfx; f.yfx = a.yfx;
+  f.xunit = a.x_mass_flux ? a.x_mass_flux : a.xfx;
+  f.yunit = a.y_mass_flux ? a.y_mass_flux : a.yfx;
+  f.area = c.F("grid.area"); f.dxa = c.F("grid.dxa"); f.dya = c.F("grid.dya");
+  f.fx = a.fx; f.fy = a.fy;
+  f.nk = a.nk;
+  if (!c.err.empty()) return 1;
+  const int oo = a.hord < 0 ? -a.hord : a.hord;
+  const int oi = oo == 10 ? 8 : oo;
+  static const int rows_env = [] { const char* v = getenv("PACE_B200_FVTP2D_ROWS"); return v ? atoi(v) : 0; }();
+  f.rows = rows_env > 0 ? rows_env : 32;
+  if (f.rows > g.ny) f.rows = g.ny;
+  f.nstrips = (g.nx + SW - 1) / SW;
+  f.nchunks = (g.ny + f.rows - 1) / f.rows;
+  f.items = (long long)f.nstrips * f.nchunks * a.nk * g.nt;
+  const int blocks = (int)((f.items + WPB - 1) / WPB);
+  const size_t smem = (size_t)WPB * WARP_SMEM * sizeof(double);
+  LaunchScope scope(c.stream, "fvtp2d_march");
+  if (oi == 5 && oo == 5) launch<5, 5>(blocks, smem, c.stream, g, f);
+  else if (oi == 6 && oo == 6) launch<6, 6>(blocks, smem, c.stream, g, f);
+  else if (oi == 7 && oo == 7) launch<7, 7>(blocks, smem, c.stream, g, f);
+  else if (oi == 8 && oo == 8) launch<8, 8>(blocks, smem, c.stream, g, f);
+  else if (oi == 8 && oo == 10) launch<8, 10>(blocks, smem, c.stream, g, f);
+  else return -1;  // not instantiated: the caller falls back to the tiled kernel
+  return 0;
+}
+
+#else  // host emulation keeps the straightforward three-kernel version (transport.cu)
+int fvtp2d_march_launch(Core&, const Fvtp2dArgs&) { return -1; }
+#endif
+
+}  // namespace pace

@@ -19,6 +19,7 @@
 namespace pace {
 
 int fvtp2d_fused_launch(Core& c, const Fvtp2dArgs& a);
+int fvtp2d_march_launch(Core& c, const Fvtp2dArgs& a);
 
 // ---- materialised copy_corners ---------------------------------------------------------------------
 __device__ __forceinline__ void copy_corner_cell(const Geo& g, double* q, bool ydir, int t, int k, int c, int a, int b) {
@@ -63,8 +64,6 @@ int fvtp2d(Core& c, const Fvtp2dArgs& a) {
   const Geo g = c.g;
   cudaStream_t st = c.stream;
   const double *area = c.F("grid.area"), *dxa = c.F("grid.dxa"), *dya = c.F("grid.dya");
-  double *fy_in = c.S("tp.q_y_advected_mean"), *fx_in = c.S("tp.q_x_advected_mean"), *q_i = c.S("tp.q_advected_y"),
-         *q_j = c.S("tp.q_advected_x");
   if (!c.err.empty()) return 1;
   double* q = a.q;
   const double *crx = a.crx, *cry = a.cry, *xfx = a.xfx, *yfx = a.yfx;
@@ -78,11 +77,18 @@ int fvtp2d(Core& c, const Fvtp2dArgs& a) {
   copy_corners(c, q, false, nk);
 
 #ifndef PACE_HOST_EMU
-  // production path: one fused shared-memory kernel (fvtp2d_fused.cu); PACE_B200_FVTP2D=unfused selects the
-  // three-kernel version below (same arithmetic) for A/B measurements
-  static const bool unfused = [] { const char* v = getenv("PACE_B200_FVTP2D"); return v && std::string(v) == "unfused"; }();
+  // production path: one row-marching kernel (fvtp2d_march.cu).  PACE_B200_FVTP2D=tile selects the CTA-tiled fused
+  // kernel (fvtp2d_fused.cu), =unfused the three-kernel version below (same arithmetic) for A/B measurements
+  static const int mode = [] {
+    const char* v = getenv("PACE_B200_FVTP2D");
+    std::string m = v ? v : "";
+    return m == "unfused" ? 2 : (m == "tile" || m == "fused") ? 1 : 0;
+  }();
+  const bool unfused = mode == 2;
   if (!unfused) {
-    if (fvtp2d_fused_launch(c, a)) return 1;
+    int rc = mode == 0 ? fvtp2d_march_launch(c, a) : -1;
+    if (rc < 0) rc = fvtp2d_fused_launch(c, a);
+    if (rc) return 1;
     if (a.nord_col) {
       DelnArgs d;
       d.q = q; d.fx = fx; d.fy = fy; d.mass = a.mass; d.nord_col = a.nord_col; d.damp = a.damp; d.nk = nk;
@@ -92,6 +98,9 @@ int fvtp2d(Core& c, const Fvtp2dArgs& a) {
     return 0;
   }
 #endif
+  double *fy_in = c.S("tp.q_y_advected_mean"), *fx_in = c.S("tp.q_x_advected_mean"), *q_i = c.S("tp.q_advected_y"),
+         *q_j = c.S("tp.q_advected_x");
+  if (!c.err.empty()) return 1;
 
   // K1: inner sweeps.  q_y_advected_mean on [is-3..ie+3]x[js..je+1] (y-PPM of y-copied q, courant cry),
   //                    q_x_advected_mean on [is..ie+1]x[js-3..je+3] (x-PPM of x-copied q, courant crx)

@@ -1,6 +1,7 @@
-"""The shared-memory fused fvtp2d kernel (pace_b200/csrc/fvtp2d_fused.cu) against the straightforward three-kernel
-version (transport.cu, the one validated stencil by stencil against the reference) on a domain that spans several
-CTA tiles in both directions: one full dycore step at C48 (6 subdomains of 48x48x79), bit for bit."""
+"""The fused fvtp2d kernels — row-marching (pace_b200/csrc/fvtp2d_march.cu, the production path) and CTA-tiled
+(fvtp2d_fused.cu) — against the straightforward three-kernel version (transport.cu, the one validated stencil by
+stencil against the reference) on a domain that spans several CTA tiles / row chunks / column strips: one full dycore
+step at C48 (6 subdomains of 48x48x79), bit for bit."""
 import os
 import subprocess
 import sys
@@ -26,12 +27,19 @@ np.savez(sys.argv[1], **out)
 @pytest.mark.gpu
 def test_fused_matches_three_kernel_version(tmp_path):
     res = {}
-    for mode in ("fused", "unfused"):
-        env = dict(os.environ, PACE_B200_FVTP2D=mode)
+    modes = {"march": {"PACE_B200_FVTP2D": "march"},
+             "march_chunks_strips": {"PACE_B200_FVTP2D": "march", "PACE_B200_FVTP2D_ROWS": "16",
+                                     "PACE_B200_FVTP2D_WIDTH": "20"},
+             "tile": {"PACE_B200_FVTP2D": "tile"}, "unfused": {"PACE_B200_FVTP2D": "unfused"}}
+    for mode, extra in modes.items():
+        env = dict(os.environ, **extra)
         path = str(tmp_path / (mode + ".npz"))
         subprocess.run([sys.executable, "-c", SCRIPT % ROOT, path], check=True, env=env, timeout=600)
         res[mode] = np.load(path)
-    for name in res["fused"].files:
-        a, b = res["fused"][name], res["unfused"][name]
-        assert np.all(np.isfinite(a)), name
-        assert np.array_equal(a, b), "%s differs: max |d| = %g" % (name, np.max(np.abs(a - b)))
+    for mode in modes:
+        if mode == "unfused":
+            continue
+        for name in res[mode].files:
+            a, b = res[mode][name], res["unfused"][name]
+            assert np.all(np.isfinite(a)), (mode, name)
+            assert np.array_equal(a, b), "%s: %s differs: max |d| = %g" % (mode, name, np.max(np.abs(a - b)))
