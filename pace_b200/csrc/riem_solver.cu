@@ -106,8 +106,22 @@ static Sim1Work sim1_work(Core& c) {
   return s;
 }
 
+int riem_solver_c_onchip(Core& c, double dt2);             // riem_solver_onchip.cu
+int riem_solver3_onchip(Core& c, double dt, int last_call);
+
+// PACE_B200_RIEM=global selects the straightforward kernels of this file on the GPU too (A/B measurements)
+static bool riem_use_onchip() {
+#ifdef PACE_HOST_EMU
+  return false;
+#else
+  static const bool on = [] { const char* v = getenv("PACE_B200_RIEM"); return !(v && std::string(v) == "global"); }();
+  return on;
+#endif
+}
+
 // riem_solver_c.py:200-278.  in: delpc, cappa, w3(omga), ptc, q_con, gz, ws3, phis -> gz, pkc(pef)
 int riem_solver_c(Core& c, double dt2) {
+  if (riem_use_onchip()) return riem_solver_c_onchip(c, dt2);
   const Geo g = c.g;
   const int km = g.nz;
   const double* delpc = c.F("csw.delpc");
@@ -166,6 +180,7 @@ int riem_solver3(Core& c, double dt, int last_call) {
   const Geo g = c.g;
   const int km = g.nz;
   if (c.cfg.a_imp <= 0.999) { c.err = "a_imp <= 0.999 is not implemented"; return 1; }
+  if (riem_use_onchip()) return riem_solver3_onchip(c, dt, last_call);
   const double *delp = c.F("delp"), *cappa = c.F("ad.cappa"), *q_con = c.F("q_con"), *pt = c.F("pt"),
                *zs = c.F("ad.zs"), *ws = c.F("ad.wsd");
   double *pe = c.F("pe"), *zh = c.F("ad.zh"), *w = c.F("w"), *delz = c.F("delz"), *ppe = c.F("ad.pkc"),

@@ -1,0 +1,450 @@
+// riem_solver_c / riem_solver3 with the tridiagonal work arrays on chip.
+//
+// The straightforward column kernels (riem_solver.cu) keep ~20 per-level work arrays in global scratch: measured
+// 4.9 GB of DRAM traffic per riem_solver_c launch at C128 against 0.5 GB of compulsory traffic, 35 long-scoreboard
+// stall cycles per issued instruction (profiles/r01_columns_c128.txt).  Here a warp owns 32 adjacent columns (lane
+// <-> i, coalesced rows) and the two arrays that must survive between the k-sweeps live in shared memory,
+// X[k][lane] and Y[k][lane]:
+//   A  forward : pressures (pem, peg cumulative sums), pm, first guess pe, tridiagonal elimination   X=gam  Y=pp
+//   B  backward: back substitution, aa                                                               X=aa   Y=pp
+//   C  forward : w elimination                                                                        X=gam' S=w
+//   D  backward: w back substitution                                                                  S=w
+//   E  forward : pe cumulative sum                                                                    Y=pe
+//   F  backward: p1 recurrence, new dz, heights, output pressures
+// Everything else is recomputed from the inputs (identical expressions give identical bits) or carried in
+// registers; pem, pm and the intermediate w (S) are the only global work arrays (written once, read 1-2 times).
+// Statement order and expression trees per level are those of riem_solver.cu / the reference (sim1_solver.py:20-141,
+// riem_solver_c.py:21-123, riem_solver3.py:26-146), so results are bit-identical.
+#include "core.hpp"
+
+namespace pace {
+
+#ifndef PACE_HOST_EMU
+
+namespace {
+
+struct RiemArgs {
+  const double *delp, *cappa, *ptv, *q_con, *w_in, *zsurf, *ws;
+  double* zh;                       // heights: ad.gz (C) / ad.zh (D), read then rewritten
+  double *pem, *pm, *wtmp;          // global work arrays
+  double *pef;                      // ad.pkc
+  double *w_out, *delz, *pk3, *peln, *pk, *pe;  // D-grid solver only
+  double ptop, p_fac, dt, t1g, rdt, peln1, ptk;
+  int km, last_call, beta_neg;
+  Box b;
+};
+
+// D3 = false: riem_solver_c, true: riem_solver3
+template <bool D3>
+__global__ void __launch_bounds__(32) k_riem(Geo g, RiemArgs a) {
+  extern __shared__ double sm[];
+  const int lane = threadIdx.x;
+  const int km = a.km;
+  double* X = sm + lane;                 // X[k] -> X[k * 32]
+  double* Y = sm + (km + 1) * 32 + lane;
+#define XS(k) X[(k) * 32]
+#define YS(k) Y[(k) * 32]
+  // columns of the box are numbered row by row and dealt to lanes in that order (no idle lanes at row ends)
+  const int col = blockIdx.x * 32 + lane;
+  if (col >= a.b.ni * a.b.nj) return;  // no barrier is used anywhere below
+  const int i = a.b.i0 + col % a.b.ni, j = a.b.j0 + col / a.b.ni, t = blockIdx.y;
+  const long long o0 = (long long)t * g.st3 + j * g.sj + i;  // level 0
+  const int o2 = t * g.sk + j * g.sj + i;
+  const long long sk = g.sk;
+#define G(f, k) (f)[o0 + (long long)(k) * sk]
+  // all arrays are distinct (w_in == w_out in the D-grid solver: neither is restrict-qualified), so loads of the
+  // following levels may be hoisted above the stores of the current one
+  const double* __restrict__ delp = a.delp;
+  const double* __restrict__ cappa = a.cappa;
+  const double* __restrict__ ptv = a.ptv;
+  const double* __restrict__ q_con = a.q_con;
+  const double* w_in = a.w_in;
+  double* w_out = a.w_out;
+  double* __restrict__ zh = a.zh;
+  double* __restrict__ pem = a.pem;
+  double* __restrict__ pm = a.pm;
+  double* __restrict__ wtmp = a.wtmp;
+  double* __restrict__ pef = a.pef;
+  double* __restrict__ delz = a.delz;
+  double* __restrict__ pk3 = a.pk3;
+  double* __restrict__ peln = a.peln;
+  double* __restrict__ pk = a.pk;
+  double* __restrict__ pe = a.pe;
+  constexpr double RGRAV = 1.0 / GRAV;
+  auto DM = [&](int k) { return D3 ? G(delp, k) * RGRAV : G(delp, k) / GRAV; };
+  auto GM = [&](int k) { return 1.0 / (1.0 - G(cappa, k)); };
+  const double ptop = a.ptop, dt = a.dt, t1g = a.t1g, rdt = a.rdt, p_fac = a.p_fac;
+  const double ws = a.ws[o2];
+
+  // Every sweep walks the column in chunks of U levels: the global inputs of the next chunk are requested before the
+  // current chunk is computed, so that ~5 x U loads per warp are in flight behind the (latency-bound) recurrences.
+#ifndef PACE_RIEM_U
+#define PACE_RIEM_U 4
+#endif
+  constexpr int U = PACE_RIEM_U;
+  // ---- A: forward ---------------------------------------------------------------------------------------------
+  {
+    double pem_k = ptop, peg_k = ptop, logpg_k = a.peln1;
+    G(pem, 0) = ptop;
+    if (D3) {
+      G(pk3, 0) = a.ptk;
+      if (a.last_call) { G(peln, 0) = a.peln1; G(pk, 0) = a.ptk; G(pe, 0) = ptop; }
+    }
+    double zh_k = G(zh, 0);
+    double dm_j = 0.0, pe0_j = 0.0;            // level k-1
+    double bet_prev = 0.0, grat_prev = 0.0, pp_prev = 0.0;
+    double n_delp[U], n_q[U], n_cap[U], n_zh[U], n_ptv[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int kk = min(u, km - 1);
+      n_delp[u] = G(delp, kk); n_q[u] = G(q_con, kk); n_cap[u] = G(cappa, kk); n_zh[u] = G(zh, kk + 1);
+      n_ptv[u] = G(ptv, kk);
+    }
+    for (int k0 = 0; k0 < km; k0 += U) {
+      double c_delp[U], c_q[U], c_cap[U], c_zh[U], c_ptv[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        c_delp[u] = n_delp[u]; c_q[u] = n_q[u]; c_cap[u] = n_cap[u]; c_zh[u] = n_zh[u]; c_ptv[u] = n_ptv[u];
+      }
+      if (k0 + U < km) {
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const int kk = min(k0 + U + u, km - 1);
+          n_delp[u] = G(delp, kk); n_q[u] = G(q_con, kk); n_cap[u] = G(cappa, kk); n_zh[u] = G(zh, kk + 1);
+          n_ptv[u] = G(ptv, kk);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int k = k0 + u;
+        if (k < km) {
+          const double delp_k = c_delp[u];
+          const double pem_n = pem_k + delp_k;
+          const double peg_n = peg_k + delp_k * (1.0 - c_q[u]);
+          double pm_k;
+          if (D3) {
+            const double lp = fv_log(pem_n);
+            const double logpg_n = fv_log(peg_n);
+            const double pk3_n = fv_exp(KAPPA * lp);
+            G(pk3, k + 1) = pk3_n;
+            if (a.last_call) { G(peln, k + 1) = lp; G(pk, k + 1) = pk3_n; G(pe, k + 1) = pem_n; }
+            pm_k = (peg_n - peg_k) / (logpg_n - logpg_k);
+            logpg_k = logpg_n;
+          } else {
+            pm_k = (peg_n - peg_k) / fv_log(peg_n / peg_k);
+          }
+          G(pem, k + 1) = pem_n;
+          G(pm, k) = pm_k;
+          pem_k = pem_n;
+          peg_k = peg_n;
+          const double dm_k = D3 ? delp_k * RGRAV : delp_k / GRAV;
+          const double gm_k = 1.0 / (1.0 - c_cap[u]);
+          const double zh_n = c_zh[u];
+          const double dz_k = zh_n - zh_k;
+          zh_k = zh_n;
+          const double pe0_k = fv_exp(gm_k * fv_log(((-dm_k) / dz_k * RDGAS) * c_ptv[u])) - pm_k;
+          if (k >= 1) {  // elimination step of level j = k-1
+            const int jl = k - 1;
+            const double gr = dm_j / dm_k;
+            const double bb = 2.0 * (1.0 + gr);
+            const double dd = 3.0 * (pe0_j + gr * pe0_k);
+            if (jl == 0) {
+              YS(0) = 0.0;
+              pp_prev = dd / bb;
+              YS(1) = pp_prev;
+              bet_prev = bb;
+            } else {
+              const double gam = grat_prev / bet_prev;
+              const double bet = bb - gam;
+              XS(jl) = gam;
+              pp_prev = (dd - pp_prev) / bet;
+              YS(jl + 1) = pp_prev;
+              bet_prev = bet;
+            }
+            grat_prev = gr;
+          }
+          dm_j = dm_k;
+          pe0_j = pe0_k;
+        }
+      }
+    }
+    {  // level j = km-1: bb = 2, dd = 3 pe
+      const int jl = km - 1;
+      const double bb = 2.0;
+      const double dd = 3.0 * pe0_j;
+      const double gam = grat_prev / bet_prev;
+      const double bet = bb - gam;
+      XS(jl) = gam;
+      YS(jl + 1) = (dd - pp_prev) / bet;
+    }
+  }
+  // ---- B: backward, pp and aa (k = km-1 .. 1) -----------------------------------------------------------------
+  {
+    double pp_next = YS(km);
+    double zh_k = G(zh, km - 1);
+    double dz_k = G(zh, km) - zh_k;      // dz(km-1)
+    double gm_k = GM(km - 1);
+    double n_zh[U], n_cap[U], n_pem[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int kk = max(km - 1 - u, 1);
+      n_zh[u] = G(zh, kk - 1); n_cap[u] = G(cappa, kk - 1); n_pem[u] = G(pem, kk);
+    }
+    for (int k0 = km - 1; k0 >= 1; k0 -= U) {
+      double c_zh[U], c_cap[U], c_pem[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) { c_zh[u] = n_zh[u]; c_cap[u] = n_cap[u]; c_pem[u] = n_pem[u]; }
+      if (k0 - U >= 1) {
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const int kk = max(k0 - U - u, 1);
+          n_zh[u] = G(zh, kk - 1); n_cap[u] = G(cappa, kk - 1); n_pem[u] = G(pem, kk);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int k = k0 - u;
+        if (k >= 1) {
+          const double ppk = YS(k) - XS(k) * pp_next;
+          YS(k) = ppk;
+          const double zh_m = c_zh[u];
+          const double dz_m = zh_k - zh_m;  // dz(k-1)
+          const double gm_m = 1.0 / (1.0 - c_cap[u]);
+          XS(k) = t1g * 0.5 * (gm_m + gm_k) / (dz_m + dz_k) * (c_pem[u] + ppk);
+          pp_next = ppk;
+          zh_k = zh_m; dz_k = dz_m; gm_k = gm_m;
+        }
+      }
+    }
+  }
+  // ---- C: forward, w elimination ------------------------------------------------------------------------------
+  {
+    const double dm0 = DM(0);
+    double betk = dm0 - XS(1);
+    double wprev = (dm0 * G(w_in, 0) + dt * YS(1)) / betk;
+    G(wtmp, 0) = wprev;
+    double pp_k = YS(1);
+    double n_delp[U], n_w[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int kk = min(1 + u, km - 1);
+      n_delp[u] = G(delp, kk); n_w[u] = G(w_in, kk);
+    }
+    for (int k0 = 1; k0 < km - 1; k0 += U) {
+      double c_delp[U], c_w[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) { c_delp[u] = n_delp[u]; c_w[u] = n_w[u]; }
+      if (k0 + U < km - 1) {
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const int kk = min(k0 + U + u, km - 1);
+          n_delp[u] = G(delp, kk); n_w[u] = G(w_in, kk);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int k = k0 + u;
+        if (k < km - 1) {
+          const double aak = XS(k);
+          const double gm = aak / betk;
+          XS(k) = gm;
+          const double dm_k = D3 ? c_delp[u] * RGRAV : c_delp[u] / GRAV;
+          betk = dm_k - (aak + XS(k + 1) + aak * gm);
+          const double pp_n = YS(k + 1);
+          wprev = (dm_k * c_w[u] + dt * (pp_n - pp_k) - aak * wprev) / betk;
+          G(wtmp, k) = wprev;
+          pp_k = pp_n;
+        }
+      }
+    }
+    {
+      const int k = km - 1;
+      const double aak = XS(k);
+      const double dz_k = G(zh, k + 1) - G(zh, k);
+      const double pp_n = YS(k + 1);
+      const double p1 = t1g * GM(k) / dz_k * (G(pem, k + 1) + pp_n);
+      const double gm = aak / betk;
+      XS(k) = gm;
+      const double dm_k = DM(k);
+      betk = dm_k - (aak + p1 + aak * gm);
+      wprev = (dm_k * G(w_in, k) + dt * (pp_n - pp_k) - p1 * ws - aak * wprev) / betk;
+      G(wtmp, k) = wprev;
+    }
+  }
+  // ---- D: backward, w back substitution; the corrected w goes to shared memory (Y is free until E) ------------
+  {
+    double wn = G(wtmp, km - 1);
+    double n_w[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) n_w[u] = G(wtmp, max(km - 2 - u, 0));
+    for (int k0 = km - 2; k0 >= 0; k0 -= U) {
+      double c_w[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) c_w[u] = n_w[u];
+      if (k0 - U >= 0) {
+#pragma unroll
+        for (int u = 0; u < U; ++u) n_w[u] = G(wtmp, max(k0 - U - u, 0));
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int k = k0 - u;
+        if (k >= 0) {
+          wn = c_w[u] - XS(k + 1) * wn;
+          G(wtmp, k) = wn;
+        }
+      }
+    }
+  }
+  // ---- E: forward, pe; the D-grid solver publishes w here (its old value is needed up to this point) ---------
+  {
+    double pe_k = 0.0;
+    YS(0) = 0.0;
+    double n_w[U], n_delp[U], n_w1[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int kk = min(u, km - 1);
+      n_w[u] = G(wtmp, kk); n_delp[u] = G(delp, kk); n_w1[u] = G(w_in, kk);
+    }
+    for (int k0 = 1; k0 <= km; k0 += U) {
+      double c_w[U], c_delp[U], c_w1[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) { c_w[u] = n_w[u]; c_delp[u] = n_delp[u]; c_w1[u] = n_w1[u]; }
+      if (k0 + U <= km) {
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const int kk = min(k0 + U + u - 1, km - 1);
+          n_w[u] = G(wtmp, kk); n_delp[u] = G(delp, kk); n_w1[u] = G(w_in, kk);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int k = k0 + u;
+        if (k <= km) {
+          const double wk = c_w[u];
+          const double dm_m = D3 ? c_delp[u] * RGRAV : c_delp[u] / GRAV;
+          pe_k = pe_k + dm_m * (wk - c_w1[u]) * rdt;
+          YS(k) = pe_k;
+          if (D3) G(w_out, k - 1) = wk;
+        }
+      }
+    }
+  }
+  // ---- F: backward, p1, new dz, heights, output pressures ----------------------------------------------------
+  {
+    double zcur = a.zsurf[o2];
+    G(zh, km) = zcur;
+    double p1_next = 0.0;
+    double dm_n = 0.0;  // dm(k+1)
+    double n_delp[U], n_pm[U], n_ptv[U], n_cap[U], n_pem[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int kk = max(km - 1 - u, 0);
+      n_delp[u] = G(delp, kk); n_pm[u] = G(pm, kk); n_ptv[u] = G(ptv, kk); n_cap[u] = G(cappa, kk);
+      n_pem[u] = G(pem, kk + 1);
+    }
+    for (int k0 = km - 1; k0 >= 0; k0 -= U) {
+      double c_delp[U], c_pm[U], c_ptv[U], c_cap[U], c_pem[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        c_delp[u] = n_delp[u]; c_pm[u] = n_pm[u]; c_ptv[u] = n_ptv[u]; c_cap[u] = n_cap[u]; c_pem[u] = n_pem[u];
+      }
+      if (k0 - U >= 0) {
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const int kk = max(k0 - U - u, 0);
+          n_delp[u] = G(delp, kk); n_pm[u] = G(pm, kk); n_ptv[u] = G(ptv, kk); n_cap[u] = G(cappa, kk);
+          n_pem[u] = G(pem, kk + 1);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int k = k0 - u;
+        if (k >= 0) {
+          const double dm_k = D3 ? c_delp[u] * RGRAV : c_delp[u] / GRAV;
+          double p1;
+          if (k == km - 1) {
+            p1 = (YS(k) + 2.0 * YS(k + 1)) * 1.0 / 3.0;
+          } else {
+            const double gr = dm_k / dm_n;
+            const double bb = 2.0 * (1.0 + gr);
+            p1 = (YS(k) + bb * YS(k + 1) + gr * YS(k + 2)) * 1.0 / 3.0 - gr * p1_next;
+          }
+          const double pm_k = c_pm[u];
+          const double aa = p1 + pm_k;
+          const double maxp = (p_fac * dm_k > aa) ? p_fac * pm_k : aa;
+          const double dzn = (-dm_k) * RDGAS * c_ptv[u] * fv_exp((c_cap[u] - 1.0) * fv_log(maxp));
+          if (D3) {
+            G(delz, k) = dzn;
+            zcur = zcur - dzn;
+            G(pef, k + 1) = a.beta_neg ? YS(k + 1) + c_pem[u] : YS(k + 1);
+          } else {
+            zcur = zcur - dzn * GRAV;
+            G(pef, k + 1) = YS(k + 1) + c_pem[u];
+          }
+          G(zh, k) = zcur;
+          p1_next = p1;
+          dm_n = dm_k;
+        }
+      }
+    }
+    if (D3) G(pef, 0) = a.beta_neg ? YS(0) + G(pem, 0) : YS(0);
+    else G(pef, 0) = ptop;
+  }
+#undef G
+#undef XS
+#undef YS
+}
+
+template <bool D3>
+int launch_riem(Core& c, RiemArgs& a, const char* label) {
+  const Geo g = c.g;
+  a.pem = c.S("sim1.pem"); a.pm = c.S("sim1.pm"); a.wtmp = c.S("sim1.w");
+  if (!c.err.empty()) return 1;
+  const size_t smem = 2 * (size_t)(a.km + 1) * 32 * sizeof(double);
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaFuncSetAttribute(k_riem<D3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
+    attr_set = true;
+  }
+  if (smem > 96 * 1024) { c.err = "riem_solver: too many levels for the on-chip kernel"; return 1; }
+  dim3 grd((a.b.ni * a.b.nj + 31) / 32, g.nt, 1);
+  LaunchScope scope(c.stream, label);
+  k_riem<D3><<<grd, 32, smem, c.stream>>>(g, a);
+  return 0;
+}
+
+}  // namespace
+
+int riem_solver_c_onchip(Core& c, double dt2) {
+  const Geo g = c.g;
+  RiemArgs a{};
+  a.delp = c.F("csw.delpc"); a.cappa = c.F("ad.cappa"); a.w_in = c.F("omga"); a.ptv = c.F("csw.ptc");
+  a.q_con = c.F("q_con"); a.zsurf = c.F("phis"); a.ws = c.F("ad.ws3"); a.zh = c.F("ad.gz"); a.pef = c.F("ad.pkc");
+  if (!c.err.empty()) return 1;
+  a.ptop = c.cfg.ptop; a.p_fac = c.cfg.p_fac; a.dt = dt2; a.t1g = 2.0 * dt2 * dt2; a.rdt = 1.0 / dt2;
+  a.peln1 = 0.0; a.ptk = 0.0; a.km = g.nz; a.last_call = 0; a.beta_neg = 0;
+  a.b = box_compute(g, -1, -1, 2, 2, 1);
+  return launch_riem<false>(c, a, "riem_solver_c");
+}
+
+int riem_solver3_onchip(Core& c, double dt, int last_call) {
+  const Geo g = c.g;
+  RiemArgs a{};
+  a.delp = c.F("delp"); a.cappa = c.F("ad.cappa"); a.q_con = c.F("q_con"); a.ptv = c.F("pt"); a.zsurf = c.F("ad.zs");
+  a.ws = c.F("ad.wsd"); a.pe = c.F("pe"); a.zh = c.F("ad.zh"); a.w_out = c.F("w"); a.w_in = a.w_out;
+  a.delz = c.F("delz"); a.pef = c.F("ad.pkc"); a.pk3 = c.F("ad.pk3"); a.pk = c.F("pk"); a.peln = c.F("peln");
+  if (!c.err.empty()) return 1;
+  a.ptop = c.cfg.ptop; a.p_fac = c.cfg.p_fac; a.dt = dt; a.t1g = 2.0 * dt * dt; a.rdt = 1.0 / dt;
+  a.peln1 = std::log(a.ptop);           // math.log(ptop)           (riem_solver3.py:287)
+  a.ptk = std::exp(KAPPA * a.peln1);    // math.exp(KAPPA * peln1)  (riem_solver3.py:288)
+  a.km = g.nz; a.last_call = last_call; a.beta_neg = c.cfg.beta < -0.1;
+  a.b = box_compute(g, 0, 0, 0, 0, 1);
+  return launch_riem<true>(c, a, "riem_solver3");
+}
+
+#else
+int riem_solver_c_onchip(Core&, double) { return -1; }
+int riem_solver3_onchip(Core&, double, int) { return -1; }
+#endif
+
+}  // namespace pace
