@@ -3,8 +3,9 @@
 // The straightforward column kernels (riem_solver.cu) keep ~20 per-level work arrays in global scratch: measured
 // 4.9 GB of DRAM traffic per riem_solver_c launch at C128 against 0.5 GB of compulsory traffic, 35 long-scoreboard
 // stall cycles per issued instruction (profiles/r01_columns_c128.txt).  Here a warp owns 32 adjacent columns (lane
-// <-> i, coalesced rows) and the two arrays that must survive between the k-sweeps live in shared memory,
-// X[k][lane] and Y[k][lane]:
+// <-> column, coalesced rows); of the two arrays that must survive between the k-sweeps, Y[k][lane] lives in shared
+// memory and X in one global work array that every sweep prefetches a chunk ahead (two shared arrays would cap the
+// SM at 5 warps; these sweeps are chains of dependent fp64 divisions / exp / log and need the occupancy):
 //   A  forward : pressures (pem, peg cumulative sums), pm, first guess pe, tridiagonal elimination   X=gam  Y=pp
 //   B  backward: back substitution, aa                                                               X=aa   Y=pp
 //   C  forward : w elimination                                                                        X=gam' S=w
@@ -12,7 +13,7 @@
 //   E  forward : pe cumulative sum                                                                    Y=pe
 //   F  backward: p1 recurrence, new dz, heights, output pressures
 // Everything else is recomputed from the inputs (identical expressions give identical bits) or carried in
-// registers; pem, pm and the intermediate w (S) are the only global work arrays (written once, read 1-2 times).
+// registers; pem, pm, X and the intermediate w (S) are the only global work arrays.
 // Statement order and expression trees per level are those of riem_solver.cu / the reference (sim1_solver.py:20-141,
 // riem_solver_c.py:21-123, riem_solver3.py:26-146), so results are bit-identical.
 #include "core.hpp"
@@ -26,7 +27,7 @@ namespace {
 struct RiemArgs {
   const double *delp, *cappa, *ptv, *q_con, *w_in, *zsurf, *ws;
   double* zh;                       // heights: ad.gz (C) / ad.zh (D), read then rewritten
-  double *pem, *pm, *wtmp;          // global work arrays
+  double *pem, *pm, *wtmp, *xwork;  // global work arrays
   double *pef;                      // ad.pkc
   double *w_out, *delz, *pk3, *peln, *pk, *pe;  // D-grid solver only
   double ptop, p_fac, dt, t1g, rdt, peln1, ptk;
@@ -40,9 +41,7 @@ __global__ void __launch_bounds__(32) k_riem(Geo g, RiemArgs a) {
   extern __shared__ double sm[];
   const int lane = threadIdx.x;
   const int km = a.km;
-  double* X = sm + lane;                 // X[k] -> X[k * 32]
-  double* Y = sm + (km + 1) * 32 + lane;
-#define XS(k) X[(k) * 32]
+  double* Y = sm + lane;                 // Y[k] -> Y[k * 32]
 #define YS(k) Y[(k) * 32]
   // columns of the box are numbered row by row and dealt to lanes in that order (no idle lanes at row ends)
   const int col = blockIdx.x * 32 + lane;
@@ -64,6 +63,7 @@ __global__ void __launch_bounds__(32) k_riem(Geo g, RiemArgs a) {
   double* __restrict__ pem = a.pem;
   double* __restrict__ pm = a.pm;
   double* __restrict__ wtmp = a.wtmp;
+  double* __restrict__ xg = a.xwork;
   double* __restrict__ pef = a.pef;
   double* __restrict__ delz = a.delz;
   double* __restrict__ pk3 = a.pk3;
@@ -156,7 +156,7 @@ __global__ void __launch_bounds__(32) k_riem(Geo g, RiemArgs a) {
             } else {
               const double gam = grat_prev / bet_prev;
               const double bet = bb - gam;
-              XS(jl) = gam;
+              G(xg, jl) = gam;
               pp_prev = (dd - pp_prev) / bet;
               YS(jl + 1) = pp_prev;
               bet_prev = bet;
@@ -174,7 +174,7 @@ __global__ void __launch_bounds__(32) k_riem(Geo g, RiemArgs a) {
       const double dd = 3.0 * pe0_j;
       const double gam = grat_prev / bet_prev;
       const double bet = bb - gam;
-      XS(jl) = gam;
+      G(xg, jl) = gam;
       YS(jl + 1) = (dd - pp_prev) / bet;
     }
   }
@@ -184,33 +184,33 @@ __global__ void __launch_bounds__(32) k_riem(Geo g, RiemArgs a) {
     double zh_k = G(zh, km - 1);
     double dz_k = G(zh, km) - zh_k;      // dz(km-1)
     double gm_k = GM(km - 1);
-    double n_zh[U], n_cap[U], n_pem[U];
+    double n_zh[U], n_cap[U], n_pem[U], n_x[U];
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       const int kk = max(km - 1 - u, 1);
-      n_zh[u] = G(zh, kk - 1); n_cap[u] = G(cappa, kk - 1); n_pem[u] = G(pem, kk);
+      n_zh[u] = G(zh, kk - 1); n_cap[u] = G(cappa, kk - 1); n_pem[u] = G(pem, kk); n_x[u] = G(xg, kk);
     }
     for (int k0 = km - 1; k0 >= 1; k0 -= U) {
-      double c_zh[U], c_cap[U], c_pem[U];
+      double c_zh[U], c_cap[U], c_pem[U], c_x[U];
 #pragma unroll
-      for (int u = 0; u < U; ++u) { c_zh[u] = n_zh[u]; c_cap[u] = n_cap[u]; c_pem[u] = n_pem[u]; }
+      for (int u = 0; u < U; ++u) { c_zh[u] = n_zh[u]; c_cap[u] = n_cap[u]; c_pem[u] = n_pem[u]; c_x[u] = n_x[u]; }
       if (k0 - U >= 1) {
 #pragma unroll
         for (int u = 0; u < U; ++u) {
           const int kk = max(k0 - U - u, 1);
-          n_zh[u] = G(zh, kk - 1); n_cap[u] = G(cappa, kk - 1); n_pem[u] = G(pem, kk);
+          n_zh[u] = G(zh, kk - 1); n_cap[u] = G(cappa, kk - 1); n_pem[u] = G(pem, kk); n_x[u] = G(xg, kk);
         }
       }
 #pragma unroll
       for (int u = 0; u < U; ++u) {
         const int k = k0 - u;
         if (k >= 1) {
-          const double ppk = YS(k) - XS(k) * pp_next;
+          const double ppk = YS(k) - c_x[u] * pp_next;
           YS(k) = ppk;
           const double zh_m = c_zh[u];
           const double dz_m = zh_k - zh_m;  // dz(k-1)
           const double gm_m = 1.0 / (1.0 - c_cap[u]);
-          XS(k) = t1g * 0.5 * (gm_m + gm_k) / (dz_m + dz_k) * (c_pem[u] + ppk);
+          G(xg, k) = t1g * 0.5 * (gm_m + gm_k) / (dz_m + dz_k) * (c_pem[u] + ppk);
           pp_next = ppk;
           zh_k = zh_m; dz_k = dz_m; gm_k = gm_m;
         }
@@ -220,36 +220,42 @@ __global__ void __launch_bounds__(32) k_riem(Geo g, RiemArgs a) {
   // ---- C: forward, w elimination ------------------------------------------------------------------------------
   {
     const double dm0 = DM(0);
-    double betk = dm0 - XS(1);
+    double betk = dm0 - G(xg, 1);
     double wprev = (dm0 * G(w_in, 0) + dt * YS(1)) / betk;
     G(wtmp, 0) = wprev;
     double pp_k = YS(1);
-    double n_delp[U], n_w[U];
+    double n_delp[U], n_w[U], n_x[U + 1];  // n_x: aa(k0 .. k0+U)
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       const int kk = min(1 + u, km - 1);
       n_delp[u] = G(delp, kk); n_w[u] = G(w_in, kk);
     }
+#pragma unroll
+    for (int u = 0; u <= U; ++u) n_x[u] = G(xg, min(1 + u, km - 1));
     for (int k0 = 1; k0 < km - 1; k0 += U) {
-      double c_delp[U], c_w[U];
+      double c_delp[U], c_w[U], c_x[U + 1];
 #pragma unroll
       for (int u = 0; u < U; ++u) { c_delp[u] = n_delp[u]; c_w[u] = n_w[u]; }
+#pragma unroll
+      for (int u = 0; u <= U; ++u) c_x[u] = n_x[u];
       if (k0 + U < km - 1) {
 #pragma unroll
         for (int u = 0; u < U; ++u) {
           const int kk = min(k0 + U + u, km - 1);
           n_delp[u] = G(delp, kk); n_w[u] = G(w_in, kk);
         }
+#pragma unroll
+        for (int u = 0; u <= U; ++u) n_x[u] = G(xg, min(k0 + U + u, km - 1));
       }
 #pragma unroll
       for (int u = 0; u < U; ++u) {
         const int k = k0 + u;
         if (k < km - 1) {
-          const double aak = XS(k);
+          const double aak = c_x[u];
           const double gm = aak / betk;
-          XS(k) = gm;
+          G(xg, k) = gm;
           const double dm_k = D3 ? c_delp[u] * RGRAV : c_delp[u] / GRAV;
-          betk = dm_k - (aak + XS(k + 1) + aak * gm);
+          betk = dm_k - (aak + c_x[u + 1] + aak * gm);
           const double pp_n = YS(k + 1);
           wprev = (dm_k * c_w[u] + dt * (pp_n - pp_k) - aak * wprev) / betk;
           G(wtmp, k) = wprev;
@@ -259,12 +265,12 @@ __global__ void __launch_bounds__(32) k_riem(Geo g, RiemArgs a) {
     }
     {
       const int k = km - 1;
-      const double aak = XS(k);
+      const double aak = G(xg, k);
       const double dz_k = G(zh, k + 1) - G(zh, k);
       const double pp_n = YS(k + 1);
       const double p1 = t1g * GM(k) / dz_k * (G(pem, k + 1) + pp_n);
       const double gm = aak / betk;
-      XS(k) = gm;
+      G(xg, k) = gm;
       const double dm_k = DM(k);
       betk = dm_k - (aak + p1 + aak * gm);
       wprev = (dm_k * G(w_in, k) + dt * (pp_n - pp_k) - p1 * ws - aak * wprev) / betk;
@@ -274,22 +280,22 @@ __global__ void __launch_bounds__(32) k_riem(Geo g, RiemArgs a) {
   // ---- D: backward, w back substitution; the corrected w goes to shared memory (Y is free until E) ------------
   {
     double wn = G(wtmp, km - 1);
-    double n_w[U];
+    double n_w[U], n_x[U];
 #pragma unroll
-    for (int u = 0; u < U; ++u) n_w[u] = G(wtmp, max(km - 2 - u, 0));
+    for (int u = 0; u < U; ++u) { n_w[u] = G(wtmp, max(km - 2 - u, 0)); n_x[u] = G(xg, max(km - 2 - u, 0) + 1); }
     for (int k0 = km - 2; k0 >= 0; k0 -= U) {
-      double c_w[U];
+      double c_w[U], c_x[U];
 #pragma unroll
-      for (int u = 0; u < U; ++u) c_w[u] = n_w[u];
+      for (int u = 0; u < U; ++u) { c_w[u] = n_w[u]; c_x[u] = n_x[u]; }
       if (k0 - U >= 0) {
 #pragma unroll
-        for (int u = 0; u < U; ++u) n_w[u] = G(wtmp, max(k0 - U - u, 0));
+        for (int u = 0; u < U; ++u) { n_w[u] = G(wtmp, max(k0 - U - u, 0)); n_x[u] = G(xg, max(k0 - U - u, 0) + 1); }
       }
 #pragma unroll
       for (int u = 0; u < U; ++u) {
         const int k = k0 - u;
         if (k >= 0) {
-          wn = c_w[u] - XS(k + 1) * wn;
+          wn = c_w[u] - c_x[u] * wn;
           G(wtmp, k) = wn;
         }
       }
@@ -391,16 +397,15 @@ __global__ void __launch_bounds__(32) k_riem(Geo g, RiemArgs a) {
     else G(pef, 0) = ptop;
   }
 #undef G
-#undef XS
 #undef YS
 }
 
 template <bool D3>
 int launch_riem(Core& c, RiemArgs& a, const char* label) {
   const Geo g = c.g;
-  a.pem = c.S("sim1.pem"); a.pm = c.S("sim1.pm"); a.wtmp = c.S("sim1.w");
+  a.pem = c.S("sim1.pem"); a.pm = c.S("sim1.pm"); a.wtmp = c.S("sim1.w"); a.xwork = c.S("sim1.x");
   if (!c.err.empty()) return 1;
-  const size_t smem = 2 * (size_t)(a.km + 1) * 32 * sizeof(double);
+  const size_t smem = (size_t)(a.km + 1) * 32 * sizeof(double);
   static bool attr_set = false;
   if (!attr_set) {
     cudaFuncSetAttribute(k_riem<D3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
