@@ -155,12 +155,22 @@ typedef struct pace_b200_halo_op {
   int aii, aij, bi, aji, ajj, bj;
 } pace_b200_halo_op;
 
-/* Upload a plan (list of ops between subdomains of this GPU) under plan_id in [0,16). */
+/* Upload a plan (list of ops between subdomains of this GPU) under plan_id in [0,64). */
 int pace_b200_halo_plan_set(void* handle, int plan_id, const void* ops, int n_ops);
 /* HaloUpdater.update() for up to 8 fields (or vector pairs when y_names != NULL) sharing one plan
  * (NDSL/ndsl/halo/updater.py:150-303), levels [0, nk). */
 int pace_b200_halo_update(void* handle, int plan_id, const char* const* x_names, const char* const* y_names,
                           int n, int nk);
+/* The two halves of HaloUpdater.start()/wait() for neighbours that live on another GPU (NDSL/ndsl/halo/updater.py:217-303
+ * pack + Isend / Irecv + unpack; data_transformer.py:404-560 with the rotation applied while packing).  A pack plan
+ * holds ops whose source subdomain is local and whose dst_t field is the op's cell offset in the message; an unpack
+ * plan holds ops whose destination is local and whose src_t field is that offset.  Message element of (op, field q,
+ * level k, cell c) = (offset * n + q * cells) * nk + k * cells + c, doubles; both sides list the ops in the same order.
+ * `message` is a device buffer the caller transfers (NCCL send/recv in pace_b200/distributed.py). */
+int pace_b200_halo_pack(void* handle, int plan_id, const char* const* x_names, const char* const* y_names, int n, int nk,
+                        void* message);
+int pace_b200_halo_unpack(void* handle, int plan_id, const char* const* x_names, const char* const* y_names, int n, int nk,
+                          const void* message);
 
 /* FiniteVolumeFluxPrep.__call__ (pyFV3/stencils/fxadv.py:590-691).
  * in: uc vc   out: ad.crx ad.cry ad.xfx ad.yfx dsw.uc_contra dsw.vc_contra */

@@ -89,6 +89,8 @@ def bind(lib):
     lib.pace_b200_set_column.argtypes = [vp, ctypes.c_char_p, ctypes.POINTER(ctypes.c_double), _I]
     lib.pace_b200_halo_plan_set.argtypes = [vp, _I, vp, _I]
     lib.pace_b200_halo_update.argtypes = [vp, _I, ctypes.POINTER(_S), ctypes.POINTER(_S), _I, _I]
+    lib.pace_b200_halo_pack.argtypes = [vp, _I, ctypes.POINTER(_S), ctypes.POINTER(_S), _I, _I, vp]
+    lib.pace_b200_halo_unpack.argtypes = [vp, _I, ctypes.POINTER(_S), ctypes.POINTER(_S), _I, _I, vp]
     lib.pace_b200_launch_count.argtypes = []
     lib.pace_b200_launch_count.restype = ctypes.c_longlong
     lib.pace_b200_profile_enable.argtypes = [_I]
@@ -143,5 +145,5 @@ MODULE_CALLS = {
 }
 
 EXPORTS = ["pace_b200_row_stride", "pace_b200_create", "pace_b200_destroy", "pace_b200_last_error",
-           "pace_b200_set_stream", "pace_b200_set_field", "pace_b200_set_column", "pace_b200_halo_plan_set", "pace_b200_halo_update", "pace_b200_math_eval", "pace_b200_sat_adjust", "pace_b200_launch_count", "pace_b200_profile_enable",
+           "pace_b200_set_stream", "pace_b200_set_field", "pace_b200_set_column", "pace_b200_halo_plan_set", "pace_b200_halo_update", "pace_b200_halo_pack", "pace_b200_halo_unpack", "pace_b200_math_eval", "pace_b200_sat_adjust", "pace_b200_launch_count", "pace_b200_profile_enable",
            "pace_b200_profile_report"] + ["pace_b200_" + n for n in MODULE_CALLS]

@@ -267,6 +267,14 @@ int pace_b200_halo_plan_set(void* h, int plan_id, const void* ops, int n_ops) { 
 int pace_b200_halo_update(void* h, int plan_id, const char* const* x_names, const char* const* y_names, int n, int nk) {
   ENTRY(halo_update(*c, plan_id, x_names, y_names, n, nk))
 }
+int pace_b200_halo_pack(void* h, int plan_id, const char* const* x_names, const char* const* y_names, int n, int nk,
+                        void* message) {
+  ENTRY(halo_pack(*c, plan_id, x_names, y_names, n, nk, (double*)message))
+}
+int pace_b200_halo_unpack(void* h, int plan_id, const char* const* x_names, const char* const* y_names, int n, int nk,
+                          const void* message) {
+  ENTRY(halo_unpack(*c, plan_id, x_names, y_names, n, nk, (const double*)message))
+}
 int pace_b200_riem_solver3(void* h, double dt, int last_call) { ENTRY(riem_solver3(*c, dt, last_call)) }
 int pace_b200_update_dz_d(void* h, double dt) { ENTRY(update_dz_d(*c, dt)) }
 int pace_b200_zero_data(void* h, int first_timestep) { ENTRY(zero_data(*c, first_timestep)) }

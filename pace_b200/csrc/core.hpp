@@ -35,8 +35,8 @@ struct Core {
   std::map<std::string, double*> scratch;   // library-owned 3-D scratch, allocated on first use
   std::map<std::string, std::vector<double>> hcol;  // host copies of K-columns set via pace_b200_set_column
   std::map<std::string, int> colsize;
-  void* halo_ops[16] = {nullptr};               // device copies of halo plans (pace_b200_halo_plan_set)
-  int halo_nops[16] = {0};
+  void* halo_ops[64] = {nullptr};               // device copies of halo plans (pace_b200_halo_plan_set)
+  int halo_nops[64] = {0};
   std::vector<void*> owned;
   std::string err;
 
@@ -58,6 +58,9 @@ int p_grad_c(Core& c, double dt2);
 int set_column(Core& c, const char* name, const double* host_values, int n);
 int halo_plan_set(Core& c, int plan_id, const void* host_ops, int n_ops);
 int halo_update(Core& c, int plan_id, const char* const* x_names, const char* const* y_names, int n, int nk);
+int halo_pack(Core& c, int plan_id, const char* const* x_names, const char* const* y_names, int n, int nk, double* buf);
+int halo_unpack(Core& c, int plan_id, const char* const* x_names, const char* const* y_names, int n, int nk,
+                const double* buf);
 int tracer_flux_prep(Core& c, int n_split);
 int tracer_substep(Core& c, int nq);
 int tracer_swap_dp(Core& c);

@@ -41,13 +41,21 @@ def nk_heat_dissipation(cfg, npz):
 
 
 class DycoreEngine:
-    def __init__(self, n_tile, layout, npz, grids, ranks=None, device="cuda:0", _lib_handle=None, **cfg):
+    def __init__(self, n_tile, layout, npz, grids, ranks=None, comm=None, device="cuda:0", _lib_handle=None, **cfg):
         """grids: list (one per resident subdomain) of dicts with the reference's GridData / DampingCoefficients
-        arrays ("grid.*", "damp.*", reference layout).  ranks: cube ranks of those subdomains (default: all)."""
+        arrays ("grid.*", "damp.*", reference layout).  ranks: cube ranks of those subdomains (default: all).
+        comm: pace_b200.distributed.TorchComm when the cube is spread over several GPUs (one process per GPU,
+        contiguous blocks of subdomains, see distributed.Placement); ranks then defaults to this GPU's block."""
+        from .distributed import HaloExchanger, Placement
+
         self.planner = HaloPlanner(n_tile, layout)
-        self.ranks = list(range(self.planner.total_ranks)) if ranks is None else list(ranks)
-        if len(self.ranks) != self.planner.total_ranks:
-            raise NotImplementedError("multi-GPU placement goes through pace_b200.distributed")
+        world = comm.world_size if comm is not None else 1
+        self.placement = Placement(self.planner.total_ranks, world)
+        mine = self.placement.ranks_of(comm.rank if comm is not None else 0)
+        self.ranks = mine if ranks is None else list(ranks)
+        if self.ranks != mine:
+            raise ValueError("resident subdomains must be this GPU's block of the placement: %s" % mine)
+        self.comm = comm
         n = self.planner.n
         g0 = grids[0]
         cfg = dict(cfg)
@@ -69,12 +77,10 @@ class DycoreEngine:
         core.set_columns_from_config()
         local = {r: n for n, r in enumerate(self.ranks)}
         pl = self.planner
-        core.set_halo_plan(A3, pl.scalar_plan(False, False, 3, self.ranks), local)
-        core.set_halo_plan(A2, pl.scalar_plan(False, False, 2, self.ranks), local)
-        core.set_halo_plan(B3, pl.scalar_plan(True, True, 3, self.ranks), local)
-        core.set_halo_plan(D3, pl.vector_plan("d", 3, self.ranks), local)
-        core.set_halo_plan(C3, pl.vector_plan("c", 3, self.ranks), local)
-        core.set_halo_plan(SYNC, pl.interface_sync_plan(self.ranks), local)
+        plans = {A3: pl.scalar_plan(False, False, 3), A2: pl.scalar_plan(False, False, 2),
+                 B3: pl.scalar_plan(True, True, 3), D3: pl.vector_plan("d", 3), C3: pl.vector_plan("c", 3),
+                 SYNC: pl.interface_sync_plan()}
+        self.halo = {pid: HaloExchanger(core, pid, ops, self.placement, comm, local) for pid, ops in plans.items()}
         self._nk_heat = nk_heat_dissipation(self.cfg, npz)
         self._do_del2cubed = self._nk_heat != 0 and self.cfg["d_con"] > 1.0e-5
         # LagrangianToEulerian.__init__ (remapping.py:347-351): first level with pfull > 10 hPa
@@ -85,6 +91,9 @@ class DycoreEngine:
                 self._kmp = k
                 break
         self._check_config()
+
+    def _halo(self, plan_id, x_names, y_names=None, nk=None):
+        self.halo[plan_id].update(x_names, y_names, nk)
 
     def _check_config(self):
         """Unimplemented-option guards of the reference, same messages (fv_dynamics.py:178-203, 462-499;
@@ -133,35 +142,35 @@ class DycoreEngine:
         end_step = n_map == int(c["k_split"])
         dt = timestep / n_split
         dt2 = 0.5 * dt
-        core.halo_update(A3, ["q_con", "ad.cappa"])
+        self._halo(A3, ["q_con", "ad.cappa"])
         core.call("zero_data", int(n_map == 1))
         for it in range(n_split):
             remap_step = it == n_split - 1
             if it == 0:
                 core.call("gz_from_zs_delz")
-                core.halo_update(A3, ["delp", "pt"])
+                self._halo(A3, ["delp", "pt"])
             if it == n_split - 1 and end_step and c["use_old_omega"]:
                 core.call("pem_from_delp")
-            core.halo_update(D3, ["u"], ["v"])
-            core.halo_update(A3, ["w"])
+            self._halo(D3, ["u"], ["v"])
+            self._halo(A3, ["w"])
             core.call("c_sw", dt2)
             if c["nord"] > 0:
-                core.halo_update(B3, ["ad.divgd"])
+                self._halo(B3, ["ad.divgd"])
             if it == 0:
-                core.halo_update(A3, ["ad.gz"], nk=npz + 1)
+                self._halo(A3, ["ad.gz"], nk=npz + 1)
                 core.call("copy_full", "ad.gz", "ad.zh")
             else:
                 core.call("copy_full", "ad.zh", "ad.gz")
             core.call("update_dz_c", dt2)
             core.call("riem_solver_c", dt2)
             core.call("p_grad_c", dt2)
-            core.halo_update(C3, ["uc"], ["vc"])
+            self._halo(C3, ["uc"], ["vc"])
             core.call("d_sw", dt)
-            core.halo_update(A3, ["delp", "pt", "q_con"])
+            self._halo(A3, ["delp", "pt", "q_con"])
             core.call("update_dz_d", dt)
             core.call("riem_solver3", dt, int(remap_step))
-            core.halo_update(A3, ["ad.zh"], nk=npz + 1)
-            core.halo_update(A2, ["ad.pkc"], nk=npz + 1)
+            self._halo(A3, ["ad.zh"], nk=npz + 1)
+            self._halo(A2, ["ad.pkc"], nk=npz + 1)
             if remap_step:
                 core.call("edge_pe")
             core.call("pk3_halo")
@@ -170,9 +179,9 @@ class DycoreEngine:
             if c["rf_fast"]:
                 core.call("ray_fast", dt)
             if it == n_split - 1 and c["grid_type"] < 4:
-                core.halo_update(SYNC, ["u"], ["v"])
+                self._halo(SYNC, ["u"], ["v"])
         if self._do_del2cubed:
-            core.halo_update(A3, ["ad.heat_source"])
+            self._halo(A3, ["ad.heat_source"])
             cd = CNST_0P20 * c["da_min"]
             core.call("del2cubed", "ad.heat_source", cd, min(3, int(c["nord"]) + 1))
             core.call("apply_diffusive_heating", abs(dt * c["delt_max"]), self._nk_heat)
@@ -185,11 +194,11 @@ class DycoreEngine:
         cmax_max_all_ranks = 2.0  # the reference hard-codes this in place of an allreduce (tracer_2d_1l.py:337-364)
         n_split = int(np.floor(1.0 + cmax_max_all_ranks))
         core.call("tracer_flux_prep", n_split)
-        core.halo_update(A3, self.TRACERS)
+        self._halo(A3, self.TRACERS)
         for it in range(n_split):
             core.call("tracer_substep", len(self.TRACERS))
             if it != n_split - 1:
-                core.halo_update(A3, self.TRACERS)
+                self._halo(A3, self.TRACERS)
                 core.call("tracer_swap_dp")
 
     # -- LagrangianToEulerian.__call__ (remapping.py:522-731) --------------------------------------------------
@@ -216,10 +225,10 @@ class DycoreEngine:
                 if last_step:
                     core.call("omega_from_w")
                     if c["nf_omega"] > 0:
-                        core.halo_update(A3, ["omga"])
+                        self._halo(A3, ["omga"])
                         core.call("del2cubed", "omga", 0.18 * c["da_min"], int(c["nf_omega"]))
         core.call("neg_adj3")
-        core.halo_update(D3, ["u"], ["v"])
+        self._halo(D3, ["u"], ["v"])
         core.call("c2l_ord4")
 
     # -- DynamicalCore.compute_preamble (fv_dynamics.py:461-508) -------------------------------------------------

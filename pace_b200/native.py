@@ -160,6 +160,31 @@ class NativeCore:
         if rc != 0:
             raise NativeError("halo_plan_set: %s" % self.lib.pace_b200_last_error(self.handle).decode())
 
+    def set_halo_plan_raw(self, plan_id, rows):
+        """rows: (dst_t, src_t, HaloOp) with the two subdomain slots given explicitly — for pack / unpack plans one
+        of them is the op's cell offset in the message (include/pace_b200.h, pace_b200_halo_pack)."""
+        arr = (_lib.HaloOp * max(1, len(rows)))()
+        for n, (dst_t, src_t, o) in enumerate(rows):
+            arr[n] = _lib.HaloOp(dst_t, src_t, o.comp, o.src_comp, o.sign, o.i0, o.j0, o.ni, o.nj, o.aii, o.aij, o.bi,
+                                 o.aji, o.ajj, o.bj)
+        rc = self.lib.pace_b200_halo_plan_set(self.handle, plan_id, ctypes.cast(arr, ctypes.c_void_p), len(rows))
+        if rc != 0:
+            raise NativeError("halo_plan_set: %s" % self.lib.pace_b200_last_error(self.handle).decode())
+
+    def _halo_msg(self, fn, what, plan_id, x_names, y_names, nk, buf):
+        n = len(x_names)
+        xs = (ctypes.c_char_p * n)(*[s.encode() for s in x_names])
+        ys = (ctypes.c_char_p * n)(*[s.encode() for s in y_names]) if y_names else None
+        rc = fn(self.handle, plan_id, xs, ys, n, nk, ctypes.c_void_p(buf.data_ptr()))
+        if rc != 0:
+            raise NativeError("%s: %s" % (what, self.lib.pace_b200_last_error(self.handle).decode()))
+
+    def halo_pack(self, plan_id, x_names, y_names, nk, buf):
+        self._halo_msg(self.lib.pace_b200_halo_pack, "halo_pack", plan_id, x_names, y_names, nk, buf)
+
+    def halo_unpack(self, plan_id, x_names, y_names, nk, buf):
+        self._halo_msg(self.lib.pace_b200_halo_unpack, "halo_unpack", plan_id, x_names, y_names, nk, buf)
+
     def halo_update(self, plan_id, x_names, y_names=None, nk=None):
         n = len(x_names)
         xs = (ctypes.c_char_p * n)(*[s.encode() for s in x_names])

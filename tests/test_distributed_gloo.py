@@ -1,0 +1,82 @@
+"""The multi-GPU path on CPU: 2 processes (gloo), each owning 3 of the 6 C12 subdomains and running the kernels'
+host emulation, exchange halos through pace_b200.distributed (pack -> send/recv -> unpack + local gather) and step the
+dycore once.  Every subdomain must end bit-identical to the 6-rank reference run, i.e. to the single-process result."""
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, layout, q):
+    try:
+        sys.path.insert(0, ROOT)
+        import torch.distributed as dist
+
+        from pace_b200.distributed import Placement, TorchComm
+        from pace_b200.engine import DycoreEngine
+        from tests import hostemu
+        from tests.golden_util import report
+        from tests.module_harness import K_INTERFACE
+        from tests.test_engine_acoustic import STEP_OUT, load_six
+        from tests.test_engine_layout2 import load24
+
+        dist.init_process_group("gloo", init_method="tcp://127.0.0.1:%d" % port, rank=rank, world_size=world)
+        comm = TorchComm()
+        load = load_six if layout == 1 else load24
+        n = 12 // layout
+        mine = Placement(6 * layout * layout, world).ranks_of(rank)
+        grids, init, final = load("grid"), load("init"), load("final")
+        eng = DycoreEngine(12, layout, 79, [grids[r] for r in mine], comm=comm, device="cpu",
+                           _lib_handle=hostemu.load())
+        eng.set_state([init[r] for r in mine])
+        eng.step_dynamics()
+        bad = []
+        for name in STEP_OUT:
+            got = eng.core.get(name)
+            for slot, r in enumerate(mine):
+                g, w = got[slot], final[r][name]
+                if g.ndim == 3 and name not in K_INTERFACE:
+                    g, w = g[:, :, :-1], w[:, :, :-1]
+                g, w = g[3:3 + n, 3:3 + n], w[3:3 + n, 3:3 + n]
+                err, nbad = report(name, g, w)
+                if nbad:
+                    bad.append((name, r, err, nbad))
+        dist.barrier()
+        dist.destroy_process_group()
+        q.put((rank, bad))
+    except Exception as e:  # surface the failure in the parent
+        import traceback
+
+        q.put((rank, "EXC: %s\n%s" % (e, traceback.format_exc())))
+
+
+@pytest.mark.parametrize("layout,world", [(1, 2), (2, 2)])
+def test_two_process_step_matches_reference(layout, world):
+    import torch.multiprocessing as mp
+
+    from tests import hostemu
+
+    hostemu.load()  # build once in the parent
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, layout, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    results = [q.get(timeout=900) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    for rank, bad in sorted(results):
+        assert bad == [], "rank %d: %s" % (rank, bad)
