@@ -132,6 +132,8 @@ def main():
     if args.workload is None:
         args.workload = "c384"
     if args.impl == "reference":
+        if int(os.environ.get("RANK", "0")) != 0:
+            return  # under torchrun rank 0 alone times the CPU implementation
         return run_reference(args)
 
     import torch
@@ -139,14 +141,36 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    if world > 1:
-        raise SystemExit("multi-GPU placement is not wired into bench.py yet")
     from pace_b200 import _lib
     from pace_b200.synthetic import make_engine
 
     torch.cuda.set_device(local_rank)
+    comm = None
+    dist = None
+    if world > 1:
+        # one process per GPU; each holds a contiguous block of subdomains, halos cross GPUs by NCCL send/recv
+        import torch.distributed as dist
+
+        from pace_b200.distributed import TorchComm
+
+        dist.init_process_group("nccl", device_id=torch.device("cuda:%d" % local_rank))
+        comm = TorchComm()
     n_tile, layout, desc = WORKLOADS[args.workload]
-    eng = make_engine(n_tile, layout, npz=NPZ, device="cuda:%d" % local_rank, n_split=N_SPLIT, k_split=1, dt_atmos=DT_ATMOS)
+    eng = make_engine(n_tile, layout, npz=NPZ, device="cuda:%d" % local_rank, comm=comm, n_split=N_SPLIT, k_split=1,
+                      dt_atmos=DT_ATMOS)
+
+    def fence():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if dist is None:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda:%d" % local_rank)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
     core = eng.core
     lib = core.lib
     n_sub = 6 * layout * layout
@@ -155,22 +179,22 @@ def main():
 
     for _ in range(args.warmup):
         eng.step_dynamics()
-    torch.cuda.synchronize()
+    fence()
 
     sampler = ClockSampler(local_rank)
     sampler.start()
     lib.pace_b200_profile_enable(1)
     l0 = lib.pace_b200_launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    torch.cuda.synchronize()
+    fence()
     torch.cuda.profiler.start()  # lets `ncu --profile-from-start off` capture exactly the timed steps
     e0.record()
     for _ in range(args.steps):
         eng.step_dynamics()
     e1.record()
-    torch.cuda.synchronize()
+    fence()
     torch.cuda.profiler.stop()
-    ms = e0.elapsed_time(e1) / args.steps
+    ms = max_over_ranks(e0.elapsed_time(e1) / args.steps)
     launches = (lib.pace_b200_launch_count() - l0) // args.steps
     lib.pace_b200_profile_enable(0)
     buf = ctypes.create_string_buffer(65536)
@@ -192,7 +216,7 @@ def main():
         per_launch_ms = tot / cnt
         bytes_per_cell = {"fvtp2d_inner_ppm": 5 * 8, "fvtp2d_qi_qj": 7 * 8, "fvtp2d_outer_ppm": 10 * 8,
                           "fvtp2d_fused": 8.4 * 8, "fvtp2d_march": 8.4 * 8, "riem_solver_c": 8 * 8, "riem_solver3": 15 * 8, "remap_scalars_column": 40 * 8}.get(top, 8 * 8)
-        alg_bytes = cells * bytes_per_cell
+        alg_bytes = cells / world * bytes_per_cell  # this GPU's share of the cells
         achieved = alg_bytes / (per_launch_ms / 1000.0) / 1e9
         roof = {"kernel": top, "bound": "hbm", "achieved": achieved, "peak": pk["hbm_gbs"], "peak_source": pk_kind,
                 "unit": "GB/s", "frac": achieved / pk["hbm_gbs"], "traffic": None, "launches_timed": cnt,
@@ -209,7 +233,7 @@ def main():
             host[k].copy_(core.t[k])
         nbytes = sum(h.numel() * 8 for h in host.values())
         k_e2e = max(1, min(args.steps, 2))
-        torch.cuda.synchronize()
+        fence()
         t0 = time.time()
         for _ in range(k_e2e):
             for k in names:
@@ -218,13 +242,13 @@ def main():
             for k in names:
                 host[k].copy_(core.t[k], non_blocking=True)
             torch.cuda.synchronize()
-        e2e_ms = (time.time() - t0) / k_e2e * 1000.0
+        e2e_ms = max_over_ranks((time.time() - t0) / k_e2e * 1000.0)
         e2e = {"value": DT_ATMOS / (e2e_ms / 1000.0), "unit": "simulated days / day", "ms_per_step": e2e_ms,
-               "h2d_bytes_per_step": nbytes, "d2h_bytes_per_step": nbytes, "steps": k_e2e}
+               "h2d_bytes_per_step": nbytes * world, "d2h_bytes_per_step": nbytes * world, "steps": k_e2e}
         del host
 
     cpu = None
-    if not args.no_cpu_baseline:
+    if not args.no_cpu_baseline and world == 1:
         cores = os.cpu_count() or 1
         sample_tile = 48
         rate, dt = cpu_port_rate(sample_tile, cores, steps=1)
@@ -236,10 +260,14 @@ def main():
         "metric": "dycore simulated-days/day", "value": value, "unit": "simulated days / day", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic (C12 reference fixture resampled, see pace_b200/synthetic.py)",
-        "config": {"workload": desc, "cells": cells, "l2": "working set (%.0f GB) >> L2, no flush needed" % (cells * 8 * 130 / 1e9)},
+        "config": {"workload": desc, "cells": cells, "placement": "%d subdomains per GPU, halo exchange by NCCL send/recv" % (n_sub // world) if world > 1 else "%d subdomains on one GPU" % n_sub, "l2": "working set (%.0f GB) >> L2, no flush needed" % (cells * 8 * 130 / 1e9)},
         "gpu_launches": int(launches), "clocks": sampler.summary(), "roofline": roof, "cpu_baseline": cpu, "e2e": e2e,
     }
-    print(json.dumps(line))
+    if rank == 0:
+        print(json.dumps(line))
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
 
 
 if __name__ == "__main__":

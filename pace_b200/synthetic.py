@@ -80,14 +80,19 @@ def _load(kind):
     return out
 
 
-def make_engine(n_tile, layout, npz=79, device="cuda:0", ranks=None, **cfg):
-    """A DycoreEngine for C<n_tile> with `layout` x `layout` subdomains per tile, filled with resampled inputs."""
+def make_engine(n_tile, layout, npz=79, device="cuda:0", comm=None, **cfg):
+    """A DycoreEngine for C<n_tile> with `layout` x `layout` subdomains per tile, filled with resampled inputs.
+    comm: pace_b200.distributed.TorchComm — this process then holds only its block of subdomains."""
+    from .distributed import Placement
     from .engine import STATE_2D, STATE_3D, DycoreEngine
     from .hostprep import a2b_corner_coefficients
 
     grid6, init6 = _load("grid"), _load("init")
     n = n_tile // layout
-    total = 6 * layout * layout
+    mine = Placement(6 * layout * layout, comm.world_size if comm is not None else 1).ranks_of(
+        comm.rank if comm is not None else 0)
+    slot = {r: s for s, r in enumerate(mine)}
+    total = len(mine)
     # DycoreEngine wants per-subdomain grid dicts for the small things (columns, scalars); the big 2-D arrays are
     # written straight into its device tensors below, so hand it light-weight dicts of the right shape
     stub = {}
@@ -100,7 +105,7 @@ def make_engine(n_tile, layout, npz=79, device="cuda:0", ranks=None, **cfg):
             continue
         else:
             stub[k] = v
-    eng = DycoreEngine(n_tile, layout, npz, [stub] * total, device=device, **cfg)
+    eng = DycoreEngine(n_tile, layout, npz, [stub] * total, comm=comm, device=device, **cfg)
     core = eng.core
     dev = core.device
 
@@ -108,7 +113,9 @@ def make_engine(n_tile, layout, npz=79, device="cuda:0", ranks=None, **cfg):
         dst = core.t[name]
         for jy in range(layout):
             for ix in range(layout):
-                r = tile * layout * layout + jy * layout + ix
+                r = slot.get(tile * layout * layout + jy * layout + ix)
+                if r is None:
+                    continue
                 sub = tile_tensor[:, jy * n:jy * n + n + 7, ix * n:ix * n + n + 7]
                 if dst.ndim == 4:
                     dst[r, :sub.shape[0], :, :n + 7] = sub
@@ -117,8 +124,9 @@ def make_engine(n_tile, layout, npz=79, device="cuda:0", ranks=None, **cfg):
 
     coef = np.zeros((total, 12))
     for tile in range(6):
+        if not any(r // (layout * layout) == tile for r in mine):
+            continue
         g = grid6[tile]
-        lonlat = {}
         for name, a in g.items():
             if np.ndim(a) == 2:
                 t = resample_tile(a, n_tile, STAGGER.get(name, (0, 0)), dev)
@@ -129,9 +137,9 @@ def make_engine(n_tile, layout, npz=79, device="cuda:0", ranks=None, **cfg):
         # a2b_ord4 corner-extrapolation weights: those of the fixture tile (ratios of great-circle distances,
         # resolution independent to first order); longitudes cannot be interpolated across the date line
         tile_coef = a2b_corner_coefficients(g["grid.lon"], g["grid.lat"], g["grid.lon_agrid"], g["grid.lat_agrid"], N0, N0)
-        for jy in range(layout):
-            for ix in range(layout):
-                coef[tile * layout * layout + jy * layout + ix] = tile_coef
+        for r, sl in slot.items():
+            if r // (layout * layout) == tile:
+                coef[sl] = tile_coef
         s = init6[tile]
         for name in STATE_3D + STATE_2D:
             a = s[name]

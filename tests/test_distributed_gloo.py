@@ -19,7 +19,7 @@ def _free_port():
     return p
 
 
-def _worker(rank, world, port, layout, q):
+def _worker(rank, world, port, layout, q, backend="gloo"):
     try:
         sys.path.insert(0, ROOT)
         import torch.distributed as dist
@@ -32,16 +32,25 @@ def _worker(rank, world, port, layout, q):
         from tests.test_engine_acoustic import STEP_OUT, load_six
         from tests.test_engine_layout2 import load24
 
-        dist.init_process_group("gloo", init_method="tcp://127.0.0.1:%d" % port, rank=rank, world_size=world)
+        kw = dict(device="cpu", _lib_handle=hostemu.load())
+        if backend == "nccl":
+            import torch
+
+            torch.cuda.set_device(rank)
+            kw = dict(device="cuda:%d" % rank)
+            dist.init_process_group("nccl", init_method="tcp://127.0.0.1:%d" % port, rank=rank, world_size=world,
+                                    device_id=torch.device("cuda:%d" % rank))
+        else:
+            dist.init_process_group("gloo", init_method="tcp://127.0.0.1:%d" % port, rank=rank, world_size=world)
         comm = TorchComm()
         load = load_six if layout == 1 else load24
         n = 12 // layout
         mine = Placement(6 * layout * layout, world).ranks_of(rank)
         grids, init, final = load("grid"), load("init"), load("final")
-        eng = DycoreEngine(12, layout, 79, [grids[r] for r in mine], comm=comm, device="cpu",
-                           _lib_handle=hostemu.load())
+        eng = DycoreEngine(12, layout, 79, [grids[r] for r in mine], comm=comm, **kw)
         eng.set_state([init[r] for r in mine])
         eng.step_dynamics()
+        eng.core.sync()
         bad = []
         for name in STEP_OUT:
             got = eng.core.get(name)
@@ -62,17 +71,17 @@ def _worker(rank, world, port, layout, q):
         q.put((rank, "EXC: %s\n%s" % (e, traceback.format_exc())))
 
 
-@pytest.mark.parametrize("layout,world", [(1, 2), (2, 2)])
-def test_two_process_step_matches_reference(layout, world):
+def _run(layout, world, backend):
     import torch.multiprocessing as mp
 
-    from tests import hostemu
+    if backend == "gloo":
+        from tests import hostemu
 
-    hostemu.load()  # build once in the parent
+        hostemu.load()  # build once in the parent
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_worker, args=(r, world, port, layout, q)) for r in range(world)]
+    procs = [ctx.Process(target=_worker, args=(r, world, port, layout, q, backend)) for r in range(world)]
     for p in procs:
         p.start()
     results = [q.get(timeout=900) for _ in procs]
@@ -80,3 +89,18 @@ def test_two_process_step_matches_reference(layout, world):
         p.join(timeout=60)
     for rank, bad in sorted(results):
         assert bad == [], "rank %d: %s" % (rank, bad)
+
+
+@pytest.mark.parametrize("layout,world", [(1, 2), (2, 2)])
+def test_two_process_step_matches_reference(layout, world):
+    _run(layout, world, "gloo")
+
+
+@pytest.mark.gpu
+def test_two_gpu_step_matches_reference():
+    """Same check on two B200s over NCCL (skipped on a one-GPU box)."""
+    import torch
+
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    _run(2, 2, "nccl")
