@@ -20,6 +20,7 @@ namespace pace {
 
 int fvtp2d_fused_launch(Core& c, const Fvtp2dArgs& a);
 int fvtp2d_march_launch(Core& c, const Fvtp2dArgs& a);
+int delnflux_fused_launch(Core& c, const DelnArgs& a);
 
 // ---- materialised copy_corners ---------------------------------------------------------------------
 __device__ __forceinline__ void copy_corner_cell(const Geo& g, double* q, bool ydir, int t, int k, int c, int a, int b) {
@@ -157,6 +158,14 @@ int fvtp2d(Core& c, const Fvtp2dArgs& a) {
 // DelnFluxNoSG.__call__ (delnflux.py:1243-1278), optionally followed by DelnFlux's add_diffusive_component /
 // diffusive_damp (delnflux.py:1023-1044) when a.accumulate.
 int delnflux(Core& c, const DelnArgs& a) {
+#ifndef PACE_HOST_EMU
+  // production path: one shared-memory tiled kernel (delnflux_fused.cu); PACE_B200_DELNFLUX=unfused for A/B runs
+  static const bool fused = [] { const char* v = getenv("PACE_B200_DELNFLUX"); return !(v && std::string(v) == "unfused"); }();
+  if (fused) {
+    const int rc = delnflux_fused_launch(c, a);
+    if (rc >= 0) return rc;
+  }
+#endif
   const Geo g = c.g;
   cudaStream_t st = c.stream;
   const double *del6_u = c.F("damp.del6_u"), *del6_v = c.F("damp.del6_v"), *rarea = c.F("grid.rarea");

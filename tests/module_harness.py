@@ -33,8 +33,9 @@ K_INTERFACE = {"pe", "peln", "pk", "ad.gz", "ad.zh", "ad.pkc", "ad.pk3", "ad.pem
 
 
 def interior(a, nx=12, ny=12, pad=0):
-    """compute-domain (+pad) view of a reference-layout array"""
-    return a[3 - pad:3 + nx + pad, 3 - pad:3 + ny + pad]
+    """compute-domain (+pad) view of a reference-layout array; pad = n or (low side, high side)"""
+    lo, hi = pad if isinstance(pad, tuple) else (pad, pad)
+    return a[3 - lo:3 + nx + hi, 3 - lo:3 + ny + hi]
 
 
 def check_module(backend, golden, grid, stage, call, args, tol=0.0, near_zero=0.0, cfg=None, skip=(), begin=None,

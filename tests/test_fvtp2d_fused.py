@@ -1,7 +1,8 @@
 """The fused fvtp2d kernels — row-marching (pace_b200/csrc/fvtp2d_march.cu, the production path) and CTA-tiled
 (fvtp2d_fused.cu) — against the straightforward three-kernel version (transport.cu, the one validated stencil by
 stencil against the reference) on a domain that spans several CTA tiles / row chunks / column strips: one full dycore
-step at C48 (6 subdomains of 48x48x79), bit for bit."""
+step at C48 (6 subdomains of 48x48x79), bit for bit.  The baseline run also uses the unfused DelnFlux kernels and the
+global-memory Riemann solvers, so the fused / on-chip versions of those are covered by the same comparison."""
 import os
 import subprocess
 import sys
@@ -30,7 +31,7 @@ def test_fused_matches_three_kernel_version(tmp_path):
     modes = {"march": {"PACE_B200_FVTP2D": "march"},
              "march_chunks_strips": {"PACE_B200_FVTP2D": "march", "PACE_B200_FVTP2D_ROWS": "16",
                                      "PACE_B200_FVTP2D_WIDTH": "20"},
-             "tile": {"PACE_B200_FVTP2D": "tile"}, "unfused": {"PACE_B200_FVTP2D": "unfused"}}
+             "tile": {"PACE_B200_FVTP2D": "tile"}, "unfused": {"PACE_B200_FVTP2D": "unfused", "PACE_B200_DELNFLUX": "unfused", "PACE_B200_RIEM": "global"}}
     for mode, extra in modes.items():
         env = dict(os.environ, **extra)
         path = str(tmp_path / (mode + ".npz"))
