@@ -154,6 +154,11 @@ int pace_b200_create(const pace_b200_config* cfg, const unsigned char* edge_flag
   g.sj = pace_b200_row_stride(cfg->nx);
   g.sk = g.sj * (cfg->ny + 2 * HALO + 1);
   g.st3 = (long long)g.sk * (cfg->npz + 1);
+  if (g.st3 * (long long)cfg->n_tiles_local >= (1LL << 31)) {
+    g_err = "pace_b200_create: 2^31 or more points per field on one GPU (32-bit field offsets); use more GPUs";
+    delete c;
+    return 1;
+  }
   g.is = HALO; g.ie = HALO + g.nx - 1; g.js = HALO; g.je = HALO + g.ny - 1;
   memset(g.edge, 0, sizeof g.edge);
   for (int t = 0; t < g.nt; ++t) g.edge[t] = edge_flags ? edge_flags[t] : 15;

@@ -55,8 +55,16 @@ struct Geo {
 };
 
 // One grid point handed to a stencil body.
+// Linear offsets into 3-D fields: 32-bit on the device (one IMAD.WIDE per access instead of 64-bit index chains;
+// pace_b200_create refuses configurations with 2^31 or more points per field), 64-bit in the host emulation.
+#ifdef PACE_HOST_EMU
+typedef long long off3_t;
+#else
+typedef int off3_t;
+#endif
+
 struct Pt {
-  long long o;   // linear offset of (t,k,j,i) in 3-D fields
+  off3_t o;      // linear offset of (t,k,j,i) in 3-D fields
   int o2;        // linear offset of (t,j,i) in 2-D fields
   int i, j, k, t;
   int sj, sk;
@@ -68,14 +76,14 @@ __device__ __forceinline__ Pt make_pt(const Geo& g, int t, int i, int j, int k) 
   p.i = i; p.j = j; p.k = k; p.t = t;
   p.sj = g.sj; p.sk = g.sk;
   p.o2 = t * g.sk + j * g.sj + i;
-  p.o = (long long)t * g.st3 + (long long)k * g.sk + j * g.sj + i;
+  p.o = (off3_t)((off3_t)t * (off3_t)g.st3 + (off3_t)k * g.sk + j * g.sj + i);
   unsigned char e = g.edge[t];
   p.W = e & EDGE_W; p.E = e & EDGE_E; p.S = e & EDGE_S; p.N = e & EDGE_N;
   return p;
 }
 
 // field access relative to the current point `p`
-#define A(f, di, dj, dk) (f)[p.o + (di) + (dj) * p.sj + (long long)(dk) * p.sk]
+#define A(f, di, dj, dk) (f)[p.o + (di) + (dj) * p.sj + (off3_t)(dk) * p.sk]
 #define A0(f) (f)[p.o]
 #define A2(f, di, dj) (f)[p.o2 + (di) + (dj) * p.sj]
 #define A20(f) (f)[p.o2]

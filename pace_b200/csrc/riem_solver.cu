@@ -15,7 +15,7 @@ struct Sim1Work {  // per-column work arrays, stored as scratch 3-D fields (coal
   double *w1, *g_rat, *bb, *dd, *bet, *gam, *pp, *aa, *p1;
 };
 
-#define K_(f, kk) (f)[p.o + (long long)(kk) * p.sk]
+#define K_(f, kk) (f)[p.o + (off3_t)(kk) * p.sk]
 
 // sim1_solver.py:20-141.  km = number of layers; arrays indexed [0,km] (interfaces) or [0,km).
 __device__ __forceinline__ void sim1_column(const Pt& p, int km, double* w, const double* dm,
