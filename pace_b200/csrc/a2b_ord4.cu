@@ -17,9 +17,23 @@ constexpr double b1 = 7.0 / 12.0, b2 = -1.0 / 12.0;
 constexpr double a1 = 9.0 / 16.0, a2 = -1.0 / 16.0;
 }  // namespace
 
+int a2b_ord4_fused_launch(Core& c, const double* qin, double* qout, int k0, int nk);  // a2b_ord4_fused.cu
+
 int a2b_ord4(Core& c, const double* qin_c, double* qout, int k0, int nk, bool replace) {
   const Geo g = c.g;
   cudaStream_t st = c.stream;
+#ifndef PACE_HOST_EMU
+  // production path: one shared-memory tiled kernel; PACE_B200_A2B=unfused keeps the two-kernel version (A/B runs)
+  static const bool fused = [] { const char* v = getenv("PACE_B200_A2B"); return !(v && std::string(v) == "unfused"); }();
+  if (fused) {
+    if (a2b_ord4_fused_launch(c, qin_c, qout, k0, nk)) return 1;
+    if (replace) {
+      double* qin_w = const_cast<double*>(qin_c);
+      launch_ijk(st, g, Box{g.is, g.js, k0, g.nx + 1, g.ny + 1, nk}, [=] __device__(const Pt& p) { A0(qin_w) = A0(qout); });
+    }
+    return 0;
+  }
+#endif
   const double *dxa = c.F("grid.dxa"), *dya = c.F("grid.dya"), *edge_w = c.F("grid.edge_w"),
                *edge_e = c.F("grid.edge_e"), *edge_s = c.F("grid.edge_s"), *edge_n = c.F("grid.edge_n"),
                *coef = c.F("grid.a2b_corner_coef");
