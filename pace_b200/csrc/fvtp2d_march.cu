@@ -104,7 +104,7 @@ __device__ __forceinline__ double cells_flux(double c, double qm, double blm, do
 
 constexpr int NSLOT = 3, NSTREAM = 10;
 constexpr int SW = 26;         // cells per warp strip (32 lanes - 2 x 3 apron)
-constexpr int WPB = 4;         // warps per CTA (independent work items)
+constexpr int WPB = 1;         // warps per CTA (independent work items)
 constexpr int PITCH = 34;      // doubles per staged row
 constexpr int WARP_SMEM = (NSTREAM * NSLOT + 1) * PITCH;  // doubles per warp
 constexpr unsigned FULL = 0xffffffffu;
@@ -170,7 +170,7 @@ __device__ __forceinline__ double xsweep_flux(const double* row, int L, int i, d
 }
 
 template <int OIN, int OOUT>
-__global__ void __launch_bounds__(WPB * 32, 4) k_fvtp2d_march(Geo g, MarchArgs a) {
+__global__ void __launch_bounds__(WPB * 32, 16) k_fvtp2d_march(Geo g, MarchArgs a) {
   extern __shared__ double smem[];
   const int L = threadIdx.x & 31, wid = threadIdx.x >> 5;
   // work item of this warp: (strip, row chunk, level, subdomain)
@@ -357,7 +357,7 @@ int fvtp2d_march_launch(Core& c, const Fvtp2dArgs& a) {
   const int oo = a.hord < 0 ? -a.hord : a.hord;
   const int oi = oo == 10 ? 8 : oo;
   static const int rows_env = [] { const char* v = getenv("PACE_B200_FVTP2D_ROWS"); return v ? atoi(v) : 0; }();
-  f.rows = rows_env > 0 ? rows_env : 32;
+  f.rows = rows_env > 0 ? rows_env : 64;
   if (f.rows > g.ny) f.rows = g.ny;
   f.nstrips = (g.nx + SW - 1) / SW;
   f.nchunks = (g.ny + f.rows - 1) / f.rows;
