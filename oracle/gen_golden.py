@@ -39,6 +39,9 @@ def main():
     ap.add_argument("--steps", type=int, default=1)
     ap.add_argument("--skip-run", action="store_true")
     ap.add_argument("--stages-only", action="store_true")
+    ap.add_argument("--k-split", type=int, default=1)
+    ap.add_argument("--final-only", action="store_true",
+                    help="only the state after --steps steps of every rank (multi-substep / multi-step fixture)")
     ap.add_argument("--layout", type=int, default=1, help="layout x layout subdomains per tile (no stage log if > 1)")
     ap.add_argument("--deep", action="store_true", help="also hook d_sw/updatedzd/nh_p_grad internals (dev only)")
     args = ap.parse_args()
@@ -49,6 +52,8 @@ def main():
     raw = args.raw + suffix
     if args.layout > 1:
         return multi_layout(args, tag, raw + "_l%d" % args.layout)
+    if args.final_only:
+        return final_only(args, tag, raw + "_ks%d_s%d" % (args.k_split, args.steps))
     if not args.skip_run:
         cfg = default_config_kwargs(npx=args.npx, n_split=args.n_split)
         res = run_ranks(6, rank_main, (cfg, args.steps, (0,), raw, 0, args.deep), timeout=7200)
@@ -80,6 +85,24 @@ def main():
     np.savez_compressed(os.path.join(out, "%s_6rank_grid.npz" % tag), **grid)
     np.savez_compressed(os.path.join(out, "%s_6rank_init%s.npz" % (tag, suffix)), **init)
     np.savez_compressed(os.path.join(out, "%s_6rank_final%s.npz" % (tag, suffix)), **final)
+
+
+def final_only(args, tag, raw):
+    """6 ranks, n_split / k_split / steps as given: the final state only (the initial state and the grid are those
+    of the n_split=1 fixture)."""
+    if not args.skip_run:
+        cfg = default_config_kwargs(npx=args.npx, n_split=args.n_split, k_split=args.k_split)
+        for r in run_ranks(6, rank_main, (cfg, args.steps, (), raw, 0, False), timeout=7200):
+            print(r)
+    final = {}
+    for r in range(6):
+        s = np.load(os.path.join(raw, "rank%d_final.npz" % r))
+        for k in s.files:
+            a = s[k]
+            final["%d:%s" % (r, k)] = a[3:-3, 3:-3] if a.ndim == 3 else a
+    out = os.path.join(ROOT, "tests", "golden")
+    np.savez_compressed(os.path.join(out, "%s_6rank_final_ns%d_ks%d_s%d.npz" % (tag, args.n_split, args.k_split, args.steps)),
+                        **final)
 
 
 def multi_layout(args, tag, raw):

@@ -106,7 +106,7 @@ constexpr int NSLOT = 3, NSTREAM = 10;
 constexpr int SW = 26;         // cells per warp strip (32 lanes - 2 x 3 apron)
 constexpr int WPB = 1;         // warps per CTA (independent work items)
 constexpr int PITCH = 34;      // doubles per staged row
-constexpr int WARP_SMEM = (NSTREAM * NSLOT + 1) * PITCH;  // doubles per warp
+constexpr int WARP_SMEM = (NSTREAM * NSLOT + 2) * PITCH;  // doubles per warp
 constexpr unsigned FULL = 0xffffffffu;
 
 __device__ __forceinline__ void cp_async8(double* smem_dst, const double* gmem_src) {
@@ -182,8 +182,8 @@ __global__ void __launch_bounds__(WPB * 32, 16) k_fvtp2d_march(Geo g, MarchArgs 
   item /= a.nchunks;
   const int k = (int)(item % a.nk), t = (int)(item / a.nk);
 
-  double* bufC = smem + wid * WARP_SMEM;  // q_i row
-  double* rings = bufC + PITCH;           // NSTREAM x NSLOT staged input rows
+  double* bufC0 = smem + wid * WARP_SMEM;  // q_i row, two copies used alternately (no barrier between the last
+  double* rings = bufC0 + 2 * PITCH;       // read of one step and the write of the next); then the staged input rows
 
   const int is = g.is, ie = g.ie, js = g.js, je = g.je, sj = g.sj;
   const unsigned char ed = g.edge[t];
@@ -321,13 +321,13 @@ __global__ void __launch_bounds__(WPB * 32, 16) k_fvtp2d_march(Geo g, MarchArgs 
     }
     // 4. outer x flux on row R-3
     if (s >= 6) {
+      double* bufC = bufC0 + (s & 1) * PITCH;
       bufC[L] = qi;
       __syncwarp();
       const int orow = o - 3 * sj;
       auto D = [&](int d) { return dxa[orow + d]; };
       const double outer = xsweep_flux<MO>(bufC, L, i, ring(8, slot)[L], D, is, ie, W, E);
       if (xface_out) fx[orow] = 0.5 * (outer + fxq3) * ring(9, slot)[L];
-      __syncwarp();  // bufC is rewritten in the next step
     }
   }
   asm volatile("cp.async.wait_group 0;\n" ::: "memory");

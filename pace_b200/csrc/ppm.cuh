@@ -16,9 +16,15 @@ constexpr double p1 = 7.0 / 12.0, p2 = -1.0 / 12.0;
 constexpr double s11 = 11.0 / 14.0, s14 = 4.0 / 7.0, s15 = 3.0 / 14.0;
 }  // namespace ppmc
 
-__device__ __forceinline__ double fv_sign(double a, double b) {  // basic_operations.py:32-39
+__device__ __forceinline__ double fv_sign(double a, double b) {  // basic_operations.py:32-39: |a| if b > 0 else -|a|
+#ifdef PACE_HOST_EMU
   double r = fabs(a);
   return b > 0 ? r : -r;
+#else
+  // same value, built from the sign bit: one compare + two integer ops instead of two fp64 moves and two selects
+  const unsigned hi = ((unsigned)__double2hiint(a) & 0x7fffffffu) | (b > 0 ? 0u : 0x80000000u);
+  return __hiloint2double((int)hi, __double2loint(a));
+#endif
 }
 
 // compute_al (xppm.py:147-185), al at interface offset d
