@@ -218,8 +218,17 @@ def main():
                           "fvtp2d_fused": 8.4 * 8, "fvtp2d_march": 8.4 * 8, "riem_solver_c": 8 * 8, "riem_solver3": 15 * 8, "remap_scalars_column": 40 * 8}.get(top, 8 * 8)
         alg_bytes = cells / world * bytes_per_cell  # this GPU's share of the cells
         achieved = alg_bytes / (per_launch_ms / 1000.0) / 1e9
+        # measured DRAM bytes per launch of that kernel from the committed ncu capture (profiles/traffic_r01.json),
+        # scaled by this GPU's share of the cells; null when no capture exists for this workload / kernel
+        traffic = None
+        tpath = os.path.join(ROOT, "profiles", "traffic_r01.json")
+        if os.path.exists(tpath):
+            rec = json.load(open(tpath)).get(args.workload, {}).get(top)
+            if rec:
+                traffic = rec["dram_bytes_per_launch"] / world
         roof = {"kernel": top, "bound": "hbm", "achieved": achieved, "peak": pk["hbm_gbs"], "peak_source": pk_kind,
-                "unit": "GB/s", "frac": achieved / pk["hbm_gbs"], "traffic": None, "launches_timed": cnt,
+                "unit": "GB/s", "frac": achieved / pk["hbm_gbs"], "traffic": traffic,
+                "algorithmic_bytes_per_launch": alg_bytes, "launches_timed": cnt,
                 "ms_per_launch": per_launch_ms, "share_of_step": tot / args.steps / ms,
                 "labelled_kernels_ms_per_step": {k: v[1] / args.steps for k, v in sorted(prof.items())}}
 
