@@ -357,9 +357,17 @@ int fvtp2d_march_launch(Core& c, const Fvtp2dArgs& a) {
   const int oo = a.hord < 0 ? -a.hord : a.hord;
   const int oi = oo == 10 ? 8 : oo;
   static const int rows_env = [] { const char* v = getenv("PACE_B200_FVTP2D_ROWS"); return v ? atoi(v) : 0; }();
-  f.rows = rows_env > 0 ? rows_env : 64;
-  if (f.rows > g.ny) f.rows = g.ny;
   f.nstrips = (g.nx + SW - 1) / SW;
+  // rows per chunk: 64 (6 warm-up rows = 9 % extra work) unless that leaves fewer than ~6 waves of warps on the
+  // GPU (148 SMs x 16 resident warps), then 32 or 16 — small per-GPU domains (multi-GPU runs) need the parallelism
+  f.rows = 64;
+  if (rows_env > 0) {
+    f.rows = rows_env;
+  } else {
+    const long long slots = 148LL * 16;
+    while (f.rows > 16 && (long long)f.nstrips * ((g.ny + f.rows - 1) / f.rows) * a.nk * g.nt < 6 * slots) f.rows /= 2;
+  }
+  if (f.rows > g.ny) f.rows = g.ny;
   f.nchunks = (g.ny + f.rows - 1) / f.rows;
   f.items = (long long)f.nstrips * f.nchunks * a.nk * g.nt;
   const int blocks = (int)((f.items + WPB - 1) / WPB);

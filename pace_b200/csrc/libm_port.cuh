@@ -45,9 +45,12 @@ __device__ __forceinline__ unsigned long long as_u(double d) {
 __device__ __forceinline__ double fma_(double a, double b, double c) { return fma(a, b, c); }
 
 // exp core shared by exp() and pow(): x = xhi (+ xtail), result scaled by 2^(sign_bias bit) (pow only)
+template <bool CHECK = true>
 __device__ __forceinline__ bool exp_core(double x, double xtail, bool has_tail, double& out) {
-  const unsigned abstop = (unsigned)(as_u(x) >> 52) & 0x7ff;
-  if (abstop - 0x3c9u > 0x3eu) return false;  // |x| < 2^-54 or |x| >= 512: library path
+  if (CHECK) {
+    const unsigned abstop = (unsigned)(as_u(x) >> 52) & 0x7ff;
+    if (abstop - 0x3c9u > 0x3eu) return false;  // |x| < 2^-54 or |x| >= 512: library path
+  }
   const double InvLn2N = as_d(EXP_HEAD[0]), Shift = as_d(EXP_HEAD[1]), NegLn2hiN = as_d(EXP_HEAD[2]),
                NegLn2loN = as_d(EXP_HEAD[3]), C2 = as_d(EXP_HEAD[4]), C3 = as_d(EXP_HEAD[5]), C4 = as_d(EXP_HEAD[6]),
                C5 = as_d(EXP_HEAD[7]);
@@ -122,6 +125,103 @@ __device__ __forceinline__ double log_(double x) {
   const double q = fma_(fma_(r, A4, A3), r2, fma_(r, A2, A1));
   const double y = fma_(r3, q, fma_(r2, A0, lo));
   return y + hi;
+}
+
+// ---- N independent evaluations at once ----------------------------------------------------------------------
+// exp_ / log_ return early on their rare paths, which keeps the compiler from interleaving several calls.  These
+// evaluate the main path of N arguments as straight-line code (N independent dependency chains for the scheduler)
+// when all of them are main-path arguments, and fall back to the scalar routines otherwise.  Same operations per
+// argument, hence the same bits.
+__device__ __forceinline__ bool exp_is_main(double x) {
+  const unsigned abstop = (unsigned)(as_u(x) >> 52) & 0x7ff;
+  return abstop - 0x3c9u <= 0x3eu;
+}
+__device__ __forceinline__ bool log_is_main(double x) {
+  const unsigned long long ix = as_u(x);
+  const unsigned top = (unsigned)(ix >> 48);
+  return top - 0x0010u < 0x7ff0u - 0x0010u && !(ix - 0x3fee000000000000ULL < 0x3090000000000ULL);
+}
+__device__ __forceinline__ double log_main(double x) {  // the table-driven path of log_ (x normal, not near 1)
+  const unsigned long long ix = as_u(x);
+  const double Ln2hi = as_d(LOG_HEAD[0]), Ln2lo = as_d(LOG_HEAD[1]), A0 = as_d(LOG_HEAD[2]), A1 = as_d(LOG_HEAD[3]),
+               A2 = as_d(LOG_HEAD[4]), A3 = as_d(LOG_HEAD[5]), A4 = as_d(LOG_HEAD[6]);
+  const unsigned long long tmp = ix - 0x3fe6000000000000ULL;
+  const unsigned i = (unsigned)(tmp >> 45) & 127;
+  const int k = (int)((long long)tmp >> 52);
+  const unsigned long long iz = ix - (tmp & 0xfff0000000000000ULL);
+  const double invc = as_d(LOG_TAB[2 * i]), logc = as_d(LOG_TAB[2 * i + 1]);
+  const double z = as_d(iz);
+  const double kd = (double)k;
+  const double r = fma_(z, invc, -1.0);
+  const double w = fma_(kd, Ln2hi, logc);
+  const double hi = r + w;
+  const double lo = fma_(kd, Ln2lo, (w - hi) + r);
+  const double r2 = r * r;
+  const double r3 = r * r2;
+  const double q = fma_(fma_(r, A4, A3), r2, fma_(r, A2, A1));
+  const double y = fma_(r3, q, fma_(r2, A0, lo));
+  return y + hi;
+}
+__device__ __forceinline__ bool log_is_near1(double x) {  // 1 - 0x1p-4 <= x < 1 + 0x1.09p-4 and x != 1
+  const unsigned long long ix = as_u(x);
+  return ix - 0x3fee000000000000ULL < 0x3090000000000ULL && ix != 0x3ff0000000000000ULL;
+}
+__device__ __forceinline__ double log_near1(double x) {  // the polynomial path of log_ around 1
+  const double B0 = as_d(LOG_HEAD[7]), B1 = as_d(LOG_HEAD[8]), B2 = as_d(LOG_HEAD[9]), B3 = as_d(LOG_HEAD[10]),
+               B4 = as_d(LOG_HEAD[11]), B5 = as_d(LOG_HEAD[12]), B6 = as_d(LOG_HEAD[13]), B7 = as_d(LOG_HEAD[14]),
+               B8 = as_d(LOG_HEAD[15]), B9 = as_d(LOG_HEAD[16]), B10 = as_d(LOG_HEAD[17]);
+  const double r = x - 1.0;
+  const double r2 = r * r;
+  const double r3 = r * r2;
+  const double p1 = fma_(r2, B3, fma_(r, B2, B1));
+  const double p2 = fma_(r2, B6, fma_(r, B5, B4));
+  const double p3 = fma_(r3, B10, fma_(r2, B9, fma_(r, B8, B7)));
+  const double poly = fma_(fma_(p3, r3, p2), r3, p1);
+  const double t = fma_(r, 134217728.0, r);
+  const double rhi = fma_(-134217728.0, r, t);
+  const double rlo = r - rhi;
+  const double rhi2 = rhi * rhi;
+  const double hi = fma_(rhi2, B0, r);
+  double lo = fma_(rhi2, B0, r - hi);
+  lo = fma_(B0 * rlo, rhi + r, lo);
+  const double y = fma_(poly, r3, lo);
+  return y + hi;
+}
+template <int N>
+__device__ __forceinline__ void log_n(const double (&x)[N], double (&y)[N]) {
+  bool all_main = true, all_near1 = true;
+#pragma unroll
+  for (int u = 0; u < N; ++u) {
+    all_main = all_main && log_is_main(x[u]);
+    all_near1 = all_near1 && log_is_near1(x[u]);
+  }
+  if (all_main) {
+#pragma unroll
+    for (int u = 0; u < N; ++u) y[u] = log_main(x[u]);
+  } else if (all_near1) {
+#pragma unroll
+    for (int u = 0; u < N; ++u) y[u] = log_near1(x[u]);
+  } else {
+#pragma unroll
+    for (int u = 0; u < N; ++u) y[u] = log_(x[u]);
+  }
+}
+template <int N>
+__device__ __forceinline__ void exp_n(const double (&x)[N], double (&y)[N]) {
+  bool all_main = true;
+#pragma unroll
+  for (int u = 0; u < N; ++u) all_main = all_main && exp_is_main(x[u]);
+  if (all_main) {
+#pragma unroll
+    for (int u = 0; u < N; ++u) {
+      double out;
+      exp_core<false>(x[u], 0.0, false, out);
+      y[u] = out;
+    }
+  } else {
+#pragma unroll
+    for (int u = 0; u < N; ++u) y[u] = exp_(x[u]);
+  }
 }
 
 __device__ __forceinline__ double pow_(double x, double y) {

@@ -114,35 +114,66 @@ __global__ void __launch_bounds__(32) k_riem(Geo g, RiemArgs a) {
           n_ptv[u] = G(ptv, kk);
         }
       }
+      // The U levels of the chunk: first the cheap sequential sums, then the exp / log of all U levels as independent
+      // chains (libm::log_n / exp_n), then the sequential elimination steps.  Levels >= km of the last chunk compute
+      // on clamped inputs and are never stored.
+      double pemn[U], pegn[U], pegk[U], dmv[U], gmv[U], dzv[U], pmv[U], pe0v[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        pegk[u] = peg_k;
+        pemn[u] = pem_k + c_delp[u];
+        pegn[u] = peg_k + c_delp[u] * (1.0 - c_q[u]);
+        pem_k = pemn[u];
+        peg_k = pegn[u];
+        dmv[u] = D3 ? c_delp[u] * RGRAV : c_delp[u] / GRAV;
+        gmv[u] = 1.0 / (1.0 - c_cap[u]);
+        dzv[u] = c_zh[u] - zh_k;
+        zh_k = c_zh[u];
+      }
+      if (D3) {
+        double lp[U], lg[U], ka[U], pk3n[U];
+        libm::log_n(pemn, lp);
+        libm::log_n(pegn, lg);
+#pragma unroll
+        for (int u = 0; u < U; ++u) ka[u] = KAPPA * lp[u];
+        libm::exp_n(ka, pk3n);
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          pmv[u] = (pegn[u] - pegk[u]) / (lg[u] - logpg_k);
+          logpg_k = lg[u];
+          const int k = k0 + u;
+          if (k < km) {
+            G(pk3, k + 1) = pk3n[u];
+            if (a.last_call) { G(peln, k + 1) = lp[u]; G(pk, k + 1) = pk3n[u]; G(pe, k + 1) = pemn[u]; }
+          }
+        }
+      } else {
+        double ratio[U], lr[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) ratio[u] = pegn[u] / pegk[u];
+        libm::log_n(ratio, lr);
+#pragma unroll
+        for (int u = 0; u < U; ++u) pmv[u] = (pegn[u] - pegk[u]) / lr[u];
+      }
+      {
+        double targ[U], tl[U], earg[U], ev[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) targ[u] = ((-dmv[u]) / dzv[u] * RDGAS) * c_ptv[u];
+        libm::log_n(targ, tl);
+#pragma unroll
+        for (int u = 0; u < U; ++u) earg[u] = gmv[u] * tl[u];
+        libm::exp_n(earg, ev);
+#pragma unroll
+        for (int u = 0; u < U; ++u) pe0v[u] = ev[u] - pmv[u];
+      }
 #pragma unroll
       for (int u = 0; u < U; ++u) {
         const int k = k0 + u;
         if (k < km) {
-          const double delp_k = c_delp[u];
-          const double pem_n = pem_k + delp_k;
-          const double peg_n = peg_k + delp_k * (1.0 - c_q[u]);
-          double pm_k;
-          if (D3) {
-            const double lp = fv_log(pem_n);
-            const double logpg_n = fv_log(peg_n);
-            const double pk3_n = fv_exp(KAPPA * lp);
-            G(pk3, k + 1) = pk3_n;
-            if (a.last_call) { G(peln, k + 1) = lp; G(pk, k + 1) = pk3_n; G(pe, k + 1) = pem_n; }
-            pm_k = (peg_n - peg_k) / (logpg_n - logpg_k);
-            logpg_k = logpg_n;
-          } else {
-            pm_k = (peg_n - peg_k) / fv_log(peg_n / peg_k);
-          }
-          G(pem, k + 1) = pem_n;
-          G(pm, k) = pm_k;
-          pem_k = pem_n;
-          peg_k = peg_n;
-          const double dm_k = D3 ? delp_k * RGRAV : delp_k / GRAV;
-          const double gm_k = 1.0 / (1.0 - c_cap[u]);
-          const double zh_n = c_zh[u];
-          const double dz_k = zh_n - zh_k;
-          zh_k = zh_n;
-          const double pe0_k = fv_exp(gm_k * fv_log(((-dm_k) / dz_k * RDGAS) * c_ptv[u])) - pm_k;
+          G(pem, k + 1) = pemn[u];
+          G(pm, k) = pmv[u];
+          const double dm_k = dmv[u];
+          const double pe0_k = pe0v[u];
           if (k >= 1) {  // elimination step of level j = k-1
             const int jl = k - 1;
             const double gr = dm_j / dm_k;
@@ -362,23 +393,36 @@ __global__ void __launch_bounds__(32) k_riem(Geo g, RiemArgs a) {
           n_pem[u] = G(pem, kk + 1);
         }
       }
+      // sequential p1 recurrence of the U levels, then their exp / log as independent chains, then the stores
+      double dmv[U], maxp[U], lm[U], earg[U], ev[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int k = max(k0 - u, 0);
+        const double dm_k = D3 ? c_delp[u] * RGRAV : c_delp[u] / GRAV;
+        double p1;
+        if (k == km - 1) {
+          p1 = (YS(k) + 2.0 * YS(k + 1)) * 1.0 / 3.0;
+        } else {
+          const double gr = dm_k / dm_n;
+          const double bb = 2.0 * (1.0 + gr);
+          p1 = (YS(k) + bb * YS(k + 1) + gr * YS(k + 2)) * 1.0 / 3.0 - gr * p1_next;
+        }
+        const double pm_k = c_pm[u];
+        const double aa = p1 + pm_k;
+        maxp[u] = (p_fac * dm_k > aa) ? p_fac * pm_k : aa;
+        dmv[u] = dm_k;
+        p1_next = p1;
+        dm_n = dm_k;
+      }
+      libm::log_n(maxp, lm);
+#pragma unroll
+      for (int u = 0; u < U; ++u) earg[u] = (c_cap[u] - 1.0) * lm[u];
+      libm::exp_n(earg, ev);
 #pragma unroll
       for (int u = 0; u < U; ++u) {
         const int k = k0 - u;
         if (k >= 0) {
-          const double dm_k = D3 ? c_delp[u] * RGRAV : c_delp[u] / GRAV;
-          double p1;
-          if (k == km - 1) {
-            p1 = (YS(k) + 2.0 * YS(k + 1)) * 1.0 / 3.0;
-          } else {
-            const double gr = dm_k / dm_n;
-            const double bb = 2.0 * (1.0 + gr);
-            p1 = (YS(k) + bb * YS(k + 1) + gr * YS(k + 2)) * 1.0 / 3.0 - gr * p1_next;
-          }
-          const double pm_k = c_pm[u];
-          const double aa = p1 + pm_k;
-          const double maxp = (p_fac * dm_k > aa) ? p_fac * pm_k : aa;
-          const double dzn = (-dm_k) * RDGAS * c_ptv[u] * fv_exp((c_cap[u] - 1.0) * fv_log(maxp));
+          const double dzn = (-dmv[u]) * RDGAS * c_ptv[u] * ev[u];
           if (D3) {
             G(delz, k) = dzn;
             zcur = zcur - dzn;
@@ -388,8 +432,6 @@ __global__ void __launch_bounds__(32) k_riem(Geo g, RiemArgs a) {
             G(pef, k + 1) = YS(k + 1) + c_pem[u];
           }
           G(zh, k) = zcur;
-          p1_next = p1;
-          dm_n = dm_k;
         }
       }
     }
