@@ -17,7 +17,7 @@ import sys, numpy as np, torch
 sys.path.insert(0, %r)
 from pace_b200.synthetic import make_engine
 from pace_b200.engine import STATE_3D
-eng = make_engine(48, 1, n_split=2)
+eng = make_engine(int(sys.argv[2]), 1, n_split=2)
 eng.step_dynamics()
 eng.core.sync()
 out = {n: eng.core.t[n].cpu().numpy() for n in STATE_3D}
@@ -35,7 +35,7 @@ def test_fused_matches_three_kernel_version(tmp_path):
     for mode, extra in modes.items():
         env = dict(os.environ, **extra)
         path = str(tmp_path / (mode + ".npz"))
-        subprocess.run([sys.executable, "-c", SCRIPT % ROOT, path], check=True, env=env, timeout=600)
+        subprocess.run([sys.executable, "-c", SCRIPT % ROOT, path, "48"], check=True, env=env, timeout=600)
         res[mode] = np.load(path)
     for mode in modes:
         if mode == "unfused":
@@ -44,3 +44,20 @@ def test_fused_matches_three_kernel_version(tmp_path):
             a, b = res[mode][name], res["unfused"][name]
             assert np.all(np.isfinite(a)), (mode, name)
             assert np.array_equal(a, b), "%s: %s differs: max |d| = %g" % (mode, name, np.max(np.abs(a - b)))
+
+
+@pytest.mark.gpu
+def test_production_kernels_match_unfused_at_c96(tmp_path):
+    """Same comparison for the production configuration only, on 96 x 96 subdomains: 4 column strips (the last one
+    narrower), several row chunks, 3 x 3 DelnFlux / a2b tiles."""
+    res = {}
+    for mode, extra in {"production": {}, "unfused": {"PACE_B200_FVTP2D": "unfused", "PACE_B200_DELNFLUX": "unfused",
+                                                      "PACE_B200_RIEM": "global", "PACE_B200_A2B": "unfused"}}.items():
+        env = dict(os.environ, **extra)
+        path = str(tmp_path / (mode + ".npz"))
+        subprocess.run([sys.executable, "-c", SCRIPT % ROOT, path, "96"], check=True, env=env, timeout=900)
+        res[mode] = np.load(path)
+    for name in res["production"].files:
+        a, b = res["production"][name], res["unfused"][name]
+        assert np.all(np.isfinite(a)), name
+        assert np.array_equal(a, b), "%s differs: max |d| = %g" % (name, np.max(np.abs(a - b)))
