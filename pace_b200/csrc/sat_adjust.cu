@@ -72,15 +72,30 @@ __device__ __forceinline__ double ap1_for_wqs2(double ta) {
   double ap1 = 10.0 * dimf(ta, T_SAT_MIN) + 1.0;
   return fv_min(ap1, QS_LENGTH) - 1;
 }
+// The reference evaluates its saturation tables as functions (no stored table): table(i) costs an exp and a log, and
+// wqs2 asks for table(it), des(it), des(it2), des(it2+1) with des(i) = max(0, table(i+1) - table(i)) — 7 table
+// evaluations of which only 3 are distinct, because it is it2 or it2 + 1.  Each distinct value is computed once
+// here; a pure function evaluated once instead of twice gives the same bits.
+template <bool W>
+__device__ __forceinline__ double sat_table(double i) { return W ? qs_tablew_fn(i) : qs_table2_fn(i); }
+// des2_table / desw_table given table(i) and table(i+1) (the last table entry differences backwards: des_end)
+template <bool W>
+__device__ __forceinline__ double sat_des(double i, double ti, double tip1) {
+  double d = fv_max(0.0, tip1 - ti);
+  if (i == QS_LENGTH - 1) d = fv_max(0.0, ti - sat_table<W>(i - 1));
+  return d;
+}
 // wqs2_fn_w / wqs2_fn_2 (saturation_adjustment.py:501-520)
 template <bool W>
 __device__ void wqs2(double ta, double den, double& wqsat, double& dqdt) {
   double ap1 = ap1_for_wqs2(ta);
-  double it = floor(ap1), it2 = floor(ap1 - 0.5), it2_p1 = it2 + 1;
-  double tab = W ? qs_tablew_fn(it) : qs_table2_fn(it);
-  double des = W ? desw_table(it) : des2_table(it);
-  double des2 = W ? desw_table(it2) : des2_table(it2);
-  double des_p1 = W ? desw_table(it2_p1) : des2_table(it2_p1);
+  double it = floor(ap1), it2 = floor(ap1 - 0.5);
+  const double t0 = sat_table<W>(it2), t1 = sat_table<W>(it2 + 1), t2 = sat_table<W>(it2 + 2);
+  const double des2 = sat_des<W>(it2, t0, t1);
+  const double des_p1 = sat_des<W>(it2 + 1, t1, t2);
+  const bool same = it == it2;  // otherwise it == it2 + 1
+  const double tab = same ? t0 : t1;
+  const double des = same ? des2 : des_p1;
   double es = tab + (ap1 - it) * des;
   double denom = RVGAS * ta * den;
   wqsat = es / denom;
@@ -89,8 +104,8 @@ __device__ void wqs2(double ta, double den, double& wqsat, double& dqdt) {
 }
 template <bool W>
 __device__ double wqs1(double it, double ap1, double ta, double den) {
-  double tab = W ? qs_tablew_fn(it) : qs_table2_fn(it);
-  double des = W ? desw_table(it) : des2_table(it);
+  const double tab = sat_table<W>(it);
+  const double des = sat_des<W>(it, tab, sat_table<W>(it + 1));
   double es = tab + (ap1 - it) * des;
   return es / (RVGAS * ta * den);
 }
