@@ -52,7 +52,7 @@ int update_dz_d(Core& c, double dt) {
         A(qi, 0, 0, k) = prev;
       }
     }
-  });
+  }, "dzd_spline");
   Fvtp2dArgs a;
   a.q = zh; a.crx = crx_i; a.cry = cry_i; a.xfx = xfx_i; a.yfx = yfx_i; a.fx = fx; a.fy = fy; a.hord = c.cfg.hord_tm; a.nk = km + 1;
   if (fvtp2d(c, a)) return 1;
