@@ -235,3 +235,79 @@ class DycoreEngine:
     def compute_preamble(self):
         self.core.call("fv_setup")
         self.core.call("pt_to_potential_density_pt")
+
+
+class HostPipeline:
+    """Steps a HOST-resident model state through a DycoreEngine: the call a coupled driver makes when the rest of the
+    model lives in host memory.  Every step uploads the full DycoreState (STATE_3D + STATE_2D) from pinned host
+    buffers and downloads the updated state; with two device copies of the state the upload of step n+1 and the
+    download of step n-1 run on their own CUDA streams while step n computes (PCIe is full duplex), so the cost per
+    step tends to max(compute, upload, download) instead of their sum.  phis (static) is expected to stay unchanged
+    (ad.zs is derived from it once in set_state)."""
+
+    def __init__(self, eng, names=None):
+        import torch
+
+        self.torch = torch
+        self.eng = eng
+        self.names = list(names) if names is not None else STATE_3D + STATE_2D
+        core = eng.core
+        self.sets = [{n: core.t[n] for n in self.names}, {n: torch.empty_like(core.t[n]) for n in self.names}]
+        for n in self.names:
+            self.sets[1][n].copy_(core.t[n])
+        self.s_up, self.s_down = torch.cuda.Stream(core.device), torch.cuda.Stream(core.device)
+        self.bytes_per_step = sum(t.numel() * t.element_size() for t in self.sets[0].values())
+
+    def pinned_like(self):
+        """A dict of pinned host tensors shaped like the state (one upload or download buffer)."""
+        return {n: self.torch.empty(t.shape, dtype=t.dtype).pin_memory() for n, t in self.sets[0].items()}
+
+    def run(self, steps, host_in, host_out):
+        """steps dycore steps; step n reads its inputs from host_in (dict, or callable n -> dict) and leaves its
+        result in host_out (dict, or callable n -> dict).  Returns after everything has completed."""
+        torch, eng, core = self.torch, self.eng, self.eng.core
+        get_in = host_in if callable(host_in) else (lambda n: host_in)
+        get_out = host_out if callable(host_out) else (lambda n: host_out)
+        main = torch.cuda.current_stream(core.device)
+        up_done = [torch.cuda.Event(), torch.cuda.Event()]
+        step_done = [torch.cuda.Event(), torch.cuda.Event()]
+        down_done = [None, None]
+
+        def upload(n):
+            tgt = self.sets[n % 2]
+            with torch.cuda.stream(self.s_up):
+                if down_done[n % 2] is not None:
+                    self.s_up.wait_event(down_done[n % 2])   # the previous result must have left this copy
+                if n >= 2:
+                    self.s_up.wait_event(step_done[n % 2])
+                src = get_in(n)
+                for name in self.names:
+                    tgt[name].copy_(src[name], non_blocking=True)
+                up_done[n % 2].record(self.s_up)
+
+        upload(0)
+        for n in range(steps):
+            cur = self.sets[n % 2]
+            for name in self.names:
+                core._register(name, cur[name])
+            main.wait_event(up_done[n % 2])
+            if n + 1 < steps:
+                upload(n + 1)
+            eng.step_dynamics()
+            step_done[n % 2].record(main)
+            with torch.cuda.stream(self.s_down):
+                self.s_down.wait_event(step_done[n % 2])
+                dst = get_out(n)
+                for name in self.names:
+                    dst[name].copy_(cur[name], non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record(self.s_down)
+                down_done[n % 2] = ev
+        torch.cuda.synchronize(core.device)
+        for name in self.names:  # leave the engine bound to its original tensors
+            core._register(name, self.sets[0][name])
+        if steps % 2 == 0 and steps > 0:
+            # the last step ran on the second copy: bring its result home
+            for name in self.names:
+                self.sets[0][name].copy_(self.sets[1][name])
+            torch.cuda.synchronize(core.device)

@@ -185,3 +185,33 @@ def test_two_steps_ksplit2_nsplit2_hostemu():
 @pytest.mark.gpu
 def test_two_steps_ksplit2_nsplit2_gpu():
     run_two_steps("cuda", 0.0)
+
+
+@pytest.mark.gpu
+def test_host_pipeline_matches_plain_steps_gpu():
+    """HostPipeline (state streamed from / to pinned host memory on side streams, two device copies): three steps
+    that each start from the same host-resident initial state must each return the reference's one-step result."""
+    import torch
+
+    from pace_b200.engine import HostPipeline
+
+    eng = make_engine("cuda")
+    pipe = HostPipeline(eng)
+    hin = pipe.pinned_like()
+    for name in pipe.names:
+        hin[name].copy_(eng.core.t[name])
+    outs = [pipe.pinned_like() for _ in range(3)]
+    pipe.run(3, hin, lambda n: outs[n])
+    want = load_six("final")
+    for n in range(3):
+        for name in ("u", "v", "w", "delp", "pt", "delz", "qvapor", "pe", "pkz", "q_con"):
+            t = outs[n][name].numpy()
+            for r in range(6):
+                got = np.ascontiguousarray(t[r, :, :, :19].transpose(2, 1, 0))[3:15, 3:15]
+                w = want[r][name][3:15, 3:15]
+                if name not in K_INTERFACE:
+                    got, w = got[:, :, :-1], w[:, :, :-1]
+                assert np.array_equal(got, w), "step %d %s rank %d differs" % (n, name, r)
+    # the engine is bound to its own tensors again and holds the last result
+    assert eng.core.t["u"].data_ptr() == pipe.sets[0]["u"].data_ptr()
+    assert torch.equal(eng.core.t["delp"].cpu(), outs[2]["delp"])
