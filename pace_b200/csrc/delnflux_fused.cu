@@ -157,17 +157,17 @@ __global__ void __launch_bounds__(TX * NTY) k_delnflux_fused(Geo g, DelnFusedArg
 
   // d2_0 on the whole tile + apron (cells outside the arrays: 0, never used).  fx2 / fy2 are not initialised: what a
   // pass leaves unwritten on the rim of the apron is never read by anything that reaches the tile's own cells.
-  for (int lj = ty; lj < H; lj += NTY) {
-    const int j = j0 - AP + lj;
-    for (int li = tx; li < W; li += TX) {
-      const int i = i0 - AP + li;
-      double v = 0.0;
-      if (i >= 0 && j >= 0 && i <= imax && j <= jmax) {
-        const double qv = a.q[base3 + j * sj + i];
-        v = has_mass ? qv : dampk * qv;
-      }
-      d2[lj][li] = v;
+  const int tid = ty * TX + tx;
+  constexpr int NTHR = TX * NTY;
+  for (int n = tid; n < W * H; n += NTHR) {  // flat loops: the tile widths are not multiples of the warp size
+    const int lj = n / W, li = n % W;
+    const int i = i0 - AP + li, j = j0 - AP + lj;
+    double v = 0.0;
+    if (i >= 0 && j >= 0 && i <= imax && j <= jmax) {
+      const double qv = a.q[base3 + j * sj + i];
+      v = has_mass ? qv : dampk * qv;
     }
+    d2[lj][li] = v;
   }
   __syncthreads();
 
@@ -181,10 +181,10 @@ __global__ void __launch_bounds__(TX * NTY) k_delnflux_fused(Geo g, DelnFusedArg
 
   // results: this tile owns the cells [i0, i0+TX) x [j0, j0+TY) and their low-side interfaces; the last tile in x / y
   // also owns the closing interface ie+1 / je+1
-  for (int lj = ty; lj < TY + 1; lj += NTY) {
-    const int j = j0 + lj;
-    for (int li = tx; li < TX + 1; li += TX) {
-      const int i = i0 + li;
+  for (int n = tid; n < (TX + 1) * (TY + 1); n += NTHR) {
+    {
+      const int lj = n / (TX + 1), li = n % (TX + 1);
+      const int i = i0 + li, j = j0 + lj;
       const bool own_i = li < TX || i == ie + 1, own_j = lj < TY || j == je + 1;
       if (!own_i || !own_j) continue;
       const long long o = base3 + j * sj + i;
@@ -210,10 +210,10 @@ __global__ void __launch_bounds__(TX * NTY) k_delnflux_fused(Geo g, DelnFusedArg
   }
   if (a.d2out) {
     // the last d2 on [is-1, ie+1]^2: the tiles on the low / high side also own the row / column just outside
-    for (int lj = ty; lj < TY + 2; lj += NTY) {
-      const int j = j0 - 1 + lj;
-      for (int li = tx; li < TX + 2; li += TX) {
-        const int i = i0 - 1 + li;
+    for (int n = tid; n < (TX + 2) * (TY + 2); n += NTHR) {
+      {
+        const int lj = n / (TX + 2), li = n % (TX + 2);
+        const int i = i0 - 1 + li, j = j0 - 1 + lj;
         const bool own_i = (i >= i0 && i < i0 + TX && i <= ie) || (i == is - 1) || (i == ie + 1 && i <= i0 + TX);
         const bool own_j = (j >= j0 && j < j0 + TY && j <= je) || (j == js - 1) || (j == je + 1 && j <= j0 + TY);
         if (own_i && own_j) a.d2out[base3 + j * sj + i] = d2[j - j0 + AP][i - i0 + AP];
