@@ -169,6 +169,20 @@ __global__ void __launch_bounds__(TX * NTY) k_delnflux_fused(Geo g, DelnFusedArg
     }
     d2[lj][li] = v;
   }
+  // ask for the lines the result phase will read-modify-write (fx, fy, mass) now, so that they arrive in L2 while
+  // the tile iterates in shared memory
+  if (a.accumulate) {
+    for (int n = tid; n < (TX + 1) * (TY + 1); n += NTHR) {
+      const int lj = n / (TX + 1), li = n % (TX + 1);
+      const int i = i0 + li, j = j0 + lj;
+      if (i <= ie + 1 && j <= je + 1 && (li & 3) == 0) {  // one request per 32-byte sector
+        const long long o = base3 + j * sj + i;
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(a.fx + o));
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(a.fy + o));
+        if (has_mass) asm volatile("prefetch.global.L2 [%0];" ::"l"(a.mass + o));
+      }
+    }
+  }
   __syncthreads();
 
   // do cube-corner cells (both a west/east and a south/north tile edge within the apron) enter this tile?
