@@ -155,7 +155,7 @@ typedef struct pace_b200_halo_op {
   int aii, aij, bi, aji, ajj, bj;
 } pace_b200_halo_op;
 
-/* Upload a plan (list of ops between subdomains of this GPU) under plan_id in [0,64). */
+/* Upload a plan (list of ops between subdomains of this GPU) under plan_id in [0,256). */
 int pace_b200_halo_plan_set(void* handle, int plan_id, const void* ops, int n_ops);
 /* HaloUpdater.update() for up to 8 fields (or vector pairs when y_names != NULL) sharing one plan
  * (NDSL/ndsl/halo/updater.py:150-303), levels [0, nk). */

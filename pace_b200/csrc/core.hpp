@@ -35,8 +35,8 @@ struct Core {
   std::map<std::string, double*> scratch;   // library-owned 3-D scratch, allocated on first use
   std::map<std::string, std::vector<double>> hcol;  // host copies of K-columns set via pace_b200_set_column
   std::map<std::string, int> colsize;
-  void* halo_ops[64] = {nullptr};               // device copies of halo plans (pace_b200_halo_plan_set)
-  int halo_nops[64] = {0};
+  void* halo_ops[256] = {nullptr};               // device copies of halo plans (pace_b200_halo_plan_set)
+  int halo_nops[256] = {0};
   std::vector<void*> owned;
   std::string err;
 

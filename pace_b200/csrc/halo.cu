@@ -73,7 +73,7 @@ __global__ void k_halo(Geo g, const HaloOpDev* ops, HaloFields f, int nk, int mo
 #endif
 
 int halo_plan_set(Core& c, int plan_id, const void* host_ops, int n_ops) {
-  if (plan_id < 0 || plan_id >= 64) { c.err = "halo plan id out of range"; return 1; }
+  if (plan_id < 0 || plan_id >= 256) { c.err = "halo plan id out of range"; return 1; }
   static_assert(sizeof(HaloOpDev) == 64, "HaloOpDev layout is part of the C ABI (pace_b200_halo_op)");
   void* dev = nullptr;
   size_t bytes = sizeof(HaloOpDev) * (size_t)n_ops;
@@ -89,7 +89,7 @@ int halo_plan_set(Core& c, int plan_id, const void* host_ops, int n_ops) {
 // mode 0: local update; 1: pack the ops of `plan_id` into buf; 2: unpack them from buf
 static int halo_run(Core& c, int plan_id, const char* const* x_names, const char* const* y_names, int n, int nk,
                     int mode, double* buf) {
-  if (plan_id < 0 || plan_id >= 64 || !c.halo_ops[plan_id]) { c.err = "halo plan not set"; return 1; }
+  if (plan_id < 0 || plan_id >= 256 || !c.halo_ops[plan_id]) { c.err = "halo plan not set"; return 1; }
   if (n < 1 || n > 8) { c.err = "halo_update: 1..8 fields per call"; return 1; }
   HaloFields f;
   f.n = n;

@@ -5,9 +5,10 @@ blocks (24/12/6/3 per GPU at 1/2/4/8 GPUs for the 2x2 layout), every GPU steps i
 exchange is the halo update — point to point between neighbours, no collective on the step path.  Replaces the
 reference's one-MPI-rank-per-subdomain HaloUpdater (NDSL/ndsl/halo/updater.py:217-303, comm/communicator.py) with,
 per halo update and per peer GPU, ONE message: a pack kernel gathers the cells every remote neighbour needs (rotation
-and vector sign applied while packing), torch.distributed sends / receives the messages (NCCL over NVLink on GPUs,
-gloo in the CPU tests), an unpack kernel scatters them; halo cells whose source is on the same GPU are filled by the
-local gather kernel meanwhile.
+and vector sign applied while packing) and, on GPUs, stores them directly into the receiver's buffer over NVLink
+(PeerArena: torch symmetric memory + device-side barrier); an unpack kernel scatters them; halo cells whose source
+is on the same GPU are filled by the local gather kernel meanwhile.  Without peer memory (CPU tests with gloo, or
+PACE_B200_HALO=p2p) the messages travel by torch.distributed isend / irecv.
 """
 from typing import Dict, List
 
@@ -51,11 +52,52 @@ class TorchComm:
         return lambda: [r.wait() for r in reqs]
 
 
+class PeerArena:
+    """Receive buffers that every GPU of the node can write: torch symmetric memory (one allocation per process,
+    mapped into all peers over NVLink / NVSwitch) plus its device-side barrier.  With it a halo update needs no
+    send / receive at all: the pack kernel of the sender stores straight into the receiver's buffer, a stream-ordered
+    barrier across the GPUs tells everybody the stores have landed, the unpack kernel reads the local buffer.  Two
+    halves are used alternately so that the stores of update n+1 cannot overtake a peer still unpacking update n
+    (the barrier of update n+1 separates update n's unpack from update n+2's stores)."""
+
+    def __init__(self, comm, cap_doubles, device):
+        import torch.distributed._symmetric_memory as symm_mem
+
+        self.cap = int(cap_doubles)
+        self.buf = symm_mem.empty(2 * self.cap, dtype=torch.float64, device=device)
+        self.buf.zero_()
+        self.hdl = symm_mem.rendezvous(self.buf, comm.dist.group.WORLD.group_name if comm.group is None else comm.group.group_name)
+        self.ptrs = [int(p) for p in self.hdl.buffer_ptrs]
+        self.rank = comm.rank
+        self.count = 0
+        self.hdl.barrier()
+
+    def next_half(self):
+        self.count += 1
+        return (self.count & 1) * self.cap * 8  # byte offset of the half used by this update
+
+    def barrier(self):
+        self.hdl.barrier()
+
+
 class HaloExchanger:
     """One halo plan (scalar / vector / interface sync) of a DycoreEngine whose neighbours may be remote."""
 
-    def __init__(self, core, plan_id: int, global_ops: List[HaloOp], placement: Placement, comm, local_index):
-        self.core, self.comm, self.plan_id = core, comm, plan_id
+    NQ_MAX = 8  # fields per update (pace_b200_halo_update limit)
+
+    @staticmethod
+    def max_recv_cells(global_ops: List[HaloOp], placement: Placement) -> int:
+        """Largest number of remotely sourced halo cells any GPU receives in one update of this plan."""
+        per = {}
+        for o in global_ops:
+            d, s = placement.owner(o.dst_rank), placement.owner(o.src_rank)
+            if d != s:
+                per[d] = per.get(d, 0) + o.ni * o.nj
+        return max(per.values()) if per else 0
+
+    def __init__(self, core, plan_id: int, global_ops: List[HaloOp], placement: Placement, comm, local_index,
+                 arena=None):
+        self.core, self.comm, self.plan_id, self.arena = core, comm, plan_id, arena
         me = comm.rank if comm is not None else 0
         own = placement.owner
         local = [o for o in global_ops if own(o.dst_rank) == me and own(o.src_rank) == me]
@@ -87,6 +129,20 @@ class HaloExchanger:
             core.set_halo_plan_raw(self.pack_id, pack_rows)
             core.set_halo_plan_raw(self.unpack_id, unpack_rows)
         self._bufs = {}
+        # peer-store mode: one pack plan per peer whose message offsets are those of the PEER's receive layout
+        self.peer_packs = []
+        if arena is not None:
+            for n_peer, p in enumerate(sorted(self.send_seg)):
+                layout = sorted((o for o in global_ops if own(o.dst_rank) == p and own(o.src_rank) != p),
+                                key=lambda o: own(o.src_rank))
+                rows, off = [], 0
+                for o in layout:
+                    if own(o.src_rank) == me:
+                        rows.append((off, local_index[o.src_rank], o))
+                    off += o.ni * o.nj
+                pid = 64 + plan_id * 16 + n_peer
+                core.set_halo_plan_raw(pid, rows)
+                self.peer_packs.append((p, pid))
 
     def _buffers(self, nq, nk):
         key = (nq, nk)
@@ -99,10 +155,21 @@ class HaloExchanger:
     def update(self, x_names, y_names=None, nk=None):
         core = self.core
         nk = core.npz if nk is None else nk
-        if not self.remote:
+        if not self.remote and self.arena is None:
             core.halo_update(self.plan_id, x_names, y_names, nk)
             return
         nq = len(x_names)
+        if self.arena is not None:
+            # direct peer stores over NVLink: pack into the receivers' buffers, barrier, unpack the local buffer
+            ar = self.arena
+            assert self.recv_cells * nq * nk <= ar.cap
+            half = ar.next_half()
+            for p, pid in self.peer_packs:
+                core.halo_pack(pid, x_names, y_names, nk, ar.ptrs[p] + half)
+            core.halo_update(self.plan_id, x_names, y_names, nk)  # same-GPU neighbours meanwhile
+            ar.barrier()
+            core.halo_unpack(self.unpack_id, x_names, y_names, nk, ar.ptrs[ar.rank] + half)
+            return
         sbuf, rbuf = self._buffers(nq, nk)
         core.halo_pack(self.pack_id, x_names, y_names, nk, sbuf)
         per = nq * nk

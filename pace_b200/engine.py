@@ -80,7 +80,20 @@ class DycoreEngine:
         plans = {A3: pl.scalar_plan(False, False, 3), A2: pl.scalar_plan(False, False, 2),
                  B3: pl.scalar_plan(True, True, 3), D3: pl.vector_plan("d", 3), C3: pl.vector_plan("c", 3),
                  SYNC: pl.interface_sync_plan()}
-        self.halo = {pid: HaloExchanger(core, pid, ops, self.placement, comm, local) for pid, ops in plans.items()}
+        # several GPUs: halo messages are stored straight into the receiver's memory over NVLink when torch's symmetric
+        # memory is available (PeerArena); PACE_B200_HALO=p2p keeps the isend / irecv transport (always used on CPU)
+        arena = None
+        if comm is not None and comm.world_size > 1 and core.device.type == "cuda":
+            import os
+
+            if os.environ.get("PACE_B200_HALO", "peer") != "p2p":
+                from .distributed import PeerArena
+
+                cap = max(HaloExchanger.max_recv_cells(ops, self.placement) for ops in plans.values())
+                arena = PeerArena(comm, cap * HaloExchanger.NQ_MAX * (npz + 1), core.device)
+        self.arena = arena
+        self.halo = {pid: HaloExchanger(core, pid, ops, self.placement, comm, local, arena=arena)
+                     for pid, ops in plans.items()}
         self._nk_heat = nk_heat_dissipation(self.cfg, npz)
         self._do_del2cubed = self._nk_heat != 0 and self.cfg["d_con"] > 1.0e-5
         # LagrangianToEulerian.__init__ (remapping.py:347-351): first level with pfull > 10 hPa

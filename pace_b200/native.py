@@ -175,7 +175,8 @@ class NativeCore:
         n = len(x_names)
         xs = (ctypes.c_char_p * n)(*[s.encode() for s in x_names])
         ys = (ctypes.c_char_p * n)(*[s.encode() for s in y_names]) if y_names else None
-        rc = fn(self.handle, plan_id, xs, ys, n, nk, ctypes.c_void_p(buf.data_ptr()))
+        ptr = buf if isinstance(buf, int) else buf.data_ptr()  # a raw device address (peer memory) or a tensor
+        rc = fn(self.handle, plan_id, xs, ys, n, nk, ctypes.c_void_p(ptr))
         if rc != 0:
             raise NativeError("%s: %s" % (what, self.lib.pace_b200_last_error(self.handle).decode()))
 
