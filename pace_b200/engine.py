@@ -90,7 +90,19 @@ class DycoreEngine:
                 from .distributed import PeerArena
 
                 cap = max(HaloExchanger.max_recv_cells(ops, self.placement) for ops in plans.values())
-                arena = PeerArena(comm, cap * HaloExchanger.NQ_MAX * (npz + 1), core.device)
+                try:
+                    arena = PeerArena(comm, cap * HaloExchanger.NQ_MAX * (npz + 1), core.device)
+                except Exception as exc:  # no symmetric memory on this box: every rank falls back together
+                    import warnings
+
+                    warnings.warn("pace_b200: peer-memory halo exchange unavailable (%s); using isend/irecv" % exc)
+                    arena = None
+                import torch
+
+                ok = torch.tensor([1 if arena is not None else 0], device=core.device)
+                comm.dist.all_reduce(ok, op=comm.dist.ReduceOp.MIN, group=comm.group)
+                if int(ok.item()) == 0:
+                    arena = None
         self.arena = arena
         self.halo = {pid: HaloExchanger(core, pid, ops, self.placement, comm, local, arena=arena)
                      for pid, ops in plans.items()}
