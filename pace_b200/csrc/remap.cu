@@ -236,11 +236,14 @@ __device__ void remap_profile(Col& c, int km, int iv, int kord, double qs, doubl
 }
 
 // MapSingle.__call__ on one column: q (in/out, km levels) from source interfaces pe1 to target interfaces pe2
-__device__ void map_single_column(const Pt& p, Col& c, int km, double* q, const double* pe1, const double* pe2, int iv,
-                                  int kord, double qs, double qmin) {
+// keep_dp: c.dp already holds the layer thicknesses of pe1 (previous call with the same pe1).  Returns whether any
+// remapped value is negative (the only case in which fillz changes a column).
+__device__ bool map_single_column(const Pt& p, Col& c, int km, double* q, const double* pe1, const double* pe2, int iv,
+                                  int kord, double qs, double qmin, bool keep_dp = false) {
+  bool any_negative = false;
   for (int k = 0; k < km; ++k) {
     c.a1[k] = A(q, 0, 0, k);
-    c.dp[k] = A(pe1, 0, 0, k + 1) - A(pe1, 0, 0, k);
+    if (!keep_dp) c.dp[k] = A(pe1, 0, 0, k + 1) - A(pe1, 0, 0, k);
   }
   remap_profile(c, km, iv, kord, qs, qmin);
   // lagrangian_contributions (map_single.py:21-81); L = k + lev is the absolute source layer.  Variable-k reads
@@ -271,7 +274,9 @@ __device__ void map_single_column(const Pt& p, Col& c, int km, double* q, const 
       qv = qsum / (pe2k1 - pe2k);
     }
     A(q, 0, 0, k) = qv;
+    any_negative = any_negative || qv < 0.0;
   }
+  return any_negative;
 }
 
 // fix_tracer (fillz.py:16-107) on one column
@@ -437,15 +442,19 @@ int remap_main(Core& c, int nq) {
   launch_ij(st, g, box_compute(g), [=] __device__(const Pt& p) {
     COL_DECL;
     map_single_column(p, col, km, pt, peln, pn2, 1, kord_tm, 0.0, t_min);
+    unsigned negative = 0;  // tracers whose remapped column holds a negative value
     for (int n = 0; n < nq; ++n) {
       // mapn_tracer.py:40-41: every tracer uses kord_tr, entry 5 is forced to 9
       int kord = n == 5 ? 9 : kord_tr;
-      map_single_column(p, col, km, trp.p[n], pe1, pe2, 0, kord, 0.0, 0.0);
+      if (map_single_column(p, col, km, trp.p[n], pe1, pe2, 0, kord, 0.0, 0.0, n > 0)) negative |= 1u << n;
     }
+    // fillz leaves a column without negative values exactly as it is (no borrowing, zfix == 0): only the others
+    // go through it.  It uses col.dp as scratch, so the thicknesses are rebuilt afterwards if it ran.
     if (fill)
-      for (int n = 0; n < nq; ++n) fillz_column(p, col, km, trp.p[n], dp2);
-    map_single_column(p, col, km, w, pe1, pe2, -2, kord_wz, A20(wsd), 0.0);
-    map_single_column(p, col, km, delz, pe1, pe2, 1, kord_wz, 0.0, 0.0);
+      for (int n = 0; n < nq; ++n)
+        if (negative & (1u << n)) fillz_column(p, col, km, trp.p[n], dp2);
+    map_single_column(p, col, km, w, pe1, pe2, -2, kord_wz, A20(wsd), 0.0, nq > 0 && !(fill && negative));
+    map_single_column(p, col, km, delz, pe1, pe2, 1, kord_wz, 0.0, 0.0, true);
     // undo_delz_adjust_and_copy_peln
     for (int k = 0; k < km; ++k) A(delz, 0, 0, k) = -A(delz, 0, 0, k) * A(delp, 0, 0, k);
     for (int k = 0; k <= km; ++k) {
