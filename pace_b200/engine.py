@@ -83,7 +83,7 @@ class DycoreEngine:
         # several GPUs: halo messages are stored straight into the receiver's memory over NVLink when torch's symmetric
         # memory is available (PeerArena); PACE_B200_HALO=p2p keeps the isend / irecv transport (always used on CPU)
         arena = None
-        if comm is not None and comm.world_size > 1 and core.device.type == "cuda":
+        if comm is not None and comm.world_size > 1 and core.device.type == "cuda" and hasattr(comm, "dist"):
             import os
 
             if os.environ.get("PACE_B200_HALO", "peer") != "p2p":
