@@ -35,8 +35,21 @@ template <class QF, class DF>
 __device__ __forceinline__ double adv_along(QF Q, DF D, double ub, double cfl, int pos, int lo, int hi, bool elo,
                                             bool ehi, bool zero_row, int mord) {
   double bl, br, blm, brm;
-  adv_blbr(Q, D, pos, lo, hi, elo, ehi, zero_row, 0, bl, br);
-  adv_blbr(Q, D, pos, lo, hi, elo, ehi, zero_row, -1, blm, brm);
+  if ((elo && pos <= lo + 2) || (ehi && pos >= hi - 1)) {  // an edge formula or the zeroed rows may apply
+    adv_blbr(Q, D, pos, lo, hi, elo, ehi, zero_row, 0, bl, br);
+    adv_blbr(Q, D, pos, lo, hi, elo, ehi, zero_row, -1, blm, brm);
+  } else {
+    // interior: the same edge values, each computed once and without the edge case analysis
+    using namespace ppmc;
+    const double q3 = Q(-3), q2 = Q(-2), qm = Q(-1), q0 = Q(0), qp = Q(1), qpp = Q(2);
+    const double alm = p1 * (q2 + qm) + p2 * (q3 + q0);
+    const double al0 = p1 * (qm + q0) + p2 * (q2 + qp);
+    const double alp = p1 * (q0 + qp) + p2 * (qm + qpp);
+    bl = al0 - q0;
+    br = alp - q0;
+    blm = alm - qm;
+    brm = al0 - qm;
+  }
   double b0 = bl + br, b0m = blm + brm;
   double fx0 = cfl > 0.0 ? (1.0 - cfl) * (brm - cfl * b0m) : (1.0 + cfl) * (bl + cfl * b0);
   bool s0, sm;

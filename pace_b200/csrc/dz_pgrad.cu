@@ -36,14 +36,16 @@ int update_dz_c(Core& c, double dt) {
         return A(vel, di, dj, -1) + (A(vel, di, dj, -1) - A(vel, di, dj, -2)) * ratio;
       }
     };
+    // cells of the compute domain proper never read a corner-filled value (the fills concern the ring around it)
+    const bool plain = p.i >= g.is && p.i <= g.ie && p.j >= g.js && p.j <= g.je;
     auto gzx = [&](int di, int dj) {
       int i = p.i + di, j = p.j + dj;
-      xfill_src(e, 2, i, j);
+      if (!plain) xfill_src(e, 2, i, j);
       return gz0[p.o + (i - p.i) + (j - p.j) * p.sj];
     };
     auto gzy = [&](int di, int dj) {
       int i = p.i + di, j = p.j + dj;
-      yfill_src(e, 2, i, j);
+      if (!plain) yfill_src(e, 2, i, j);
       return gz0[p.o + (i - p.i) + (j - p.j) * p.sj];
     };
     double xfx0 = favg(ut, 0, 0), xfx1 = favg(ut, 1, 0), yfx0 = favg(vt, 0, 0), yfx1 = favg(vt, 0, 1);
