@@ -213,19 +213,15 @@ int divergence_damping(Core& c, double* vort_b, double* delpc, double* ke, const
     });
   }
   const double absdt = fabs(dt);
-  if (dddmp < 1e-5) {
-    launch_ijk(st, g, Box{0, 0, kstart, g.nx + 7, g.ny + 7, nkh}, [=] __device__(const Pt& p) { A0(vort_b) = 0.0; });
-  } else {
-    if (a2b_ord4(c, vort_a, vort_b, kstart, nkh, false)) return 1;
-    // smagorinsky_diffusion_approx: x**2.0 and x**0.5 evaluate as x*x and sqrt(x) in the numpy backend
-    launch_ijk(st, g, Box{is, js, kstart, g.nx + 1, g.ny + 1, nkh}, [=] __device__(const Pt& p) {
-      A0(vort_b) = absdt * fv_sqrt(A0(delpc) * A0(delpc) + A0(vort_b) * A0(vort_b));
-    });
-  }
   const double dd8 = std::pow(da_min_c * c.cfg.d4_bg, (double)(nonzero_nord + 1));
-  // damping_nord_highorder_stencil
+  if (dddmp >= 1e-5 && a2b_ord4(c, vort_a, vort_b, kstart, nkh, false)) return 1;
+  // smagorinsky_diffusion_approx (x**2.0 and x**0.5 evaluate as x*x and sqrt(x) in the numpy backend; vort = 0
+  // where dddmp < 1e-5) and damping_nord_highorder_stencil on the same points: one kernel, vort stays in a register
+  const bool smag = dddmp >= 1e-5;
+  if (!smag) launch_ijk(st, g, Box{0, 0, kstart, g.nx + 7, g.ny + 7, nkh}, [=] __device__(const Pt& p) { A0(vort_b) = 0.0; });
   launch_ijk(st, g, Box{is, js, kstart, g.nx + 1, g.ny + 1, nkh}, [=] __device__(const Pt& p) {
-    double damp = da_min_c * fv_max(d2_bg[p.k], fv_min(0.2, dddmp * fabs(A0(vort_b))));
+    const double vort = smag ? absdt * fv_sqrt(A0(delpc) * A0(delpc) + A0(vort_b) * A0(vort_b)) : A0(vort_b);
+    double damp = da_min_c * fv_max(d2_bg[p.k], fv_min(0.2, dddmp * fabs(vort)));
     double vo = damp * A0(delpc) + dd8 * A0(divg_d);
     A0(vort_b) = vo;
     A0(ke) = A0(ke) + vo;
