@@ -35,7 +35,7 @@ struct March {
   double w[5];        // transported scalar at rows R-4 .. R; the cell being completed is w[2]
   double al_lo;       // MORD < 8: edge value at the lower interface of w[2]
   double dm_m, dm_0;  // MORD >= 8: limited slopes of w[1], w[2]
-  double pq, pbl, pbr;  // previous cell: value and PPM perturbations
+  double pbl, pbr;    // previous cell (w[1]): PPM perturbations
   bool ps;
   __device__ __forceinline__ void push(double v) {
     w[0] = w[1]; w[1] = w[2]; w[2] = w[3]; w[3] = w[4]; w[4] = v;
@@ -106,7 +106,7 @@ constexpr int NSLOT = 3, NSTREAM = 10;
 constexpr int SW = 26;         // cells per warp strip (32 lanes - 2 x 3 apron)
 constexpr int WPB = 1;         // warps per CTA (independent work items)
 constexpr int PITCH = 34;      // doubles per staged row
-constexpr int WARP_SMEM = (NSTREAM * NSLOT + 2) * PITCH;  // doubles per warp
+constexpr int WARP_SMEM = (NSTREAM * NSLOT + 2 + 4) * PITCH;  // doubles per warp
 constexpr unsigned FULL = 0xffffffffu;
 
 __device__ __forceinline__ void cp_async8(double* smem_dst, const double* gmem_src) {
@@ -170,7 +170,7 @@ __device__ __forceinline__ double xsweep_flux(const double* row, int L, int i, d
 }
 
 template <int OIN, int OOUT>
-__global__ void __launch_bounds__(WPB * 32, 16) k_fvtp2d_march(Geo g, MarchArgs a) {
+__global__ void __launch_bounds__(WPB * 32, 18) k_fvtp2d_march(Geo g, MarchArgs a) {
   extern __shared__ double smem[];
   const int L = threadIdx.x & 31, wid = threadIdx.x >> 5;
   // work item of this warp: (strip, row chunk, level, subdomain)
@@ -183,7 +183,8 @@ __global__ void __launch_bounds__(WPB * 32, 16) k_fvtp2d_march(Geo g, MarchArgs 
   const int k = (int)(item % a.nk), t = (int)(item / a.nk);
 
   double* bufC0 = smem + wid * WARP_SMEM;  // q_i row, two copies used alternately (no barrier between the last
-  double* rings = bufC0 + 2 * PITCH;       // read of one step and the write of the next); then the staged input rows
+  double* fxring = bufC0 + 2 * PITCH;      // read of one step and the write of the next); inner x flux of the last
+  double* rings = fxring + 4 * PITCH;      // 4 rows (own lane only: no synchronisation); then the staged input rows
 
   const int is = g.is, ie = g.ie, js = g.js, je = g.je, sj = g.sj;
   const unsigned char ed = g.edge[t];
@@ -211,9 +212,8 @@ __global__ void __launch_bounds__(WPB * 32, 16) k_fvtp2d_march(Geo g, MarchArgs 
 #pragma unroll
   for (int n = 0; n < 5; ++n) mi.w[n] = mo.w[n] = 0.0;
   mi.al_lo = mo.al_lo = mi.dm_m = mi.dm_0 = mo.dm_m = mo.dm_0 = 0.0;
-  mi.pq = mi.pbl = mi.pbr = mo.pq = mo.pbl = mo.pbr = 0.0;
+  mi.pbl = mi.pbr = mo.pbl = mo.pbr = 0.0;
   mi.ps = mo.ps = false;
-  double fxq0 = 0.0, fxq1 = 0.0, fxq2 = 0.0, fxq3 = 0.0;  // inner x flux of rows R, R-1, R-2, R-3
   double fyin_prev = 0.0;                                 // inner y flux at interface R-3
   double yfx_prev = 0.0;                                  // yfx(i, R-3)
 
@@ -283,7 +283,7 @@ __global__ void __launch_bounds__(WPB * 32, 16) k_fvtp2d_march(Geo g, MarchArgs 
       const double area_with_x_flux = ar + xf0 - xf1;
       qj = (qx * ar + fx10 - fx11) / area_with_x_flux;
     }
-    fxq3 = fxq2; fxq2 = fxq1; fxq1 = fxq0; fxq0 = fxin;
+    fxring[(s & 3) * PITCH + L] = fxin;  // needed again at step s + 3 (outer x flux of this row)
     // 3. y sweeps: cell jc = R-2 is complete
     mi.push(qy);
     mo.push(qj);
@@ -301,9 +301,9 @@ __global__ void __launch_bounds__(WPB * 32, 16) k_fvtp2d_march(Geo g, MarchArgs 
         double fyin = 0.0;
         if (col_ok) {
           const double cy = ring(4, slot)[L];
-          fyin = cells_flux<MI>(cy, mi.pq, mi.pbl, mi.pbr, mi.ps, mi.w[2], bli, bri, si);
+          fyin = cells_flux<MI>(cy, mi.w[1], mi.pbl, mi.pbr, mi.ps, mi.w[2], bli, bri, si);
           if (cell_out && (jc <= j_hi || last_chunk)) {
-            const double outer = cells_flux<MO>(cy, mo.pq, mo.pbl, mo.pbr, mo.ps, mo.w[2], blo, bro, so);
+            const double outer = cells_flux<MO>(cy, mo.w[1], mo.pbl, mo.pbr, mo.ps, mo.w[2], blo, bro, so);
             fy[oc] = 0.5 * (outer + fyin) * ring(5, slot)[L];
           }
           const double yf1 = ring(6, slot)[L];
@@ -316,8 +316,8 @@ __global__ void __launch_bounds__(WPB * 32, 16) k_fvtp2d_march(Geo g, MarchArgs 
         }
         fyin_prev = fyin;
       }
-      mi.pq = mi.w[2]; mi.pbl = bli; mi.pbr = bri; mi.ps = si;
-      mo.pq = mo.w[2]; mo.pbl = blo; mo.pbr = bro; mo.ps = so;
+      mi.pbl = bli; mi.pbr = bri; mi.ps = si;
+      mo.pbl = blo; mo.pbr = bro; mo.ps = so;
     }
     // 4. outer x flux on row R-3
     if (s >= 6) {
@@ -327,7 +327,7 @@ __global__ void __launch_bounds__(WPB * 32, 16) k_fvtp2d_march(Geo g, MarchArgs 
       const int orow = o - 3 * sj;
       auto D = [&](int d) { return dxa[orow + d]; };
       const double outer = xsweep_flux<MO>(bufC, L, i, ring(8, slot)[L], D, is, ie, W, E);
-      if (xface_out) fx[orow] = 0.5 * (outer + fxq3) * ring(9, slot)[L];
+      if (xface_out) fx[orow] = 0.5 * (outer + fxring[((s + 1) & 3) * PITCH + L]) * ring(9, slot)[L];
     }
   }
   asm volatile("cp.async.wait_group 0;\n" ::: "memory");
