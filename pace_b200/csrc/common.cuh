@@ -112,12 +112,14 @@ struct LaunchScope {
 };
 
 #ifndef PACE_HOST_EMU
+// The points of one level are numbered row by row and dealt to the threads in that order: no idle lanes at the row
+// ends (box widths such as 199 would leave 11 % of a 32-wide block column idle).
 template <class F>
 __global__ void __launch_bounds__(256) k_ijk(Geo g, Box b, F f) {
-  int i = blockIdx.x * blockDim.x + threadIdx.x;
-  int j = blockIdx.y * blockDim.y + threadIdx.y;
-  if (i >= b.ni || j >= b.nj) return;
-  int k = blockIdx.z % b.nk, t = blockIdx.z / b.nk;
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= b.ni * b.nj) return;
+  const int j = n / b.ni, i = n - j * b.ni;
+  int k = blockIdx.y % b.nk, t = blockIdx.y / b.nk;
   Pt p = make_pt(g, t, b.i0 + i, b.j0 + j, b.k0 + k);
   f(p);
 }
@@ -137,8 +139,8 @@ template <class F>
 inline void launch_ijk(cudaStream_t s, const Geo& g, Box b, F f, const char* label = nullptr) {
   if (b.ni <= 0 || b.nj <= 0 || b.nk <= 0) return;
   LaunchScope scope(s, label);
-  dim3 blk(32, 8, 1);
-  dim3 grd((b.ni + 31) / 32, (b.nj + 7) / 8, b.nk * g.nt);
+  dim3 blk(256, 1, 1);
+  dim3 grd((b.ni * b.nj + 255) / 256, b.nk * g.nt, 1);
   k_ijk<<<grd, blk, 0, s>>>(g, b, f);
 }
 

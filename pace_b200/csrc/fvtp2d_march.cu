@@ -170,7 +170,7 @@ __device__ __forceinline__ double xsweep_flux(const double* row, int L, int i, d
 }
 
 template <int OIN, int OOUT>
-__global__ void __launch_bounds__(WPB * 32, 18) k_fvtp2d_march(Geo g, MarchArgs a) {
+__global__ void __launch_bounds__(WPB * 32, 20) k_fvtp2d_march(Geo g, MarchArgs a) {
   extern __shared__ double smem[];
   const int L = threadIdx.x & 31, wid = threadIdx.x >> 5;
   // work item of this warp: (strip, row chunk, level, subdomain)
