@@ -58,6 +58,36 @@ __global__ void __launch_bounds__(TX * NTY, 4) k_a2b_fused(Geo g, A2bArgs a) {
   const bool edge_x = (W && i0 - 3 <= is + 1) || (E && i0 + TX + 2 >= ie);
   const bool edge_y = (S && j0 - 3 <= js + 1) || (N && j0 + TY + 2 >= je);
 
+  if (!edge_x && !edge_y) {
+    // Interior tile (no tile edge within reach): a thread owns one column and a group of rows, so that the shared
+    // memory addresses are a running row index plus constants and nothing but the interpolation is executed.
+    {
+      const int c = tid % (TX + 1), rg = tid / (TX + 1);  // qx: 33 columns x 7 groups of 6 rows
+      if (rg < 7 && c < ni)
+        for (int lj = rg * 6; lj < min(rg * 6 + 6, QH); ++lj)
+          sqx[lj][c] = b2 * (sq[lj][c + 1] + sq[lj][c + 4]) + b1 * (sq[lj][c + 2] + sq[lj][c + 3]);
+    }
+    {
+      const int c = tid % QW, rg = tid / QW;  // qy: 38 columns x 6 groups of 6 rows
+      if (rg < 6)
+        for (int lj = rg * 6; lj < min(rg * 6 + 6, nj); ++lj)
+          sqy[lj][c] = b2 * (sq[lj + 1][c] + sq[lj + 4][c]) + b1 * (sq[lj + 2][c] + sq[lj + 3][c]);
+    }
+    __syncthreads();
+    {
+      const int c = tid % (TX + 1), rg = tid / (TX + 1);  // qout: 33 columns x 7 groups of 5 rows
+      if (rg < 7 && c < ni) {
+        double* out = a.qout + base3 + j0 * sj + i0 + c;
+        for (int lj = rg * 5; lj < min(rg * 5 + 5, nj); ++lj) {
+          const double qxx = a2 * (sqx[lj + 1][c] + sqx[lj + 4][c]) + a1 * (sqx[lj + 2][c] + sqx[lj + 3][c]);
+          const double qyy = a2 * (sqy[lj][c + 1] + sqy[lj][c + 4]) + a1 * (sqy[lj][c + 2] + sqy[lj][c + 3]);
+          out[lj * sj] = 0.5 * (qxx + qyy);
+        }
+      }
+    }
+    return;
+  }
+
   // qx(i, j) on i in [i0, i0+ni), j in [j0-2, j0+nj+1] (rows beyond the arrays are never used)
   for (int n = tid; n < QH * (TX + 1); n += NTHR) {
     {
