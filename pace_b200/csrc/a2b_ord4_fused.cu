@@ -88,12 +88,23 @@ __global__ void __launch_bounds__(TX * NTY, 4) k_a2b_fused(Geo g, A2bArgs a) {
     return;
   }
 
-  // qx(i, j) on i in [i0, i0+ni), j in [j0-2, j0+nj+1] (rows beyond the arrays are never used)
-  for (int n = tid; n < QH * (TX + 1); n += NTHR) {
+  // Tiles within reach of a tile edge: the interpolation of the interior path everywhere it applies, and the case
+  // analysis only on the (at most four) columns / rows next to the edges.
+  auto xspecial = [&](int i) { return edge_x && ((W && (i == is || i == is + 1)) || (E && (i == ie || i == ie + 1))); };
+  auto yspecial = [&](int j) { return edge_y && ((S && (j == js || j == js + 1)) || (N && (j == je || j == je + 1))); };
+  const int xcand[4] = {is, is + 1, ie, ie + 1}, ycand[4] = {js, js + 1, je, je + 1};
+  {
+    const int c = tid % (TX + 1), rg = tid / (TX + 1);  // qx, plain columns
+    if (rg < 7 && c < ni && !xspecial(i0 + c))
+      for (int lj = rg * 6; lj < min(rg * 6 + 6, QH); ++lj)
+        if (j0 - 3 + lj <= jmax) sqx[lj][c] = b2 * (sq[lj][c + 1] + sq[lj][c + 4]) + b1 * (sq[lj][c + 2] + sq[lj][c + 3]);
+  }
+  // qx(i, j) on the special columns, j in [j0-3, j0+TY+2] (rows beyond the arrays are never used)
+  for (int n = tid; n < QH * 4; n += NTHR) {
     {
-      const int lj = n / (TX + 1), li = n % (TX + 1);
-      const int i = i0 + li, j = j0 - 3 + lj;
-      if (li >= ni || j > jmax) continue;
+      const int lj = n >> 2, i = xcand[n & 3], li = i - i0;
+      const int j = j0 - 3 + lj;
+      if (li < 0 || li >= ni || !xspecial(i) || j > jmax) continue;
       double v;
       if (edge_x && W && i == is) {  // qx_edge_west
         double g_in = DXA(i + 1, j) / DXA(i, j);
@@ -125,12 +136,18 @@ __global__ void __launch_bounds__(TX * NTY, 4) k_a2b_fused(Geo g, A2bArgs a) {
       sqx[lj][li] = v;
     }
   }
-  // qy(i, j) on i in [i0-2, i0+ni+1], j in [j0, j0+nj)
-  for (int n = tid; n < (TY + 1) * QW; n += NTHR) {
+  {
+    const int c = tid % QW, rg = tid / QW;  // qy, plain rows
+    if (rg < 6 && i0 - 3 + c <= imax)
+      for (int lj = rg * 6; lj < min(rg * 6 + 6, nj); ++lj)
+        if (!yspecial(j0 + lj)) sqy[lj][c] = b2 * (sq[lj + 1][c] + sq[lj + 4][c]) + b1 * (sq[lj + 2][c] + sq[lj + 3][c]);
+  }
+  // qy(i, j) on the special rows, i in [i0-3, i0+TX+2]
+  for (int n = tid; n < 4 * QW; n += NTHR) {
     {
-      const int lj = n / QW, li = n % QW;
-      const int i = i0 - 3 + li, j = j0 + lj;
-      if (lj >= nj || i > imax) continue;
+      const int li = n % QW, j = ycand[n / QW], lj = j - j0;
+      const int i = i0 - 3 + li;
+      if (lj < 0 || lj >= nj || !yspecial(j) || i > imax) continue;
       double v;
       if (edge_y && S && j == js) {  // qy_edge_south
         double g_in = DYA(i, j + 1) / DYA(i, j);
@@ -204,11 +221,33 @@ __global__ void __launch_bounds__(TX * NTY, 4) k_a2b_fused(Geo g, A2bArgs a) {
     }
   };
 
-  for (int n = tid; n < (TY + 1) * (TX + 1); n += NTHR) {
+  {
+    const int c = tid % (TX + 1), rg = tid / (TX + 1);  // qout, points on plain columns and rows
+    if (rg < 7 && c < ni && !xspecial(i0 + c)) {
+      double* outp = a.qout + base3 + j0 * sj + i0 + c;
+      for (int lj = rg * 5; lj < min(rg * 5 + 5, nj); ++lj) {
+        if (yspecial(j0 + lj)) continue;
+        const double qxx = a2 * (sqx[lj + 1][c] + sqx[lj + 4][c]) + a1 * (sqx[lj + 2][c] + sqx[lj + 3][c]);
+        const double qyy = a2 * (sqy[lj][c + 1] + sqy[lj][c + 4]) + a1 * (sqy[lj][c + 2] + sqy[lj][c + 3]);
+        outp[lj * sj] = 0.5 * (qxx + qyy);
+      }
+    }
+  }
+  // the points on special columns (all rows), then those on special rows (plain columns only)
+  for (int n = tid; n < 4 * (TY + 1) + 4 * (TX + 1); n += NTHR) {
     {
-      const int lj = n / (TX + 1), li = n % (TX + 1);
+      int li, lj;
+      if (n < 4 * (TY + 1)) {
+        li = xcand[n & 3] - i0;
+        lj = n >> 2;
+        if (li < 0 || li >= ni || lj >= nj || !xspecial(i0 + li)) continue;
+      } else {
+        const int m = n - 4 * (TY + 1);
+        lj = ycand[m & 3] - j0;
+        li = m >> 2;
+        if (lj < 0 || lj >= nj || li >= ni || !yspecial(j0 + lj) || xspecial(i0 + li)) continue;
+      }
       const int i = i0 + li, j = j0 + lj;
-      if (li >= ni || lj >= nj) continue;
       double out;
       if ((edge_x || edge_y) && ((W && i == is) || (E && i == ie + 1) || (S && j == js) || (N && j == je + 1))) {
         out = qout_edge(i, j);
