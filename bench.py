@@ -232,6 +232,36 @@ def main():
                 "ms_per_launch": per_launch_ms, "share_of_step": tot / args.steps / ms,
                 "labelled_kernels_ms_per_step": {k: v[1] / args.steps for k, v in sorted(prof.items())}}
 
+    # the sections the reference's own Timer brackets (fv_dynamics.py:551-590), on one extra step outside the timed
+    # region, clocked with CUDA events on the launching stream; the acoustic substep's algorithmic GB/s is the second
+    # half of BASELINE.json's metric: 97 field passes x 8 B = 776 B per cell per substep
+    class EventTimer:
+        def __init__(self):
+            self.ev = {}
+
+        def start(self, name):
+            e = torch.cuda.Event(enable_timing=True)
+            e.record()
+            self.ev.setdefault(name, []).append([e, None])
+
+        def stop(self, name):
+            e = torch.cuda.Event(enable_timing=True)
+            e.record()
+            self.ev[name][-1][1] = e
+
+        def ms(self):
+            return {k: sum(a.elapsed_time(b) for a, b in v) for k, v in self.ev.items()}
+
+    et = EventTimer()
+    eng.step_dynamics(timer=et)
+    fence()
+    sect = {k: max_over_ranks(v) for k, v in sorted(et.ms().items())}
+    sub_ms = sect["DynCore"] / N_SPLIT
+    sub_bytes = cells / world * 776.0
+    acoustic = {"ms_per_substep": sub_ms, "algorithmic_bytes_per_substep": sub_bytes, "bytes_per_cell": 776,
+                "achieved": sub_bytes / (sub_ms / 1000.0) / 1e9, "unit": "GB/s", "peak": pk["hbm_gbs"],
+                "frac": sub_bytes / (sub_ms / 1000.0) / 1e9 / pk["hbm_gbs"], "sections_ms": sect}
+
     # end-to-end through the public API for a host-resident model (pace_b200.engine.HostPipeline): every step uploads
     # the full DycoreState from pinned host memory and downloads the updated state; uploads / downloads of
     # neighbouring steps overlap the compute on their own streams.  Pipeline fill and drain are inside the timing.
@@ -269,7 +299,8 @@ def main():
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic (C12 reference fixture resampled, see pace_b200/synthetic.py)",
         "config": {"workload": desc, "cells": cells, "placement": "%d subdomains per GPU, halo exchange by NCCL send/recv" % (n_sub // world) if world > 1 else "%d subdomains on one GPU" % n_sub, "l2": "working set (%.0f GB) >> L2, no flush needed" % (cells * 8 * 130 / 1e9)},
-        "gpu_launches": int(launches), "clocks": sampler.summary(), "roofline": roof, "cpu_baseline": cpu, "e2e": e2e,
+        "gpu_launches": int(launches), "clocks": sampler.summary(), "roofline": roof, "acoustic_substep": acoustic,
+        "cpu_baseline": cpu, "e2e": e2e,
     }
     if rank == 0:
         print(json.dumps(line))

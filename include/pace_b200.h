@@ -120,6 +120,13 @@ int pace_b200_math_eval(void* handle, int op, int n, const double* x, const doub
 int pace_b200_map_single(void* handle, const char* q, const char* pe1, const char* pe2, const char* qs, int iv,
                          int kord, int x_interface, int y_interface, double qmin);
 
+/* The same MapSingle.__call__ in the reference's single-precision mode (PACE_FLOAT_PRECISION=32: Float = np.float32,
+ * NDSL/ndsl/dsl/typing.py:25-45; every field, literal and intermediate of map_single.py / remap_profile.py is then
+ * float32).  The handle's registry holds fp64 fields, so the fp32 fields are passed as raw device pointers; they use
+ * the handle's layout ([t][k][j][i], row stride pace_b200_row_stride(nx) ELEMENTS, npz + 1 levels).  qs may be NULL. */
+int pace_b200_map_single_f32(void* handle, float* q, const float* pe1, const float* pe2, const float* qs, int iv,
+                             int kord, int x_interface, int y_interface, float qmin);
+
 /* LagrangianToEulerian.__call__ (pyFV3/stencils/remapping.py:522-731) in two pieces around the saturation
  * adjustment: remap_main = init_pe .. copy_from_below (13 MapSingle + fillz); remap_finish = moist_pt_last_step
  * (last_step) or pt /= pkz. */

@@ -2,7 +2,9 @@
 columns), produced by the UNMODIFIED reference class pyFV3.stencils.map_single.MapSingle (numpy backend) in this
 container.
 
-    python oracle/gen_mapsingle_golden.py       ->  tests/golden/mapsingle_l91.npz
+    python oracle/gen_mapsingle_golden.py          ->  tests/golden/mapsingle_l91.npz       (fp64)
+    python oracle/gen_mapsingle_golden.py --fp32   ->  tests/golden/mapsingle_l91_f32.npz   (PACE_FLOAT_PRECISION=32:
+                                                       the reference's Float is np.float32, ndsl/dsl/typing.py:25-45)
 
 Columns (seed 0): pe1 = cumulative sum of positive random layer thicknesses from ptop to ps in [950, 1030] hPa,
 pe2 = ptop + (ps - ptop) * eta_k with a smooth monotone eta (synthetic L91 coordinate), q smooth + noise (positive
@@ -13,6 +15,9 @@ import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
+FP32 = "--fp32" in sys.argv
+if FP32:
+    os.environ["PACE_FLOAT_PRECISION"] = "32"  # read when ndsl.dsl.typing is imported
 from oracle.refshim.bootstrap import bootstrap  # noqa: E402
 
 bootstrap()
@@ -71,11 +76,16 @@ def main():
     quantity_factory = QuantityFactory.from_backend(sizer=sizer, backend=backend)
     stencil_factory = ndsl.dsl.stencil.StencilFactory(config=stencil_config, grid_indexing=grid_indexing)
 
-    pe1, pe2, q, qpos, qs = columns()
+    from ndsl.dsl.typing import Float
+
+    assert np.dtype(Float) == (np.float32 if FP32 else np.float64)
+    pe1, pe2, q, qpos, qs = (a.astype(Float) for a in columns())
+    if FP32:
+        pe2[:, :, NZ] = pe1[:, :, NZ]  # keep the exact common bottom after rounding
     out = {"pe1": pe1, "pe2": pe2, "q": q, "qpos": qpos, "qs": qs}
 
     def quantity(a, dims):
-        qq = quantity_factory.zeros(dims, units="unknown", dtype=float)
+        qq = quantity_factory.zeros(dims, units="unknown", dtype=Float)
         np.asarray(qq.data)[...] = a
         return qq
 
@@ -86,13 +96,14 @@ def main():
         p1 = quantity(pe1, [X_DIM, Y_DIM, Z_DIM])
         p2 = quantity(pe2, [X_DIM, Y_DIM, Z_DIM])
         if with_qs:
-            ms(q1.data, p1.data, p2.data, qs=quantity(qs, [X_DIM, Y_DIM]).data, qmin=qmin)
+            ms(q1.data, p1.data, p2.data, qs=quantity(qs, [X_DIM, Y_DIM]).data, qmin=Float(qmin))
         else:
-            ms(q1.data, p1.data, p2.data, qmin=qmin)
+            ms(q1.data, p1.data, p2.data, qmin=Float(qmin))
         key = "out_kord%d_iv%d" % (kord, iv)
         out[key] = np.asarray(q1.data).copy()
+        assert out[key].dtype == np.dtype(Float)
         print(key, float(np.abs(out[key][3:15, 3:15, :NZ] - src[3:15, 3:15, :NZ]).max()), flush=True)
-    np.savez_compressed(os.path.join(ROOT, "tests", "golden", "mapsingle_l91.npz"), **out)
+    np.savez_compressed(os.path.join(ROOT, "tests", "golden", "mapsingle_l91_f32.npz" if FP32 else "mapsingle_l91.npz"), **out)
 
 
 if __name__ == "__main__":

@@ -97,6 +97,7 @@ def bind(lib):
     lib.pace_b200_profile_report.argtypes = [ctypes.c_char_p, _I]
     lib.pace_b200_math_eval.argtypes = [vp, _I, _I, vp, vp, vp]
     lib.pace_b200_sat_adjust.argtypes = [vp, ctypes.POINTER(SatAdjConfig), _D, _I, _I]
+    lib.pace_b200_map_single_f32.argtypes = [vp, vp, vp, vp, vp, _I, _I, _I, _I, ctypes.c_float]
     for name, extra in MODULE_CALLS.items():
         fn = getattr(lib, "pace_b200_" + name)
         fn.argtypes = [vp] + extra
@@ -145,5 +146,5 @@ MODULE_CALLS = {
 }
 
 EXPORTS = ["pace_b200_row_stride", "pace_b200_create", "pace_b200_destroy", "pace_b200_last_error",
-           "pace_b200_set_stream", "pace_b200_set_field", "pace_b200_set_column", "pace_b200_halo_plan_set", "pace_b200_halo_update", "pace_b200_halo_pack", "pace_b200_halo_unpack", "pace_b200_math_eval", "pace_b200_sat_adjust", "pace_b200_launch_count", "pace_b200_profile_enable",
+           "pace_b200_set_stream", "pace_b200_set_field", "pace_b200_set_column", "pace_b200_halo_plan_set", "pace_b200_halo_update", "pace_b200_halo_pack", "pace_b200_halo_unpack", "pace_b200_math_eval", "pace_b200_sat_adjust", "pace_b200_map_single_f32", "pace_b200_launch_count", "pace_b200_profile_enable",
            "pace_b200_profile_report"] + ["pace_b200_" + n for n in MODULE_CALLS]

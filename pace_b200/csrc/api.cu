@@ -259,6 +259,13 @@ int pace_b200_map_single(void* h, const char* q, const char* pe1, const char* pe
   if (!c->err.empty()) return 1;
   return finish(c, map_single(*c, qp, p1, p2, qsp, iv, kord, x_interface != 0, y_interface != 0, qmin));
 }
+int pace_b200_map_single_f32(void* h, float* q, const float* pe1, const float* pe2, const float* qs, int iv, int kord,
+                             int x_interface, int y_interface, float qmin) {
+  Core* c = (Core*)h;
+  c->err.clear();
+  if (!q || !pe1 || !pe2) { c->err = "map_single_f32: null field pointer"; return 1; }
+  return finish(c, map_single_f32(*c, q, pe1, pe2, qs, iv, kord, x_interface != 0, y_interface != 0, qmin));
+}
 int pace_b200_math_eval(void* h, int op, int n, const double* x, const double* y, double* out) {
   ENTRY(math_eval(*c, op, n, x, y, out))
 }

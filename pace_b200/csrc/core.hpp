@@ -67,6 +67,8 @@ int tracer_swap_dp(Core& c);
 int math_eval(Core& c, int op, int n, const double* x, const double* y, double* out);
 int map_single(Core& c, double* q, const double* pe1, const double* pe2, const double* qs, int iv, int kord, bool xi,
                bool yi, double qmin);
+int map_single_f32(Core& c, float* q, const float* pe1, const float* pe2, const float* qs, int iv, int kord, bool xi,
+                   bool yi, float qmin);
 int remap_main(Core& c, int nq);
 int remap_finish(Core& c, int last_step);
 struct SatCfg;

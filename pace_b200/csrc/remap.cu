@@ -18,88 +18,97 @@ namespace {
 
 constexpr int KMAX = 96;  // thread-local column length (npz + 1 <= KMAX; 79 and 91 level configurations)
 
-struct Col {
-  double q[KMAX + 1], gam[KMAX + 1], a1[KMAX], a2[KMAX], a3[KMAX], a4[KMAX], dp[KMAX];
+template <class T>
+struct ColT {
+  T q[KMAX + 1], gam[KMAX + 1], a1[KMAX], a2[KMAX], a3[KMAX], a4[KMAX], dp[KMAX];
   bool extm[KMAX], ext5[KMAX], ext6[KMAX];
 };
+using Col = ColT<double>;
 
-__device__ __forceinline__ void a4_from(double a1, double a2, double a3, double& a4) { a4 = 3.0 * (2.0 * a1 - (a2 + a3)); }
+template <class T>
+__device__ __forceinline__ void a4_from(T a1, T a2, T a3, T& a4) { a4 = T(3.0) * (T(2.0) * a1 - (a2 + a3)); }
 
 // remap_profile.py:88-111 posdef_constraint_iv1
-__device__ __forceinline__ void posdef_iv1(double& a1, double& a2, double& a3, double& a4) {
-  double da1 = a3 - a2, da2 = da1 * da1, a6da = a4 * da1;
-  if (((a1 - a2) * (a1 - a3)) >= 0.0) { a2 = a1; a3 = a1; a4 = 0.0; }
-  else if (a6da < -1.0 * da2) { a4 = 3.0 * (a2 - a1); a3 = a2 - a4; }
-  else if (a6da > da2) { a4 = 3.0 * (a3 - a1); a2 = a3 - a4; }
+template <class T>
+__device__ __forceinline__ void posdef_iv1(T& a1, T& a2, T& a3, T& a4) {
+  T da1 = a3 - a2, da2 = da1 * da1, a6da = a4 * da1;
+  if (((a1 - a2) * (a1 - a3)) >= T(0.0)) { a2 = a1; a3 = a1; a4 = T(0.0); }
+  else if (a6da < -T(1.0) * da2) { a4 = T(3.0) * (a2 - a1); a3 = a2 - a4; }
+  else if (a6da > da2) { a4 = T(3.0) * (a3 - a1); a2 = a3 - a4; }
 }
 // remap_profile.py:56-85 posdef_constraint_iv0
-__device__ __forceinline__ void posdef_iv0(double& a1, double& a2, double& a3, double& a4) {
-  if (a1 <= 0.0) { a2 = a1; a3 = a1; a4 = 0.0; }
-  else if (fabs(a3 - a2) < -a4 && (a1 + 0.25 * ((a3 - a2) * (a3 - a2)) / a4 + a4 * (1.0 / 12.0)) < 0.0) {
-    if (a1 < a3 && a1 < a2) { a3 = a1; a2 = a1; a4 = 0.0; }
-    else if (a3 > a2) { a4 = 3.0 * (a2 - a1); a3 = a2 - a4; }
-    else { a4 = 3.0 * (a3 - a1); a2 = a3 - a4; }
+template <class T>
+__device__ __forceinline__ void posdef_iv0(T& a1, T& a2, T& a3, T& a4) {
+  if (a1 <= T(0.0)) { a2 = a1; a3 = a1; a4 = T(0.0); }
+  else if (fabs(a3 - a2) < -a4 && (a1 + T(0.25) * ((a3 - a2) * (a3 - a2)) / a4 + a4 * (T(1.0) / T(12.0))) < T(0.0)) {
+    if (a1 < a3 && a1 < a2) { a3 = a1; a2 = a1; a4 = T(0.0); }
+    else if (a3 > a2) { a4 = T(3.0) * (a2 - a1); a3 = a2 - a4; }
+    else { a4 = T(3.0) * (a3 - a1); a2 = a3 - a4; }
   }
 }
 // remap_profile.py:114-135 remap_constraint
-__device__ __forceinline__ void remap_constraint(double& a1, double& a2, double& a3, double& a4, bool extm) {
-  double da1 = a3 - a2, da2 = da1 * da1, a6da = a4 * da1;
-  if (extm) { a2 = a1; a3 = a1; a4 = 0.0; }
-  else if (a6da < -da2) { a4 = 3.0 * (a2 - a1); a3 = a2 - a4; }
-  else if (a6da > da2) { a4 = 3.0 * (a3 - a1); a2 = a3 - a4; }
+template <class T>
+__device__ __forceinline__ void remap_constraint(T& a1, T& a2, T& a3, T& a4, bool extm) {
+  T da1 = a3 - a2, da2 = da1 * da1, a6da = a4 * da1;
+  if (extm) { a2 = a1; a3 = a1; a4 = T(0.0); }
+  else if (a6da < -da2) { a4 = T(3.0) * (a2 - a1); a3 = a2 - a4; }
+  else if (a6da > da2) { a4 = T(3.0) * (a3 - a1); a2 = a3 - a4; }
 }
-__device__ __forceinline__ double lim3_min(double a, double b, double c) {  // a if a<b and a<c else b if b<c else c
+template <class T>
+__device__ __forceinline__ T lim3_min(T a, T b, T c) {  // a if a<b and a<c else b if b<c else c
   return (a < b && a < c) ? a : (b < c ? b : c);
 }
-__device__ __forceinline__ double lim3_max(double a, double b, double c) {
+template <class T>
+__device__ __forceinline__ T lim3_max(T a, T b, T c) {
   return (a > b && a > c) ? a : (b > c ? b : c);
 }
 
 // RemapProfile.__call__ (remap_profile.py:644-697) on one column.  in: c.a1 (cell means), c.dp; out: c.a2..a4
-__device__ void remap_profile(Col& c, int km, int iv, int kord, double qs, double qmin) {
-  double* q = c.q;
-  double* gam = c.gam;
-  const double *a1 = c.a1, *delp = c.dp;
+template <class T>
+__device__ void remap_profile(ColT<T>& c, int km, int iv, int kord, T qs, T qmin) {
+  T* q = c.q;
+  T* gam = c.gam;
+  const T *a1 = c.a1, *delp = c.dp;
   // ---- set_initial_vals (domain: km+1 interface levels) ----
   if (iv != -2) {
-    double gr = delp[1] / delp[0];
-    double bet = gr * (gr + 0.5);
-    q[0] = ((gr + gr) * (gr + 1.0) * a1[0] + a1[1]) / bet;
-    gam[0] = (1.0 + gr * (gr + 1.5)) / bet;
+    T gr = delp[1] / delp[0];
+    T bet = gr * (gr + T(0.5));
+    q[0] = ((gr + gr) * (gr + T(1.0)) * a1[0] + a1[1]) / bet;
+    gam[0] = (T(1.0) + gr * (gr + T(1.5))) / bet;
     for (int k = 1; k < km; ++k) {
-      double d4 = delp[k - 1] / delp[k];
-      bet = 2.0 + d4 + d4 - gam[k - 1];
-      q[k] = (3.0 * (a1[k - 1] + d4 * a1[k]) - q[k - 1]) / bet;
+      T d4 = delp[k - 1] / delp[k];
+      bet = T(2.0) + d4 + d4 - gam[k - 1];
+      q[k] = (T(3.0) * (a1[k - 1] + d4 * a1[k]) - q[k - 1]) / bet;
       gam[k] = d4 / bet;
     }
     {
-      double d4 = delp[km - 2] / delp[km - 1];
-      double a_bot = 1.0 + d4 * (d4 + 1.5);
-      q[km] = (2.0 * d4 * (d4 + 1.0) * a1[km - 1] + a1[km - 2] - a_bot * q[km - 1]) / (d4 * (d4 + 0.5) - a_bot * gam[km - 1]);
+      T d4 = delp[km - 2] / delp[km - 1];
+      T a_bot = T(1.0) + d4 * (d4 + T(1.5));
+      q[km] = (T(2.0) * d4 * (d4 + T(1.0)) * a1[km - 1] + a1[km - 2] - a_bot * q[km - 1]) / (d4 * (d4 + T(0.5)) - a_bot * gam[km - 1]);
     }
     for (int k = km - 1; k >= 0; --k) q[k] = q[k] - gam[k] * q[k + 1];
   } else {
-    q[0] = 1.5 * a1[0];
-    gam[1] = 0.5;
+    q[0] = T(1.5) * a1[0];
+    gam[1] = T(0.5);
     {
-      double gr = delp[0] / delp[1];
-      double bet = 2.0 + gr + gr - gam[1];
-      q[1] = (3.0 * (a1[0] + a1[1]) - q[0]) / bet;
+      T gr = delp[0] / delp[1];
+      T bet = T(2.0) + gr + gr - gam[1];
+      q[1] = (T(3.0) * (a1[0] + a1[1]) - q[0]) / bet;
     }
     for (int k = 2; k < km; ++k) {
-      double old_gr = delp[k - 2] / delp[k - 1];
-      double old_bet = 2.0 + old_gr + old_gr - gam[k - 1];
+      T old_gr = delp[k - 2] / delp[k - 1];
+      T old_bet = T(2.0) + old_gr + old_gr - gam[k - 1];
       gam[k] = old_gr / old_bet;
     }
     for (int k = 2; k < km - 1; ++k) {
-      double gr = delp[k - 1] / delp[k];
-      double bet = 2.0 + gr + gr - gam[k];
-      q[k] = (3.0 * (a1[k - 1] + a1[k]) - q[k - 1]) / bet;
+      T gr = delp[k - 1] / delp[k];
+      T bet = T(2.0) + gr + gr - gam[k];
+      q[k] = (T(3.0) * (a1[k - 1] + a1[k]) - q[k - 1]) / bet;
     }
     {
       int k = km - 1;
-      double gr = delp[k - 1] / delp[k];
-      q[k] = (3.0 * (a1[k - 1] + a1[k]) - gr * qs - q[k - 1]) / (2.0 + gr + gr - gam[k]);
+      T gr = delp[k - 1] / delp[k];
+      q[k] = (T(3.0) * (a1[k - 1] + a1[k]) - gr * qs - q[k - 1]) / (T(2.0) + gr + gr - gam[k]);
     }
     q[km] = qs;
     for (int k = km - 2; k >= 0; --k) q[k] = q[k] - gam[k + 1] * q[k + 1];
@@ -115,7 +124,7 @@ __device__ void remap_profile(Col& c, int km, int iv, int kord, double qs, doubl
     if (q[k] <= tmpmin(k)) q[k] = tmpmin(k);
   }
   for (int k = 2; k < km - 1; ++k) {
-    double tmp = tmpmax(k), tmp2 = tmpmin(k);
+    T tmp = tmpmax(k), tmp2 = tmpmin(k);
     if ((gam[k - 1] * gam[k + 1]) > 0) {
       if (q[k] >= tmp) q[k] = tmp;
       if (q[k] <= tmp2) q[k] = tmp2;
@@ -123,7 +132,7 @@ __device__ void remap_profile(Col& c, int km, int iv, int kord, double qs, doubl
       if (q[k] <= tmp2) q[k] = tmp2;
     } else {
       if (q[k] >= tmp) q[k] = tmp;
-      if (iv == 0 && q[k] < 0.0) q[k] = 0.0;
+      if (iv == 0 && q[k] < T(0.0)) q[k] = T(0.0);
     }
   }
   {
@@ -131,34 +140,34 @@ __device__ void remap_profile(Col& c, int km, int iv, int kord, double qs, doubl
     if (q[k] >= tmpmax(k)) q[k] = tmpmax(k);
     if (q[k] <= tmpmin(k)) q[k] = tmpmin(k);
   }
-  double *a2 = c.a2, *a3 = c.a3, *a4 = c.a4;
+  T *a2 = c.a2, *a3 = c.a3, *a4 = c.a4;
   for (int k = 0; k < km; ++k) { a2[k] = q[k]; a3[k] = q[k + 1]; }
-  c.extm[0] = (a2[0] - a1[0]) * (a3[0] - a1[0]) > 0.0;
-  for (int k = 1; k < km - 1; ++k) c.extm[k] = gam[k] * gam[k + 1] < 0.0;
-  c.extm[km - 1] = (a2[km - 1] - a1[km - 1]) * (a3[km - 1] - a1[km - 1]) > 0.0;
+  c.extm[0] = (a2[0] - a1[0]) * (a3[0] - a1[0]) > T(0.0);
+  for (int k = 1; k < km - 1; ++k) c.extm[k] = gam[k] * gam[k + 1] < T(0.0);
+  c.extm[km - 1] = (a2[km - 1] - a1[km - 1]) * (a3[km - 1] - a1[km - 1]) > T(0.0);
   if (kord > 9) {
     for (int k = 0; k < km; ++k) {
-      double x0 = 2.0 * a1[k] - (a2[k] + a3[k]);
-      double x1 = fabs(a2[k] - a3[k]);
-      a4[k] = 3.0 * x0;
+      T x0 = T(2.0) * a1[k] - (a2[k] + a3[k]);
+      T x1 = fabs(a2[k] - a3[k]);
+      a4[k] = T(3.0) * x0;
       c.ext5[k] = fabs(x0) > x1;
       c.ext6[k] = fabs(a4[k]) > x1;
     }
   }
   // ---- set_interpolation_coefficients (domain: km levels); a1 is modified only formally (returned unchanged) ----
-  double* a1w = c.a1;
+  T* a1w = c.a1;
   if (iv == 0) {
-    if (a2[0] < 0.0) a2[0] = 0.0;
+    if (a2[0] < T(0.0)) a2[0] = T(0.0);
     a4_from(a1[0], a2[0], a3[0], a4[0]);
     a4_from(a1[1], a2[1], a3[1], a4[1]);
   }
   if (iv == -1) {
-    if (a2[0] * a1[0] <= 0.0) a2[0] = 0.0;
+    if (a2[0] * a1[0] <= T(0.0)) a2[0] = T(0.0);
     a4_from(a1[0], a2[0], a3[0], a4[0]);
     a4_from(a1[1], a2[1], a3[1], a4[1]);
   }
   if (iv == 2) {
-    a2[0] = a1[0]; a3[0] = a1[0]; a4[0] = 0.0;
+    a2[0] = a1[0]; a3[0] = a1[0]; a4[0] = T(0.0);
     a4_from(a1[1], a2[1], a3[1], a4[1]);
   }
   if (iv < -1 || iv == 1 || iv > 2) {
@@ -169,53 +178,53 @@ __device__ void remap_profile(Col& c, int km, int iv, int kord, double qs, doubl
   remap_constraint(a1w[1], a2[1], a3[1], a4[1], c.extm[1]);
   for (int k = 2; k < km - 2; ++k) {
     if (kord < 9) {
-      double pmp_1 = a1[k] - gam[k + 1];
-      double lac_1 = pmp_1 + 1.5 * gam[k + 2];
-      double tmp_min = lim3_min(a1[k], pmp_1, lac_1);
-      double tmp_max0 = a2[k] > tmp_min ? a2[k] : tmp_min;
-      double tmp_max = lim3_max(a1[k], pmp_1, lac_1);
+      T pmp_1 = a1[k] - gam[k + 1];
+      T lac_1 = pmp_1 + T(1.5) * gam[k + 2];
+      T tmp_min = lim3_min(a1[k], pmp_1, lac_1);
+      T tmp_max0 = a2[k] > tmp_min ? a2[k] : tmp_min;
+      T tmp_max = lim3_max(a1[k], pmp_1, lac_1);
       a2[k] = tmp_max0 < tmp_max ? tmp_max0 : tmp_max;
-      double pmp_2 = a1[k] + 2.0 * gam[k + 1];
-      double lac_2 = pmp_2 - 1.5 * gam[k - 1];
+      T pmp_2 = a1[k] + T(2.0) * gam[k + 1];
+      T lac_2 = pmp_2 - T(1.5) * gam[k - 1];
       tmp_min = lim3_min(a1[k], pmp_2, lac_2);
       tmp_max0 = a3[k] > tmp_min ? a3[k] : tmp_min;
       tmp_max = lim3_max(a1[k], pmp_2, lac_2);
       a3[k] = tmp_max0 < tmp_max ? tmp_max0 : tmp_max;
       a4_from(a1[k], a2[k], a3[k], a4[k]);
     } else if (kord == 9) {
-      double pmp_1 = a1[k] - 2.0 * gam[k + 1];
-      double lac_1 = pmp_1 + 1.5 * gam[k + 2];
-      double pmp_2 = a1[k] + 2.0 * gam[k];
-      double lac_2 = pmp_2 - 1.5 * gam[k - 1];
-      if ((c.extm[k] && c.extm[k - 1]) || (c.extm[k] && c.extm[k + 1]) || (c.extm[k] && (qmin > 0.0 && a1[k] < qmin))) {
-        a2[k] = a1[k]; a3[k] = a1[k]; a4[k] = 0.0;
+      T pmp_1 = a1[k] - T(2.0) * gam[k + 1];
+      T lac_1 = pmp_1 + T(1.5) * gam[k + 2];
+      T pmp_2 = a1[k] + T(2.0) * gam[k];
+      T lac_2 = pmp_2 - T(1.5) * gam[k - 1];
+      if ((c.extm[k] && c.extm[k - 1]) || (c.extm[k] && c.extm[k + 1]) || (c.extm[k] && (qmin > T(0.0) && a1[k] < qmin))) {
+        a2[k] = a1[k]; a3[k] = a1[k]; a4[k] = T(0.0);
       } else {
-        a4[k] = 6.0 * a1[k] - 3.0 * (a2[k] + a3[k]);
+        a4[k] = T(6.0) * a1[k] - T(3.0) * (a2[k] + a3[k]);
         if (fabs(a4[k]) > fabs(a2[k] - a3[k])) {
-          double tmp_min = lim3_min(a1[k], pmp_1, lac_1);
-          double tmp_max0 = a2[k] > tmp_min ? a2[k] : tmp_min;
-          double tmp_max = lim3_max(a1[k], pmp_1, lac_1);
+          T tmp_min = lim3_min(a1[k], pmp_1, lac_1);
+          T tmp_max0 = a2[k] > tmp_min ? a2[k] : tmp_min;
+          T tmp_max = lim3_max(a1[k], pmp_1, lac_1);
           a2[k] = tmp_max0 < tmp_max ? tmp_max0 : tmp_max;
           tmp_min = lim3_min(a1[k], pmp_2, lac_2);
           tmp_max0 = a3[k] > tmp_min ? a3[k] : tmp_min;
           tmp_max = lim3_max(a1[k], pmp_2, lac_2);
           a3[k] = tmp_max0 < tmp_max ? tmp_max0 : tmp_max;
-          a4[k] = 6.0 * a1[k] - 3.0 * (a2[k] + a3[k]);
+          a4[k] = T(6.0) * a1[k] - T(3.0) * (a2[k] + a3[k]);
         }
       }
     } else {  // kord == 10
-      double pmp_1 = a1[k] - 2.0 * gam[k + 1];
-      double lac_1 = pmp_1 + 1.5 * gam[k + 2];
-      double pmp_2 = a1[k] + 2.0 * gam[k];
-      double lac_2 = pmp_2 - 1.5 * gam[k - 1];
-      double tmp_min2 = lim3_min(a1[k], pmp_1, lac_1);
-      double tmp_max2 = lim3_max(a1[k], pmp_1, lac_1);
-      double tmp2 = a2[k] > tmp_min2 ? a2[k] : tmp_min2;
-      double tmp_min3 = a1[k] < pmp_2 ? a1[k] : pmp_2;
+      T pmp_1 = a1[k] - T(2.0) * gam[k + 1];
+      T lac_1 = pmp_1 + T(1.5) * gam[k + 2];
+      T pmp_2 = a1[k] + T(2.0) * gam[k];
+      T lac_2 = pmp_2 - T(1.5) * gam[k - 1];
+      T tmp_min2 = lim3_min(a1[k], pmp_1, lac_1);
+      T tmp_max2 = lim3_max(a1[k], pmp_1, lac_1);
+      T tmp2 = a2[k] > tmp_min2 ? a2[k] : tmp_min2;
+      T tmp_min3 = a1[k] < pmp_2 ? a1[k] : pmp_2;
       tmp_min3 = lac_2 < tmp_min3 ? lac_2 : tmp_min3;
-      double tmp_max3 = a1[k] > pmp_2 ? a1[k] : pmp_2;
+      T tmp_max3 = a1[k] > pmp_2 ? a1[k] : pmp_2;
       tmp_max3 = lac_2 > tmp_max3 ? lac_2 : tmp_max3;
-      double tmp3 = a3[k] > tmp_min3 ? a3[k] : tmp_min3;
+      T tmp3 = a3[k] > tmp_min3 ? a3[k] : tmp_min3;
       bool n5 = c.ext5[k - 1] || c.ext5[k + 1], n6 = c.ext6[k - 1] || c.ext6[k + 1];
       if (c.ext5[k]) {
         if (n5) { a2[k] = a1[k]; a3[k] = a1[k]; }
@@ -227,8 +236,8 @@ __device__ void remap_profile(Col& c, int km, int iv, int kord, double qs, doubl
     }
     if (iv == 0) posdef_iv0(a1w[k], a2[k], a3[k], a4[k]);
   }
-  if (iv == 0 && a3[km - 1] < 0.0) a3[km - 1] = 0.0;
-  if (iv == -1 && a3[km - 1] * a1[km - 1] <= 0.0) a3[km - 1] = 0.0;
+  if (iv == 0 && a3[km - 1] < T(0.0)) a3[km - 1] = T(0.0);
+  if (iv == -1 && a3[km - 1] * a1[km - 1] <= T(0.0)) a3[km - 1] = T(0.0);
   a4_from(a1[km - 2], a2[km - 2], a3[km - 2], a4[km - 2]);
   a4_from(a1[km - 1], a2[km - 1], a3[km - 1], a4[km - 1]);
   remap_constraint(a1w[km - 2], a2[km - 2], a3[km - 2], a4[km - 2], c.extm[km - 2]);
@@ -238,8 +247,9 @@ __device__ void remap_profile(Col& c, int km, int iv, int kord, double qs, doubl
 // MapSingle.__call__ on one column: q (in/out, km levels) from source interfaces pe1 to target interfaces pe2
 // keep_dp: c.dp already holds the layer thicknesses of pe1 (previous call with the same pe1).  Returns whether any
 // remapped value is negative (the only case in which fillz changes a column).
-__device__ bool map_single_column(const Pt& p, Col& c, int km, double* q, const double* pe1, const double* pe2, int iv,
-                                  int kord, double qs, double qmin, bool keep_dp = false) {
+template <class T>
+__device__ bool map_single_column(const Pt& p, ColT<T>& c, int km, T* q, const T* pe1, const T* pe2, int iv,
+                                  int kord, T qs, T qmin, bool keep_dp = false) {
   bool any_negative = false;
   for (int k = 0; k < km; ++k) {
     c.a1[k] = A(q, 0, 0, k);
@@ -252,29 +262,29 @@ __device__ bool map_single_column(const Pt& p, Col& c, int km, double* q, const 
   auto cl = [&](int L) { return L > km - 1 ? km - 1 : L; };  // layer arrays: km entries meaningful
   int L = 0;
   for (int k = 0; k < km; ++k) {
-    const double pe2k = A(pe2, 0, 0, k), pe2k1 = A(pe2, 0, 0, k + 1);
+    const T pe2k = A(pe2, 0, 0, k), pe2k1 = A(pe2, 0, 0, k + 1);
     int Lc = cl(L);
-    double pl = (pe2k - P1(L)) / c.dp[Lc];
-    double qv;
+    T pl = (pe2k - P1(L)) / c.dp[Lc];
+    T qv;
     if (pe2k1 <= P1(L + 1)) {
-      double pr = (pe2k1 - P1(L)) / c.dp[Lc];
-      qv = c.a2[Lc] + 0.5 * (c.a4[Lc] + c.a3[Lc] - c.a2[Lc]) * (pr + pl) - c.a4[Lc] * 1.0 / 3.0 * (pr * (pr + pl) + pl * pl);
+      T pr = (pe2k1 - P1(L)) / c.dp[Lc];
+      qv = c.a2[Lc] + T(0.5) * (c.a4[Lc] + c.a3[Lc] - c.a2[Lc]) * (pr + pl) - c.a4[Lc] * T(1.0) / T(3.0) * (pr * (pr + pl) + pl * pl);
     } else {
-      double qsum = (P1(L + 1) - pe2k) *
-                    (c.a2[Lc] + 0.5 * (c.a4[Lc] + c.a3[Lc] - c.a2[Lc]) * (1.0 + pl) - c.a4[Lc] * 1.0 / 3.0 * (1.0 + pl * (1.0 + pl)));
+      T qsum = (P1(L + 1) - pe2k) *
+                    (c.a2[Lc] + T(0.5) * (c.a4[Lc] + c.a3[Lc] - c.a2[Lc]) * (T(1.0) + pl) - c.a4[Lc] * T(1.0) / T(3.0) * (T(1.0) + pl * (T(1.0) + pl)));
       L = L + 1;
       while (L < km && P1(L + 1) < pe2k1) {
         qsum += c.dp[cl(L)] * c.a1[cl(L)];
         L = L + 1;
       }
       Lc = cl(L);
-      double dp = pe2k1 - P1(L);
-      double esl = dp / c.dp[Lc];
-      qsum += dp * (c.a2[Lc] + 0.5 * esl * (c.a3[Lc] - c.a2[Lc] + c.a4[Lc] * (1.0 - (2.0 / 3.0) * esl)));
+      T dp = pe2k1 - P1(L);
+      T esl = dp / c.dp[Lc];
+      qsum += dp * (c.a2[Lc] + T(0.5) * esl * (c.a3[Lc] - c.a2[Lc] + c.a4[Lc] * (T(1.0) - (T(2.0) / T(3.0)) * esl)));
       qv = qsum / (pe2k1 - pe2k);
     }
     A(q, 0, 0, k) = qv;
-    any_negative = any_negative || qv < 0.0;
+    any_negative = any_negative || qv < T(0.0);
   }
   return any_negative;
 }
@@ -347,8 +357,10 @@ struct TrPtrs { double* p[9]; };
 
 #ifndef PACE_HOST_EMU
 #define COL_DECL Col col
+#define COLT_DECL ColT<T> col
 #else
 #define COL_DECL static thread_local Col col
+#define COLT_DECL static thread_local ColT<T> col
 #endif
 
 }  // namespace
@@ -357,17 +369,27 @@ const char* tracer_name(int n);
 
 // MapSingle.__call__ exposed on registered fields (also used by the test-suite on synthetic columns).
 // xi / yi: the field's horizontal staggering (dims [X(_INTERFACE), Y(_INTERFACE), Z]).
-int map_single(Core& c, double* q, const double* pe1, const double* pe2, const double* qs, int iv, int kord, bool xi,
-               bool yi, double qmin) {
+// T = double is the reference's default precision, T = float its PACE_FLOAT_PRECISION=32 mode (Float = np.float32,
+// ndsl/dsl/typing.py:25-45): fields, literals and every intermediate are T, as in the GT4Py numpy code.
+template <class T>
+int map_single_impl(Core& c, T* q, const T* pe1, const T* pe2, const T* qs, int iv, int kord, bool xi, bool yi, T qmin) {
   const Geo g = c.g;
   const int km = g.nz;
   if (km + 1 > KMAX) { c.err = "map_single: npz + 1 exceeds the thread-local column length (96)"; return 1; }
   if (kord > 10) { c.err = "Remap Profile: kord > 10 not implemented. kord <= 10 available."; return 1; }
   launch_ij(c.stream, g, box_dims(g, xi, yi, false), [=] __device__(const Pt& p) {
-    COL_DECL;
-    map_single_column(p, col, km, q, pe1, pe2, iv, kord, qs ? A20(qs) : 0.0, qmin);
-  });
+    COLT_DECL;
+    map_single_column<T>(p, col, km, q, pe1, pe2, iv, kord, qs ? A20(qs) : T(0.0), qmin);
+  }, sizeof(T) == 4 ? "map_single_f32" : "map_single");
   return 0;
+}
+int map_single(Core& c, double* q, const double* pe1, const double* pe2, const double* qs, int iv, int kord, bool xi,
+               bool yi, double qmin) {
+  return map_single_impl<double>(c, q, pe1, pe2, qs, iv, kord, xi, yi, qmin);
+}
+int map_single_f32(Core& c, float* q, const float* pe1, const float* pe2, const float* qs, int iv, int kord, bool xi,
+                   bool yi, float qmin) {
+  return map_single_impl<float>(c, q, pe1, pe2, qs, iv, kord, xi, yi, qmin);
 }
 
 // LagrangianToEulerian.__call__ up to (not including) the saturation adjustment (remapping.py:590-668)

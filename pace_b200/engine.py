@@ -235,7 +235,10 @@ class DycoreEngine:
         core.call("remap_finish", int(last_step))
 
     # -- DynamicalCore.step_dynamics / _compute (fv_dynamics.py:445-655) ----------------------------------------
-    def step_dynamics(self):
+    def step_dynamics(self, timer=None):
+        """timer: optional object with start(name) / stop(name), called around the sections the reference times
+        (fv_dynamics.py:551-590: "DynCore", "TracerAdvection", "Remapping"); the caller decides how to clock them
+        (bench.py records CUDA events on the launching stream)."""
         core, c = self.core, self.cfg
         k_split = int(c["k_split"])
         self.compute_preamble()
@@ -243,10 +246,21 @@ class DycoreEngine:
             n_map = k + 1
             last_step = k == k_split - 1
             core.call("copy_levels", "delp", "dyn.dp1")
+            if timer is not None:
+                timer.start("DynCore")
             self.acoustic_dynamics(c["dt_atmos"] / k_split, n_map=n_map)
+            if timer is not None:
+                timer.stop("DynCore")
+                timer.start("TracerAdvection")
             self.tracer_advection()
+            if timer is not None:
+                timer.stop("TracerAdvection")
             if self.npz > 4:
+                if timer is not None:
+                    timer.start("Remapping")
                 self.remapping(last_step, c["dt_atmos"] / k_split)
+                if timer is not None:
+                    timer.stop("Remapping")
                 if last_step:
                     core.call("omega_from_w")
                     if c["nf_omega"] > 0:

@@ -115,6 +115,41 @@ class NativeCore:
             return [np.ascontiguousarray(t[n, :, :ni].T) for n in range(self.nt)]
         return [t]
 
+    # -- single-precision fields (the reference's PACE_FLOAT_PRECISION=32 mode; MapSingle only) ---------------
+    def put32(self, arrays):
+        """float32 device tensor in the library layout from per-subdomain reference-layout (i,j,k) / (i,j) arrays."""
+        a0 = np.asarray(arrays[0])
+        shape = (self.nt, self.npz + 1, self.nj, self.sj) if a0.ndim == 3 else (self.nt, self.nj, self.sj)
+        host = np.zeros(shape, dtype=np.float32)
+        for n, a in enumerate(arrays):
+            a = np.asarray(a, dtype=np.float32)
+            if a.ndim == 3:
+                ni, nj, nk = a.shape
+                host[n, :nk, :nj, :ni] = a.transpose(2, 1, 0)
+            else:
+                ni, nj = a.shape
+                host[n, :nj, :ni] = a.T
+        return torch.from_numpy(host).to(self.device)
+
+    def get32(self, t):
+        t = t.cpu().numpy()
+        ni = self.nx + 7
+        if t.ndim == 4:
+            return [np.ascontiguousarray(t[n, :, :, :ni].transpose(2, 1, 0)) for n in range(self.nt)]
+        return [np.ascontiguousarray(t[n, :, :ni].T) for n in range(self.nt)]
+
+    def map_single_f32(self, q, pe1, pe2, qs=None, iv=1, kord=9, x_interface=False, y_interface=False, qmin=0.0):
+        """MapSingle.__call__ on float32 tensors in the library layout (q is remapped in place)."""
+        for t in (q, pe1, pe2) + ((qs,) if qs is not None else ()):
+            if t.dtype != torch.float32 or not t.is_contiguous():
+                raise NativeError("map_single_f32 needs contiguous float32 tensors")
+        rc = self.lib.pace_b200_map_single_f32(
+            self.handle, ctypes.c_void_p(q.data_ptr()), ctypes.c_void_p(pe1.data_ptr()), ctypes.c_void_p(pe2.data_ptr()),
+            ctypes.c_void_p(qs.data_ptr()) if qs is not None else None, int(iv), int(kord), int(x_interface),
+            int(y_interface), float(qmin))
+        if rc != 0:
+            raise NativeError("map_single_f32: %s" % self.lib.pace_b200_last_error(self.handle).decode())
+
     def set_column(self, name, values):
         """Small per-level column (host values; the library keeps host + device copies)."""
         v = np.ascontiguousarray(values, dtype=np.float64)
