@@ -90,6 +90,7 @@ __device__ __forceinline__ Pt make_pt(const Geo& g, int t, int i, int j, int k) 
 
 struct Box {
   int i0, j0, k0, ni, nj, nk;
+  unsigned magic = 0;  // set by launch_ijk: floor(2^32 / ni) + 1 when n / ni == umulhi(n, magic) for every point n of a level
 };
 
 // ---- launch accounting (api.cu): every kernel launch is counted; launches given a label are additionally
@@ -118,7 +119,7 @@ template <class F>
 __global__ void __launch_bounds__(256) k_ijk(Geo g, Box b, F f) {
   const int n = blockIdx.x * blockDim.x + threadIdx.x;
   if (n >= b.ni * b.nj) return;
-  const int j = n / b.ni, i = n - j * b.ni;
+  const int j = b.magic ? (int)__umulhi((unsigned)n, b.magic) : n / b.ni, i = n - j * b.ni;
   int k = blockIdx.y % b.nk, t = blockIdx.y / b.nk;
   Pt p = make_pt(g, t, b.i0 + i, b.j0 + j, b.k0 + k);
   f(p);
@@ -141,6 +142,8 @@ inline void launch_ijk(cudaStream_t s, const Geo& g, Box b, F f, const char* lab
   LaunchScope scope(s, label);
   dim3 blk(256, 1, 1);
   dim3 grd((b.ni * b.nj + 255) / 256, b.nk * g.nt, 1);
+  // row index by multiplication: exact while n * ni < 2^32 for all n < ni * nj (n * (magic * ni - 2^32) < 2^32)
+  if (b.ni > 1 && (unsigned long long)b.ni * b.nj * b.ni < (1ull << 32)) b.magic = (unsigned)((1ull << 32) / (unsigned)b.ni) + 1u;
   k_ijk<<<grd, blk, 0, s>>>(g, b, f);
 }
 
@@ -207,6 +210,15 @@ __device__ __forceinline__ double fv_abs(double x) { return fabs(x); }
 // non-NaN data; sign(a,b) = |a| if b>=0 else -|a|, basic_operations.py:32-45)
 __device__ __forceinline__ double fv_min(double a, double b) { return a < b ? a : b; }
 __device__ __forceinline__ double fv_max(double a, double b) { return a > b ? a : b; }
+// n / d.  A zero numerator over a positive denominator is n itself (same bits, signed zero included); answering that
+// without dividing keeps fields that are zero over most of the domain (condensates, q_con) off the out-of-line
+// special-operand path of the fp64 division, which a warp enters as soon as one lane has a zero numerator.
+__device__ __forceinline__ double fv_div(double n, double d) {
+#ifndef PACE_HOST_EMU
+  if (n == 0.0 && d > 0.0) return n;
+#endif
+  return n / d;
+}
 
 #define CUDA_CHECK_RET(call)                                                              \
   do {                                                                                    \

@@ -52,8 +52,8 @@ __device__ __forceinline__ void march_cell(March<MORD>& m, int pos, bool first, 
     using namespace ppmc;
     double al_hi;
     if (near) {
-      if (first) m.al_lo = ppm_al(Q, D, pos, lo, hi, elo, ehi, 0);
-      al_hi = ppm_al(Q, D, pos, lo, hi, elo, ehi, 1);
+      if (first) m.al_lo = ppm_al_vals(Q(-2), Q(-1), Q(0), Q(1), D(-2), D(-1), D(0), D(1), pos, lo, hi, elo, ehi);
+      al_hi = ppm_al_vals(Q(-1), Q(0), Q(1), Q(2), D(-1), D(0), D(1), D(2), pos + 1, lo, hi, elo, ehi);
     } else {
       if (first) m.al_lo = p1 * (m.w[1] + m.w[2]) + p2 * (m.w[0] + m.w[3]);
       al_hi = p1 * (m.w[2] + m.w[3]) + p2 * (m.w[1] + m.w[4]);
@@ -70,7 +70,9 @@ __device__ __forceinline__ void march_cell(March<MORD>& m, int pos, bool first, 
     }
     const double dm_p = ppm_dm8_v(m.w[2], m.w[3], m.w[4]);
     if (near) {
-      ppm_blbr8(Q, D, pos, lo, hi, elo, ehi, 0, bl, br);
+      const BlBr r = ppm_blbr8_vals(Q(-2), Q(-1), Q(0), Q(1), Q(2), D(-2), D(-1), D(0), D(1), D(2), pos, lo, hi, elo, ehi);
+      bl = r.bl;
+      br = r.br;
     } else {
       const double al_lo = 0.5 * (m.w[1] + m.w[2]) + 1.0 / 3.0 * (m.dm_m - m.dm_0);
       const double al_hi = 0.5 * (m.w[2] + m.w[3]) + 1.0 / 3.0 * (m.dm_0 - dm_p);
@@ -127,7 +129,7 @@ __device__ __forceinline__ double xsweep_flux(const double* row, int L, int i, d
     double al = 0.0;
     if (L >= 2 && L <= 30) {
       const bool special = (W && i >= is - 1 && i <= is + 1) || (E && i >= ie && i <= ie + 2);
-      if (special) al = ppm_al(Q, D, i, is, ie, W, E, 0);
+      if (special) al = ppm_al_vals(Q(-2), Q(-1), Q(0), Q(1), D(-2), D(-1), D(0), D(1), i, is, ie, W, E);
       else al = p1 * (row[L - 1] + row[L]) + p2 * (row[L - 2] + row[L + 1]);
     }
     const double alm = __shfl_up_sync(FULL, al, 1), alp = __shfl_down_sync(FULL, al, 1);
@@ -154,7 +156,9 @@ __device__ __forceinline__ double xsweep_flux(const double* row, int L, int i, d
     if (L >= 2 && L <= 29) {
       const bool special = (W && i >= is - 1 && i <= is + 1) || (E && i >= ie - 1 && i <= ie + 1);
       if (special) {
-        ppm_blbr8(Q, D, i, is, ie, W, E, 0, bl, br);
+        const BlBr r = ppm_blbr8_vals(Q(-2), Q(-1), Q(0), Q(1), Q(2), D(-2), D(-1), D(0), D(1), D(2), i, is, ie, W, E);
+        bl = r.bl;
+        br = r.br;
       } else {
         const double al_lo = 0.5 * (row[L - 1] + q) + 1.0 / 3.0 * (dm_m - dm);
         const double al_hi = 0.5 * (q + row[L + 1]) + 1.0 / 3.0 * (dm - dm_p);
@@ -281,7 +285,7 @@ __global__ void __launch_bounds__(WPB * 32, 20) k_fvtp2d_march(Geo g, MarchArgs 
       const double xf0 = ring(2, slot)[L], xf1 = ring(2, slot)[L + 1], ar = ring(3, slot)[L];
       const double fx10 = xf0 * fxin, fx11 = xf1 * fxin_p;
       const double area_with_x_flux = ar + xf0 - xf1;
-      qj = (qx * ar + fx10 - fx11) / area_with_x_flux;
+      qj = fv_div(qx * ar + fx10 - fx11, area_with_x_flux);
     }
     fxring[(s & 3) * PITCH + L] = fxin;  // needed again at step s + 3 (outer x flux of this row)
     // 3. y sweeps: cell jc = R-2 is complete
@@ -310,7 +314,7 @@ __global__ void __launch_bounds__(WPB * 32, 20) k_fvtp2d_march(Geo g, MarchArgs 
           if (s >= 6) {  // q_i on row R-3
             const double yf0 = yfx_prev, ar = ring(7, slot)[L];
             const double fyy0 = yf0 * fyin_prev, fyy1 = yf1 * fyin;
-            qi = (mi.w[1] * ar + fyy0 - fyy1) / (ar + yf0 - yf1);
+            qi = fv_div(mi.w[1] * ar + fyy0 - fyy1, ar + yf0 - yf1);
           }
           yfx_prev = yf1;
         }

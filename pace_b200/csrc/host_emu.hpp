@@ -7,6 +7,7 @@
 #define __host__
 #define __global__
 #define __forceinline__ inline
+#define __noinline__
 #define __launch_bounds__(...)
 typedef void* cudaStream_t;
 typedef int cudaError_t;

@@ -150,6 +150,31 @@ __device__ __forceinline__ void ppm_blbr8(QF Q, DF D, int pos, int lo, int hi, b
   }
 }
 
+// ---- out-of-line copies of the tile-edge formulas -------------------------------------------------------
+// The kernels that keep a whole transport call in one loop body (fvtp2d_march.cu) reach the edge formulas from
+// several places; inlined there they made up most of a 70 KB kernel whose loop no longer fitted the instruction
+// cache.  These are the same functions on values (q[n] = Q(n - 2), dx[n] = D(n - 2) around the cell / interface at
+// index x), compiled once and called only by the lanes next to a tile edge.
+struct BlBr {
+  double bl, br;
+};
+static __device__ __noinline__ BlBr ppm_blbr8_vals(double qa, double qb, double qc, double qd, double qe, double da,
+                                                   double db, double dc, double dd, double de, int x, int lo, int hi,
+                                                   bool elo, bool ehi) {
+  auto Q = [&](int d) { return d == -2 ? qa : d == -1 ? qb : d == 0 ? qc : d == 1 ? qd : qe; };
+  auto D = [&](int d) { return d == -2 ? da : d == -1 ? db : d == 0 ? dc : d == 1 ? dd : de; };
+  BlBr r;
+  ppm_blbr8(Q, D, x, lo, hi, elo, ehi, 0, r.bl, r.br);
+  return r;
+}
+// compute_al at interface x from Q(-2..1), D(-2..1)
+static __device__ __noinline__ double ppm_al_vals(double qa, double qb, double qc, double qd, double da, double db,
+                                                  double dc, double dd, int x, int lo, int hi, bool elo, bool ehi) {
+  auto Q = [&](int d) { return d == -2 ? qa : d == -1 ? qb : d == 0 ? qc : qd; };
+  auto D = [&](int d) { return d == -2 ? da : d == -1 ? db : d == 0 ? dc : dd; };
+  return ppm_al(Q, D, x, lo, hi, elo, ehi, 0);
+}
+
 template <class QF, class DF>
 __device__ __forceinline__ double ppm_flux_8(QF Q, DF D, double c, int pos, int lo, int hi, bool elo, bool ehi) {
   double bl, br;

@@ -63,13 +63,23 @@ __device__ __forceinline__ T lim3_max(T a, T b, T c) {
   return (a > b && a > c) ? a : (b > c ? b : c);
 }
 
-// RemapProfile.__call__ (remap_profile.py:644-697) on one column.  in: c.a1 (cell means), c.dp; out: c.a2..a4
+// RemapProfile.__call__ (remap_profile.py:644-697) on one column, in two parts.
+//
+// The reference runs three stencils through full-size a4_1..a4_4 / gam / extm arrays.  Only the first one
+// (set_initial_vals) is a recurrence over the column: a tridiagonal solve for the interface values q.  Everything
+// after it - the monotonicity constraints on q (apply_constraints) and the parabola coefficients a4_2..a4_4 of a layer
+// (set_interpolation_coefficients) - is a function of q and the cell means a4_1 = a1 within two levels of that layer.
+// So the column keeps a1, dp and q only, and the coefficients of a source layer are evaluated when the remap reaches
+// it (coef_at), with the same expressions in the same order as the reference's statements: results are bit-identical,
+// and the thread-local working set (which does not fit any cache at full occupancy and is DRAM traffic) drops from 7
+// arrays passed over ~30 times to 4 arrays passed over ~10 times per MapSingle.
+
+// set_initial_vals (remap_profile.py:150-250): interface values q[0..km] from the cell means c.a1 and thicknesses c.dp
 template <class T>
-__device__ void remap_profile(ColT<T>& c, int km, int iv, int kord, T qs, T qmin) {
+__device__ __forceinline__ void profile_solve(ColT<T>& c, int km, int iv, T qs) {
   T* q = c.q;
   T* gam = c.gam;
   const T *a1 = c.a1, *delp = c.dp;
-  // ---- set_initial_vals (domain: km+1 interface levels) ----
   if (iv != -2) {
     T gr = delp[1] / delp[0];
     T bet = gr * (gr + T(0.5));
@@ -113,135 +123,138 @@ __device__ void remap_profile(ColT<T>& c, int km, int iv, int kord, T qs, T qmin
     q[km] = qs;
     for (int k = km - 2; k >= 0; --k) q[k] = q[k] - gam[k + 1] * q[k + 1];
   }
-  // ---- apply_constraints (domain: km levels) ----
-  // gam[k] = a1[k] - a1[k-1] for k >= 1 (gam[0] keeps its set_initial_vals value)
-  for (int k = 1; k < km; ++k) gam[k] = a1[k] - a1[k - 1];
-  auto tmpmax = [&](int k) { return a1[k - 1] > a1[k] ? a1[k - 1] : a1[k]; };
-  auto tmpmin = [&](int k) { return a1[k - 1] < a1[k] ? a1[k - 1] : a1[k]; };
-  {
-    int k = 1;
-    if (q[k] >= tmpmax(k)) q[k] = tmpmax(k);
-    if (q[k] <= tmpmin(k)) q[k] = tmpmin(k);
+}
+
+// apply_constraints (remap_profile.py:253-337): gam[k] = a1[k] - a1[k-1] (1 <= k <= km-1), and the interface value k
+// limited by its two cell means / clipped according to the signs of the neighbouring differences
+template <class T>
+__device__ __forceinline__ T gam_at(const ColT<T>& c, int k) { return c.a1[k] - c.a1[k - 1]; }
+
+template <class T>
+__device__ __forceinline__ T qc_at(const ColT<T>& c, int km, int iv, int k) {
+  T q = c.q[k];
+  if (k == 0 || k == km) return q;
+  const T tmp = c.a1[k - 1] > c.a1[k] ? c.a1[k - 1] : c.a1[k];   // tmpmax
+  const T tmp2 = c.a1[k - 1] < c.a1[k] ? c.a1[k - 1] : c.a1[k];  // tmpmin
+  if (k == 1 || k == km - 1) {
+    if (q >= tmp) q = tmp;
+    if (q <= tmp2) q = tmp2;
+    return q;
   }
-  for (int k = 2; k < km - 1; ++k) {
-    T tmp = tmpmax(k), tmp2 = tmpmin(k);
-    if ((gam[k - 1] * gam[k + 1]) > 0) {
-      if (q[k] >= tmp) q[k] = tmp;
-      if (q[k] <= tmp2) q[k] = tmp2;
-    } else if (gam[k - 1] > 0) {
-      if (q[k] <= tmp2) q[k] = tmp2;
+  const T gm = gam_at(c, k - 1), gp = gam_at(c, k + 1);
+  if ((gm * gp) > 0) {
+    if (q >= tmp) q = tmp;
+    if (q <= tmp2) q = tmp2;
+  } else if (gm > 0) {
+    if (q <= tmp2) q = tmp2;
+  } else {
+    if (q >= tmp) q = tmp;
+    if (iv == 0 && q < T(0.0)) q = T(0.0);
+  }
+  return q;
+}
+// extm of layer k, 1 <= k <= km-2 (the values of layers 0 and km-1 are never read)
+template <class T>
+__device__ __forceinline__ bool extm_at(const ColT<T>& c, int k) { return gam_at(c, k) * gam_at(c, k + 1) < T(0.0); }
+
+// a4_2, a4_3, a4_4 of source layer k as set_interpolation_coefficients leaves them (remap_profile.py:340-563)
+template <class T>
+__device__ __forceinline__ void coef_at(const ColT<T>& c, int km, int iv, int kord, T qmin, int k, T& a2, T& a3, T& a4) {
+  T a1 = c.a1[k];  // a4_1 is an argument of the constraint functions but comes back unchanged
+  a2 = qc_at(c, km, iv, k);
+  a3 = qc_at(c, km, iv, k + 1);
+  if (k == 0) {
+    if (iv == 0 && a2 < T(0.0)) a2 = T(0.0);
+    if (iv == -1 && a2 * a1 <= T(0.0)) a2 = T(0.0);
+    if (iv == 2) { a2 = a1; a3 = a1; a4 = T(0.0); }
+    else { a4_from(a1, a2, a3, a4); posdef_iv1(a1, a2, a3, a4); }
+    return;
+  }
+  if (k == 1 || k == km - 2) {
+    a4_from(a1, a2, a3, a4);
+    remap_constraint(a1, a2, a3, a4, extm_at(c, k));
+    return;
+  }
+  if (k == km - 1) {
+    if (iv == 0 && a3 < T(0.0)) a3 = T(0.0);
+    if (iv == -1 && a3 * a1 <= T(0.0)) a3 = T(0.0);
+    a4_from(a1, a2, a3, a4);
+    posdef_iv1(a1, a2, a3, a4);
+    return;
+  }
+  // 2 <= k <= km-3
+  if (kord < 9) {
+    T pmp_1 = a1 - gam_at(c, k + 1);
+    T lac_1 = pmp_1 + T(1.5) * gam_at(c, k + 2);
+    T tmp_min = lim3_min(a1, pmp_1, lac_1);
+    T tmp_max0 = a2 > tmp_min ? a2 : tmp_min;
+    T tmp_max = lim3_max(a1, pmp_1, lac_1);
+    a2 = tmp_max0 < tmp_max ? tmp_max0 : tmp_max;
+    T pmp_2 = a1 + T(2.0) * gam_at(c, k + 1);
+    T lac_2 = pmp_2 - T(1.5) * gam_at(c, k - 1);
+    tmp_min = lim3_min(a1, pmp_2, lac_2);
+    tmp_max0 = a3 > tmp_min ? a3 : tmp_min;
+    tmp_max = lim3_max(a1, pmp_2, lac_2);
+    a3 = tmp_max0 < tmp_max ? tmp_max0 : tmp_max;
+    a4_from(a1, a2, a3, a4);
+  } else if (kord == 9) {
+    T pmp_1 = a1 - T(2.0) * gam_at(c, k + 1);
+    T lac_1 = pmp_1 + T(1.5) * gam_at(c, k + 2);
+    T pmp_2 = a1 + T(2.0) * gam_at(c, k);
+    T lac_2 = pmp_2 - T(1.5) * gam_at(c, k - 1);
+    const bool ex = extm_at(c, k);
+    if ((ex && extm_at(c, k - 1)) || (ex && extm_at(c, k + 1)) || (ex && (qmin > T(0.0) && a1 < qmin))) {
+      a2 = a1; a3 = a1; a4 = T(0.0);
     } else {
-      if (q[k] >= tmp) q[k] = tmp;
-      if (iv == 0 && q[k] < T(0.0)) q[k] = T(0.0);
-    }
-  }
-  {
-    int k = km - 1;
-    if (q[k] >= tmpmax(k)) q[k] = tmpmax(k);
-    if (q[k] <= tmpmin(k)) q[k] = tmpmin(k);
-  }
-  T *a2 = c.a2, *a3 = c.a3, *a4 = c.a4;
-  for (int k = 0; k < km; ++k) { a2[k] = q[k]; a3[k] = q[k + 1]; }
-  c.extm[0] = (a2[0] - a1[0]) * (a3[0] - a1[0]) > T(0.0);
-  for (int k = 1; k < km - 1; ++k) c.extm[k] = gam[k] * gam[k + 1] < T(0.0);
-  c.extm[km - 1] = (a2[km - 1] - a1[km - 1]) * (a3[km - 1] - a1[km - 1]) > T(0.0);
-  if (kord > 9) {
-    for (int k = 0; k < km; ++k) {
-      T x0 = T(2.0) * a1[k] - (a2[k] + a3[k]);
-      T x1 = fabs(a2[k] - a3[k]);
-      a4[k] = T(3.0) * x0;
-      c.ext5[k] = fabs(x0) > x1;
-      c.ext6[k] = fabs(a4[k]) > x1;
-    }
-  }
-  // ---- set_interpolation_coefficients (domain: km levels); a1 is modified only formally (returned unchanged) ----
-  T* a1w = c.a1;
-  if (iv == 0) {
-    if (a2[0] < T(0.0)) a2[0] = T(0.0);
-    a4_from(a1[0], a2[0], a3[0], a4[0]);
-    a4_from(a1[1], a2[1], a3[1], a4[1]);
-  }
-  if (iv == -1) {
-    if (a2[0] * a1[0] <= T(0.0)) a2[0] = T(0.0);
-    a4_from(a1[0], a2[0], a3[0], a4[0]);
-    a4_from(a1[1], a2[1], a3[1], a4[1]);
-  }
-  if (iv == 2) {
-    a2[0] = a1[0]; a3[0] = a1[0]; a4[0] = T(0.0);
-    a4_from(a1[1], a2[1], a3[1], a4[1]);
-  }
-  if (iv < -1 || iv == 1 || iv > 2) {
-    a4_from(a1[0], a2[0], a3[0], a4[0]);
-    a4_from(a1[1], a2[1], a3[1], a4[1]);
-  }
-  if (iv != 2) posdef_iv1(a1w[0], a2[0], a3[0], a4[0]);
-  remap_constraint(a1w[1], a2[1], a3[1], a4[1], c.extm[1]);
-  for (int k = 2; k < km - 2; ++k) {
-    if (kord < 9) {
-      T pmp_1 = a1[k] - gam[k + 1];
-      T lac_1 = pmp_1 + T(1.5) * gam[k + 2];
-      T tmp_min = lim3_min(a1[k], pmp_1, lac_1);
-      T tmp_max0 = a2[k] > tmp_min ? a2[k] : tmp_min;
-      T tmp_max = lim3_max(a1[k], pmp_1, lac_1);
-      a2[k] = tmp_max0 < tmp_max ? tmp_max0 : tmp_max;
-      T pmp_2 = a1[k] + T(2.0) * gam[k + 1];
-      T lac_2 = pmp_2 - T(1.5) * gam[k - 1];
-      tmp_min = lim3_min(a1[k], pmp_2, lac_2);
-      tmp_max0 = a3[k] > tmp_min ? a3[k] : tmp_min;
-      tmp_max = lim3_max(a1[k], pmp_2, lac_2);
-      a3[k] = tmp_max0 < tmp_max ? tmp_max0 : tmp_max;
-      a4_from(a1[k], a2[k], a3[k], a4[k]);
-    } else if (kord == 9) {
-      T pmp_1 = a1[k] - T(2.0) * gam[k + 1];
-      T lac_1 = pmp_1 + T(1.5) * gam[k + 2];
-      T pmp_2 = a1[k] + T(2.0) * gam[k];
-      T lac_2 = pmp_2 - T(1.5) * gam[k - 1];
-      if ((c.extm[k] && c.extm[k - 1]) || (c.extm[k] && c.extm[k + 1]) || (c.extm[k] && (qmin > T(0.0) && a1[k] < qmin))) {
-        a2[k] = a1[k]; a3[k] = a1[k]; a4[k] = T(0.0);
-      } else {
-        a4[k] = T(6.0) * a1[k] - T(3.0) * (a2[k] + a3[k]);
-        if (fabs(a4[k]) > fabs(a2[k] - a3[k])) {
-          T tmp_min = lim3_min(a1[k], pmp_1, lac_1);
-          T tmp_max0 = a2[k] > tmp_min ? a2[k] : tmp_min;
-          T tmp_max = lim3_max(a1[k], pmp_1, lac_1);
-          a2[k] = tmp_max0 < tmp_max ? tmp_max0 : tmp_max;
-          tmp_min = lim3_min(a1[k], pmp_2, lac_2);
-          tmp_max0 = a3[k] > tmp_min ? a3[k] : tmp_min;
-          tmp_max = lim3_max(a1[k], pmp_2, lac_2);
-          a3[k] = tmp_max0 < tmp_max ? tmp_max0 : tmp_max;
-          a4[k] = T(6.0) * a1[k] - T(3.0) * (a2[k] + a3[k]);
-        }
+      a4 = T(6.0) * a1 - T(3.0) * (a2 + a3);
+      if (fabs(a4) > fabs(a2 - a3)) {
+        T tmp_min = lim3_min(a1, pmp_1, lac_1);
+        T tmp_max0 = a2 > tmp_min ? a2 : tmp_min;
+        T tmp_max = lim3_max(a1, pmp_1, lac_1);
+        a2 = tmp_max0 < tmp_max ? tmp_max0 : tmp_max;
+        tmp_min = lim3_min(a1, pmp_2, lac_2);
+        tmp_max0 = a3 > tmp_min ? a3 : tmp_min;
+        tmp_max = lim3_max(a1, pmp_2, lac_2);
+        a3 = tmp_max0 < tmp_max ? tmp_max0 : tmp_max;
+        a4 = T(6.0) * a1 - T(3.0) * (a2 + a3);
       }
-    } else {  // kord == 10
-      T pmp_1 = a1[k] - T(2.0) * gam[k + 1];
-      T lac_1 = pmp_1 + T(1.5) * gam[k + 2];
-      T pmp_2 = a1[k] + T(2.0) * gam[k];
-      T lac_2 = pmp_2 - T(1.5) * gam[k - 1];
-      T tmp_min2 = lim3_min(a1[k], pmp_1, lac_1);
-      T tmp_max2 = lim3_max(a1[k], pmp_1, lac_1);
-      T tmp2 = a2[k] > tmp_min2 ? a2[k] : tmp_min2;
-      T tmp_min3 = a1[k] < pmp_2 ? a1[k] : pmp_2;
-      tmp_min3 = lac_2 < tmp_min3 ? lac_2 : tmp_min3;
-      T tmp_max3 = a1[k] > pmp_2 ? a1[k] : pmp_2;
-      tmp_max3 = lac_2 > tmp_max3 ? lac_2 : tmp_max3;
-      T tmp3 = a3[k] > tmp_min3 ? a3[k] : tmp_min3;
-      bool n5 = c.ext5[k - 1] || c.ext5[k + 1], n6 = c.ext6[k - 1] || c.ext6[k + 1];
-      if (c.ext5[k]) {
-        if (n5) { a2[k] = a1[k]; a3[k] = a1[k]; }
-        else if (n6) { a2[k] = tmp2 < tmp_max2 ? tmp2 : tmp_max2; a3[k] = tmp3 < tmp_max3 ? tmp3 : tmp_max3; }
-      } else if (c.ext6[k]) {
-        if (n5) { a2[k] = tmp2 < tmp_max2 ? tmp2 : tmp_max2; a3[k] = tmp3 < tmp_max3 ? tmp3 : tmp_max3; }
-      }
-      a4_from(a1[k], a2[k], a3[k], a4[k]);
     }
-    if (iv == 0) posdef_iv0(a1w[k], a2[k], a3[k], a4[k]);
+  } else {  // kord == 10
+    // ext5 / ext6 of layers k-1, k, k+1 from their constrained edge values (apply_constraints, kord > 9 part)
+    bool e5[3], e6[3];
+    T qe[4];
+#pragma unroll
+    for (int n = 0; n < 4; ++n) qe[n] = (n == 1) ? a2 : (n == 2) ? a3 : qc_at(c, km, iv, k - 1 + n);
+#pragma unroll
+    for (int n = 0; n < 3; ++n) {
+      T x0 = T(2.0) * c.a1[k - 1 + n] - (qe[n] + qe[n + 1]);
+      T x1 = fabs(qe[n] - qe[n + 1]);
+      T a40 = T(3.0) * x0;
+      e5[n] = fabs(x0) > x1;
+      e6[n] = fabs(a40) > x1;
+    }
+    T pmp_1 = a1 - T(2.0) * gam_at(c, k + 1);
+    T lac_1 = pmp_1 + T(1.5) * gam_at(c, k + 2);
+    T pmp_2 = a1 + T(2.0) * gam_at(c, k);
+    T lac_2 = pmp_2 - T(1.5) * gam_at(c, k - 1);
+    T tmp_min2 = lim3_min(a1, pmp_1, lac_1);
+    T tmp_max2 = lim3_max(a1, pmp_1, lac_1);
+    T tmp2 = a2 > tmp_min2 ? a2 : tmp_min2;
+    T tmp_min3 = a1 < pmp_2 ? a1 : pmp_2;
+    tmp_min3 = lac_2 < tmp_min3 ? lac_2 : tmp_min3;
+    T tmp_max3 = a1 > pmp_2 ? a1 : pmp_2;
+    tmp_max3 = lac_2 > tmp_max3 ? lac_2 : tmp_max3;
+    T tmp3 = a3 > tmp_min3 ? a3 : tmp_min3;
+    bool n5 = e5[0] || e5[2], n6 = e6[0] || e6[2];
+    if (e5[1]) {
+      if (n5) { a2 = a1; a3 = a1; }
+      else if (n6) { a2 = tmp2 < tmp_max2 ? tmp2 : tmp_max2; a3 = tmp3 < tmp_max3 ? tmp3 : tmp_max3; }
+    } else if (e6[1]) {
+      if (n5) { a2 = tmp2 < tmp_max2 ? tmp2 : tmp_max2; a3 = tmp3 < tmp_max3 ? tmp3 : tmp_max3; }
+    }
+    a4_from(a1, a2, a3, a4);
   }
-  if (iv == 0 && a3[km - 1] < T(0.0)) a3[km - 1] = T(0.0);
-  if (iv == -1 && a3[km - 1] * a1[km - 1] <= T(0.0)) a3[km - 1] = T(0.0);
-  a4_from(a1[km - 2], a2[km - 2], a3[km - 2], a4[km - 2]);
-  a4_from(a1[km - 1], a2[km - 1], a3[km - 1], a4[km - 1]);
-  remap_constraint(a1w[km - 2], a2[km - 2], a3[km - 2], a4[km - 2], c.extm[km - 2]);
-  posdef_iv1(a1w[km - 1], a2[km - 1], a3[km - 1], a4[km - 1]);
+  if (iv == 0) posdef_iv0(a1, a2, a3, a4);
 }
 
 // MapSingle.__call__ on one column: q (in/out, km levels) from source interfaces pe1 to target interfaces pe2
@@ -255,32 +268,37 @@ __device__ bool map_single_column(const Pt& p, ColT<T>& c, int km, T* q, const T
     c.a1[k] = A(q, 0, 0, k);
     if (!keep_dp) c.dp[k] = A(pe1, 0, 0, k + 1) - A(pe1, 0, 0, k);
   }
-  remap_profile(c, km, iv, kord, qs, qmin);
+  profile_solve(c, km, iv, qs);
   // lagrangian_contributions (map_single.py:21-81); L = k + lev is the absolute source layer.  Variable-k reads
   // are clipped to the allocated levels [0, km] like the numpy backend does.
   auto P1 = [&](int L) { return A(pe1, 0, 0, L > km ? km : L); };
   auto cl = [&](int L) { return L > km - 1 ? km - 1 : L; };  // layer arrays: km entries meaningful
   int L = 0;
+  int Lc = 0;
+  T a2, a3, a4;  // coefficients of source layer Lc; re-evaluated when the walk moves to another layer
+  coef_at(c, km, iv, kord, qmin, Lc, a2, a3, a4);
   for (int k = 0; k < km; ++k) {
     const T pe2k = A(pe2, 0, 0, k), pe2k1 = A(pe2, 0, 0, k + 1);
-    int Lc = cl(L);
     T pl = (pe2k - P1(L)) / c.dp[Lc];
     T qv;
     if (pe2k1 <= P1(L + 1)) {
       T pr = (pe2k1 - P1(L)) / c.dp[Lc];
-      qv = c.a2[Lc] + T(0.5) * (c.a4[Lc] + c.a3[Lc] - c.a2[Lc]) * (pr + pl) - c.a4[Lc] * T(1.0) / T(3.0) * (pr * (pr + pl) + pl * pl);
+      qv = a2 + T(0.5) * (a4 + a3 - a2) * (pr + pl) - a4 * T(1.0) / T(3.0) * (pr * (pr + pl) + pl * pl);
     } else {
       T qsum = (P1(L + 1) - pe2k) *
-                    (c.a2[Lc] + T(0.5) * (c.a4[Lc] + c.a3[Lc] - c.a2[Lc]) * (T(1.0) + pl) - c.a4[Lc] * T(1.0) / T(3.0) * (T(1.0) + pl * (T(1.0) + pl)));
+                    (a2 + T(0.5) * (a4 + a3 - a2) * (T(1.0) + pl) - a4 * T(1.0) / T(3.0) * (T(1.0) + pl * (T(1.0) + pl)));
       L = L + 1;
       while (L < km && P1(L + 1) < pe2k1) {
         qsum += c.dp[cl(L)] * c.a1[cl(L)];
         L = L + 1;
       }
-      Lc = cl(L);
+      if (cl(L) != Lc) {
+        Lc = cl(L);
+        coef_at(c, km, iv, kord, qmin, Lc, a2, a3, a4);
+      }
       T dp = pe2k1 - P1(L);
       T esl = dp / c.dp[Lc];
-      qsum += dp * (c.a2[Lc] + T(0.5) * esl * (c.a3[Lc] - c.a2[Lc] + c.a4[Lc] * (T(1.0) - (T(2.0) / T(3.0)) * esl)));
+      qsum += dp * (a2 + T(0.5) * esl * (a3 - a2 + a4 * (T(1.0) - (T(2.0) / T(3.0)) * esl)));
       qv = qsum / (pe2k1 - pe2k);
     }
     A(q, 0, 0, k) = qv;

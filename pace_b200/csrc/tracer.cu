@@ -65,7 +65,7 @@ int tracer_substep(Core& c, int nq) {
     a.x_mass_flux = mfx; a.y_mass_flux = mfy; a.hord = c.cfg.hord_tr; a.nk = g.nz;
     if (fvtp2d(c, a)) return 1;
     launch_ijk(st, g, box_compute(g), [=] __device__(const Pt& p) {
-      A0(q) = (A0(q) * A0(dp1) + (A0(fx) - A(fx, 1, 0, 0) + A0(fy) - A(fy, 0, 1, 0)) * A20(rarea)) / A0(dp2);
+      A0(q) = fv_div(A0(q) * A0(dp1) + (A0(fx) - A(fx, 1, 0, 0) + A0(fy) - A(fy, 0, 1, 0)) * A20(rarea), A0(dp2));
     });
   }
   return 0;
