@@ -136,6 +136,26 @@ __global__ void __launch_bounds__(128) k_ij(Geo g, Box b, F f) {
   f(p);
 }
 
+// column kernel compiled for at least MINB resident CTAs per SM (register cap 65536 / (128 MINB)): the long column
+// kernels are bound by the latency of their thread-local arrays and scale with the number of resident warps
+template <int MINB, class F>
+__global__ void __launch_bounds__(128, MINB) k_ij_occ(Geo g, Box b, F f) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  int j = blockIdx.y * blockDim.y + threadIdx.y;
+  if (i >= b.ni || j >= b.nj) return;
+  int t = blockIdx.z;
+  Pt p = make_pt(g, t, b.i0 + i, b.j0 + j, b.k0);
+  f(p);
+}
+template <int MINB, class F>
+inline void launch_ij_occ(cudaStream_t s, const Geo& g, Box b, F f, const char* label = nullptr) {
+  if (b.ni <= 0 || b.nj <= 0) return;
+  LaunchScope scope(s, label);
+  dim3 blk(32, 4, 1);
+  dim3 grd((b.ni + 31) / 32, (b.nj + 3) / 4, g.nt);
+  k_ij_occ<MINB><<<grd, blk, 0, s>>>(g, b, f);
+}
+
 template <class F>
 inline void launch_ijk(cudaStream_t s, const Geo& g, Box b, F f, const char* label = nullptr) {
   if (b.ni <= 0 || b.nj <= 0 || b.nk <= 0) return;
@@ -147,13 +167,16 @@ inline void launch_ijk(cudaStream_t s, const Geo& g, Box b, F f, const char* lab
   k_ijk<<<grd, blk, 0, s>>>(g, b, f);
 }
 
+// pad_smem: dynamic shared memory the kernel does not use; it only lowers the number of resident CTAs per SM for
+// column kernels whose thread-local arrays should stay within the L2
 template <class F>
-inline void launch_ij(cudaStream_t s, const Geo& g, Box b, F f, const char* label = nullptr) {
+inline void launch_ij(cudaStream_t s, const Geo& g, Box b, F f, const char* label = nullptr, int pad_smem = 0) {
   if (b.ni <= 0 || b.nj <= 0) return;
   LaunchScope scope(s, label);
   dim3 blk(32, 4, 1);
   dim3 grd((b.ni + 31) / 32, (b.nj + 3) / 4, g.nt);
-  k_ij<<<grd, blk, 0, s>>>(g, b, f);
+  if (pad_smem > 48 * 1024) cudaFuncSetAttribute(k_ij<F>, cudaFuncAttributeMaxDynamicSharedMemorySize, pad_smem);
+  k_ij<<<grd, blk, pad_smem, s>>>(g, b, f);
 }
 
 #else   // PACE_HOST_EMU: plain loops, same iteration space
@@ -168,8 +191,12 @@ inline void launch_ijk(cudaStream_t, const Geo& g, Box b, F f, const char* = nul
       for (int j = 0; j < b.nj; ++j)
         for (int i = 0; i < b.ni; ++i) f(make_pt(g, t, b.i0 + i, b.j0 + j, b.k0 + k));
 }
+template <int MINB, class F>
+inline void launch_ij_occ(cudaStream_t s, const Geo& g, Box b, F f, const char* label = nullptr) {
+  launch_ij(s, g, b, f, label);
+}
 template <class F>
-inline void launch_ij(cudaStream_t, const Geo& g, Box b, F f, const char* = nullptr) {
+inline void launch_ij(cudaStream_t, const Geo& g, Box b, F f, const char* = nullptr, int = 0) {
   ++launch_counter();
 #ifdef PACE_HOST_EMU_OMP
 #pragma omp parallel for collapse(2) schedule(static)
@@ -213,9 +240,10 @@ __device__ __forceinline__ double fv_max(double a, double b) { return a > b ? a 
 // n / d.  A zero numerator over a positive denominator is n itself (same bits, signed zero included); answering that
 // without dividing keeps fields that are zero over most of the domain (condensates, q_con) off the out-of-line
 // special-operand path of the fp64 division, which a warp enters as soon as one lane has a zero numerator.
-__device__ __forceinline__ double fv_div(double n, double d) {
+template <class T>
+__device__ __forceinline__ T fv_div(T n, T d) {
 #ifndef PACE_HOST_EMU
-  if (n == 0.0 && d > 0.0) return n;
+  if (n == T(0.0) && d > T(0.0)) return n;
 #endif
   return n / d;
 }

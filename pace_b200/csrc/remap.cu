@@ -85,10 +85,11 @@ __device__ __forceinline__ void profile_solve(ColT<T>& c, int km, int iv, T qs) 
     T bet = gr * (gr + T(0.5));
     q[0] = ((gr + gr) * (gr + T(1.0)) * a1[0] + a1[1]) / bet;
     gam[0] = (T(1.0) + gr * (gr + T(1.5))) / bet;
+#pragma unroll 4
     for (int k = 1; k < km; ++k) {
       T d4 = delp[k - 1] / delp[k];
       bet = T(2.0) + d4 + d4 - gam[k - 1];
-      q[k] = (T(3.0) * (a1[k - 1] + d4 * a1[k]) - q[k - 1]) / bet;
+      q[k] = fv_div(T(3.0) * (a1[k - 1] + d4 * a1[k]) - q[k - 1], bet);
       gam[k] = d4 / bet;
     }
     {
@@ -96,6 +97,7 @@ __device__ __forceinline__ void profile_solve(ColT<T>& c, int km, int iv, T qs) 
       T a_bot = T(1.0) + d4 * (d4 + T(1.5));
       q[km] = (T(2.0) * d4 * (d4 + T(1.0)) * a1[km - 1] + a1[km - 2] - a_bot * q[km - 1]) / (d4 * (d4 + T(0.5)) - a_bot * gam[km - 1]);
     }
+#pragma unroll 4
     for (int k = km - 1; k >= 0; --k) q[k] = q[k] - gam[k] * q[k + 1];
   } else {
     q[0] = T(1.5) * a1[0];
@@ -277,32 +279,43 @@ __device__ bool map_single_column(const Pt& p, ColT<T>& c, int km, T* q, const T
   int Lc = 0;
   T a2, a3, a4;  // coefficients of source layer Lc; re-evaluated when the walk moves to another layer
   coef_at(c, km, iv, kord, qmin, Lc, a2, a3, a4);
+  // the values the walk needs of its current source layer live in registers: p1L = P1(L), p1L1 = P1(L + 1),
+  // dpL = c.dp[Lc]; pe2 is read once per level
+  T p1L = P1(0), p1L1 = P1(1), dpL = c.dp[0];
+  T pe2k = A(pe2, 0, 0, 0);
   for (int k = 0; k < km; ++k) {
-    const T pe2k = A(pe2, 0, 0, k), pe2k1 = A(pe2, 0, 0, k + 1);
-    T pl = (pe2k - P1(L)) / c.dp[Lc];
+    const T pe2k1 = A(pe2, 0, 0, k + 1);
+    T pl = fv_div(pe2k - p1L, dpL);
     T qv;
-    if (pe2k1 <= P1(L + 1)) {
-      T pr = (pe2k1 - P1(L)) / c.dp[Lc];
+    if (pe2k1 <= p1L1) {
+      T pr = (pe2k1 - p1L) / dpL;
       qv = a2 + T(0.5) * (a4 + a3 - a2) * (pr + pl) - a4 * T(1.0) / T(3.0) * (pr * (pr + pl) + pl * pl);
     } else {
-      T qsum = (P1(L + 1) - pe2k) *
+      T qsum = (p1L1 - pe2k) *
                     (a2 + T(0.5) * (a4 + a3 - a2) * (T(1.0) + pl) - a4 * T(1.0) / T(3.0) * (T(1.0) + pl * (T(1.0) + pl)));
       L = L + 1;
-      while (L < km && P1(L + 1) < pe2k1) {
+      T pa = p1L1, pb = P1(L + 1);  // P1(L), P1(L + 1) of the layer the walk is at
+      while (L < km && pb < pe2k1) {
         qsum += c.dp[cl(L)] * c.a1[cl(L)];
         L = L + 1;
+        pa = pb;
+        pb = P1(L + 1);
       }
+      p1L = pa;
+      p1L1 = pb;
       if (cl(L) != Lc) {
         Lc = cl(L);
         coef_at(c, km, iv, kord, qmin, Lc, a2, a3, a4);
       }
-      T dp = pe2k1 - P1(L);
-      T esl = dp / c.dp[Lc];
+      dpL = c.dp[Lc];
+      T dp = pe2k1 - p1L;
+      T esl = fv_div(dp, dpL);
       qsum += dp * (a2 + T(0.5) * esl * (a3 - a2 + a4 * (T(1.0) - (T(2.0) / T(3.0)) * esl)));
-      qv = qsum / (pe2k1 - pe2k);
+      qv = fv_div(qsum, pe2k1 - pe2k);
     }
     A(q, 0, 0, k) = qv;
     any_negative = any_negative || qv < T(0.0);
+    pe2k = pe2k1;
   }
   return any_negative;
 }
@@ -384,6 +397,12 @@ struct TrPtrs { double* p[9]; };
 }  // namespace
 
 const char* tracer_name(int n);
+
+// Resident CTAs per SM the scalar column kernel is compiled for (8, 10 or 12; see launch_ij_occ).
+static int remap_occupancy() {
+  static const int n = [] { const char* v = getenv("PACE_B200_REMAP_OCC"); return v ? atoi(v) : 12; }();
+  return n;
+}
 
 // MapSingle.__call__ exposed on registered fields (also used by the test-suite on synthetic columns).
 // xi / yi: the field's horizontal staggering (dims [X(_INTERFACE), Y(_INTERFACE), Z]).
@@ -479,7 +498,7 @@ int remap_main(Core& c, int nq) {
   TrPtrs trp;
   for (int n = 0; n < 9; ++n) trp.p[n] = n < nq ? tr[n] : nullptr;
   const bool fill = cf.fill != 0;
-  launch_ij(st, g, box_compute(g), [=] __device__(const Pt& p) {
+  auto scalars_column = [=] __device__(const Pt& p) {
     COL_DECL;
     map_single_column(p, col, km, pt, peln, pn2, 1, kord_tm, 0.0, t_min);
     unsigned negative = 0;  // tracers whose remapped column holds a negative value
@@ -515,7 +534,12 @@ int remap_main(Core& c, int nq) {
       A(cappa, 0, 0, k) = cap;
       A(pkz, 0, 0, k) = fv_exp(cap * fv_log(RDG * A(delp, 0, 0, k) / A(delz, 0, 0, k) * A(pt, 0, 0, k)));
     }
-  }, "remap_scalars_column");
+  };
+  switch (remap_occupancy()) {
+    case 8: launch_ij_occ<8>(st, g, box_compute(g), scalars_column, "remap_scalars_column"); break;
+    case 10: launch_ij_occ<10>(st, g, box_compute(g), scalars_column, "remap_scalars_column"); break;
+    default: launch_ij_occ<12>(st, g, box_compute(g), scalars_column, "remap_scalars_column"); break;
+  }
   // pressures_mapu + map_single_u on [is..ie] x [js..je+1]
   launch_ij(st, g, Box{is, js, 0, g.nx, g.ny + 1, 1}, [=] __device__(const Pt& p) {
     COL_DECL;
