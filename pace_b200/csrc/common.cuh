@@ -115,12 +115,15 @@ struct LaunchScope {
 #ifndef PACE_HOST_EMU
 // The points of one level are numbered row by row and dealt to the threads in that order: no idle lanes at the row
 // ends (box widths such as 199 would leave 11 % of a 32-wide block column idle).
+// Grid: x = blocks of 256 points of one level, y = level, z = subdomain (no division for k / t); the row of a point is
+// a multiply-high by the launch's magic number (launch_ijk).  The index preamble is ~12 instructions: for the many
+// light stencils it used to be more than half of the executed instructions.
 template <class F>
 __global__ void __launch_bounds__(256) k_ijk(Geo g, Box b, F f) {
   const int n = blockIdx.x * blockDim.x + threadIdx.x;
   if (n >= b.ni * b.nj) return;
   const int j = b.magic ? (int)__umulhi((unsigned)n, b.magic) : n / b.ni, i = n - j * b.ni;
-  int k = blockIdx.y % b.nk, t = blockIdx.y / b.nk;
+  const int k = blockIdx.y, t = blockIdx.z;
   Pt p = make_pt(g, t, b.i0 + i, b.j0 + j, b.k0 + k);
   f(p);
 }
@@ -161,7 +164,7 @@ inline void launch_ijk(cudaStream_t s, const Geo& g, Box b, F f, const char* lab
   if (b.ni <= 0 || b.nj <= 0 || b.nk <= 0) return;
   LaunchScope scope(s, label);
   dim3 blk(256, 1, 1);
-  dim3 grd((b.ni * b.nj + 255) / 256, b.nk * g.nt, 1);
+  dim3 grd((b.ni * b.nj + 255) / 256, b.nk, g.nt);
   // row index by multiplication: exact while n * ni < 2^32 for all n < ni * nj (n * (magic * ni - 2^32) < 2^32)
   if (b.ni > 1 && (unsigned long long)b.ni * b.nj * b.ni < (1ull << 32)) b.magic = (unsigned)((1ull << 32) / (unsigned)b.ni) + 1u;
   k_ijk<<<grd, blk, 0, s>>>(g, b, f);

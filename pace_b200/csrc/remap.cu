@@ -541,7 +541,7 @@ int remap_main(Core& c, int nq) {
     default: launch_ij_occ<12>(st, g, box_compute(g), scalars_column, "remap_scalars_column"); break;
   }
   // pressures_mapu + map_single_u on [is..ie] x [js..je+1]
-  launch_ij(st, g, Box{is, js, 0, g.nx, g.ny + 1, 1}, [=] __device__(const Pt& p) {
+  launch_ij_occ<12>(st, g, Box{is, js, 0, g.nx, g.ny + 1, 1}, [=] __device__(const Pt& p) {
     COL_DECL;
     double pe_bottom_m = A(pe, 0, -1, km), pe1_bottom = A(pe, 0, 0, km);
     A(pe0, 0, 0, 0) = A(pe, 0, 0, 0);
@@ -553,7 +553,7 @@ int remap_main(Core& c, int nq) {
     map_single_column(p, col, km, u, pe0, pe3, -1, kord_mt, 0.0, 0.0);
   });
   // pressures_mapv + map_single_v on [is..ie+1] x [js..je]
-  launch_ij(st, g, Box{is, js, 0, g.nx + 1, g.ny, 1}, [=] __device__(const Pt& p) {
+  launch_ij_occ<12>(st, g, Box{is, js, 0, g.nx + 1, g.ny, 1}, [=] __device__(const Pt& p) {
     COL_DECL;
     double pe_bottom_m = A(pe, -1, 0, km), pe_bottom = A(pe, 0, 0, km);
     A(pe3, 0, 0, 0) = ak[0];
