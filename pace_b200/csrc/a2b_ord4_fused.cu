@@ -26,7 +26,7 @@ struct A2bArgs {
   int k0, nk;
 };
 
-__global__ void __launch_bounds__(TX * NTY, 4) k_a2b_fused(Geo g, A2bArgs a) {
+__global__ void __launch_bounds__(TX * NTY, 6) k_a2b_fused(Geo g, A2bArgs a) {
   __shared__ double sq[QH][QW];           // qin(i0-3+li, j0-3+lj)
   __shared__ double sqx[QH][TX + 1];      // qx(i0+li, j0-3+lj)
   __shared__ double sqy[TY + 1][QW];      // qy(i0-3+li, j0+lj)

@@ -138,7 +138,7 @@ __device__ __forceinline__ void deln_tile_corner(const Geo& g, const DelnFusedAr
   }
 }
 
-__global__ void __launch_bounds__(TX * NTY) k_delnflux_fused(Geo g, DelnFusedArgs a) {
+__global__ void __launch_bounds__(TX * NTY, 6) k_delnflux_fused(Geo g, DelnFusedArgs a) {
   __shared__ double d2[H][W];          // cell (i0-AP+li, j0-AP+lj)
   __shared__ double fx2[H][W + 1];     // x interface, same indexing
   __shared__ double fy2[H + 1][W];     // y interface

@@ -123,17 +123,19 @@ __device__ __forceinline__ void cp_async8(double* smem_dst, const double* gmem_s
 template <int MORD, class DF>
 __device__ __forceinline__ double xsweep_flux(const double* row, int L, int i, double c, DF D, int is, int ie, bool W,
                                               bool E) {
-  auto Q = [&](int d) { return row[L + d]; };
+  // Every lane evaluates the interior formulas on its own (clamped) neighbourhood without a branch, so that the
+  // independent chains of a step share basic blocks and can be interleaved by the scheduler; what the out-of-range
+  // lanes 0, 1, 30, 31 produce is never used by a lane whose result is.  Lanes next to a tile edge then replace their
+  // value by the edge formula.
+  const int Lm1 = L > 0 ? L - 1 : 0, Lm2 = L > 1 ? L - 2 : 0;
+  const double qm2 = row[Lm2], qm = row[Lm1], q0 = row[L], qp = row[L + 1];
+  auto D5 = D;
   if (MORD < 8) {
     using namespace ppmc;
-    double al = 0.0;
-    if (L >= 2 && L <= 30) {
-      const bool special = (W && i >= is - 1 && i <= is + 1) || (E && i >= ie && i <= ie + 2);
-      if (special) al = ppm_al_vals(Q(-2), Q(-1), Q(0), Q(1), D(-2), D(-1), D(0), D(1), i, is, ie, W, E);
-      else al = p1 * (row[L - 1] + row[L]) + p2 * (row[L - 2] + row[L + 1]);
-    }
+    double al = p1 * (qm + q0) + p2 * (qm2 + qp);
+    if (L >= 2 && L <= 30 && ((W && i >= is - 1 && i <= is + 1) || (E && i >= ie && i <= ie + 2)))
+      al = ppm_al_vals(qm2, qm, q0, qp, D5(-2), D5(-1), D5(0), D5(1), i, is, ie, W, E);
     const double alm = __shfl_up_sync(FULL, al, 1), alp = __shfl_down_sync(FULL, al, 1);
-    const double q0 = row[L], qm = row[L > 0 ? L - 1 : 0];
     const double bl = al - q0, br = alp - q0, b0 = bl + br;
     const double blm = alm - qm, brm = al - qm, b0m = blm + brm;
     bool s0, sm;
@@ -148,28 +150,20 @@ __device__ __forceinline__ double xsweep_flux(const double* row, int L, int i, d
     const double fx1 = c > 0.0 ? (1.0 - c) * (brm - c * b0m) : (1.0 + c) * (bl + c * b0);
     return c > 0.0 ? qm + fx1 * mask : q0 + fx1 * mask;
   } else {
-    double dm = 0.0;
-    if (L >= 1 && L <= 30) dm = ppm_dm8_v(row[L - 1], row[L], row[L + 1]);
+    const double dm = ppm_dm8_v(qm, q0, qp);
     const double dm_m = __shfl_up_sync(FULL, dm, 1), dm_p = __shfl_down_sync(FULL, dm, 1);
-    const double q = row[L];
-    double bl = 0.0, br = 0.0;
-    if (L >= 2 && L <= 29) {
-      const bool special = (W && i >= is - 1 && i <= is + 1) || (E && i >= ie - 1 && i <= ie + 1);
-      if (special) {
-        const BlBr r = ppm_blbr8_vals(Q(-2), Q(-1), Q(0), Q(1), Q(2), D(-2), D(-1), D(0), D(1), D(2), i, is, ie, W, E);
-        bl = r.bl;
-        br = r.br;
-      } else {
-        const double al_lo = 0.5 * (row[L - 1] + q) + 1.0 / 3.0 * (dm_m - dm);
-        const double al_hi = 0.5 * (q + row[L + 1]) + 1.0 / 3.0 * (dm - dm_p);
-        const double xt = 2.0 * dm;
-        bl = -1.0 * fv_sign(fv_min(fabs(xt), fabs(al_lo - q)), xt);
-        br = fv_sign(fv_min(fabs(xt), fabs(al_hi - q)), xt);
-      }
+    const double al_lo = 0.5 * (qm + q0) + 1.0 / 3.0 * (dm_m - dm);
+    const double al_hi = 0.5 * (q0 + qp) + 1.0 / 3.0 * (dm - dm_p);
+    const double xt = 2.0 * dm;
+    double bl = -1.0 * fv_sign(fv_min(fabs(xt), fabs(al_lo - q0)), xt);
+    double br = fv_sign(fv_min(fabs(xt), fabs(al_hi - q0)), xt);
+    if (L >= 2 && L <= 29 && ((W && i >= is - 1 && i <= is + 1) || (E && i >= ie - 1 && i <= ie + 1))) {
+      const BlBr r = ppm_blbr8_vals(qm2, qm, q0, qp, row[L + 2], D5(-2), D5(-1), D5(0), D5(1), D5(2), i, is, ie, W, E);
+      bl = r.bl;
+      br = r.br;
     }
     const double blm = __shfl_up_sync(FULL, bl, 1), brm = __shfl_up_sync(FULL, br, 1);
-    const double qm = row[L > 0 ? L - 1 : 0];
-    return cells_flux<8>(c, qm, blm, brm, false, q, bl, br, false);
+    return cells_flux<8>(c, qm, blm, brm, false, q0, bl, br, false);
   }
 }
 
@@ -281,11 +275,11 @@ __global__ void __launch_bounds__(WPB * 32, 20) k_fvtp2d_march(Geo g, MarchArgs 
     }
     const double fxin_p = __shfl_down_sync(FULL, fxin, 1);
     double qj = 0.0;
-    if (cell_out) {
+    {
       const double xf0 = ring(2, slot)[L], xf1 = ring(2, slot)[L + 1], ar = ring(3, slot)[L];
       const double fx10 = xf0 * fxin, fx11 = xf1 * fxin_p;
       const double area_with_x_flux = ar + xf0 - xf1;
-      qj = fv_div(qx * ar + fx10 - fx11, area_with_x_flux);
+      if (cell_out) qj = fv_div(qx * ar + fx10 - fx11, area_with_x_flux);
     }
     fxring[(s & 3) * PITCH + L] = fxin;  // needed again at step s + 3 (outer x flux of this row)
     // 3. y sweeps: cell jc = R-2 is complete
@@ -299,25 +293,25 @@ __global__ void __launch_bounds__(WPB * 32, 20) k_fvtp2d_march(Geo g, MarchArgs 
       auto D = [&](int d) { return dya[oc + d * sj]; };
       double bli = 0.0, bri = 0.0, blo = 0.0, bro = 0.0;
       bool si = false, so = false;
-      if (col_ok) march_cell<MI>(mi, jc, first, near, D, js, je, S, N, bli, bri, si);
-      if (cell_out) march_cell<MO>(mo, jc, first, near, D, js, je, S, N, blo, bro, so);
+      if (near) {  // rows next to a tile edge (row-uniform): the edge formulas read the grid spacing
+        if (col_ok) march_cell<MI>(mi, jc, first, true, D, js, je, S, N, bli, bri, si);
+        if (cell_out) march_cell<MO>(mo, jc, first, true, D, js, je, S, N, blo, bro, so);
+      } else {     // registers only: all lanes, the two sweeps in one basic block (columns that do not exist carry zeros)
+        march_cell<MI>(mi, jc, first, false, D, js, je, S, N, bli, bri, si);
+        march_cell<MO>(mo, jc, first, false, D, js, je, S, N, blo, bro, so);
+      }
       if (s >= 5) {  // interface jc, between cells jc-1 and jc
-        double fyin = 0.0;
-        if (col_ok) {
-          const double cy = ring(4, slot)[L];
-          fyin = cells_flux<MI>(cy, mi.w[1], mi.pbl, mi.pbr, mi.ps, mi.w[2], bli, bri, si);
-          if (cell_out && (jc <= j_hi || last_chunk)) {
-            const double outer = cells_flux<MO>(cy, mo.w[1], mo.pbl, mo.pbr, mo.ps, mo.w[2], blo, bro, so);
-            fy[oc] = 0.5 * (outer + fyin) * ring(5, slot)[L];
-          }
-          const double yf1 = ring(6, slot)[L];
-          if (s >= 6) {  // q_i on row R-3
-            const double yf0 = yfx_prev, ar = ring(7, slot)[L];
-            const double fyy0 = yf0 * fyin_prev, fyy1 = yf1 * fyin;
-            qi = fv_div(mi.w[1] * ar + fyy0 - fyy1, ar + yf0 - yf1);
-          }
-          yfx_prev = yf1;
+        const double cy = ring(4, slot)[L];
+        const double fyin = cells_flux<MI>(cy, mi.w[1], mi.pbl, mi.pbr, mi.ps, mi.w[2], bli, bri, si);
+        const double outer = cells_flux<MO>(cy, mo.w[1], mo.pbl, mo.pbr, mo.ps, mo.w[2], blo, bro, so);
+        if (cell_out && (jc <= j_hi || last_chunk)) fy[oc] = 0.5 * (outer + fyin) * ring(5, slot)[L];
+        const double yf1 = ring(6, slot)[L];
+        if (s >= 6 && col_ok) {  // q_i on row R-3
+          const double yf0 = yfx_prev, ar = ring(7, slot)[L];
+          const double fyy0 = yf0 * fyin_prev, fyy1 = yf1 * fyin;
+          qi = fv_div(mi.w[1] * ar + fyy0 - fyy1, ar + yf0 - yf1);
         }
+        yfx_prev = yf1;
         fyin_prev = fyin;
       }
       mi.pbl = bli; mi.pbr = bri; mi.ps = si;
