@@ -33,7 +33,7 @@ __global__ void __launch_bounds__(TX * NTY, 6) k_a2b_fused(Geo g, A2bArgs a) {
   const int k = a.k0 + blockIdx.z % a.nk, t = blockIdx.z / a.nk;
   const int is = g.is, ie = g.ie, js = g.js, je = g.je, sj = g.sj;
   const int i0 = is + blockIdx.x * TX, j0 = js + blockIdx.y * TY;
-  const unsigned char ed = g.edge[t];
+  const unsigned ed = edge_of(g, t);
   const bool W = ed & EDGE_W, E = ed & EDGE_E, S = ed & EDGE_S, N = ed & EDGE_N;
   const int base3 = t * (int)g.st3 + k * g.sk, base2 = t * g.sk;
   const int tx = threadIdx.x, ty = threadIdx.y;

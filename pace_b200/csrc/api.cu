@@ -160,8 +160,9 @@ int pace_b200_create(const pace_b200_config* cfg, const unsigned char* edge_flag
     return 1;
   }
   g.is = HALO; g.ie = HALO + g.nx - 1; g.js = HALO; g.je = HALO + g.ny - 1;
-  memset(g.edge, 0, sizeof g.edge);
-  for (int t = 0; t < g.nt; ++t) g.edge[t] = edge_flags ? edge_flags[t] : 15;
+  g.edge_bits[0] = g.edge_bits[1] = 0;
+  for (int t = 0; t < g.nt; ++t)
+    g.edge_bits[t >> 4] |= (unsigned long long)((edge_flags ? edge_flags[t] : 15) & 15) << ((t & 15) * 4);
   *handle = c;
   return 0;
 }

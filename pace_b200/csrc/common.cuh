@@ -51,8 +51,14 @@ struct Geo {
   int sj, sk;           // row / plane strides (elements)
   long long st3;        // subdomain stride of 3-D fields
   int is, ie, js, je;   // first/last compute cell (3, nx+2, 3, ny+2)
-  unsigned char edge[MAX_TILES];  // EdgeBits per subdomain: does it touch the tile edge?
+  // EdgeBits per subdomain (does it touch the tile edge?), 4 bits each, subdomains 0-15 / 16-31.  Packed words and not
+  // an array: a kernel parameter array indexed by the subdomain makes the compiler copy the whole struct to local
+  // memory in every thread.
+  unsigned long long edge_bits[2];
 };
+__host__ __device__ __forceinline__ unsigned edge_of(const Geo& g, int t) {
+  return (unsigned)((t < 16 ? g.edge_bits[0] : g.edge_bits[1]) >> ((t & 15) * 4)) & 15u;
+}
 
 // One grid point handed to a stencil body.
 // Linear offsets into 3-D fields: 32-bit on the device (one IMAD.WIDE per access instead of 64-bit index chains;
@@ -77,7 +83,7 @@ __device__ __forceinline__ Pt make_pt(const Geo& g, int t, int i, int j, int k) 
   p.sj = g.sj; p.sk = g.sk;
   p.o2 = t * g.sk + j * g.sj + i;
   p.o = (off3_t)((off3_t)t * (off3_t)g.st3 + (off3_t)k * g.sk + j * g.sj + i);
-  unsigned char e = g.edge[t];
+  const unsigned e = edge_of(g, t);
   p.W = e & EDGE_W; p.E = e & EDGE_E; p.S = e & EDGE_S; p.N = e & EDGE_N;
   return p;
 }
@@ -120,6 +126,17 @@ struct LaunchScope {
 // light stencils it used to be more than half of the executed instructions.
 template <class F>
 __global__ void __launch_bounds__(256) k_ijk(Geo g, Box b, F f) {
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= b.ni * b.nj) return;
+  const int j = b.magic ? (int)__umulhi((unsigned)n, b.magic) : n / b.ni, i = n - j * b.ni;
+  const int k = blockIdx.y, t = blockIdx.z;
+  Pt p = make_pt(g, t, b.i0 + i, b.j0 + j, b.k0 + k);
+  f(p);
+}
+
+// the same kernel compiled for at least MINB resident CTAs per SM (stencils with long per-point code)
+template <int MINB, class F>
+__global__ void __launch_bounds__(256, MINB) k_ijk_occ(Geo g, Box b, F f) {
   const int n = blockIdx.x * blockDim.x + threadIdx.x;
   if (n >= b.ni * b.nj) return;
   const int j = b.magic ? (int)__umulhi((unsigned)n, b.magic) : n / b.ni, i = n - j * b.ni;
@@ -172,6 +189,16 @@ inline void launch_ijk(cudaStream_t s, const Geo& g, Box b, F f, const char* lab
 
 // pad_smem: dynamic shared memory the kernel does not use; it only lowers the number of resident CTAs per SM for
 // column kernels whose thread-local arrays should stay within the L2
+template <int MINB, class F>
+inline void launch_ijk_occ(cudaStream_t s, const Geo& g, Box b, F f, const char* label = nullptr) {
+  if (b.ni <= 0 || b.nj <= 0 || b.nk <= 0) return;
+  LaunchScope scope(s, label);
+  dim3 blk(256, 1, 1);
+  dim3 grd((b.ni * b.nj + 255) / 256, b.nk, g.nt);
+  if (b.ni > 1 && (unsigned long long)b.ni * b.nj * b.ni < (1ull << 32)) b.magic = (unsigned)((1ull << 32) / (unsigned)b.ni) + 1u;
+  k_ijk_occ<MINB><<<grd, blk, 0, s>>>(g, b, f);
+}
+
 template <class F>
 inline void launch_ij(cudaStream_t s, const Geo& g, Box b, F f, const char* label = nullptr, int pad_smem = 0) {
   if (b.ni <= 0 || b.nj <= 0) return;
@@ -197,6 +224,10 @@ inline void launch_ijk(cudaStream_t, const Geo& g, Box b, F f, const char* = nul
 template <int MINB, class F>
 inline void launch_ij_occ(cudaStream_t s, const Geo& g, Box b, F f, const char* label = nullptr) {
   launch_ij(s, g, b, f, label);
+}
+template <int MINB, class F>
+inline void launch_ijk_occ(cudaStream_t s, const Geo& g, Box b, F f, const char* label = nullptr) {
+  launch_ijk(s, g, b, f, label);
 }
 template <class F>
 inline void launch_ij(cudaStream_t, const Geo& g, Box b, F f, const char* = nullptr, int = 0) {

@@ -28,7 +28,7 @@ struct CornerOps {
 //   y:  q(is-1, js-n) = sw*qc(is-1+n, js-1)   q(ie+1, js-n) = se*qc(ie+1-n, js-1)
 //       q(is-1, je+n) = nw*qc(is-1+n, je+1)   q(ie+1, je+n) = ne*qc(ie+1-n, je+1)
 __device__ __forceinline__ void corner_fill_cell(const Geo& g, const CornerOp& o, int t, int k, int c, int n) {
-  unsigned char e = g.edge[t];
+  const unsigned e = edge_of(g, t);
   bool W = e & EDGE_W, E = e & EDGE_E, S = e & EDGE_S, N = e & EDGE_N;
   int is = g.is, ie = g.ie, js = g.js, je = g.je;
   int wi, wj, ri, rj;

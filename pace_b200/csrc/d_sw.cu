@@ -164,7 +164,7 @@ int d_sw(Core& c, double dt) {
   const int mord_mt = cf.hord_mt < 0 ? -cf.hord_mt : cf.hord_mt;
   const double *dxa = c.F("grid.dxa"), *dya = c.F("grid.dya");
   (void)dxa; (void)dya;
-  launch_ijk(st, g, box_dims(g, 1, 1, 0), [=] __device__(const Pt& p) {
+  launch_ijk_occ<6>(st, g, box_dims(g, 1, 1, 0), [=] __device__(const Pt& p) {
     const int i = p.i, j = p.j;
     const bool iW = p.W && i == is, iE = p.E && i == ie + 1, jS = p.S && j == js, jN = p.N && j == je + 1;
     // interpolate_uc_vc_to_cell_corners (d_sw.py:694-741)
@@ -207,7 +207,7 @@ int d_sw(Core& c, double dt) {
                        ((io2 + 1) * A0(u) - (io2 * A(u, -1, 0, 0))));
     }
     A0(ke) = kev;
-  });
+  }, "d_sw_ke");
   // 14. compute_vorticity (compute + 3 halo)
   launch_ijk(st, g, box_dims(g, 0, 0, 0, 3, 3), [=] __device__(const Pt& p) {
     double rdy_tmp = A20(rarea) * A20(dx);

@@ -145,7 +145,7 @@ __global__ void __launch_bounds__(TX * NTY, 6) k_delnflux_fused(Geo g, DelnFused
   const int k = blockIdx.z % a.nk, t = blockIdx.z / a.nk;
   const int is = g.is, ie = g.ie, js = g.js, je = g.je, sj = g.sj;
   const int i0 = is + blockIdx.x * TX, j0 = js + blockIdx.y * TY;
-  const unsigned char ed = g.edge[t];
+  const unsigned ed = edge_of(g, t);
   const EdgeInfo e{is, ie, js, je, (bool)(ed & EDGE_W), (bool)(ed & EDGE_E), (bool)(ed & EDGE_S), (bool)(ed & EDGE_N)};
   const int N = (int)a.nord_col[k < 3 ? k : 3];
   const bool has_mass = a.mass != nullptr;

@@ -20,7 +20,7 @@ namespace {
 //   y:  (is-a, js-b) <- (is+b, js-a)    (ie1+a, js-b) <- (ie1-b, js-a)
 //       (is-a, je1+b) <- (is+b, je1+a)  (ie1+a, je1+b) <- (ie1-b, je1+a)
 __device__ __forceinline__ void bgrid_fill_cell(const Geo& g, double* q, bool ydir, int t, int k, int c, int a, int b) {
-  unsigned char ed = g.edge[t];
+  const unsigned ed = edge_of(g, t);
   bool W = ed & EDGE_W, E = ed & EDGE_E, S = ed & EDGE_S, N = ed & EDGE_N;
   const int is = g.is, ie1 = g.ie + 1, js = g.js, je1 = g.je + 1;
   int i, j, si, sj;
@@ -77,7 +77,7 @@ constexpr int DG_N = sizeof(DG_TABLE) / sizeof(DgEntry);
 
 __device__ __forceinline__ void dgrid_fill_entry(const Geo& g, double* x, double* y, double mysign, int t, int k, int n) {
   const DgEntry e = DG_TABLE[n];
-  unsigned char ed = g.edge[t];
+  const unsigned ed = edge_of(g, t);
   bool W = ed & EDGE_W, E = ed & EDGE_E, S = ed & EDGE_S, N = ed & EDGE_N;
   int bi, bj;
   bool on;

@@ -43,7 +43,7 @@ __global__ void __launch_bounds__(TX* TY) k_fvtp2d_fused(Geo g, FusedArgs a) {
   const int k = blockIdx.z % a.nk, t = blockIdx.z / a.nk;
   const int i0 = g.is + blockIdx.x * TX, j0 = g.js + blockIdx.y * TY;
   const int is = g.is, ie = g.ie, js = g.js, je = g.je;
-  const unsigned char ed = g.edge[t];
+  const unsigned ed = edge_of(g, t);
   const bool W = ed & EDGE_W, E = ed & EDGE_E, S = ed & EDGE_S, N = ed & EDGE_N;
   const EdgeInfo e{is, ie, js, je, W, E, S, N};
   const long long base3 = (long long)t * g.st3 + (long long)k * g.sk;

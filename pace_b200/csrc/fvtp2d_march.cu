@@ -185,7 +185,7 @@ __global__ void __launch_bounds__(WPB * 32, 20) k_fvtp2d_march(Geo g, MarchArgs 
   double* rings = fxring + 4 * PITCH;      // 4 rows (own lane only: no synchronisation); then the staged input rows
 
   const int is = g.is, ie = g.ie, js = g.js, je = g.je, sj = g.sj;
-  const unsigned char ed = g.edge[t];
+  const unsigned ed = edge_of(g, t);
   const bool W = ed & EDGE_W, E = ed & EDGE_E, S = ed & EDGE_S, N = ed & EDGE_N;
   const EdgeInfo e{is, ie, js, je, W, E, S, N};
   const int i0 = is + strip * SW;                     // first cell / interface this strip writes

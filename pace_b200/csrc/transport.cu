@@ -24,7 +24,7 @@ int delnflux_fused_launch(Core& c, const DelnArgs& a);
 
 // ---- materialised copy_corners ---------------------------------------------------------------------
 __device__ __forceinline__ void copy_corner_cell(const Geo& g, double* q, bool ydir, int t, int k, int c, int a, int b) {
-  unsigned char ed = g.edge[t];
+  const unsigned ed = edge_of(g, t);
   bool W = ed & EDGE_W, E = ed & EDGE_E, S = ed & EDGE_S, N = ed & EDGE_N;
   EdgeInfo e{g.is, g.ie, g.js, g.je, W, E, S, N};
   int i, j;
