@@ -214,6 +214,7 @@ __global__ void __launch_bounds__(WPB * 32, 20) k_fvtp2d_march(Geo g, MarchArgs 
   mi.ps = mo.ps = false;
   double fyin_prev = 0.0;                                 // inner y flux at interface R-3
   double yfx_prev = 0.0;                                  // yfx(i, R-3)
+  int zrun = 0;  // consecutive rows, ending at R, on which q is zero in all 32 columns of the strip
 
   // Asynchronous staging: every input row is copied global -> shared two steps ahead of its use (cp.async, no
   // registers held), in a ring of NSLOT slots per stream.  Streams and the row they carry at step R:
@@ -266,6 +267,20 @@ __global__ void __launch_bounds__(WPB * 32, 20) k_fvtp2d_march(Geo g, MarchArgs 
         qrow[L] = qx;
       }
       __syncwarp();
+    }
+    // Rows of zeros.  Every flux, q_i and q_j of this step is formed from rows R-6 .. R of the strip.  If q is zero on
+    // all of them (condensate species outside clouds and precipitation, q_con in dry air, w at rest), every PPM
+    // perturbation is a zero, the fluxes through the interfaces are +0 and so are q_i and q_j, whatever the Courant
+    // numbers: the step reduces to storing the zero fluxes (times the mass fluxes: their sign is the sign of the stored
+    // zero).  The carried sweep state is already the one a window of zeros leaves and stays as it is.
+    zrun = __all_sync(FULL, qx == 0.0 && qy == 0.0) ? zrun + 1 : 0;
+    if (zrun >= 7) {
+      const int jc = R - 2;
+      if (cell_out && (jc <= j_hi || last_chunk)) fy[o - 2 * sj] = 0.5 * (0.0 + 0.0) * ring(5, slot)[L];
+      yfx_prev = ring(6, slot)[L];
+      if (xface_out) fx[o - 3 * sj] = 0.5 * (0.0 + 0.0) * ring(9, slot)[L];
+      fxring[(s & 3) * PITCH + L] = 0.0;
+      continue;
     }
     // 2. inner x flux and q_j on row R
     double fxin;
