@@ -266,9 +266,19 @@ template <class T>
 __device__ bool map_single_column(const Pt& p, ColT<T>& c, int km, T* q, const T* pe1, const T* pe2, int iv,
                                   int kord, T qs, T qmin, bool keep_dp = false) {
   bool any_negative = false;
+  bool all_zero = true;
   for (int k = 0; k < km; ++k) {
-    c.a1[k] = A(q, 0, 0, k);
+    const T v = A(q, 0, 0, k);
+    c.a1[k] = v;
+    all_zero = all_zero && v == T(0.0);
     if (!keep_dp) c.dp[k] = A(pe1, 0, 0, k + 1) - A(pe1, 0, 0, k);
+  }
+  // A column of zeros of a positive-definite tracer (a condensate species outside clouds) remaps to +0 on every
+  // level: the tridiagonal solve, the constraints and the integrals only combine zeros.  c.dp is filled above
+  // because the following fields of the column reuse it.
+  if (iv == 0 && all_zero) {
+    for (int k = 0; k < km; ++k) A(q, 0, 0, k) = T(0.0);
+    return false;
   }
   profile_solve(c, km, iv, qs);
   // lagrangian_contributions (map_single.py:21-81); L = k + lev is the absolute source layer.  Variable-k reads
