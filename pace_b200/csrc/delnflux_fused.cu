@@ -159,6 +159,7 @@ __global__ void __launch_bounds__(TX * NTY, 6) k_delnflux_fused(Geo g, DelnFused
   // pass leaves unwritten on the rim of the apron is never read by anything that reaches the tile's own cells.
   const int tid = ty * TX + tx;
   constexpr int NTHR = TX * NTY;
+  bool nonzero = false;
   for (int n = tid; n < W * H; n += NTHR) {  // flat loops: the tile widths are not multiples of the warp size
     const int lj = n / W, li = n % W;
     const int i = i0 - AP + li, j = j0 - AP + lj;
@@ -167,8 +168,12 @@ __global__ void __launch_bounds__(TX * NTY, 6) k_delnflux_fused(Geo g, DelnFused
       const double qv = a.q[base3 + j * sj + i];
       v = has_mass ? qv : dampk * qv;
     }
+    nonzero = nonzero || v != 0.0;
     d2[lj][li] = v;
   }
+  // A tile (with its apron) of zeros - q_con in dry air, a condensate outside clouds - has zero damping fluxes: when
+  // they are to be added to existing fluxes there is nothing to do.
+  if (!__syncthreads_or(nonzero) && a.accumulate) return;
   // ask for the lines the result phase will read-modify-write (fx, fy, mass) now, so that they arrive in L2 while
   // the tile iterates in shared memory
   if (a.accumulate) {
@@ -183,7 +188,6 @@ __global__ void __launch_bounds__(TX * NTY, 6) k_delnflux_fused(Geo g, DelnFused
       }
     }
   }
-  __syncthreads();
 
   // do cube-corner cells (both a west/east and a south/north tile edge within the apron) enter this tile?
   const bool near_w = e.W && i0 - AP < is, near_e = e.E && i0 + TX + AP - 1 > ie;

@@ -27,30 +27,48 @@ int update_dz_d(Core& c, double dt) {
   }
 
   // cubic_spline_interpolation_from_layer_center_to_interfaces x4, full horizontal domain
+  // The four fields are independent: their recurrences advance together, level by level, so that four division
+  // chains are in flight per thread instead of one (the kernel is bound by the latency of the dependent divisions).
   launch_ij(st, g, box_full(g), [=] __device__(const Pt& p) {
-    const double* src[4] = {crx, xfx, cry, yfx};
-    double* dst[4] = {crx_i, xfx_i, cry_i, yfx_i};
-    for (int f = 0; f < 4; ++f) {
-      const double* q = src[f];
-      double* qi = dst[f];
-      double xt1 = 2.0 * gk[0] * (gk[0] + 1.0);
-      double prev = (xt1 * A(q, 0, 0, 0) + A(q, 0, 0, 1)) / beta[0];
-      A(qi, 0, 0, 0) = prev;
-      for (int k = 1; k < km; ++k) {
-        prev = (3.0 * (A(q, 0, 0, k - 1) + gk[k] * A(q, 0, 0, k)) - prev) / beta[k];
-        A(qi, 0, 0, k) = prev;
-      }
-      {
-        double a_bot = 1.0 + gk[km - 1] * (gk[km - 1] + 1.5);
-        double xt1b = 2.0 * gk[km - 1] * (gk[km - 1] + 1.0);
-        double xt2 = gk[km - 1] * (gk[km - 1] + 0.5) - a_bot * gamma[km - 1];
-        prev = (xt1b * A(q, 0, 0, km - 1) + A(q, 0, 0, km - 2) - a_bot * prev) / xt2;
-        A(qi, 0, 0, km) = prev;
-      }
-      for (int k = km - 1; k >= 0; --k) {
-        prev = A(qi, 0, 0, k) - gamma[k] * prev;
-        A(qi, 0, 0, k) = prev;
-      }
+    double p0, p1, p2, p3;  // crx, xfx, cry, yfx
+    {
+      const double xt1 = 2.0 * gk[0] * (gk[0] + 1.0), b0 = beta[0];
+      p0 = (xt1 * A(crx, 0, 0, 0) + A(crx, 0, 0, 1)) / b0;
+      p1 = (xt1 * A(xfx, 0, 0, 0) + A(xfx, 0, 0, 1)) / b0;
+      p2 = (xt1 * A(cry, 0, 0, 0) + A(cry, 0, 0, 1)) / b0;
+      p3 = (xt1 * A(yfx, 0, 0, 0) + A(yfx, 0, 0, 1)) / b0;
+      A(crx_i, 0, 0, 0) = p0; A(xfx_i, 0, 0, 0) = p1; A(cry_i, 0, 0, 0) = p2; A(yfx_i, 0, 0, 0) = p3;
+    }
+    double m0 = A(crx, 0, 0, 0), m1 = A(xfx, 0, 0, 0), m2 = A(cry, 0, 0, 0), m3 = A(yfx, 0, 0, 0);  // level k-1
+    for (int k = 1; k < km; ++k) {
+      const double g_k = gk[k], b_k = beta[k];
+      const double c0 = A(crx, 0, 0, k), c1 = A(xfx, 0, 0, k), c2 = A(cry, 0, 0, k), c3 = A(yfx, 0, 0, k);
+      p0 = (3.0 * (m0 + g_k * c0) - p0) / b_k;
+      p1 = (3.0 * (m1 + g_k * c1) - p1) / b_k;
+      p2 = (3.0 * (m2 + g_k * c2) - p2) / b_k;
+      p3 = (3.0 * (m3 + g_k * c3) - p3) / b_k;
+      A(crx_i, 0, 0, k) = p0; A(xfx_i, 0, 0, k) = p1; A(cry_i, 0, 0, k) = p2; A(yfx_i, 0, 0, k) = p3;
+      m0 = c0; m1 = c1; m2 = c2; m3 = c3;
+    }
+    {
+      const double gl = gk[km - 1];
+      const double a_bot = 1.0 + gl * (gl + 1.5);
+      const double xt1b = 2.0 * gl * (gl + 1.0);
+      const double xt2 = gl * (gl + 0.5) - a_bot * gamma[km - 1];
+      // m* hold level km-1; level km-2 is read again
+      p0 = (xt1b * m0 + A(crx, 0, 0, km - 2) - a_bot * p0) / xt2;
+      p1 = (xt1b * m1 + A(xfx, 0, 0, km - 2) - a_bot * p1) / xt2;
+      p2 = (xt1b * m2 + A(cry, 0, 0, km - 2) - a_bot * p2) / xt2;
+      p3 = (xt1b * m3 + A(yfx, 0, 0, km - 2) - a_bot * p3) / xt2;
+      A(crx_i, 0, 0, km) = p0; A(xfx_i, 0, 0, km) = p1; A(cry_i, 0, 0, km) = p2; A(yfx_i, 0, 0, km) = p3;
+    }
+    for (int k = km - 1; k >= 0; --k) {
+      const double gm = gamma[k];
+      p0 = A(crx_i, 0, 0, k) - gm * p0;
+      p1 = A(xfx_i, 0, 0, k) - gm * p1;
+      p2 = A(cry_i, 0, 0, k) - gm * p2;
+      p3 = A(yfx_i, 0, 0, k) - gm * p3;
+      A(crx_i, 0, 0, k) = p0; A(xfx_i, 0, 0, k) = p1; A(cry_i, 0, 0, k) = p2; A(yfx_i, 0, 0, k) = p3;
     }
   }, "dzd_spline");
   Fvtp2dArgs a;
