@@ -228,7 +228,7 @@ int c_sw(Core& c, double dt2) {
   }
 
   // ---- E: transportdelp_update_vorticity_and_kineticenergy (c_sw.py:287-391), compute + 1 halo
-  launch_ijk(st, g, box_dims(g, 0, 0, 0, 1, 1), [=] __device__(const Pt& p) {
+  launch_ijk_occ<6>(st, g, box_dims(g, 0, 0, 0, 1, 1), [=] __device__(const Pt& p) {
     const int i = p.i, j = p.j;
     double fy1_[2], fy_[2], fy2_[2];
     for (int dj = 0; dj < 2; ++dj) {

@@ -91,10 +91,10 @@ int d_sw(Core& c, double dt) {
                *damp_w_c = c.F("col.delnflux_damp_w");
   double *tfx = c.FS("dsw.tmp_fx"), *tfy = c.FS("dsw.tmp_fy"), *gx = c.FS("dsw.tmp_gx"), *gy = c.FS("dsw.tmp_gy"),
          *fx2 = c.FS("dsw.tmp_fx2"), *fy2 = c.FS("dsw.tmp_fy2"), *dw = c.FS("dsw.tmp_dw"), *wk = c.FS("dsw.tmp_wk"),
-         *heat_s = c.FS("dsw.tmp_heat_s"), *diss_e = c.FS("dsw.tmp_diss_e"), *ke = c.FS("dsw.dt_kinetic_energy_on_cell_corners"),
+         *heat_s = c.FS("dsw.tmp_heat_s"), *ke = c.FS("dsw.dt_kinetic_energy_on_cell_corners"),
          *vort_a = c.FS("dsw.vorticity_agrid"), *vort_b = c.FS("dsw.vorticity_bgrid_damped"),
          *abs_vort = c.FS("dsw.abs_vorticity_agrid"), *tut = c.FS("dsw.tmp_ut"), *tvt = c.FS("dsw.tmp_vt"),
-         *damped_vort = c.FS("dsw.damped_rel_vorticity_agrid"), *vxd = c.FS("dsw.vort_x_delta"), *vyd = c.FS("dsw.vort_y_delta");
+         *damped_vort = c.FS("dsw.damped_rel_vorticity_agrid");
   if (!c.err.empty()) return 1;
   const int is = g.is, ie = g.ie, js = g.js, je = g.je, nz = g.nz;
   const int nmax_v = c.col_max("col.nord_v"), nmax_w = c.col_max("col.nord_w"), nmax_t = c.col_max("col.nord_t");
@@ -129,8 +129,7 @@ int d_sw(Core& c, double dt) {
       A0(dw) = dwv;
       hs = dd8 - dwv * (A0(w) + 0.5 * dwv);
     }
-    A0(heat_s) = hs;
-    A0(diss_e) = hs;
+    A0(heat_s) = hs;  // the reference's tmp_diss_e holds the same value: it is taken from here below
   });
   // 6./7. fvtp2d_vt_nodelnflux(w, mass fluxes) ; apply_fluxes(w)
   a = Fvtp2dArgs();
@@ -212,13 +211,13 @@ int d_sw(Core& c, double dt) {
   launch_ijk(st, g, box_dims(g, 0, 0, 0, 3, 3), [=] __device__(const Pt& p) {
     double rdy_tmp = A20(rarea) * A20(dx);
     double rdx_tmp = A20(rarea) * A20(dy);
-    A0(vort_a) = (A0(u) - A(u, 0, 1, 0) * A2(dx, 0, 1) / A20(dx)) * rdy_tmp +
-                 (A(v, 1, 0, 0) * A2(dy, 1, 0) / A20(dy) - A0(v)) * rdx_tmp;
+    const double vo = (A0(u) - A(u, 0, 1, 0) * A2(dx, 0, 1) / A20(dx)) * rdy_tmp +
+                      (A(v, 1, 0, 0) * A2(dy, 1, 0) / A20(dy) - A0(v)) * rdx_tmp;
+    A0(vort_a) = vo;
+    A0(abs_vort) = vo + A20(f0);  // 16. rel_vorticity_to_abs (same box; divergence_damping only reads vort_a)
   });
   // 15. divergence_damping
   if (divergence_damping(c, vort_b, delpc, ke, vort_a, dt)) return 1;
-  // 16. rel_vorticity_to_abs (compute + 3 halo)
-  launch_ijk(st, g, box_dims(g, 0, 0, 0, 3, 3), [=] __device__(const Pt& p) { A0(abs_vort) = A0(vort_a) + A20(f0); });
   // 17. fvtp2d_vt_nodelnflux(abs vorticity) -> tmp_fx, tmp_fy
   a = Fvtp2dArgs();
   a.crx = crx; a.cry = cry; a.xfx = xfx; a.yfx = yfx; a.nk = nz;
@@ -235,22 +234,20 @@ int d_sw(Core& c, double dt) {
     d.q = vort_a; d.fx = tut; d.fy = tvt; d.nord_col = col_nord_v; d.damp = damp_vt_c; d.d2 = damped_vort; d.nmax = nmax_v; d.nk = nz;
     if (delnflux(c, d)) return 1;
   }
-  // 20. vort_differencing
-  launch_ijk(st, g, box_dims(g, 1, 1, 0), [=] __device__(const Pt& p) {
-    if (col_d_con[p.k] > 1e-5) {
-      if (p.i <= ie) A0(vxd) = A0(vort_b) - A(vort_b, 1, 0, 0);
-      if (p.j <= je) A0(vyd) = A0(vort_b) - A(vort_b, 0, 1, 0);
-    }
-  });
-  // 21./22. heat_source_from_vorticity_damping + accumulate_heat_source_and_dissipation_estimate (compute domain)
+  // 20.-22. vort_differencing + heat_source_from_vorticity_damping + accumulate_heat_source_and_dissipation_estimate
+  // (compute domain).  vort_x_delta / vort_y_delta are differences of the damped B-grid vorticity and only enter here:
+  // they are formed in registers (same expression) instead of two scratch fields.
   const bool do_accum = cf.d_con > 1.0e-5;
   launch_ijk(st, g, box_dims(g, 0, 0, 0), [=] __device__(const Pt& p) {
-    double hs = A0(heat_s);
+    const double hs0 = A0(heat_s);
+    double hs = hs0;
     const double frac = col_d_con[p.k];
     if (frac > 1e-5) {
-      auto ubt = [&](int dj) { return (A(vxd, 0, dj, 0) + A(tvt, 0, dj, 0)) * A2(rdx, 0, dj); };
+      auto vxdf = [&](int dj) { return A(vort_b, 0, dj, 0) - A(vort_b, 1, dj, 0); };   // vort_x_delta(i, j+dj)
+      auto vydf = [&](int di) { return A(vort_b, di, 0, 0) - A(vort_b, di, 1, 0); };   // vort_y_delta(i+di, j)
+      auto ubt = [&](int dj) { return (vxdf(dj) + A(tvt, 0, dj, 0)) * A2(rdx, 0, dj); };
       auto fyf = [&](int dj) { return A(u, 0, dj, 0) * A2(rdx, 0, dj); };
-      auto vbt = [&](int di) { return (A(vyd, di, 0, 0) - A(tut, di, 0, 0)) * A2(rdy, di, 0); };
+      auto vbt = [&](int di) { return (vydf(di) - A(tut, di, 0, 0)) * A2(rdy, di, 0); };
       auto fxf = [&](int di) { return A(v, di, 0, 0) * A2(rdy, di, 0); };
       double ub0 = ubt(0), ub1 = ubt(1), fy0 = fyf(0), fy1 = fyf(1);
       double vb0 = vbt(0), vb1 = vbt(1), fx0 = fxf(0), fx1 = fxf(1);
@@ -264,7 +261,7 @@ int d_sw(Core& c, double dt) {
     }
     if (do_accum) {
       A0(heat_source) = A0(heat_source) + hs;
-      A0(diss_est) = A0(diss_est) + A0(diss_e);
+      A0(diss_est) = A0(diss_est) + hs0;
     }
   });
   // 23. update_u_and_v

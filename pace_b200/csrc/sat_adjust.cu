@@ -142,7 +142,7 @@ int sat_adjust(Core& c, const SatCfg& sc, double mdt, int last_step_i, int kmp) 
   Box b = box_compute(g);
   b.k0 = kmp;
   b.nk = g.nz - kmp;
-  launch_ijk(c.stream, g, b, [=] __device__(const Pt& p) {
+  launch_ijk_occ<4>(c.stream, g, b, [=] __device__(const Pt& p) {
     double qv = A0(qv_), ql = A0(ql_), qi = A0(qi_), qr = A0(qr_), qs = A0(qs_), qg = A0(qg_);
     const double pt = A0(pt_), dp = A0(dp_), delz = A0(delz_);
     double q_liq = ql + qr;

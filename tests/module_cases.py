@@ -34,7 +34,10 @@ CASES = {
                          "dsw.damped_rel_vorticity_agrid": 0,
                          # DelnFlux work fluxes: only the final box is meaningful (its closing interface row is
                          # covered through u, v); outside it the reference keeps leftovers of its wider first passes
-                         "dsw.tmp_ut": 0, "dsw.tmp_vt": 0}),
+                         "dsw.tmp_ut": 0, "dsw.tmp_vt": 0},
+                 # private work fields of the reference class that the kernels no longer materialise: the differences
+                 # of the damped vorticity are formed in registers by the heat-source kernel (its outputs are compared)
+                 skip=("dsw.vort_x_delta", "dsw.vort_y_delta")),
     "d_sw_module": dict(stage="d_sw", call="d_sw", args=(DT,), tol=0.0),
     "c_sw": dict(stage="c_sw", call="c_sw", args=(DT2,), tol=0.0),
     "updatedzc": dict(stage="updatedzc", call="update_dz_c", args=(DT2,), tol=0.0),
