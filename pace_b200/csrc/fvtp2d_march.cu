@@ -25,6 +25,7 @@ namespace {
 struct MarchArgs {
   const double *q, *crx, *cry, *xfx, *yfx, *xunit, *yunit, *area, *dxa, *dya;
   double *fx, *fy;
+  const int* lvl;                  // optional level_nonzero flags (Fvtp2dArgs)
   int nk, rows, nstrips, nchunks;  // levels; rows per chunk; column strips; row chunks
   long long items;                 // nstrips * nchunks * nk * subdomains
 };
@@ -179,6 +180,7 @@ __global__ void __launch_bounds__(WPB * 32, 20) k_fvtp2d_march(Geo g, MarchArgs 
   const int chunk = (int)(item % a.nchunks);
   item /= a.nchunks;
   const int k = (int)(item % a.nk), t = (int)(item / a.nk);
+  if (a.lvl != nullptr && a.lvl[t * a.nk + k] == 0) return;  // a level of zeros: nothing to transport
 
   double* bufC0 = smem + wid * WARP_SMEM;  // q_i row, two copies used alternately (no barrier between the last
   double* fxring = bufC0 + 2 * PITCH;      // read of one step and the write of the next); inner x flux of the last
@@ -365,6 +367,7 @@ int fvtp2d_march_launch(Core& c, const Fvtp2dArgs& a) {
   f.yunit = a.y_mass_flux ? a.y_mass_flux : a.yfx;
   f.area = c.F("grid.area"); f.dxa = c.F("grid.dxa"); f.dya = c.F("grid.dya");
   f.fx = a.fx; f.fy = a.fy;
+  f.lvl = a.level_nonzero;
   f.nk = a.nk;
   if (!c.err.empty()) return 1;
   const int oo = a.hord < 0 ? -a.hord : a.hord;

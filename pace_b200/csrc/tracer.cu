@@ -46,6 +46,48 @@ int tracer_flux_prep(Core& c, int n_split) {
   return 0;
 }
 
+#ifndef PACE_HOST_EMU
+namespace {
+// flags[t * nk + k] = does level k of subdomain t (the whole padded level, halo included) hold a non-zero value?
+__global__ void __launch_bounds__(256) k_level_nonzero(Geo g, const double* q, int nk, int* flags) {
+  const int k = blockIdx.x, t = blockIdx.y;
+  const double* lev = q + (long long)t * g.st3 + (long long)k * g.sk;
+  bool nz = false;
+  for (int n = threadIdx.x; n < g.sk; n += blockDim.x) nz = nz || lev[n] != 0.0;
+  nz = __syncthreads_or(nz);
+  if (threadIdx.x == 0) flags[t * nk + k] = nz ? 1 : 0;
+}
+}  // namespace
+#endif
+
+// Condensate species are zero on whole levels (above the clouds; everywhere in a dry test case).  One read pass finds
+// those levels; their transport (fvtp2d + apply_tracer_flux) is skipped: a level of zeros stays a level of zeros.
+const int* level_nonzero_flags(Core& c, const double* q, int nk) {
+#ifndef PACE_HOST_EMU
+  const Geo g = c.g;
+  auto it = c.scratch.find("tr.level_nonzero");
+  int* flags;
+  if (it == c.scratch.end()) {
+    void* ptr = nullptr;
+    if (cudaMalloc(&ptr, sizeof(int) * (size_t)g.nt * (g.nz + 1)) != cudaSuccess) {
+      c.err = "cudaMalloc failed for tr.level_nonzero";
+      return nullptr;
+    }
+    c.owned.push_back(ptr);
+    c.scratch["tr.level_nonzero"] = (double*)ptr;
+    flags = (int*)ptr;
+  } else {
+    flags = (int*)it->second;
+  }
+  ++launch_counter();
+  k_level_nonzero<<<dim3(nk, g.nt), 256, 0, c.stream>>>(g, q, nk, flags);
+  return flags;
+#else
+  (void)c; (void)q; (void)nk;
+  return nullptr;
+#endif
+}
+
 // one sub-cycle: apply_mass_flux, then fvtp2d + apply_tracer_flux for each tracer (tracer_2d_1l.py:381-411)
 int tracer_substep(Core& c, int nq) {
   const Geo g = c.g;
@@ -63,8 +105,13 @@ int tracer_substep(Core& c, int nq) {
     Fvtp2dArgs a;
     a.q = q; a.crx = cx; a.cry = cy; a.xfx = xfx; a.yfx = yfx; a.fx = fx; a.fy = fy;
     a.x_mass_flux = mfx; a.y_mass_flux = mfy; a.hord = c.cfg.hord_tr; a.nk = g.nz;
+    const int* lvl = level_nonzero_flags(c, q, g.nz);
+    if (!c.err.empty()) return 1;
+    a.level_nonzero = lvl;
     if (fvtp2d(c, a)) return 1;
+    const int nkf = g.nz;
     launch_ijk(st, g, box_compute(g), [=] __device__(const Pt& p) {
+      if (lvl != nullptr && lvl[p.t * nkf + p.k] == 0) return;  // q = (0 * dp1 + 0) / dp2
       A0(q) = fv_div(A0(q) * A0(dp1) + (A0(fx) - A(fx, 1, 0, 0) + A0(fy) - A(fy, 0, 1, 0)) * A20(rarea), A0(dp2));
     });
   }

@@ -15,8 +15,14 @@ struct Fvtp2dArgs {
   // optional DelnFlux (fvtp2d.py:168-180): per-level nord and damp = (damp_c*da_min)**(nord+1)
   const double *nord_col = nullptr, *damp = nullptr;
   int nmax = 0;
+  // optional, device: level_nonzero[t * nk + k] == 0 says that q is zero on the whole level k of subdomain t (halo
+  // included); the fluxes of such a level are zeros that nobody needs to form: fx / fy are then left untouched there
+  const int* level_nonzero = nullptr;
 };
 int fvtp2d(Core& c, const Fvtp2dArgs& a);
+// level_nonzero flags of a field (see Fvtp2dArgs); returns a library-owned device array of nt * nk ints, or nullptr
+// when the build has no such kernel (host emulation: everything is computed)
+const int* level_nonzero_flags(Core& c, const double* q, int nk);
 
 // DelnFluxNoSG.__call__ (+ DelnFlux accumulation when accumulate=true)
 struct DelnArgs {
