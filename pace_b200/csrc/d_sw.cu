@@ -140,9 +140,15 @@ int d_sw(Core& c, double dt) {
     A0(w) = A0(w) * A0(delp) + (A0(gx) - A(gx, 1, 0, 0) + A0(gy) - A(gy, 0, 1, 0)) * A20(rarea);
   });
   // 8./9. fvtp2d_dp_t(q_con, mass=delp) ; apply_fluxes(q_con)
+  // levels without condensate (all of them in dry air): q_con stays zero there, its transport is skipped
+  const int* qcon_levels = level_nonzero_flags(c, q_con, nz);
+  if (!c.err.empty()) return 1;
   a.q = q_con; a.hord = cf.hord_dp; a.mass = delp; a.nord_col = col_nord_t; a.damp = damp_t_fv; a.nmax = nmax_t;
+  a.level_nonzero = qcon_levels;
   if (fvtp2d(c, a)) return 1;
+  a.level_nonzero = nullptr;
   launch_ijk(st, g, box_dims(g, 0, 0, 0), [=] __device__(const Pt& p) {
+    if (qcon_levels != nullptr && qcon_levels[p.t * nz + p.k] == 0) return;  // 0 * delp + 0
     A0(q_con) = A0(q_con) * A0(delp) + (A0(gx) - A(gx, 1, 0, 0) + A0(gy) - A(gy, 0, 1, 0)) * A20(rarea);
   });
   // 10. fvtp2d_tm(pt, mass=delp)

@@ -26,6 +26,7 @@ constexpr int NTY = 8;                       // thread rows per CTA (TX x NTY th
 struct DelnFusedArgs {
   const double *q, *mass, *nord_col, *damp, *del6_u, *del6_v, *rarea;
   double *fx, *fy, *d2out;
+  const int* lvl;
   int nk, accumulate;
 };
 
@@ -143,6 +144,7 @@ __global__ void __launch_bounds__(TX * NTY, 6) k_delnflux_fused(Geo g, DelnFused
   __shared__ double fx2[H][W + 1];     // x interface, same indexing
   __shared__ double fy2[H + 1][W];     // y interface
   const int k = blockIdx.z % a.nk, t = blockIdx.z / a.nk;
+  if (a.lvl != nullptr && a.accumulate && a.lvl[t * a.nk + k] == 0) return;  // a level of zeros adds no damping flux
   const int is = g.is, ie = g.ie, js = g.js, je = g.je, sj = g.sj;
   const int i0 = is + blockIdx.x * TX, j0 = js + blockIdx.y * TY;
   const unsigned ed = edge_of(g, t);
@@ -248,6 +250,7 @@ int delnflux_fused_launch(Core& c, const DelnArgs& a) {
   f.q = a.q; f.mass = a.mass; f.nord_col = a.nord_col; f.damp = a.damp;
   f.del6_u = c.F("damp.del6_u"); f.del6_v = c.F("damp.del6_v"); f.rarea = c.F("grid.rarea");
   f.fx = a.fx; f.fy = a.fy; f.d2out = a.d2; f.nk = a.nk; f.accumulate = a.accumulate ? 1 : 0;
+  f.lvl = a.level_nonzero;
   if (!c.err.empty()) return 1;
   dim3 blk(TX, NTY, 1);
   dim3 grd((g.nx + TX - 1) / TX, (g.ny + TY - 1) / TY, a.nk * g.nt);

@@ -94,6 +94,7 @@ int fvtp2d(Core& c, const Fvtp2dArgs& a) {
       DelnArgs d;
       d.q = q; d.fx = fx; d.fy = fy; d.mass = a.mass; d.nord_col = a.nord_col; d.damp = a.damp; d.nk = nk;
       d.accumulate = true; d.d2 = nullptr; d.nmax = a.nmax;
+      d.level_nonzero = a.level_nonzero;
       return delnflux(c, d);
     }
     return 0;

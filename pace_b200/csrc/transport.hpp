@@ -33,6 +33,7 @@ struct DelnArgs {
   double* d2 = nullptr;                      // optional work/output array
   int nmax = 0, nk = 0;
   bool accumulate = false;
+  const int* level_nonzero = nullptr;        // accumulate only: levels of zeros (see Fvtp2dArgs) add nothing
 };
 int delnflux(Core& c, const DelnArgs& a);
 
