@@ -128,6 +128,7 @@ def main():
     ap.add_argument("--impl", default="pace_b200")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-dense", action="store_true", help="skip the extra run with PACE_B200_ZERO_PATHS=0")
     args = ap.parse_args()
     if args.workload is None:
         args.workload = "c384"
@@ -136,11 +137,27 @@ def main():
             return  # under torchrun rank 0 alone times the CPU implementation
         return run_reference(args)
 
-    import torch
-
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+
+    # The kernels skip work on data that is zero (rows / levels / columns / tiles of zeros; exact).  The baroclinic case
+    # has seven of its eight tracer species and q_con identically zero, so the line also says what the same step costs
+    # with those shortcuts switched off (a child process, before this one allocates its state).
+    dense = None
+    if world == 1 and not args.no_dense and os.environ.get("PACE_B200_ZERO_PATHS", "1") != "0":
+        env = dict(os.environ, PACE_B200_ZERO_PATHS="0")
+        cmd = [sys.executable, os.path.abspath(__file__), "--workload", args.workload, "--steps", str(min(args.steps, 3)),
+               "--warmup", str(min(args.warmup, 2)), "--no-cpu-baseline", "--no-e2e", "--no-dense"]
+        try:
+            out = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=600).stdout.strip().splitlines()
+            d = json.loads(out[-1])
+            dense = {"ms_per_step": d["ms_per_step"], "value": d["value"], "unit": d["unit"],
+                     "what": "same workload with PACE_B200_ZERO_PATHS=0 (no shortcuts for zero-valued tracers / q_con)"}
+        except Exception as exc:  # the headline measurement does not depend on it
+            dense = {"error": str(exc)[:200]}
+
+    import torch
     from pace_b200 import _lib
     from pace_b200.synthetic import make_engine
 
@@ -215,7 +232,9 @@ def main():
         cnt, tot = prof[top]
         per_launch_ms = tot / cnt
         bytes_per_cell = {"fvtp2d_inner_ppm": 5 * 8, "fvtp2d_qi_qj": 7 * 8, "fvtp2d_outer_ppm": 10 * 8,
-                          "fvtp2d_fused": 8.4 * 8, "fvtp2d_march": 8.4 * 8, "riem_solver_c": 8 * 8, "riem_solver3": 15 * 8, "remap_scalars_column": 40 * 8}.get(top, 8 * 8)
+                          "fvtp2d_fused": 8.4 * 8,
+                          # dense launches of a step: delp, vorticity, zh (7 passes), w, pt (9 passes) per substep -> 7.8
+                          "fvtp2d_march": 7.8 * 8, "fvtp2d_march_sparse": 9 * 8, "riem_solver_c": 8 * 8, "riem_solver3": 15 * 8, "remap_scalars_column": 40 * 8}.get(top, 8 * 8)
         alg_bytes = cells / world * bytes_per_cell  # this GPU's share of the cells
         achieved = alg_bytes / (per_launch_ms / 1000.0) / 1e9
         # measured DRAM bytes per launch of that kernel from the committed ncu capture (profiles/traffic_r01.json),
@@ -299,7 +318,7 @@ def main():
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic (C12 reference fixture resampled, see pace_b200/synthetic.py)",
         "config": {"workload": desc, "cells": cells, "placement": "%d subdomains per GPU, halo exchange by NCCL send/recv" % (n_sub // world) if world > 1 else "%d subdomains on one GPU" % n_sub, "l2": "working set (%.0f GB) >> L2, no flush needed" % (cells * 8 * 130 / 1e9)},
-        "gpu_launches": int(launches), "clocks": sampler.summary(), "roofline": roof, "acoustic_substep": acoustic,
+        "gpu_launches": int(launches), "clocks": sampler.summary(), "roofline": roof, "acoustic_substep": acoustic, "dense_path": dense,
         "cpu_baseline": cpu, "e2e": e2e,
     }
     if rank == 0:

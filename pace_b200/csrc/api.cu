@@ -1,5 +1,6 @@
 // C ABI of libpace_b200 (declared in include/pace_b200.h) and the Core plumbing behind it.
 #include <cstdarg>
+#include <cstdlib>
 #include <cstring>
 
 #include "../../include/pace_b200.h"
@@ -41,6 +42,11 @@ bool prof_enabled() { return false; }
 void prof_begin(cudaStream_t, const char*) {}
 void prof_end(cudaStream_t) {}
 #endif
+
+bool zero_paths_enabled() {
+  static const bool on = [] { const char* v = getenv("PACE_B200_ZERO_PATHS"); return !(v && v[0] == '0'); }();
+  return on;
+}
 
 void set_error(const char* fmt, ...) {
   char buf[1024];

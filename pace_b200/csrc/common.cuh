@@ -292,5 +292,9 @@ __device__ __forceinline__ T fv_div(T n, T d) {
   } while (0)
 
 void set_error(const char* fmt, ...);
+// The shortcuts for data that is zero (rows / levels / columns / tiles of zeros: fvtp2d_march.cu, tracer.cu, remap.cu,
+// delnflux_fused.cu) are exact and on by default; PACE_B200_ZERO_PATHS=0 turns them off so that the cost of the dense
+// computation can be measured on the same inputs (bench.py reports both).
+bool zero_paths_enabled();
 
 }  // namespace pace

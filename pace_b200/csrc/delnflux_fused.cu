@@ -175,7 +175,7 @@ __global__ void __launch_bounds__(TX * NTY, 6) k_delnflux_fused(Geo g, DelnFused
   }
   // A tile (with its apron) of zeros - q_con in dry air, a condensate outside clouds - has zero damping fluxes: when
   // they are to be added to existing fluxes there is nothing to do.
-  if (!__syncthreads_or(nonzero) && a.accumulate) return;
+  if (!__syncthreads_or(nonzero) && a.accumulate == 1) return;
   // ask for the lines the result phase will read-modify-write (fx, fy, mass) now, so that they arrive in L2 while
   // the tile iterates in shared memory
   if (a.accumulate) {
@@ -249,7 +249,7 @@ int delnflux_fused_launch(Core& c, const DelnArgs& a) {
   DelnFusedArgs f;
   f.q = a.q; f.mass = a.mass; f.nord_col = a.nord_col; f.damp = a.damp;
   f.del6_u = c.F("damp.del6_u"); f.del6_v = c.F("damp.del6_v"); f.rarea = c.F("grid.rarea");
-  f.fx = a.fx; f.fy = a.fy; f.d2out = a.d2; f.nk = a.nk; f.accumulate = a.accumulate ? 1 : 0;
+  f.fx = a.fx; f.fy = a.fy; f.d2out = a.d2; f.nk = a.nk; f.accumulate = a.accumulate ? (zero_paths_enabled() ? 1 : 2) : 0;  // 2: accumulate, no zero-tile shortcut
   f.lvl = a.level_nonzero;
   if (!c.err.empty()) return 1;
   dim3 blk(TX, NTY, 1);

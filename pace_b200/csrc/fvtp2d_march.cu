@@ -27,6 +27,7 @@ struct MarchArgs {
   double *fx, *fy;
   const int* lvl;                  // optional level_nonzero flags (Fvtp2dArgs)
   int nk, rows, nstrips, nchunks;  // levels; rows per chunk; column strips; row chunks
+  int zrows;                       // rows of zeros after which a step is skipped (7), or a number no chunk reaches
   long long items;                 // nstrips * nchunks * nk * subdomains
 };
 
@@ -276,7 +277,7 @@ __global__ void __launch_bounds__(WPB * 32, 20) k_fvtp2d_march(Geo g, MarchArgs 
     // numbers: the step reduces to storing the zero fluxes (times the mass fluxes: their sign is the sign of the stored
     // zero).  The carried sweep state is already the one a window of zeros leaves and stays as it is.
     zrun = __all_sync(FULL, qx == 0.0 && qy == 0.0) ? zrun + 1 : 0;
-    if (zrun >= 7) {
+    if (zrun >= a.zrows) {
       const int jc = R - 2;
       if (cell_out && (jc <= j_hi || last_chunk)) fy[o - 2 * sj] = 0.5 * (0.0 + 0.0) * ring(5, slot)[L];
       yfx_prev = ring(6, slot)[L];
@@ -368,6 +369,7 @@ int fvtp2d_march_launch(Core& c, const Fvtp2dArgs& a) {
   f.area = c.F("grid.area"); f.dxa = c.F("grid.dxa"); f.dya = c.F("grid.dya");
   f.fx = a.fx; f.fy = a.fy;
   f.lvl = a.level_nonzero;
+  f.zrows = zero_paths_enabled() ? 7 : (1 << 30);
   f.nk = a.nk;
   if (!c.err.empty()) return 1;
   const int oo = a.hord < 0 ? -a.hord : a.hord;
@@ -388,7 +390,9 @@ int fvtp2d_march_launch(Core& c, const Fvtp2dArgs& a) {
   f.items = (long long)f.nstrips * f.nchunks * a.nk * g.nt;
   const int blocks = (int)((f.items + WPB - 1) / WPB);
   const size_t smem = (size_t)WPB * WARP_SMEM * sizeof(double);
-  LaunchScope scope(c.stream, "fvtp2d_march");
+  // launches that carry level flags (tracer species, q_con) are timed apart: their duration depends on how many levels
+  // hold anything, so they would blur the per-launch figure of the dense launches the roofline is quoted on
+  LaunchScope scope(c.stream, a.level_nonzero ? "fvtp2d_march_sparse" : "fvtp2d_march");
   if (oi == 5 && oo == 5) launch<5, 5>(blocks, smem, c.stream, g, f);
   else if (oi == 6 && oo == 6) launch<6, 6>(blocks, smem, c.stream, g, f);
   else if (oi == 7 && oo == 7) launch<7, 7>(blocks, smem, c.stream, g, f);

@@ -264,9 +264,9 @@ __device__ __forceinline__ void coef_at(const ColT<T>& c, int km, int iv, int ko
 // remapped value is negative (the only case in which fillz changes a column).
 template <class T>
 __device__ bool map_single_column(const Pt& p, ColT<T>& c, int km, T* q, const T* pe1, const T* pe2, int iv,
-                                  int kord, T qs, T qmin, bool keep_dp = false) {
+                                  int kord, T qs, T qmin, bool keep_dp = false, bool zero_paths = true) {
   bool any_negative = false;
-  bool all_zero = true;
+  bool all_zero = zero_paths;
   for (int k = 0; k < km; ++k) {
     const T v = A(q, 0, 0, k);
     c.a1[k] = v;
@@ -508,6 +508,7 @@ int remap_main(Core& c, int nq) {
   TrPtrs trp;
   for (int n = 0; n < 9; ++n) trp.p[n] = n < nq ? tr[n] : nullptr;
   const bool fill = cf.fill != 0;
+  const bool zero_paths = zero_paths_enabled();
   auto scalars_column = [=] __device__(const Pt& p) {
     COL_DECL;
     map_single_column(p, col, km, pt, peln, pn2, 1, kord_tm, 0.0, t_min);
@@ -515,7 +516,7 @@ int remap_main(Core& c, int nq) {
     for (int n = 0; n < nq; ++n) {
       // mapn_tracer.py:40-41: every tracer uses kord_tr, entry 5 is forced to 9
       int kord = n == 5 ? 9 : kord_tr;
-      if (map_single_column(p, col, km, trp.p[n], pe1, pe2, 0, kord, 0.0, 0.0, n > 0)) negative |= 1u << n;
+      if (map_single_column(p, col, km, trp.p[n], pe1, pe2, 0, kord, 0.0, 0.0, n > 0, zero_paths)) negative |= 1u << n;
     }
     // fillz leaves a column without negative values exactly as it is (no borrowing, zfix == 0): only the others
     // go through it.  It uses col.dp as scratch, so the thicknesses are rebuilt afterwards if it ran.

@@ -64,6 +64,7 @@ __global__ void __launch_bounds__(256) k_level_nonzero(Geo g, const double* q, i
 // those levels; their transport (fvtp2d + apply_tracer_flux) is skipped: a level of zeros stays a level of zeros.
 const int* level_nonzero_flags(Core& c, const double* q, int nk) {
 #ifndef PACE_HOST_EMU
+  if (!zero_paths_enabled()) return nullptr;
   const Geo g = c.g;
   auto it = c.scratch.find("tr.level_nonzero");
   int* flags;
