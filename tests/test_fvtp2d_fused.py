@@ -61,3 +61,65 @@ def test_production_kernels_match_unfused_at_c96(tmp_path):
         a, b = res["production"][name], res["unfused"][name]
         assert np.all(np.isfinite(a)), name
         assert np.array_equal(a, b), "%s differs: max |d| = %g" % (name, np.max(np.abs(a - b)))
+
+
+PATCHY = r"""
+import sys, numpy as np, torch
+sys.path.insert(0, %r)
+from pace_b200.synthetic import make_engine
+from pace_b200.engine import STATE_3D
+eng = make_engine(int(sys.argv[2]), 1, n_split=2)
+t = eng.core.t
+nt, nk, nj, sj = t["qvapor"].shape
+g = torch.Generator().manual_seed(7)
+jj = torch.arange(nj).view(1, 1, nj, 1).double()
+ii = torch.arange(sj).view(1, 1, 1, sj).double()
+kk = torch.arange(nk).view(1, nk, 1, 1)
+dev = t["qvapor"].device
+def put(name, mask, amp):
+    noise = (0.5 + torch.rand(t[name].shape, generator=g, dtype=torch.float64)).to(dev)
+    t[name].copy_(torch.where(mask.to(dev).expand(t[name].shape), amp * noise, torch.zeros_like(t[name])))
+# a disk of rain on the lower levels of every subdomain (zero rows above and below it inside a strip)
+put("qrain", ((ii - 20) ** 2 + (jj - 30) ** 2 < 49) & (kk > 50), 1.0e-4)
+# snow: a single cell, and one whole row, on two levels
+put("qsnow", (((ii == 11) & (jj == 12)) | (jj == 40)) & ((kk == 30) | (kk == 31)), 2.0e-5)
+# ice: whole levels 10..19 only
+put("qice", (kk >= 10) & (kk < 20) & (ii >= 0), 1.0e-5)
+# cloud water: only in the first columns / rows next to a tile edge (aprons of the first strip and chunk)
+put("qliquid", ((ii < 6) | (jj < 5)) & (kk > 60), 3.0e-5)
+# graupel: rows of zeros interrupted every 9th row
+put("qgraupel", (jj %% 9 == 0) & (kk > 40), 1.0e-5)
+eng.step_dynamics()
+eng.core.sync()
+out = {n: eng.core.t[n].cpu().numpy() for n in STATE_3D}
+np.savez(sys.argv[1], **out)
+"""
+
+
+@pytest.mark.gpu
+def test_zero_shortcuts_match_dense_on_patchy_tracers(tmp_path):
+    """The shortcuts for zero-valued data (rows of zeros in fvtp2d_march, levels of zeros in the tracer and q_con
+    transport, columns of zeros in the remap, tiles of zeros in DelnFlux) against the dense computation
+    (PACE_B200_ZERO_PATHS=0, and the unfused kernels on top) on tracers that are zero in parts of the domain: a disk,
+    a single cell, single rows, whole levels, the cells next to a tile edge — every entry into and exit from the
+    shortcuts.  One full step at C48, bit for bit."""
+    res = {}
+    modes = {"production": {},
+             "dense": {"PACE_B200_ZERO_PATHS": "0"},
+             "dense_unfused": {"PACE_B200_ZERO_PATHS": "0", "PACE_B200_FVTP2D": "unfused", "PACE_B200_DELNFLUX": "unfused",
+                               "PACE_B200_RIEM": "global", "PACE_B200_A2B": "unfused"}}
+    for mode, extra in modes.items():
+        env = dict(os.environ, **extra)
+        path = str(tmp_path / (mode + ".npz"))
+        subprocess.run([sys.executable, "-c", PATCHY % ROOT, path, "48"], check=True, env=env, timeout=600)
+        res[mode] = np.load(path)
+    moved = 0
+    for name in res["production"].files:
+        a = res["production"][name]
+        assert np.all(np.isfinite(a)), name
+        for other in ("dense", "dense_unfused"):
+            b = res[other][name]
+            assert np.array_equal(a, b), "%s vs %s differs: max |d| = %g" % (name, other, np.max(np.abs(a - b)))
+    for name in ("qrain", "qsnow", "qice", "qliquid", "qgraupel"):
+        moved += int(np.count_nonzero(res["production"][name]))
+    assert moved > 0
