@@ -78,10 +78,12 @@ __global__ void __launch_bounds__(32) k_riem(Geo g, RiemArgs a) {
 
   // Every sweep walks the column in chunks of U levels: the global inputs of the next chunk are requested before the
   // current chunk is computed, so that ~5 x U loads per warp are in flight behind the (latency-bound) recurrences.
-#ifndef PACE_RIEM_U
-#define PACE_RIEM_U 4
-#endif
+  // Measured at C384 (ms per step, U = 2 / 3 / 4): riem_solver_c 32.5 / 35.5 / 37.5, riem_solver3 37.2 / 36.8 / 31.8.
+#ifdef PACE_RIEM_U
   constexpr int U = PACE_RIEM_U;
+#else
+  constexpr int U = D3 ? 4 : 2;
+#endif
   // ---- A: forward ---------------------------------------------------------------------------------------------
   {
     double pem_k = ptop, peg_k = ptop, logpg_k = a.peln1;
