@@ -230,7 +230,7 @@ inline void launch_ijk_occ(cudaStream_t s, const Geo& g, Box b, F f, const char*
   launch_ijk(s, g, b, f, label);
 }
 template <class F>
-inline void launch_ij(cudaStream_t, const Geo& g, Box b, F f, const char* = nullptr, int = 0) {
+inline void launch_ij(cudaStream_t, const Geo& g, Box b, F f, const char* = nullptr) {
   ++launch_counter();
 #ifdef PACE_HOST_EMU_OMP
 #pragma omp parallel for collapse(2) schedule(static)
