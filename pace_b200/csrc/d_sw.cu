@@ -163,7 +163,7 @@ int d_sw(Core& c, double dt) {
     double wv = A0(w) / dp;
     wv = col_damp_w[p.k] > 1e-5 ? wv + A0(dw) : wv;
     A0(w) = wv;
-    A0(q_con) = A0(q_con) / dp;
+    A0(q_con) = fv_div(A0(q_con), dp);  // zero wherever there is no condensate
   });
   // 13. compute_kinetic_energy on the corner compute domain
   const int mord_mt = cf.hord_mt < 0 ? -cf.hord_mt : cf.hord_mt;

@@ -23,17 +23,18 @@ int update_dz_c(Core& c, double dt) {
   launch_ijk(st, g, box_compute(g, -1, -1, 2, 2, 1), [=] __device__(const Pt& p) {
     const int k = p.k;
     const EdgeInfo e = edge_info(g, p);
-    // xfx/yfx at horizontal offset (di,dj): pressure-weighted interface average of ut/vt
+    // xfx/yfx at horizontal offset (di,dj): pressure-weighted interface average of ut/vt.  The weight depends on the
+    // level only: one division per point instead of one per average.
+    const double wgt = k == 0 ? dp_ref[0] / (dp_ref[0] + dp_ref[1])
+                     : k < km ? 1.0 / (dp_ref[k - 1] + dp_ref[k])
+                              : dp_ref[k - 1] / (dp_ref[k - 2] + dp_ref[k - 1]);
     auto favg = [&](const double* vel, int di, int dj) {
       if (k == 0) {
-        double ratio = dp_ref[0] / (dp_ref[0] + dp_ref[1]);
-        return A(vel, di, dj, 0) + (A(vel, di, dj, 0) - A(vel, di, dj, 1)) * ratio;
+        return A(vel, di, dj, 0) + (A(vel, di, dj, 0) - A(vel, di, dj, 1)) * wgt;
       } else if (k < km) {
-        double int_ratio = 1.0 / (dp_ref[k - 1] + dp_ref[k]);
-        return (dp_ref[k] * A(vel, di, dj, -1) + dp_ref[k - 1] * A(vel, di, dj, 0)) * int_ratio;
+        return (dp_ref[k] * A(vel, di, dj, -1) + dp_ref[k - 1] * A(vel, di, dj, 0)) * wgt;
       } else {
-        double ratio = dp_ref[k - 1] / (dp_ref[k - 2] + dp_ref[k - 1]);
-        return A(vel, di, dj, -1) + (A(vel, di, dj, -1) - A(vel, di, dj, -2)) * ratio;
+        return A(vel, di, dj, -1) + (A(vel, di, dj, -1) - A(vel, di, dj, -2)) * wgt;
       }
     };
     // cells of the compute domain proper never read a corner-filled value (the fills concern the ring around it)

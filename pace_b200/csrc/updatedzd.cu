@@ -33,20 +33,20 @@ int update_dz_d(Core& c, double dt) {
     double p0, p1, p2, p3;  // crx, xfx, cry, yfx
     {
       const double xt1 = 2.0 * gk[0] * (gk[0] + 1.0), b0 = beta[0];
-      p0 = (xt1 * A(crx, 0, 0, 0) + A(crx, 0, 0, 1)) / b0;
-      p1 = (xt1 * A(xfx, 0, 0, 0) + A(xfx, 0, 0, 1)) / b0;
-      p2 = (xt1 * A(cry, 0, 0, 0) + A(cry, 0, 0, 1)) / b0;
-      p3 = (xt1 * A(yfx, 0, 0, 0) + A(yfx, 0, 0, 1)) / b0;
+      p0 = fv_div(xt1 * A(crx, 0, 0, 0) + A(crx, 0, 0, 1), b0);
+      p1 = fv_div(xt1 * A(xfx, 0, 0, 0) + A(xfx, 0, 0, 1), b0);
+      p2 = fv_div(xt1 * A(cry, 0, 0, 0) + A(cry, 0, 0, 1), b0);
+      p3 = fv_div(xt1 * A(yfx, 0, 0, 0) + A(yfx, 0, 0, 1), b0);
       A(crx_i, 0, 0, 0) = p0; A(xfx_i, 0, 0, 0) = p1; A(cry_i, 0, 0, 0) = p2; A(yfx_i, 0, 0, 0) = p3;
     }
     double m0 = A(crx, 0, 0, 0), m1 = A(xfx, 0, 0, 0), m2 = A(cry, 0, 0, 0), m3 = A(yfx, 0, 0, 0);  // level k-1
     for (int k = 1; k < km; ++k) {
       const double g_k = gk[k], b_k = beta[k];
       const double c0 = A(crx, 0, 0, k), c1 = A(xfx, 0, 0, k), c2 = A(cry, 0, 0, k), c3 = A(yfx, 0, 0, k);
-      p0 = (3.0 * (m0 + g_k * c0) - p0) / b_k;
-      p1 = (3.0 * (m1 + g_k * c1) - p1) / b_k;
-      p2 = (3.0 * (m2 + g_k * c2) - p2) / b_k;
-      p3 = (3.0 * (m3 + g_k * c3) - p3) / b_k;
+      p0 = fv_div(3.0 * (m0 + g_k * c0) - p0, b_k);
+      p1 = fv_div(3.0 * (m1 + g_k * c1) - p1, b_k);
+      p2 = fv_div(3.0 * (m2 + g_k * c2) - p2, b_k);
+      p3 = fv_div(3.0 * (m3 + g_k * c3) - p3, b_k);
       A(crx_i, 0, 0, k) = p0; A(xfx_i, 0, 0, k) = p1; A(cry_i, 0, 0, k) = p2; A(yfx_i, 0, 0, k) = p3;
       m0 = c0; m1 = c1; m2 = c2; m3 = c3;
     }
