@@ -134,11 +134,13 @@ int d_sw(Core& c, double dt) {
   // 6./7. fvtp2d_vt_nodelnflux(w, mass fluxes) ; apply_fluxes(w)
   a = Fvtp2dArgs();
   a.crx = crx; a.cry = cry; a.xfx = xfx; a.yfx = yfx; a.nk = nz;
-  a.q = w; a.fx = gx; a.fy = gy; a.hord = cf.hord_vt; a.x_mass_flux = tfx; a.y_mass_flux = tfy;
+  // The fluxes of w go to their own pair of fields: apply_fluxes(w) is then evaluated inside the kernel of steps
+  // 11./12. (nothing in between reads w), which saves a pass over w, delp and the fluxes.
+  double *gxw = c.FS("dsw.tmp_gx_w"), *gyw = c.FS("dsw.tmp_gy_w");
+  if (!c.err.empty()) return 1;
+  a.q = w; a.fx = gxw; a.fy = gyw; a.hord = cf.hord_vt; a.x_mass_flux = tfx; a.y_mass_flux = tfy;
   if (fvtp2d(c, a)) return 1;
-  launch_ijk(st, g, box_dims(g, 0, 0, 0), [=] __device__(const Pt& p) {
-    A0(w) = A0(w) * A0(delp) + (A0(gx) - A(gx, 1, 0, 0) + A0(gy) - A(gy, 0, 1, 0)) * A20(rarea);
-  });
+  a.fx = gx; a.fy = gy;
   // 8./9. fvtp2d_dp_t(q_con, mass=delp) ; apply_fluxes(q_con)
   // levels without condensate (all of them in dry air): q_con stays zero there, its transport is skipped
   const int* qcon_levels = level_nonzero_flags(c, q_con, nz);
@@ -156,11 +158,13 @@ int d_sw(Core& c, double dt) {
   if (fvtp2d(c, a)) return 1;
   // 11./12. apply_pt_delp_fluxes ; adjust_w_and_qcon
   launch_ijk(st, g, box_dims(g, 0, 0, 0), [=] __device__(const Pt& p) {
-    double ptv = A0(pt) * A0(delp) + (A0(gx) - A(gx, 1, 0, 0) + A0(gy) - A(gy, 0, 1, 0)) * A20(rarea);
-    double dp = A0(delp) + (A0(tfx) - A(tfx, 1, 0, 0) + A0(tfy) - A(tfy, 0, 1, 0)) * A20(rarea);
+    const double delp0 = A0(delp);  // delp before this step: the weight of pt and w
+    double ptv = A0(pt) * delp0 + (A0(gx) - A(gx, 1, 0, 0) + A0(gy) - A(gy, 0, 1, 0)) * A20(rarea);
+    double dp = delp0 + (A0(tfx) - A(tfx, 1, 0, 0) + A0(tfy) - A(tfy, 0, 1, 0)) * A20(rarea);
     A0(delp) = dp;
     A0(pt) = ptv / dp;
-    double wv = A0(w) / dp;
+    const double wdp = A0(w) * delp0 + (A0(gxw) - A(gxw, 1, 0, 0) + A0(gyw) - A(gyw, 0, 1, 0)) * A20(rarea);  // 7. apply_fluxes(w)
+    double wv = wdp / dp;
     wv = col_damp_w[p.k] > 1e-5 ? wv + A0(dw) : wv;
     A0(w) = wv;
     A0(q_con) = fv_div(A0(q_con), dp);  // zero wherever there is no condensate
