@@ -300,8 +300,8 @@ def main():
         e2e_ms = max_over_ranks((time.time() - t0) / k_e2e * 1000.0)
         nbytes = pipe.bytes_per_step
         e2e = {"value": DT_ATMOS / (e2e_ms / 1000.0), "unit": "simulated days / day", "ms_per_step": e2e_ms,
-               "h2d_bytes_per_step": nbytes * world, "d2h_bytes_per_step": nbytes * world, "steps": k_e2e,
-               "fields": len(pipe.names), "overlap": "upload(n+1) / download(n-1) on side streams during step n"}
+               "h2d_bytes_per_step": pipe.upload_bytes_per_step * world, "d2h_bytes_per_step": nbytes * world,
+               "steps": k_e2e, "fields": len(pipe.names), "fields_uploaded": len(pipe.upload_names), "overlap": "upload(n+1) / download(n-1) on side streams during step n"}
         del hin, hout, pipe
 
     cpu = None

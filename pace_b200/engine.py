@@ -24,6 +24,12 @@ STATE_3D = [
     "diss_estd",
 ]
 STATE_2D = ["ps", "phis"]
+# The fields a step reads before it overwrites them: the prognostic variables and the surface geopotential.  Everything
+# else in DycoreState (ua, va, uc, vc, pe, peln, pk, pkz, q_con, omga, mfxd, mfyd, cxd, cyd, diss_estd, ps) is diagnosed
+# or accumulated from zero inside the step (fv_setup / zero_data / riem_solver3 / remapping / c2l_ord4): poisoning any of
+# them in the initial state leaves the result bit-identical (tools/find_step_inputs.py; tests/test_engine_acoustic.py).
+STEP_INPUTS = ["u", "v", "w", "delp", "delz", "pt", "qvapor", "qliquid", "qice", "qrain", "qsnow", "qgraupel", "qo3mr",
+               "qsgs_tke", "qcld", "phis"]
 ACOUSTIC_TEMPORARIES = ["ad.ut", "ad.vt", "ad.gz", "ad.zh", "ad.pem", "ad.pkc", "ad.pk3", "ad.heat_source", "ad.cappa",
                         "ad.divgd", "ad.crx", "ad.cry", "ad.xfx", "ad.yfx", "csw.delpc", "csw.ptc", "dyn.dp1", "dyn.cvm"]
 TEMPORARIES_2D = ["ad.ws3", "ad.wsd", "ad.zs"]
@@ -278,24 +284,26 @@ class DycoreEngine:
 
 class HostPipeline:
     """Steps a HOST-resident model state through a DycoreEngine: the call a coupled driver makes when the rest of the
-    model lives in host memory.  Every step uploads the full DycoreState (STATE_3D + STATE_2D) from pinned host
-    buffers and downloads the updated state; with two device copies of the state the upload of step n+1 and the
+    model lives in host memory.  Every step uploads the fields the step reads (STEP_INPUTS; upload_names=None uploads
+    the full DycoreState) from pinned host buffers and downloads the whole updated state (STATE_3D + STATE_2D); with two device copies of the state the upload of step n+1 and the
     download of step n-1 run on their own CUDA streams while step n computes (PCIe is full duplex), so the cost per
     step tends to max(compute, upload, download) instead of their sum.  phis (static) is expected to stay unchanged
     (ad.zs is derived from it once in set_state)."""
 
-    def __init__(self, eng, names=None):
+    def __init__(self, eng, names=None, upload_names=STEP_INPUTS):
         import torch
 
         self.torch = torch
         self.eng = eng
         self.names = list(names) if names is not None else STATE_3D + STATE_2D
+        self.upload_names = [n for n in self.names if upload_names is None or n in upload_names]
         core = eng.core
         self.sets = [{n: core.t[n] for n in self.names}, {n: torch.empty_like(core.t[n]) for n in self.names}]
         for n in self.names:
             self.sets[1][n].copy_(core.t[n])
         self.s_up, self.s_down = torch.cuda.Stream(core.device), torch.cuda.Stream(core.device)
-        self.bytes_per_step = sum(t.numel() * t.element_size() for t in self.sets[0].values())
+        self.bytes_per_step = sum(t.numel() * t.element_size() for t in self.sets[0].values())  # downloaded
+        self.upload_bytes_per_step = sum(self.sets[0][n].numel() * self.sets[0][n].element_size() for n in self.upload_names)
 
     def pinned_like(self):
         """A dict of pinned host tensors shaped like the state (one upload or download buffer)."""
@@ -320,7 +328,7 @@ class HostPipeline:
                 if n >= 2:
                     self.s_up.wait_event(step_done[n % 2])
                 src = get_in(n)
-                for name in self.names:
+                for name in self.upload_names:
                     tgt[name].copy_(src[name], non_blocking=True)
                 up_done[n % 2].record(self.s_up)
 

@@ -200,6 +200,12 @@ def test_host_pipeline_matches_plain_steps_gpu():
     hin = pipe.pinned_like()
     for name in pipe.names:
         hin[name].copy_(eng.core.t[name])
+    # the pipeline uploads the step's inputs only: whatever the other fields hold on the device must not matter
+    for dev_set in pipe.sets:
+        for name in pipe.names:
+            if name not in pipe.upload_names:
+                dev_set[name].fill_(float("nan"))
+    assert len(pipe.upload_names) == 16
     outs = [pipe.pinned_like() for _ in range(3)]
     pipe.run(3, hin, lambda n: outs[n])
     want = load_six("final")
@@ -215,6 +221,26 @@ def test_host_pipeline_matches_plain_steps_gpu():
     # the engine is bound to its own tensors again and holds the last result
     assert eng.core.t["u"].data_ptr() == pipe.sets[0]["u"].data_ptr()
     assert torch.equal(eng.core.t["delp"].cpu(), outs[2]["delp"])
+
+
+def test_step_inputs_hostemu():
+    """engine.STEP_INPUTS: with every other DycoreState field poisoned in the initial state the step returns the
+    reference's result (compute domain, bit for bit)."""
+    from pace_b200.engine import STATE_2D, STATE_3D, STEP_INPUTS
+
+    eng = make_engine("hostemu")
+    for name in STATE_3D + STATE_2D:
+        if name not in STEP_INPUTS:
+            eng.core.t[name].fill_(float("nan"))
+    eng.step_dynamics()
+    want = load_six("final")
+    for name in ("u", "v", "w", "delp", "pt", "delz", "qvapor", "pe", "pk", "peln", "pkz", "q_con", "omga", "ua", "va", "ps"):
+        got = eng.core.get(name)
+        for r in range(6):
+            a, w = got[r][3:15, 3:15], want[r][name][3:15, 3:15]
+            if a.ndim == 3 and name not in K_INTERFACE:
+                a, w = a[:, :, :-1], w[:, :, :-1]
+            assert np.array_equal(a, w), "%s rank %d differs" % (name, r)
 
 
 NEGQ_OUT = ["u", "v", "w", "delp", "pt", "delz", "qvapor", "qliquid", "qrain", "qice", "qsnow", "qgraupel", "qo3mr",
