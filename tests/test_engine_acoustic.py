@@ -6,7 +6,7 @@ import os
 import numpy as np
 import pytest
 
-from tests.golden_util import GOLDEN, report
+from tests.golden_util import GOLDEN, passes, report
 from tests.module_harness import K_INTERFACE
 
 
@@ -51,7 +51,7 @@ def compare_rank0(eng, want, names, tol):
         worst[name] = (err, nbad)
     msg = "\n".join("  %-16s max_rel=%.3e non-identical=%d" % (n, e, b) for n, (e, b) in sorted(worst.items()) if b)
     print(msg)
-    bad = {n: e for n, (e, b) in worst.items() if e > tol}
+    bad = {n: e for n, (e, b) in worst.items() if not passes(e, b, tol)}
     assert not bad, "parity failed (tol %g):\n%s" % (tol, msg)
 
 
@@ -121,9 +121,9 @@ def run_step(backend, tol):
             if g.ndim == 3 and name not in K_INTERFACE:
                 g, w = g[:, :, :-1], w[:, :, :-1]
             if g.ndim == 3:
-                g, w = g[3:15, 3:15], w[3:15, 3:15]
-                if name in ("u", "pe", "peln", "pk"):
-                    pass
+                # u lives on y interfaces, v on x interfaces: their closing row / column belongs to the comparison
+                ni, nj = (13 if name == "v" else 12), (13 if name == "u" else 12)
+                g, w = g[3:3 + ni, 3:3 + nj], w[3:3 + ni, 3:3 + nj]
             else:
                 g, w = g[3:15, 3:15], w[3:15, 3:15]
             err, nbad = report(name, g, w)
@@ -131,7 +131,7 @@ def run_step(backend, tol):
                 worst[(name, r)] = (err, nbad)
     msg = "\n".join("  %-10s rank %d max_rel=%.3e non-identical=%d" % (n, r, e, b) for (n, r), (e, b) in sorted(worst.items()))
     print(msg)
-    assert all(e <= tol for e, _ in worst.values()), "full-step parity failed (tol %g):\n%s" % (tol, msg)
+    assert all(passes(e, b, tol) for e, b in worst.values()), "full-step parity failed (tol %g):\n%s" % (tol, msg)
 
 
 def test_full_step_six_tiles_hostemu():
@@ -175,7 +175,7 @@ def run_two_steps(backend, tol):
                 worst[(name, r)] = (err, nbad)
     msg = "\n".join("  %-10s rank %d max_rel=%.3e non-identical=%d" % (n, r, e, b) for (n, r), (e, b) in sorted(worst.items()))
     print(msg)
-    assert all(e <= tol for e, _ in worst.values()), "two-step parity failed (tol %g):\n%s" % (tol, msg)
+    assert all(passes(e, b, tol) for e, b in worst.values()), "two-step parity failed (tol %g):\n%s" % (tol, msg)
 
 
 def test_two_steps_ksplit2_nsplit2_hostemu():
@@ -288,7 +288,7 @@ def run_negq(backend, tol):
                 worst[(name, r)] = (err, nbad)
     msg = "\n".join("  %-10s rank %d max_rel=%.3e non-identical=%d" % (n, r, e, b) for (n, r), (e, b) in sorted(worst.items()))
     print(msg)
-    assert all(e <= tol for e, _ in worst.values()), "perturbed-state parity failed (tol %g):\n%s" % (tol, msg)
+    assert all(passes(e, b, tol) for e, b in worst.values()), "perturbed-state parity failed (tol %g):\n%s" % (tol, msg)
 
 
 def test_perturbed_state_step_hostemu():

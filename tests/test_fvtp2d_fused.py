@@ -29,8 +29,7 @@ np.savez(sys.argv[1], **out)
 def test_fused_matches_three_kernel_version(tmp_path):
     res = {}
     modes = {"march": {"PACE_B200_FVTP2D": "march"},
-             "march_chunks_strips": {"PACE_B200_FVTP2D": "march", "PACE_B200_FVTP2D_ROWS": "16",
-                                     "PACE_B200_FVTP2D_WIDTH": "20"},
+             "march_chunks": {"PACE_B200_FVTP2D": "march", "PACE_B200_FVTP2D_ROWS": "16"},
              "tile": {"PACE_B200_FVTP2D": "tile"}, "unfused": {"PACE_B200_FVTP2D": "unfused", "PACE_B200_DELNFLUX": "unfused", "PACE_B200_RIEM": "global", "PACE_B200_A2B": "unfused"}}
     for mode, extra in modes.items():
         env = dict(os.environ, **extra)
