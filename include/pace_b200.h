@@ -1,7 +1,7 @@
 /* pace_b200 — C ABI of the B200-native FV3 dycore hot path.
  *
  * This is the drop-in boundary: plain pointers and sizes, no torch / C++ types.
- * The host-side mirror of the reference classes (pace_b200/dycore.py) binds these with ctypes; the
+ * The host-side mirror of the reference classes (pace_b200/engine.py, pace_b200/dropin.py) binds these with ctypes; the
  * reference-side binding a maintainer would add is shown in INTEGRATION.md.
  *
  * Conventions
@@ -237,6 +237,41 @@ int pace_b200_a2b_ord4(void* handle, const char* qin, const char* qout, int k0, 
 /* DivergenceDamping.__call__ (pyFV3/stencils/divergence_damping.py:549-713). */
 int pace_b200_divergence_damping(void* handle, const char* vort_b, const char* delpc, const char* ke,
                                  const char* vort_a, double dt);
+
+/* ---- Whole-phase entry points -------------------------------------------------------------------------------
+ * The call order of the reference's Python driver classes, so that a caller in any language (the GEOS wrapper
+ * precedent, pyFV3/wrappers/geos_wrapper.py:224-232) steps the core without re-stating it.  They use the module
+ * calls above on the handle's stream and need, registered beforehand: every DycoreState field and "ad." / "csw." /
+ * "dyn." temporary (INTEGRATION.md lists them), the grid, the K-columns, and halo plans under the ids
+ *   0 cell-centred 3-cell halo, 1 cell-centred 2-cell, 2 corner (x- and y-interface) 3-cell, 3 D-grid vector pair,
+ *   4 C-grid vector pair, 5 interface synchronisation of (u, v)   (pace_b200.halo.HaloPlanner builds all six). */
+
+/* HaloUpdater.update() when not every neighbour subdomain lives on this GPU (NDSL/ndsl/halo/updater.py:150-303):
+ * the phase calls hand the whole update to this callback (it packs with pace_b200_halo_pack, moves the messages and
+ * unpacks, all ordered on the handle's stream) instead of running the local gather.  Return 0 on success. */
+typedef int (*pace_b200_halo_callback)(void* user, int plan_id, const char* const* x_names, const char* const* y_names,
+                                       int n, int nk);
+int pace_b200_set_halo_callback(void* handle, pace_b200_halo_callback cb, void* user);
+
+/* The reference's checkpointer hooks (dyn_core.py:641-701, 787-893; fv_dynamics.py:342-443, 457-606): the callback is
+ * called with the savepoint name ("FVDynamics-In", "C_SW-In", "C_SW-Out", "D_SW-In", "D_SW-Out", "Tracer2D1L-In",
+ * "Tracer2D1L-Out", "Remapping-In", "Remapping-Out", "FVDynamics-Out") at the same points of the sequence.  The work
+ * queued so far is NOT synchronised: a callback that reads fields synchronises the handle's stream first. */
+typedef int (*pace_b200_stage_callback)(void* user, const char* savepoint);
+int pace_b200_set_stage_callback(void* handle, pace_b200_stage_callback cb, void* user);
+
+/* SatAdjustConfig used by pace_b200_remap / pace_b200_step when do_sat_adj is set. */
+int pace_b200_set_satadj_config(void* handle, const pace_b200_satadj_config* cfg);
+
+/* AcousticDynamics.__call__(state, timestep, n_map) (pyFV3/stencils/dyn_core.py:714-1013): n_split acoustic
+ * substeps of timestep / n_split seconds incl. every halo update, then the heat-source diffusion. */
+int pace_b200_acoustic(void* handle, double timestep, int n_map);
+/* TracerAdvection.__call__ (pyFV3/stencils/tracer_2d_1l.py:289-417) for the eight GFS tracers. */
+int pace_b200_tracer_advection(void* handle);
+/* LagrangianToEulerian.__call__ (pyFV3/stencils/remapping.py:522-731) incl. SatAdjust3d when do_sat_adj. */
+int pace_b200_remap(void* handle, int last_step, double mdt);
+/* DynamicalCore.step_dynamics (pyFV3/stencils/fv_dynamics.py:445-655): one dycore step of dt_atmos. */
+int pace_b200_step(void* handle);
 
 #ifdef __cplusplus
 }

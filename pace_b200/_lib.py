@@ -58,6 +58,9 @@ class HaloOp(ctypes.Structure):
         (n, _I) for n in ("i0", "j0", "ni", "nj", "aii", "aij", "bi", "aji", "ajj", "bj")]
 
 
+HALO_CALLBACK = ctypes.CFUNCTYPE(_I, ctypes.c_void_p, _I, ctypes.POINTER(_S), ctypes.POINTER(_S), _I, _I)
+STAGE_CALLBACK = ctypes.CFUNCTYPE(_I, ctypes.c_void_p, _S)
+
 _lib = None
 
 
@@ -98,6 +101,9 @@ def bind(lib):
     lib.pace_b200_math_eval.argtypes = [vp, _I, _I, vp, vp, vp]
     lib.pace_b200_sat_adjust.argtypes = [vp, ctypes.POINTER(SatAdjConfig), _D, _I, _I]
     lib.pace_b200_map_single_f32.argtypes = [vp, vp, vp, vp, vp, _I, _I, _I, _I, ctypes.c_float]
+    lib.pace_b200_set_satadj_config.argtypes = [vp, ctypes.POINTER(SatAdjConfig)]
+    lib.pace_b200_set_halo_callback.argtypes = [vp, HALO_CALLBACK, vp]
+    lib.pace_b200_set_stage_callback.argtypes = [vp, STAGE_CALLBACK, vp]
     for name, extra in MODULE_CALLS.items():
         fn = getattr(lib, "pace_b200_" + name)
         fn.argtypes = [vp] + extra
@@ -143,8 +149,13 @@ MODULE_CALLS = {
     "delnflux_nosg": [_S] * 6 + [_I],
     "a2b_ord4": [_S, _S, _I, _I, _I],
     "divergence_damping": [_S, _S, _S, _S, _D],
+    "acoustic": [_D, _I],
+    "tracer_advection": [],
+    "remap": [_I, _D],
+    "step": [],
 }
 
 EXPORTS = ["pace_b200_row_stride", "pace_b200_create", "pace_b200_destroy", "pace_b200_last_error",
            "pace_b200_set_stream", "pace_b200_set_field", "pace_b200_set_column", "pace_b200_halo_plan_set", "pace_b200_halo_update", "pace_b200_halo_pack", "pace_b200_halo_unpack", "pace_b200_math_eval", "pace_b200_sat_adjust", "pace_b200_map_single_f32", "pace_b200_launch_count", "pace_b200_profile_enable",
-           "pace_b200_profile_report"] + ["pace_b200_" + n for n in MODULE_CALLS]
+           "pace_b200_profile_report", "pace_b200_set_satadj_config", "pace_b200_set_halo_callback",
+           "pace_b200_set_stage_callback"] + ["pace_b200_" + n for n in MODULE_CALLS]

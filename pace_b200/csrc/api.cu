@@ -8,11 +8,6 @@
 #include "transport.hpp"
 
 namespace pace {
-struct SatCfg {
-  int rad_snow, rad_rain, rad_graupel, tintqs, icloud_f, do_qa;
-  double sat_adj0, ql_gen, qs_mlt, ql0_max, t_sub, qi_gen, qi_lim, qi0_max, dw_ocean, dw_land, cld_min;
-  double tau_i2s, tau_v2l, tau_r2g, tau_l2r, tau_l2v, tau_imlt, tau_smlt;
-};
 
 static thread_local std::string g_err;
 
@@ -256,6 +251,27 @@ int pace_b200_sat_adjust(void* h, const pace_b200_satadj_config* cfg, double mdt
   static_assert(sizeof(pace_b200_satadj_config) == sizeof(SatCfg), "satadj config mirror out of sync");
   ENTRY(sat_adjust(*c, *(const SatCfg*)cfg, mdt, last_step, kmp))
 }
+int pace_b200_set_satadj_config(void* h, const pace_b200_satadj_config* cfg) {
+  Core* c = (Core*)h;
+  if (!cfg) { c->sat_cfg = nullptr; return 0; }
+  memcpy(&c->sat_store, cfg, sizeof(SatCfg));
+  c->sat_cfg = &c->sat_store;
+  return 0;
+}
+int pace_b200_set_halo_callback(void* h, pace_b200_halo_callback cb, void* user) {
+  Core* c = (Core*)h;
+  c->halo_cb = cb; c->halo_user = user;
+  return 0;
+}
+int pace_b200_set_stage_callback(void* h, pace_b200_stage_callback cb, void* user) {
+  Core* c = (Core*)h;
+  c->stage_cb = cb; c->stage_user = user;
+  return 0;
+}
+int pace_b200_acoustic(void* h, double timestep, int n_map) { ENTRY(acoustic(*c, timestep, n_map)) }
+int pace_b200_tracer_advection(void* h) { ENTRY(tracer_advection(*c)) }
+int pace_b200_remap(void* h, int last_step, double mdt) { ENTRY(remapping(*c, last_step, mdt)) }
+int pace_b200_step(void* h) { ENTRY(step(*c)) }
 int pace_b200_remap_main(void* h, int nq) { ENTRY(remap_main(*c, nq)) }
 int pace_b200_remap_finish(void* h, int last_step) { ENTRY(remap_finish(*c, last_step)) }
 int pace_b200_map_single(void* h, const char* q, const char* pe1, const char* pe2, const char* qs, int iv, int kord,

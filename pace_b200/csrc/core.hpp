@@ -27,6 +27,17 @@ struct Config {
   int ks;
 };
 
+// mirror of pace_b200_satadj_config (SatAdjustConfig, pyFV3/_config.py:15-66)
+struct SatCfg {
+  int rad_snow, rad_rain, rad_graupel, tintqs, icloud_f, do_qa;
+  double sat_adj0, ql_gen, qs_mlt, ql0_max, t_sub, qi_gen, qi_lim, qi0_max, dw_ocean, dw_land, cld_min;
+  double tau_i2s, tau_v2l, tau_r2g, tau_l2r, tau_l2v, tau_imlt, tau_smlt;
+};
+
+typedef int (*halo_callback_t)(void* user, int plan_id, const char* const* x_names, const char* const* y_names, int n,
+                               int nk);
+typedef int (*stage_callback_t)(void* user, const char* savepoint);
+
 struct Core {
   Config cfg;
   Geo g;
@@ -39,6 +50,14 @@ struct Core {
   int halo_nops[256] = {0};
   std::vector<void*> owned;
   std::string err;
+  // whole-phase entry points (step.cu): exchange callback for halo updates whose neighbours are not all on this GPU,
+  // savepoint callback at the reference's checkpointer hooks, SatAdjust3d configuration
+  halo_callback_t halo_cb = nullptr;
+  void* halo_user = nullptr;
+  stage_callback_t stage_cb = nullptr;
+  void* stage_user = nullptr;
+  SatCfg sat_store;
+  const SatCfg* sat_cfg = nullptr;
 
   double* F(const char* name);              // caller-registered field, error if missing
   double* S(const char* name);              // zero-initialised library scratch field [nt][nz+1][ny+7][sj]
@@ -71,7 +90,6 @@ int map_single_f32(Core& c, float* q, const float* pe1, const float* pe2, const 
                    bool yi, float qmin);
 int remap_main(Core& c, int nq);
 int remap_finish(Core& c, int last_step);
-struct SatCfg;
 int sat_adjust(Core& c, const SatCfg& sc, double mdt, int last_step, int kmp);
 int neg_adj3(Core& c);
 int c2l_ord4(Core& c);
@@ -95,6 +113,10 @@ int del2cubed(Core& c, double* q, double cd, int nmax);
 int apply_diffusive_heating(Core& c, double delt_time_factor, int nk);
 int d_sw(Core& c, double dt);
 int a2b_ord4(Core& c, const double* qin, double* qout, int k0, int nk, bool replace);
+int acoustic(Core& c, double timestep, int n_map);
+int tracer_advection(Core& c);
+int remapping(Core& c, int last_step, double mdt);
+int step(Core& c);
 int divergence_damping(Core& c, double* vort_b, double* delpc, double* ke, const double* vort_a, double dt);
 
 }  // namespace pace

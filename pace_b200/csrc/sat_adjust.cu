@@ -7,11 +7,6 @@
 
 namespace pace {
 
-struct SatCfg {  // mirror of pace_b200_satadj_config
-  int rad_snow, rad_rain, rad_graupel, tintqs, icloud_f, do_qa;
-  double sat_adj0, ql_gen, qs_mlt, ql0_max, t_sub, qi_gen, qi_lim, qi0_max, dw_ocean, dw_land, cld_min;
-  double tau_i2s, tau_v2l, tau_r2g, tau_l2r, tau_l2v, tau_imlt, tau_smlt;
-};
 
 namespace {
 constexpr double HLV = 2.5e6, HLF = 3.3358e5, SAT_ADJUST_THRESHOLD = 1.0e-8;  // GFS constants

@@ -1,0 +1,198 @@
+// Whole-phase entry points: the call order of the reference's Python driver classes behind the C ABI, so that a
+// caller in any language steps the core with one call per phase (or one per dycore step).
+//
+// Reference: AcousticDynamics.__call__ (pyFV3/stencils/dyn_core.py:714-1013), TracerAdvection.__call__
+// (tracer_2d_1l.py:289-417), LagrangianToEulerian.__call__ (remapping.py:522-731), DynamicalCore.step_dynamics /
+// _compute (fv_dynamics.py:445-655).  Where the reference starts a halo update early and waits later
+// (HaloUpdater.start / wait) the fields are not modified in between, so the update is issued at the wait point.
+// Host code only: it orders module calls (each a few kernel launches on the handle's stream) and halo updates.
+#include "../../include/pace_b200.h"
+#include "core.hpp"
+
+namespace pace {
+
+namespace {
+enum Plan { A3 = 0, A2 = 1, B3 = 2, D3 = 3, C3 = 4, SYNC = 5 };  // plan ids of pace_b200.halo / INTEGRATION.md
+const char* const TRACERS[8] = {"qvapor", "qliquid", "qrain", "qice", "qsnow", "qgraupel", "qo3mr", "qsgs_tke"};
+
+struct Names {
+  const char* v[8];
+  int n;
+  Names(std::initializer_list<const char*> l) : n(0) {
+    for (const char* s : l) v[n++] = s;
+  }
+};
+
+#define RUN(call)            \
+  do {                       \
+    if ((call) != 0) return 1; \
+    if (!c.err.empty()) return 1; \
+  } while (0)
+
+// get_nk_heat_dissipation (dyn_core.py:176-191)
+int nk_heat_dissipation(const Config& cfg) {
+  if (cfg.convert_ke || cfg.vtdm4 > 1.0e-4) return cfg.npz;
+  if (cfg.d2_bg_k1 < 1.0e-3) return 0;
+  if (cfg.d2_bg_k2 < 1.0e-3) return 1;
+  return 2;
+}
+}  // namespace
+
+// One HaloUpdater.update(): fields whose neighbours all live on this GPU are filled by the gather kernel; a
+// registered exchange callback (other GPUs / processes hold neighbours) takes the whole update instead.
+static int halo(Core& c, int plan, const Names& x, const Names* y = nullptr, int nk = -1) {
+  if (nk < 0) nk = c.g.nz;
+  if (c.halo_cb) {
+    if (c.halo_cb(c.halo_user, plan, x.v, y ? y->v : nullptr, x.n, nk) != 0) {
+      if (c.err.empty()) c.err = "halo exchange callback failed";
+      return 1;
+    }
+    return 0;
+  }
+  return halo_update(c, plan, x.v, y ? y->v : nullptr, x.n, nk);
+}
+
+static int stage(Core& c, const char* savepoint) {
+  if (!c.stage_cb) return 0;
+  if (c.stage_cb(c.stage_user, savepoint) != 0) {
+    if (c.err.empty()) c.err = std::string("stage callback failed at ") + savepoint;
+    return 1;
+  }
+  return 0;
+}
+
+// ---- AcousticDynamics.__call__ (dyn_core.py:714-1013) -----------------------------------------------------
+int acoustic(Core& c, double timestep, int n_map) {
+  const Config& cfg = c.cfg;
+  const int npz = c.g.nz, n_split = cfg.n_split;
+  const bool end_step = n_map == cfg.k_split;
+  const double dt = timestep / n_split, dt2 = 0.5 * dt;
+  const Names u{"u"}, v{"v"}, uc{"uc"}, vc{"vc"};
+  RUN(halo(c, A3, Names{"q_con", "ad.cappa"}));
+  RUN(zero_data(c, n_map == 1));
+  for (int it = 0; it < n_split; ++it) {
+    const bool remap_step = it == n_split - 1;
+    if (it == 0) {
+      RUN(gz_from_zs_delz(c));
+      RUN(halo(c, A3, Names{"delp", "pt"}));
+    }
+    if (it == n_split - 1 && end_step && cfg.use_old_omega) RUN(pem_from_delp(c));
+    RUN(halo(c, D3, u, &v));
+    RUN(halo(c, A3, Names{"w"}));
+    RUN(stage(c, "C_SW-In"));
+    RUN(c_sw(c, dt2));
+    RUN(stage(c, "C_SW-Out"));
+    if (cfg.nord > 0) RUN(halo(c, B3, Names{"ad.divgd"}));
+    if (it == 0) {
+      RUN(halo(c, A3, Names{"ad.gz"}, nullptr, npz + 1));
+      RUN(copy_full(c, "ad.gz", "ad.zh"));
+    } else {
+      RUN(copy_full(c, "ad.zh", "ad.gz"));
+    }
+    RUN(update_dz_c(c, dt2));
+    RUN(riem_solver_c(c, dt2));
+    RUN(p_grad_c(c, dt2));
+    RUN(halo(c, C3, uc, &vc));
+    RUN(stage(c, "D_SW-In"));
+    RUN(d_sw(c, dt));
+    RUN(stage(c, "D_SW-Out"));
+    RUN(halo(c, A3, Names{"delp", "pt", "q_con"}));
+    RUN(update_dz_d(c, dt));
+    RUN(riem_solver3(c, dt, remap_step));
+    RUN(halo(c, A3, Names{"ad.zh"}, nullptr, npz + 1));
+    RUN(halo(c, A2, Names{"ad.pkc"}, nullptr, npz + 1));
+    if (remap_step) RUN(edge_pe(c));
+    RUN(pk3_halo(c));
+    RUN(compute_geopotential(c));
+    RUN(nh_p_grad(c, dt));
+    if (cfg.rf_fast) RUN(ray_fast(c, dt));
+    if (it == n_split - 1 && cfg.grid_type < 4) RUN(halo(c, SYNC, u, &v));
+  }
+  const int nk_heat = nk_heat_dissipation(cfg);
+  if (nk_heat != 0 && cfg.d_con > 1.0e-5) {
+    RUN(halo(c, A3, Names{"ad.heat_source"}));
+    double* hs = c.F("ad.heat_source");
+    if (!hs) return 1;
+    const int nmax = 3 < cfg.nord + 1 ? 3 : cfg.nord + 1;
+    RUN(del2cubed(c, hs, 0.2 * cfg.da_min, nmax));
+    RUN(apply_diffusive_heating(c, fabs(dt * cfg.delt_max), nk_heat));
+  }
+  return 0;
+}
+
+// ---- TracerAdvection.__call__ (tracer_2d_1l.py:289-417) ---------------------------------------------------
+int tracer_advection(Core& c) {
+  const double cmax_max_all_ranks = 2.0;  // hard-coded in the reference in place of an allreduce (:337-364)
+  const int n_split = (int)floor(1.0 + cmax_max_all_ranks);
+  Names q{};
+  for (int n = 0; n < 8; ++n) q.v[q.n++] = TRACERS[n];
+  RUN(tracer_flux_prep(c, n_split));
+  RUN(halo(c, A3, q));
+  for (int it = 0; it < n_split; ++it) {
+    RUN(tracer_substep(c, 8));
+    if (it != n_split - 1) {
+      RUN(halo(c, A3, q));
+      RUN(tracer_swap_dp(c));
+    }
+  }
+  return 0;
+}
+
+// ---- LagrangianToEulerian.__call__ (remapping.py:522-731) -------------------------------------------------
+int remapping(Core& c, int last_step, double mdt) {
+  RUN(remap_main(c, 8));
+  if (c.cfg.do_sat_adj) {
+    if (!c.sat_cfg) {
+      c.err = "do_sat_adj is set but no saturation-adjustment configuration was given (pace_b200_set_satadj_config)";
+      return 1;
+    }
+    // first level with pfull > 10 hPa (remapping.py:347-351)
+    const std::vector<double>* p = c.H("grid.p");
+    if (!p) return 1;
+    int kmp = c.g.nz - 1;
+    for (int k = 0; k < c.g.nz && k < (int)p->size(); ++k)
+      if ((*p)[k] > 10.0e2) { kmp = k; break; }
+    RUN(sat_adjust(c, *c.sat_cfg, mdt, last_step, kmp));
+  }
+  RUN(remap_finish(c, last_step));
+  return 0;
+}
+
+// ---- DynamicalCore.step_dynamics / _compute (fv_dynamics.py:445-655) --------------------------------------
+int step(Core& c) {
+  const Config& cfg = c.cfg;
+  RUN(stage(c, "FVDynamics-In"));
+  RUN(fv_setup(c));                     // compute_preamble (fv_dynamics.py:461-508)
+  RUN(pt_to_potential_density_pt(c));
+  for (int k = 0; k < cfg.k_split; ++k) {
+    const int n_map = k + 1;
+    const bool last_step = k == cfg.k_split - 1;
+    RUN(copy_levels(c, "delp", "dyn.dp1"));
+    RUN(acoustic(c, cfg.dt_atmos / cfg.k_split, n_map));
+    RUN(stage(c, "Tracer2D1L-In"));
+    RUN(tracer_advection(c));
+    RUN(stage(c, "Tracer2D1L-Out"));
+    if (c.g.nz > 4) {
+      RUN(stage(c, "Remapping-In"));
+      RUN(remapping(c, last_step, cfg.dt_atmos / cfg.k_split));
+      RUN(stage(c, "Remapping-Out"));
+      if (last_step) {
+        RUN(omega_from_w(c));
+        if (cfg.nf_omega > 0) {
+          RUN(halo(c, A3, Names{"omga"}));
+          double* om = c.F("omga");
+          if (!om) return 1;
+          RUN(del2cubed(c, om, 0.18 * cfg.da_min, cfg.nf_omega));
+        }
+      }
+    }
+  }
+  RUN(neg_adj3(c));
+  const Names u{"u"}, v{"v"};
+  RUN(halo(c, D3, u, &v));
+  RUN(c2l_ord4(c));
+  RUN(stage(c, "FVDynamics-Out"));
+  return 0;
+}
+
+}  // namespace pace

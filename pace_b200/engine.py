@@ -1,10 +1,9 @@
 """DycoreEngine: the call sequences of the reference's AcousticDynamics.__call__ and DynamicalCore._compute
 (pyFV3/stencils/dyn_core.py:714-1013, fv_dynamics.py:513-655) over ALL subdomains resident on one GPU.
 
-The numerics are the CUDA kernels behind the C ABI (include/pace_b200.h); this file only orders the module calls
-and the halo updates, like the reference's Python classes do.  Where the reference starts a halo update early and
-waits later (HaloUpdater.start / wait), the fields are not modified in between, so the exchange is issued once at
-the wait point on the same stream.
+The numerics AND the call order are behind the C ABI (include/pace_b200.h: pace_b200_acoustic / _tracer_advection /
+_remap / _step, csrc/step.cu); this file owns the buffers' registration, the halo plans and — when subdomains live on
+other GPUs — the exchange the library calls back for.
 """
 import numpy as np
 
@@ -33,17 +32,6 @@ STEP_INPUTS = ["u", "v", "w", "delp", "delz", "pt", "qvapor", "qliquid", "qice",
 ACOUSTIC_TEMPORARIES = ["ad.ut", "ad.vt", "ad.gz", "ad.zh", "ad.pem", "ad.pkc", "ad.pk3", "ad.heat_source", "ad.cappa",
                         "ad.divgd", "ad.crx", "ad.cry", "ad.xfx", "ad.yfx", "csw.delpc", "csw.ptc", "dyn.dp1", "dyn.cvm"]
 TEMPORARIES_2D = ["ad.ws3", "ad.wsd", "ad.zs"]
-
-
-def nk_heat_dissipation(cfg, npz):
-    """pyFV3/stencils/dyn_core.py:176-191 get_nk_heat_dissipation."""
-    if cfg["convert_ke"] or cfg["vtdm4"] > 1.0e-4:
-        return npz
-    if cfg["d2_bg_k1"] < 1.0e-3:
-        return 0
-    if cfg["d2_bg_k2"] < 1.0e-3:
-        return 1
-    return 2
 
 
 class DycoreEngine:
@@ -112,16 +100,8 @@ class DycoreEngine:
         self.arena = arena
         self.halo = {pid: HaloExchanger(core, pid, ops, self.placement, comm, local, arena=arena)
                      for pid, ops in plans.items()}
-        self._nk_heat = nk_heat_dissipation(self.cfg, npz)
-        self._do_del2cubed = self._nk_heat != 0 and self.cfg["d_con"] > 1.0e-5
-        # LagrangianToEulerian.__init__ (remapping.py:347-351): first level with pfull > 10 hPa
-        pfull = np.asarray(g0["grid.p"])
-        self._kmp = npz - 1
-        for k in range(npz):
-            if pfull[k] > 10.0e2:
-                self._kmp = k
-                break
         self._check_config()
+        self._install_callbacks()
 
     def _halo(self, plan_id, x_names, y_names=None, nk=None):
         self.halo[plan_id].update(x_names, y_names, nk)
@@ -166,85 +146,76 @@ class DycoreEngine:
                 out[n][name] = a
         return out
 
-    # -- AcousticDynamics.__call__ (dyn_core.py:714-1013) ------------------------------------------------------
-    def acoustic_dynamics(self, timestep, n_map=1):
-        core, c, npz = self.core, self.cfg, self.npz
-        n_split = int(c["n_split"])
-        end_step = n_map == int(c["k_split"])
-        dt = timestep / n_split
-        dt2 = 0.5 * dt
-        self._halo(A3, ["q_con", "ad.cappa"])
-        core.call("zero_data", int(n_map == 1))
-        for it in range(n_split):
-            remap_step = it == n_split - 1
-            if it == 0:
-                core.call("gz_from_zs_delz")
-                self._halo(A3, ["delp", "pt"])
-            if it == n_split - 1 and end_step and c["use_old_omega"]:
-                core.call("pem_from_delp")
-            self._halo(D3, ["u"], ["v"])
-            self._halo(A3, ["w"])
-            core.call("c_sw", dt2)
-            if c["nord"] > 0:
-                self._halo(B3, ["ad.divgd"])
-            if it == 0:
-                self._halo(A3, ["ad.gz"], nk=npz + 1)
-                core.call("copy_full", "ad.gz", "ad.zh")
-            else:
-                core.call("copy_full", "ad.zh", "ad.gz")
-            core.call("update_dz_c", dt2)
-            core.call("riem_solver_c", dt2)
-            core.call("p_grad_c", dt2)
-            self._halo(C3, ["uc"], ["vc"])
-            core.call("d_sw", dt)
-            self._halo(A3, ["delp", "pt", "q_con"])
-            core.call("update_dz_d", dt)
-            core.call("riem_solver3", dt, int(remap_step))
-            self._halo(A3, ["ad.zh"], nk=npz + 1)
-            self._halo(A2, ["ad.pkc"], nk=npz + 1)
-            if remap_step:
-                core.call("edge_pe")
-            core.call("pk3_halo")
-            core.call("compute_geopotential")
-            core.call("nh_p_grad", dt)
-            if c["rf_fast"]:
-                core.call("ray_fast", dt)
-            if it == n_split - 1 and c["grid_type"] < 4:
-                self._halo(SYNC, ["u"], ["v"])
-        if self._do_del2cubed:
-            self._halo(A3, ["ad.heat_source"])
-            cd = CNST_0P20 * c["da_min"]
-            core.call("del2cubed", "ad.heat_source", cd, min(3, int(c["nord"]) + 1))
-            core.call("apply_diffusive_heating", abs(dt * c["delt_max"]), self._nk_heat)
+    # -- the reference's driver classes: their call order lives behind the C ABI (csrc/step.cu) ---------------------
+    def _install_callbacks(self):
+        """Halo updates with neighbours on other GPUs / processes are handed back to HaloExchanger by the library."""
+        from . import _lib
 
-    # -- TracerAdvection.__call__ (tracer_2d_1l.py:289-417) ----------------------------------------------------
-    TRACERS = ["qvapor", "qliquid", "qrain", "qice", "qsnow", "qgraupel", "qo3mr", "qsgs_tke"]  # NQ = 8 (GFS)
+        core = self.core
+        self._cb_error = None
+
+        def on_halo(_user, plan_id, x_names, y_names, n, nk):
+            try:
+                xs = [x_names[i].decode() for i in range(n)]
+                ys = [y_names[i].decode() for i in range(n)] if y_names else None
+                self.halo[plan_id].update(xs, ys, nk)
+                return 0
+            except Exception as exc:  # surfaced by _call below
+                self._cb_error = exc
+                return 1
+
+        remote = any(h.remote or h.arena is not None for h in self.halo.values())
+        self._halo_cb = _lib.HALO_CALLBACK(on_halo) if remote else _lib.HALO_CALLBACK()
+        core.lib.pace_b200_set_halo_callback(core.handle, self._halo_cb, None)
+        sat = _lib.SatAdjConfig.make(do_qa=int(self.cfg["do_qa"]))
+        core.lib.pace_b200_set_satadj_config(core.handle, sat)
+
+    def set_stage_callback(self, fn):
+        """fn(savepoint_name) is called at the reference's checkpointer hooks ("C_SW-In", "D_SW-Out", "Remapping-In",
+        ...; include/pace_b200.h).  None removes it."""
+        from . import _lib
+
+        def on_stage(_user, name):
+            try:
+                fn(name.decode())
+                return 0
+            except Exception as exc:
+                self._cb_error = exc
+                return 1
+
+        self._stage_cb = _lib.STAGE_CALLBACK(on_stage) if fn is not None else _lib.STAGE_CALLBACK()
+        self.core.lib.pace_b200_set_stage_callback(self.core.handle, self._stage_cb, None)
+
+    def _call(self, name, *args):
+        try:
+            self.core.call(name, *args)
+        except Exception:
+            if self._cb_error is not None:
+                exc, self._cb_error = self._cb_error, None
+                raise exc
+            raise
+
+    def acoustic_dynamics(self, timestep, n_map=1):
+        """AcousticDynamics.__call__ (dyn_core.py:714-1013) -> pace_b200_acoustic."""
+        self._call("acoustic", float(timestep), int(n_map))
 
     def tracer_advection(self):
-        core = self.core
-        cmax_max_all_ranks = 2.0  # the reference hard-codes this in place of an allreduce (tracer_2d_1l.py:337-364)
-        n_split = int(np.floor(1.0 + cmax_max_all_ranks))
-        core.call("tracer_flux_prep", n_split)
-        self._halo(A3, self.TRACERS)
-        for it in range(n_split):
-            core.call("tracer_substep", len(self.TRACERS))
-            if it != n_split - 1:
-                self._halo(A3, self.TRACERS)
-                core.call("tracer_swap_dp")
+        """TracerAdvection.__call__ (tracer_2d_1l.py:289-417) -> pace_b200_tracer_advection."""
+        self._call("tracer_advection")
 
-    # -- LagrangianToEulerian.__call__ (remapping.py:522-731) --------------------------------------------------
     def remapping(self, last_step, mdt):
-        core = self.core
-        core.call("remap_main", len(self.TRACERS))
-        if self.cfg["do_sat_adj"]:
-            core.sat_adjust(mdt, last_step, self._kmp)
-        core.call("remap_finish", int(last_step))
+        """LagrangianToEulerian.__call__ (remapping.py:522-731) -> pace_b200_remap."""
+        self._call("remap", int(last_step), float(mdt))
 
     # -- DynamicalCore.step_dynamics / _compute (fv_dynamics.py:445-655) ----------------------------------------
     def step_dynamics(self, timer=None):
-        """timer: optional object with start(name) / stop(name), called around the sections the reference times
-        (fv_dynamics.py:551-590: "DynCore", "TracerAdvection", "Remapping"); the caller decides how to clock them
+        """One dycore step -> pace_b200_step.  timer: optional object with start(name) / stop(name), called around the
+        sections the reference times (fv_dynamics.py:551-590: "DynCore", "TracerAdvection", "Remapping"); the step is
+        then issued phase by phase (pace_b200_acoustic / _tracer_advection / _remap) so that the caller can clock them
         (bench.py records CUDA events on the launching stream)."""
+        if timer is None:
+            self._call("step")
+            return
         core, c = self.core, self.cfg
         k_split = int(c["k_split"])
         self.compute_preamble()
@@ -252,21 +223,16 @@ class DycoreEngine:
             n_map = k + 1
             last_step = k == k_split - 1
             core.call("copy_levels", "delp", "dyn.dp1")
-            if timer is not None:
-                timer.start("DynCore")
+            timer.start("DynCore")
             self.acoustic_dynamics(c["dt_atmos"] / k_split, n_map=n_map)
-            if timer is not None:
-                timer.stop("DynCore")
-                timer.start("TracerAdvection")
+            timer.stop("DynCore")
+            timer.start("TracerAdvection")
             self.tracer_advection()
-            if timer is not None:
-                timer.stop("TracerAdvection")
+            timer.stop("TracerAdvection")
             if self.npz > 4:
-                if timer is not None:
-                    timer.start("Remapping")
+                timer.start("Remapping")
                 self.remapping(last_step, c["dt_atmos"] / k_split)
-                if timer is not None:
-                    timer.stop("Remapping")
+                timer.stop("Remapping")
                 if last_step:
                     core.call("omega_from_w")
                     if c["nf_omega"] > 0:
