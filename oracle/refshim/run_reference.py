@@ -1,6 +1,6 @@
 """TEST INFRASTRUCTURE ONLY — build and step the *unmodified* reference dycore (numpy backend) on a
-multi-process Comm, and record what it does.  Used by oracle/gen_golden.py (fixtures) and by
-bench.py --impl reference when /root/reference is present.
+multi-process Comm, and record what it does.  Used by oracle/gen_golden.py and oracle/gen_c48_golden.py (fixtures; their step times are the reference-numpy timings
+quoted in profiles/ and BASELINE.md).  Needs /root/reference, so it never runs on the GPU box.
 
 Constructor sequence follows the reference's own test tests/main/fv3core/test_dycore_call.py:28-136,
 with NullComm replaced by ProcComm so halos are real.

@@ -1,6 +1,7 @@
 // Device-side halo exchange: between subdomains resident on the same GPU in one gather kernel, and, for
-// neighbours on another GPU, pack / unpack kernels around a point-to-point transfer of one message per peer
-// (pace_b200/distributed.py: NCCL send/recv; gloo in the CPU tests).
+// neighbours on another GPU, pack / unpack kernels: the pack kernel stores its message straight into the receiver's
+// buffer over NVLink when it is given a peer-mapped address (pace_b200/distributed.py PeerArena, the default on GPUs),
+// or fills a local send buffer for an isend / irecv transfer (PACE_B200_HALO=p2p; gloo in the CPU tests).
 //
 // Replaces NDSL's HaloUpdater pack / Isend / Irecv / unpack (NDSL/ndsl/halo/updater.py:217-303,
 // halo/data_transformer.py:404-560, halo/cuda_kernels.py:5-236).  The plan (which source cell fills which

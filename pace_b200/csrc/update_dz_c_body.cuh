@@ -1,0 +1,72 @@
+// The three kernels of UpdateGeopotentialHeightOnCGrid.__call__ (pyFV3/stencils/updatedzc.py:18-118, 185-226), shared by
+// pace_b200_update_dz_c (work array from the handle's scratch pool, dz_pgrad.cu) and pace_b200_update_dz_c_static (work
+// array inside the library image, update_dz_c_static.cu) so that the two entry points cannot drift apart.
+#pragma once
+#include "core.hpp"
+#include "corners.cuh"
+
+namespace pace {
+
+// The reference makes two corner-filled copies of gz (gz_x, gz_y); here one plain copy (gz0, caller-provided work array
+// of field size) keeps the pre-update values and the corner fills are applied virtually at read time (corners.cuh).
+static int update_dz_c_with(Core& c, double dt, double* gz0) {
+  const Geo g = c.g;
+  cudaStream_t st = c.stream;
+  const double *zs = c.F("ad.zs"), *ut = c.F("ad.ut"), *vt = c.F("ad.vt"), *area = c.F("grid.area"),
+               *dp_ref = c.F("grid.dp_ref");
+  double *gz = c.F("ad.gz"), *ws = c.F("ad.ws3");
+  if (!c.err.empty() || !gz0) return 1;
+  const int km = g.nz;
+  launch_ijk(st, g, box_full(g, 1), [=] __device__(const Pt& p) { A0(gz0) = A0(gz); });
+  launch_ijk(st, g, box_compute(g, -1, -1, 2, 2, 1), [=] __device__(const Pt& p) {
+    const int k = p.k;
+    const EdgeInfo e = edge_info(g, p);
+    // xfx/yfx at horizontal offset (di,dj): pressure-weighted interface average of ut/vt.  The weight depends on the
+    // level only: one division per point instead of one per average.
+    const double wgt = k == 0 ? dp_ref[0] / (dp_ref[0] + dp_ref[1])
+                     : k < km ? 1.0 / (dp_ref[k - 1] + dp_ref[k])
+                              : dp_ref[k - 1] / (dp_ref[k - 2] + dp_ref[k - 1]);
+    auto favg = [&](const double* vel, int di, int dj) {
+      if (k == 0) {
+        return A(vel, di, dj, 0) + (A(vel, di, dj, 0) - A(vel, di, dj, 1)) * wgt;
+      } else if (k < km) {
+        return (dp_ref[k] * A(vel, di, dj, -1) + dp_ref[k - 1] * A(vel, di, dj, 0)) * wgt;
+      } else {
+        return A(vel, di, dj, -1) + (A(vel, di, dj, -1) - A(vel, di, dj, -2)) * wgt;
+      }
+    };
+    // cells of the compute domain proper never read a corner-filled value (the fills concern the ring around it)
+    const bool plain = p.i >= g.is && p.i <= g.ie && p.j >= g.js && p.j <= g.je;
+    auto gzx = [&](int di, int dj) {
+      int i = p.i + di, j = p.j + dj;
+      if (!plain) xfill_src(e, 2, i, j);
+      return gz0[p.o + (i - p.i) + (j - p.j) * p.sj];
+    };
+    auto gzy = [&](int di, int dj) {
+      int i = p.i + di, j = p.j + dj;
+      if (!plain) yfill_src(e, 2, i, j);
+      return gz0[p.o + (i - p.i) + (j - p.j) * p.sj];
+    };
+    double xfx0 = favg(ut, 0, 0), xfx1 = favg(ut, 1, 0), yfx0 = favg(vt, 0, 0), yfx1 = favg(vt, 0, 1);
+    double fx0 = xfx0 * (xfx0 > 0.0 ? gzx(-1, 0) : gzx(0, 0));
+    double fx1 = xfx1 * (xfx1 > 0.0 ? gzx(0, 0) : gzx(1, 0));
+    double fy0 = yfx0 * (yfx0 > 0.0 ? gzy(0, -1) : gzy(0, 0));
+    double fy1 = yfx1 * (yfx1 > 0.0 ? gzy(0, 0) : gzy(0, 1));
+    A0(gz) = (A0(gz0) * A20(area) + fx0 - fx1 + fy0 - fy1) / (A20(area) + xfx0 - xfx1 + yfx0 - yfx1);
+  });
+  launch_ij(st, g, box_compute(g, -1, -1, 2, 2, 1), [=] __device__(const Pt& p) {
+    double rdt = 1.0 / dt;
+    double below = A(gz, 0, 0, km);
+    A20(ws) = (A20(zs) - below) * rdt;
+    for (int k = km - 1; k >= 0; --k) {
+      double gz_kp1 = below + DZ_MIN;
+      double v = A(gz, 0, 0, k);
+      v = v > gz_kp1 ? v : gz_kp1;
+      A(gz, 0, 0, k) = v;
+      below = v;
+    }
+  });
+  return 0;
+}
+
+}  // namespace pace

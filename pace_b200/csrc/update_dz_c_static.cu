@@ -25,6 +25,7 @@
 //    are the same bit for bit.
 #include "core.hpp"
 #include "corners.cuh"
+#include "update_dz_c_body.cuh"
 
 #include "../../include/pace_b200.h"  // PACE_B200_STATIC_SCRATCH_DOUBLES (2097152 doubles = 16 MiB)
 
@@ -63,10 +64,8 @@ double* static_scratch(Core& c) {
 
 }  // namespace
 
-// Same three kernels as update_dz_c (updatedzc.py:18-118, 185-226); only the home of gz0 differs.
+// Same three kernels as update_dz_c (update_dz_c_body.cuh); only the home of gz0 differs.
 static int update_dz_c_static(Core& c, double dt) {
-  const Geo g = c.g;
-  cudaStream_t st = c.stream;
   const size_t need = c.field_elems();
   if (need > (size_t)PACE_B200_STATIC_SCRATCH_DOUBLES) {
     c.err = "update_dz_c_static: this handle needs " + std::to_string(need) +
@@ -74,58 +73,9 @@ static int update_dz_c_static(Core& c, double dt) {
             "; use pace_b200_update_dz_c (which allocates) or smaller / fewer subdomains per handle";
     return 1;
   }
-  const double *zs = c.F("ad.zs"), *ut = c.F("ad.ut"), *vt = c.F("ad.vt"), *area = c.F("grid.area"),
-               *dp_ref = c.F("grid.dp_ref");
-  double *gz = c.F("ad.gz"), *ws = c.F("ad.ws3");
-  if (!c.err.empty()) return 1;
   double* gz0 = static_scratch(c);
   if (!gz0) return 1;
-  const int km = g.nz;
-  launch_ijk(st, g, box_full(g, 1), [=] __device__(const Pt& p) { A0(gz0) = A0(gz); });
-  launch_ijk(st, g, box_compute(g, -1, -1, 2, 2, 1), [=] __device__(const Pt& p) {
-    const int k = p.k;
-    const EdgeInfo e = edge_info(g, p);
-    auto favg = [&](const double* vel, int di, int dj) {
-      if (k == 0) {
-        double ratio = dp_ref[0] / (dp_ref[0] + dp_ref[1]);
-        return A(vel, di, dj, 0) + (A(vel, di, dj, 0) - A(vel, di, dj, 1)) * ratio;
-      } else if (k < km) {
-        double int_ratio = 1.0 / (dp_ref[k - 1] + dp_ref[k]);
-        return (dp_ref[k] * A(vel, di, dj, -1) + dp_ref[k - 1] * A(vel, di, dj, 0)) * int_ratio;
-      } else {
-        double ratio = dp_ref[k - 1] / (dp_ref[k - 2] + dp_ref[k - 1]);
-        return A(vel, di, dj, -1) + (A(vel, di, dj, -1) - A(vel, di, dj, -2)) * ratio;
-      }
-    };
-    auto gzx = [&](int di, int dj) {
-      int i = p.i + di, j = p.j + dj;
-      xfill_src(e, 2, i, j);
-      return gz0[p.o + (i - p.i) + (j - p.j) * p.sj];
-    };
-    auto gzy = [&](int di, int dj) {
-      int i = p.i + di, j = p.j + dj;
-      yfill_src(e, 2, i, j);
-      return gz0[p.o + (i - p.i) + (j - p.j) * p.sj];
-    };
-    double xfx0 = favg(ut, 0, 0), xfx1 = favg(ut, 1, 0), yfx0 = favg(vt, 0, 0), yfx1 = favg(vt, 0, 1);
-    double fx0 = xfx0 * (xfx0 > 0.0 ? gzx(-1, 0) : gzx(0, 0));
-    double fx1 = xfx1 * (xfx1 > 0.0 ? gzx(0, 0) : gzx(1, 0));
-    double fy0 = yfx0 * (yfx0 > 0.0 ? gzy(0, -1) : gzy(0, 0));
-    double fy1 = yfx1 * (yfx1 > 0.0 ? gzy(0, 0) : gzy(0, 1));
-    A0(gz) = (A0(gz0) * A20(area) + fx0 - fx1 + fy0 - fy1) / (A20(area) + xfx0 - xfx1 + yfx0 - yfx1);
-  });
-  launch_ij(st, g, box_compute(g, -1, -1, 2, 2, 1), [=] __device__(const Pt& p) {
-    double rdt = 1.0 / dt;
-    double below = A(gz, 0, 0, km);
-    A20(ws) = (A20(zs) - below) * rdt;
-    for (int k = km - 1; k >= 0; --k) {
-      double gz_kp1 = below + DZ_MIN;
-      double v = A(gz, 0, 0, k);
-      v = v > gz_kp1 ? v : gz_kp1;
-      A(gz, 0, 0, k) = v;
-      below = v;
-    }
-  });
+  if (update_dz_c_with(c, dt, gz0) != 0) return 1;
   cudaError_t e = cudaPeekAtLastError();
   if (e != cudaSuccess) {
     c.err = std::string("update_dz_c_static: CUDA launch error: ") + cudaGetErrorString(e);

@@ -37,22 +37,64 @@ CONFIG_NAMES = [
 
 
 def _arr(x):
-    """numpy view of a Quantity / gt4py storage / array-like."""
+    """numpy view (numpy storage) or host copy (cupy storage) of a Quantity / gt4py storage / array-like."""
     d = getattr(x, "data", x)
     if hasattr(d, "get"):  # cupy
         d = d.get()
     return np.asarray(d)
 
 
+def _write_back(dst, a):
+    """Store the result `a` into the caller's field object: in place for numpy storage, through a host-to-device copy
+    for cupy storage; anything else is refused rather than silently dropped."""
+    d = getattr(dst, "data", dst)
+    if isinstance(d, np.ndarray):
+        if d.ndim == 3 and d.shape[2] != a.shape[2]:
+            a = a[:, :, :d.shape[2]]
+        d[...] = a
+    elif hasattr(d, "get") and hasattr(d, "set"):  # cupy.ndarray
+        if d.ndim == 3 and d.shape[2] != a.shape[2]:
+            a = a[:, :, :d.shape[2]]
+        d.set(np.ascontiguousarray(a, dtype=d.dtype))
+    else:
+        raise TypeError("pace_b200.dropin: cannot write results into storage of type %s" % type(d).__name__)
+
+
 def grid_arrays(grid_data, damping_coefficients):
     """The metric terms and damping coefficients the step reads, keyed the way libpace_b200 names them."""
-    out = {"grid." + n: _arr(getattr(grid_data, n)) for n in GRID_NAMES}
+    out = {"grid." + n: _arr(getattr(grid_data, n)) for n in GRID_NAMES if hasattr(grid_data, n)}
     out["grid.ptop"] = np.float64(grid_data.ptop)
     for n in ("del6_u", "del6_v", "divg_u", "divg_v"):
         out["damp." + n] = _arr(getattr(damping_coefficients, n))
     out["damp.da_min"] = np.float64(damping_coefficients.da_min)
     out["damp.da_min_c"] = np.float64(damping_coefficients.da_min_c)
     return out
+
+
+def config_values(config):
+    """CONFIG_NAMES and the SatAdjustConfig values from a DynamicalCoreConfig or an AcousticDynamicsConfig (whose
+    options sit in the nested riemann / d_grid_shallow_water objects, pyFV3/_config.py:59-140)."""
+    places = [config] + [getattr(config, n) for n in ("acoustic_dynamics", "riemann", "d_grid_shallow_water", "remapping")
+                         if hasattr(config, n)]
+    ad = getattr(config, "acoustic_dynamics", None)
+    if ad is not None:
+        places += [getattr(ad, n) for n in ("riemann", "d_grid_shallow_water") if hasattr(ad, n)]
+    cfg = {}
+    for n in CONFIG_NAMES:
+        for pl in places:
+            try:
+                cfg[n] = getattr(pl, n)
+                break
+            except (AttributeError, NotImplementedError):
+                continue
+    sat = {}
+    src = getattr(config, "sat_adjust", config)
+    from ._lib import SatAdjConfig
+
+    for n in SatAdjConfig.DEFAULTS:
+        if hasattr(src, n):
+            sat[n] = getattr(src, n)
+    return cfg, sat
 
 
 class MpiStyleComm:
@@ -64,13 +106,19 @@ class MpiStyleComm:
         self.group = None
         self._tag = 7100
 
+    @staticmethod
+    def _wait_all(reqs):
+        for r in reqs:
+            (r.wait if hasattr(r, "wait") else r.Wait)()
+
     def exchange(self, sends, recvs):
         self._tag += 1
         tag = self._tag
-        reqs = [self.mpi.Irecv(t.numpy(), source=p, tag=tag) for p, t in sorted(recvs.items())]
-        for p, t in sorted(sends.items()):
-            self.mpi.Isend(t.numpy(), dest=p, tag=tag)
-        return lambda: [r.wait() for r in reqs]
+        rreqs = [self.mpi.Irecv(t.numpy(), source=p, tag=tag) for p, t in sorted(recvs.items())]
+        # the send requests are kept and waited for too: the send buffer is a slice of a persistent pack buffer that the
+        # next update overwrites
+        sreqs = [self.mpi.Isend(t.numpy(), dest=p, tag=tag) for p, t in sorted(sends.items())]
+        return lambda: self._wait_all(rreqs + [r for r in sreqs if r is not None])
 
 
 class _StagedComm(MpiStyleComm):
@@ -82,42 +130,52 @@ class _StagedComm(MpiStyleComm):
         self._tag += 1
         tag = self._tag
         host = {p: torch.empty(t.shape, dtype=t.dtype) for p, t in recvs.items()}
-        reqs = [self.mpi.Irecv(host[p].numpy(), source=p, tag=tag) for p in sorted(recvs)]
-        for p, t in sorted(sends.items()):
-            self.mpi.Isend(t.cpu().numpy(), dest=p, tag=tag)
+        rreqs = [self.mpi.Irecv(host[p].numpy(), source=p, tag=tag) for p in sorted(recvs)]
+        staged = {p: t.cpu() for p, t in sends.items()}  # kept alive until the sends have completed
+        sreqs = [self.mpi.Isend(staged[p].numpy(), dest=p, tag=tag) for p in sorted(staged)]
 
         def wait():
-            for r in reqs:
-                r.wait()
+            self._wait_all(rreqs + [r for r in sreqs if r is not None])
             for p, t in recvs.items():
                 t.copy_(host[p])
+            staged.clear()
 
         return wait
 
 
-class DynamicalCore:
-    """See the module docstring.  Raises the reference's own errors for the options it does not implement
-    (DycoreEngine._check_config)."""
+# savepoint -> {checkpointer keyword: library field name}: the variables the reference hands to its checkpointer
+# (dyn_core.py:641-701, fv_dynamics.py:342-443); "^T" marks the [x, z, y] transposes of pe / peln
+_CSW = dict(delpd="delp", ptd="pt", ud="u", vd="v", wd="w", ucd="uc", vcd="vc", uad="ua", vad="va", utd="ad.ut",
+            vtd="ad.vt", divgdd="ad.divgd")
+_DSW = dict(ucd="uc", vcd="vc", wd="w", delpcd="ad.vt", delpd="delp", ud="u", vd="v", ptd="pt", uad="ua", vad="va",
+            divgdd="ad.divgd", xfxd="ad.xfx", yfxd="ad.yfx", mfxd="mfxd", mfyd="mfyd")
+_FVD = dict(u="u", v="v", w="w", delz="delz", va="va", uc="uc", vc="vc", qvapor="qvapor")
+_TRC = dict(dp1="dyn.dp1", mfxd="mfxd", mfyd="mfyd", cxd="cxd", cyd="cyd")
+_RMO = dict(pt="pt", delp="delp", delz="delz", peln="peln^T", u="u", v="v", w="w", cappa="ad.cappa", pkz="pkz", pk="pk",
+            pe="pe^T", dp1="dyn.dp1")
+_RMI = dict(pt="pt", delp="delp", delz="delz", peln="peln^T", u="u", v="v", w="w", ua="ua", va="va", cappa="ad.cappa",
+            pk="pk", pe="pe^T", phis="phis", ps="ps", wsd="ad.wsd", omga="omga", dp1="dyn.dp1")
+SAVEPOINTS = {"C_SW-In": _CSW, "C_SW-Out": _CSW, "D_SW-In": dict(_DSW, zhd="ad.zh"), "D_SW-Out": _DSW,
+              "FVDynamics-In": _FVD, "FVDynamics-Out": _FVD, "Tracer2D1L-In": _TRC, "Tracer2D1L-Out": _TRC,
+              "Remapping-In": _RMI, "Remapping-Out": _RMO}
 
-    def __init__(self, comm, grid_data, stencil_factory, quantity_factory, damping_coefficients, config, phis, state,
-                 timestep, checkpointer=None, *, device="cuda:0", _lib_handle=None):
-        del stencil_factory, quantity_factory  # signature compatibility only
-        self.config = config
-        self.checkpointer = checkpointer
+
+class _Bridge:
+    """What DynamicalCore and AcousticDynamics share: the engine, the copies between the caller's state objects
+    (reference layout (i, j, k), numpy or cupy storage) and the device buffers, and the checkpointer hook."""
+
+    def _build(self, comm, grid_data, damping_coefficients, config, phis, n_tile, layout, npz, dt_atmos, checkpointer,
+               device, _lib_handle):
         many = isinstance(grid_data, (list, tuple))
         grids = [grid_arrays(g, d) for g, d in zip(grid_data, damping_coefficients)] if many else [
             grid_arrays(grid_data, damping_coefficients)]
-        layout = tuple(getattr(config, "layout", (1, 1)))
         if layout[0] != layout[1]:
             raise NotImplementedError("pace_b200: only square layouts are supported")
-        n_tile = int(config.npx) - 1
         total = 6 * layout[0] * layout[1]
-        cfg = {n: getattr(config, n) for n in CONFIG_NAMES if hasattr(config, n)}
+        cfg, sat = config_values(config)
         cfg["ks"] = int(getattr(grid_data[0] if many else grid_data, "ks", 0))
-        dt = timestep.total_seconds() if hasattr(timestep, "total_seconds") else float(timestep)
-        if "dt_atmos" in cfg and float(cfg["dt_atmos"]) != dt:
-            raise ValueError("timestep (%s s) differs from config.dt_atmos (%s s)" % (dt, cfg["dt_atmos"]))
-        cfg["dt_atmos"] = dt
+        if dt_atmos is not None:
+            cfg["dt_atmos"] = dt_atmos
         transport = None
         if many:
             if len(grids) != total:
@@ -127,37 +185,132 @@ class DynamicalCore:
             if mpi.Get_size() != total:
                 raise ValueError("one process per subdomain needs %d ranks, the communicator has %d" % (total, mpi.Get_size()))
             transport = (MpiStyleComm if str(device).startswith("cpu") else _StagedComm)(mpi)
-        self.engine = DycoreEngine(n_tile, layout[0], int(config.npz), grids, comm=transport, device=device,
-                                   _lib_handle=_lib_handle, **cfg)
+        self.engine = DycoreEngine(n_tile, layout[0], npz, grids, comm=transport, device=device,
+                                   _lib_handle=_lib_handle, sat_adjust=sat, **cfg)
         self._many = many
-        # the reference's constructor derives zs from phis and keeps it (dyn_core.py:489-496)
+        # the reference's constructors derive zs from phis and keep it (dyn_core.py:489-496)
         self._phis = [_arr(p) for p in phis] if many else [_arr(phis)]
         self.engine.core.put("ad.zs", [np.asarray(p, dtype=np.float64) / 9.80665 for p in self._phis])
         self.engine.core.put("phis", self._phis)
+        self._set_checkpointer(checkpointer)
+
+    def _set_checkpointer(self, checkpointer):
+        self.checkpointer = checkpointer
+        self.call_checkpointer = checkpointer is not None
+        if checkpointer is None:
+            self.engine.set_stage_callback(None)
+            return
+        core = self.engine.core
+
+        def hook(savepoint):
+            core.sync()
+            kw = {}
+            for key, name in SAVEPOINTS[savepoint].items():
+                tr = name.endswith("^T")
+                arrs = core.get(name[:-2] if tr else name)
+                if tr:
+                    arrs = [a.transpose(0, 2, 1) for a in arrs]
+                kw[key] = arrs if self._many else arrs[0]
+            checkpointer(savepoint, **kw)
+
+        self.engine.set_stage_callback(hook)
 
     @staticmethod
     def _fields(state):
         return {n: getattr(state, n) for n in STATE_3D + STATE_2D if hasattr(state, n)}
 
-    def step_dynamics(self, state, timer=None):
-        """Step the model state forward by one timestep, in place (fv_dynamics.py:445-460)."""
+    def _upload(self, state):
         states = list(state) if self._many else [state]
-        if timer is not None:
-            timer.start("DynCore")
         fields = [self._fields(s) for s in states]
         names = [n for n in fields[0] if n != "phis"]
         for n in names:
             self.engine.core.put(n, [_arr(f[n]) for f in fields])
-        self.engine.step_dynamics()
+        return fields, names
+
+    def _download(self, fields, names):
         self.engine.core.sync()
         for n in names:
             for f, a in zip(fields, self.engine.core.get(n)):
-                dst = _arr(f[n])
-                if dst.ndim == 3 and dst.shape[2] != a.shape[2]:
-                    a = a[:, :, :dst.shape[2]]
-                dst[...] = a
-        if timer is not None:
-            timer.stop("DynCore")
+                _write_back(f[n], a)
+
+
+class AcousticDynamics(_Bridge):
+    """Drop-in for `pyFV3.stencils.dyn_core.AcousticDynamics`: the reference's constructor arguments
+    (dyn_core.py:367-382) and `__call__(state, timestep, n_map=1)` (:714-719).  `cappa` is the reference's public
+    temporary (dyn_core.py:468): a list of (i, j, k) arrays fetched from the device on access."""
+
+    def __init__(self, comm, stencil_factory, quantity_factory, grid_data, damping_coefficients, grid_type, nested,
+                 stretched_grid, config, phis, wsd, state, checkpointer=None, *, device="cuda:0", _lib_handle=None,
+                 _engine_of=None):
+        del stencil_factory, wsd, state  # signature compatibility: nothing is compiled, temporaries live on the device
+        if _engine_of is not None:  # the instance a DynamicalCore exposes as .acoustic_dynamics shares its engine
+            self.engine, self._many = _engine_of.engine, _engine_of._many
+            self.checkpointer, self.call_checkpointer = _engine_of.checkpointer, _engine_of.call_checkpointer
+            return
+        if nested or stretched_grid:
+            raise NotImplementedError("pace_b200: nested / stretched grids are not supported")
+        g0 = grid_data[0] if isinstance(grid_data, (list, tuple)) else grid_data
+        nx = _arr(g0.rarea).shape[0] - 7
+        layout = (1, 1)
+        part = getattr(getattr(comm, "partitioner", None), "tile", None)
+        if part is not None:
+            layout = tuple(part.layout)
+        npz = int(getattr(getattr(quantity_factory, "sizer", None), "nz", 0)) or _arr(g0.ak).shape[0] - 1
+        self._build(comm, grid_data, damping_coefficients, config, phis, nx * layout[0], layout, npz, None,
+                    checkpointer, device, _lib_handle)
+        self.engine.cfg["grid_type"] = grid_type
+
+    @property
+    def cappa(self):
+        arrs = self.engine.core.get("ad.cappa")
+        return arrs if self._many else arrs[0]
+
+    def __call__(self, state, timestep, n_map=1):
+        fields, names = self._upload(state)
+        self.engine.acoustic_dynamics(float(timestep), n_map=int(n_map))
+        self._download(fields, names)
+
+
+class TracerAdvection:
+    """`DynamicalCore.tracer_advection` of the drop-in: TracerAdvection.__call__ (tracer_2d_1l.py:289-417) on the
+    engine's device state; the reference's arguments (tracers, dp1, mass fluxes, Courant numbers) are the engine's
+    own fields of the same names, so they are accepted and not read."""
+
+    def __init__(self, owner):
+        self._owner = owner
+
+    def __call__(self, *args, **kwargs):
+        self._owner.engine.tracer_advection()
+
+
+class DynamicalCore(_Bridge):
+    """See the module docstring.  Raises the reference's own errors for the options it does not implement
+    (DycoreEngine._check_config)."""
+
+    def __init__(self, comm, grid_data, stencil_factory, quantity_factory, damping_coefficients, config, phis, state,
+                 timestep, checkpointer=None, *, device="cuda:0", _lib_handle=None):
+        del stencil_factory, quantity_factory  # signature compatibility only
+        self.config = config
+        layout = tuple(getattr(config, "layout", (1, 1)))
+        dt = timestep.total_seconds() if hasattr(timestep, "total_seconds") else float(timestep)
+        if hasattr(config, "dt_atmos") and float(config.dt_atmos) != dt:
+            raise ValueError("timestep (%s s) differs from config.dt_atmos (%s s)" % (dt, config.dt_atmos))
+        self._build(comm, grid_data, damping_coefficients, config, phis, int(config.npx) - 1, layout, int(config.npz),
+                    dt, checkpointer, device, _lib_handle)
+        # the sub-objects a user of the reference reaches for (fv_dynamics.py:231, 268, 299)
+        self.acoustic_dynamics = AcousticDynamics(None, None, None, None, None, None, None, None, None, None, None, None,
+                                                  _engine_of=self)
+        self.tracer_advection = TracerAdvection(self)
+
+    @property
+    def _cappa(self):
+        return self.acoustic_dynamics.cappa
+
+    def step_dynamics(self, state, timer=None):
+        """Step the model state forward by one timestep, in place (fv_dynamics.py:445-460)."""
+        fields, names = self._upload(state)
+        self.engine.step_dynamics(timer)
+        self._download(fields, names)
 
     def __call__(self, *args, **kwargs):
         return self.step_dynamics(*args, **kwargs)

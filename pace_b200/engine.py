@@ -35,13 +35,16 @@ TEMPORARIES_2D = ["ad.ws3", "ad.wsd", "ad.zs"]
 
 
 class DycoreEngine:
-    def __init__(self, n_tile, layout, npz, grids, ranks=None, comm=None, device="cuda:0", _lib_handle=None, **cfg):
+    def __init__(self, n_tile, layout, npz, grids, ranks=None, comm=None, device="cuda:0", _lib_handle=None,
+                 sat_adjust=None, **cfg):
         """grids: list (one per resident subdomain) of dicts with the reference's GridData / DampingCoefficients
         arrays ("grid.*", "damp.*", reference layout).  ranks: cube ranks of those subdomains (default: all).
         comm: pace_b200.distributed.TorchComm when the cube is spread over several GPUs (one process per GPU,
-        contiguous blocks of subdomains, see distributed.Placement); ranks then defaults to this GPU's block."""
+        contiguous blocks of subdomains, see distributed.Placement); ranks then defaults to this GPU's block.
+        sat_adjust: SatAdjustConfig values (pyFV3/_config.py:15-41) that differ from the namelist defaults."""
         from .distributed import HaloExchanger, Placement
 
+        self._sat_adjust = dict(sat_adjust or {})
         self.planner = HaloPlanner(n_tile, layout)
         world = comm.world_size if comm is not None else 1
         self.placement = Placement(self.planner.total_ranks, world)
@@ -167,7 +170,8 @@ class DycoreEngine:
         remote = any(h.remote or h.arena is not None for h in self.halo.values())
         self._halo_cb = _lib.HALO_CALLBACK(on_halo) if remote else _lib.HALO_CALLBACK()
         core.lib.pace_b200_set_halo_callback(core.handle, self._halo_cb, None)
-        sat = _lib.SatAdjConfig.make(do_qa=int(self.cfg["do_qa"]))
+        sat = _lib.SatAdjConfig.make(**dict({k: (int(v) if isinstance(v, bool) else v) for k, v in self._sat_adjust.items()},
+                                            do_qa=int(self.cfg["do_qa"])))
         core.lib.pace_b200_set_satadj_config(core.handle, sat)
 
     def set_stage_callback(self, fn):

@@ -35,6 +35,7 @@ def test_static_scratch_variant_matches_allocating_entry_point(golden, grid0):
     # comparison below is not vacuous
     before = golden.before("updatedzc")
     assert not np.array_equal(want["ad.gz"], before["ad.gz"])
+    after = golden.after("updatedzc")
 
     core = _fresh_core(golden, grid0)
     for call_no in (1, 2):
@@ -47,6 +48,8 @@ def test_static_scratch_variant_matches_allocating_entry_point(golden, grid0):
             got = core.get(n)[0]
             assert np.array_equal(got, want[n]), "call %d: %s differs, max |d| = %g" % (
                 call_no, n, np.max(np.abs(got - want[n])))
+            # and the reference's own result of the same call, directly
+            assert np.array_equal(got, after[n]), "call %d: %s differs from the reference" % (call_no, n)
 
 
 @pytest.mark.gpu
