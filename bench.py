@@ -19,6 +19,8 @@ import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+if "reference" in sys.argv:  # before anything loads an OpenMP runtime: torchrun exports OMP_NUM_THREADS=1
+    os.environ["OMP_NUM_THREADS"] = str(os.cpu_count() or 1)
 
 WORKLOADS = {
     # name: (tile size, layout, description)
@@ -71,52 +73,109 @@ class ClockSampler(threading.Thread):
                 "samples": len(self.samples)}
 
 
-def cpu_port_rate(n_tile, threads, steps=1):
-    """simulated-days/day of the CPU port (oracle/cpu_port.py: the kernel sources compiled for the host, verified
-    bit-exact against the reference's golden vectors) on a bounded sample."""
+def set_host_threads(n):
+    """Thread count of the OpenMP runtime the CPU port uses.  The environment variable only counts before the runtime
+    is loaded (torch loads libgomp, and torchrun exports OMP_NUM_THREADS=1), so the runtime is told directly."""
+    os.environ["OMP_NUM_THREADS"] = str(n)
+    try:
+        ctypes.CDLL("libgomp.so.1").omp_set_num_threads(int(n))
+    except OSError:
+        pass
+
+
+def cpu_port_step_seconds(n_tile, layout, threads, steps=1, warmup=1):
+    """Seconds per dycore step of the CPU port (oracle/cpu_port.py: the kernel sources compiled for the host with
+    OpenMP, verified bit-exact against the reference's golden vectors) at C<n_tile>."""
     from oracle import cpu_port
     from pace_b200.synthetic import make_engine
 
-    os.environ["OMP_NUM_THREADS"] = str(threads)
+    set_host_threads(threads)
     lib = cpu_port.load(openmp=True)
-    eng = make_engine(n_tile, 1, npz=NPZ, device="cpu", _lib_handle=lib, n_split=N_SPLIT, k_split=1, dt_atmos=DT_ATMOS)
-    eng.step_dynamics()  # warm-up
+    eng = make_engine(n_tile, layout, npz=NPZ, device="cpu", _lib_handle=lib, n_split=N_SPLIT, k_split=1, dt_atmos=DT_ATMOS)
+    for _ in range(warmup):
+        eng.step_dynamics()
     t0 = time.time()
     for _ in range(steps):
         eng.step_dynamics()
-    dt = (time.time() - t0) / steps
-    return DT_ATMOS / dt, dt
+    return (time.time() - t0) / steps
+
+
+def host_sample_for(n_tile, layout):
+    """The largest configuration of the CPU port that fits the host's free memory with a wide margin: the workload
+    itself when it does (~140 work fields in the unfused host build), else a quarter / sixteenth of its cells."""
+    try:
+        import psutil
+
+        avail = psutil.virtual_memory().available
+    except Exception:
+        avail = 32e9
+    for tile, lay in ((n_tile, layout), (n_tile // 2, 1), (n_tile // 4, 1), (48, 1)):
+        n = tile // lay
+        need = 150 * 6 * lay * lay * (NPZ + 1) * (n + 7) * (n + 8) * 8
+        if tile >= 48 and need * 2.5 < avail:
+            return tile, lay
+    return 48, 1
+
+
+REFERENCE_NUMPY = {  # the reference itself cannot run on the GPU box; measured in the build container (profiles/)
+    "what": "UNMODIFIED reference, pyFV3 numpy backend, one step_dynamics at C48 L79 with n_split=1, 6 processes on 8 cores",
+    "seconds_per_step": 55.97, "source": "profiles/r02_reference_numpy_c48.json",
+    "gt_cpu_ifirst": "not buildable on this box (needs gridtools-cpp and boost; no network)",
+}
 
 
 def run_reference(args):
     """--impl reference: the CPU implementation of the path on the box's host cores.  The reference itself is
-    Python (GT4Py numpy backend) and cannot travel to the GPU box, so this arm times the CPU port."""
-    rank = int(os.environ.get("RANK", "0"))
-    if rank != 0:
-        return
+    Python (GT4Py numpy backend) with a compiled-stencil cache and cannot travel to the GPU box, so this arm times the
+    CPU port (kind "port") with every host thread: the workload itself when the host has the memory for it, otherwise
+    a bounded sample whose own time per step is printed next to the value scaled to the workload by cell count."""
     cores = os.cpu_count() or 1
     n_tile, layout, desc = WORKLOADS[args.workload]
-    sample_tile = 48
-    times = []
-    for _ in range(max(1, min(args.steps, 3))):
-        rate, dt = cpu_port_rate(sample_tile, cores, steps=1)
-        times.append(dt)
-    dt = sum(times) / len(times)
-    # a step costs time proportional to the number of cells: scale the sample to the workload
-    scale = (n_tile / sample_tile) ** 2
+    tile, lay = host_sample_for(n_tile, layout)
+    same = (tile, lay) == (n_tile, layout)
+    # one step of the full workload takes about a minute on 16 cores: one warm-up and one timed step
+    k = 1 if same else max(1, min(args.steps, 2))
+    dt = cpu_port_step_seconds(tile, lay, cores, steps=k, warmup=1)
+    scale = (n_tile / tile) ** 2
     ms = dt * scale * 1000.0
     value = DT_ATMOS / (ms / 1000.0)
+    sample = ("the workload itself: %d timed step(s) of C%d (%d subdomains) on the host after one warm-up step" % (k, tile, 6 * lay * lay)) if same else (
+        "%d timed step(s) at C%d L79 (6 subdomains, %.0f ms each), scaled by cell count (x%.0f) to the workload"
+        % (k, tile, dt * 1000.0, scale))
     line = {
         "impl": "reference", "metric": "dycore simulated-days/day", "value": value, "unit": "simulated days / day",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
         "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": desc},
-        "cpu_baseline": {"value": value, "unit": "simulated days / day", "cores": cores, "kind": "port",
-                         "sample": "one dycore step at C%d L79 (6 subdomains) timed on the host, scaled by cell count "
-                                   "(x%.0f) to the workload" % (sample_tile, scale)},
+        "steps_timed": k, "sample_ms_per_step": dt * 1000.0, "sample_is_workload": same,
+        "cpu_baseline": {"value": value, "unit": "simulated days / day", "cores": cores, "kind": "port", "sample": sample},
+        "reference_numpy_backend": REFERENCE_NUMPY,
         "e2e": {"value": value, "unit": "simulated days / day", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line))
+
+
+def state_hash(eng, dist, world):
+    """SHA-256 over the prognostic fields (compute domain, subdomains in cube order) after the timed steps: the same
+    number of steps from the same state gives the same hash at every GPU count when the partitioning changes nothing."""
+    import hashlib
+
+    import numpy as np
+
+    core = eng.core
+    n = core.nx
+    digests = []
+    arrs = {name: core.t[name].cpu().numpy() for name in ("u", "v", "w", "delp", "pt", "delz", "qvapor")}
+    for t in range(core.nt):
+        h = hashlib.sha256()
+        for name, a in arrs.items():
+            h.update(np.ascontiguousarray(a[t, :NPZ, 3:3 + n, 3:3 + n]).tobytes())
+        digests.append(h.hexdigest())
+    if dist is not None:
+        allp = [None] * world
+        dist.all_gather_object(allp, digests)
+        digests = [d for part in allp for d in part]
+    return hashlib.sha256("".join(digests).encode()).hexdigest()
 
 
 def main():
@@ -165,7 +224,7 @@ def main():
     comm = None
     dist = None
     if world > 1:
-        # one process per GPU; each holds a contiguous block of subdomains, halos cross GPUs by NCCL send/recv
+        # one process per GPU; each holds a contiguous block of subdomains (halo transport: see config.placement)
         import torch.distributed as dist
 
         from pace_b200.distributed import TorchComm
@@ -212,6 +271,7 @@ def main():
     fence()
     torch.cuda.profiler.stop()
     ms = max_over_ranks(e0.elapsed_time(e1) / args.steps)
+    state_sha256 = state_hash(eng, dist, world)
     launches = (lib.pace_b200_launch_count() - l0) // args.steps
     lib.pace_b200_profile_enable(0)
     buf = ctypes.create_string_buffer(65536)
@@ -307,18 +367,19 @@ def main():
     cpu = None
     if not args.no_cpu_baseline and world == 1:
         cores = os.cpu_count() or 1
-        sample_tile = 48
-        rate, dt = cpu_port_rate(sample_tile, cores, steps=1)
+        sample_tile = 96 if n_tile >= 96 else 48
+        dt = cpu_port_step_seconds(sample_tile, 1, cores, steps=1, warmup=1)
         scale = (n_tile / sample_tile) ** 2
         cpu = {"value": DT_ATMOS / (dt * scale), "unit": "simulated days / day", "cores": cores, "kind": "port",
-               "sample": "one dycore step at C%d L79 (%.1f s on the host), scaled by cell count (x%.0f)" % (sample_tile, dt, scale)}
+               "sample": "one dycore step at C%d L79 (%.1f s on the host), scaled by cell count (x%.0f)" % (sample_tile, dt, scale),
+               "reference_numpy_backend": REFERENCE_NUMPY}
 
     line = {
         "metric": "dycore simulated-days/day", "value": value, "unit": "simulated days / day", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic (C12 reference fixture resampled, see pace_b200/synthetic.py)",
-        "config": {"workload": desc, "cells": cells, "placement": "%d subdomains per GPU, halo exchange by NCCL send/recv" % (n_sub // world) if world > 1 else "%d subdomains on one GPU" % n_sub, "l2": "working set (%.0f GB) >> L2, no flush needed" % (cells * 8 * 130 / 1e9)},
-        "gpu_launches": int(launches), "clocks": sampler.summary(), "roofline": roof, "acoustic_substep": acoustic, "dense_path": dense,
+        "config": {"workload": desc, "cells": cells, "placement": ("%d subdomains per GPU, halo exchange: %s" % (n_sub // world, "peer stores into symmetric memory over NVLink + device-side barrier" if eng.arena is not None else "torch.distributed isend / irecv")) if world > 1 else "%d subdomains on one GPU" % n_sub, "l2": "working set (%.0f GB) >> L2, no flush needed" % (cells * 8 * 130 / 1e9)},
+        "state_sha256": state_sha256, "gpu_launches": int(launches), "clocks": sampler.summary(), "roofline": roof, "acoustic_substep": acoustic, "dense_path": dense,
         "cpu_baseline": cpu, "e2e": e2e,
     }
     if rank == 0:
