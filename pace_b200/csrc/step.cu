@@ -17,8 +17,12 @@ const char* const TRACERS[8] = {"qvapor", "qliquid", "qrain", "qice", "qsnow", "
 
 struct Names {
   const char* v[8];
-  int n;
-  Names(std::initializer_list<const char*> l) : n(0) {
+  int n = 0;
+  Names() {}
+  Names(const char* const* names, int count) {
+    for (int i = 0; i < count; ++i) v[n++] = names[i];
+  }
+  Names(std::initializer_list<const char*> l) {
     for (const char* s : l) v[n++] = s;
   }
 };
@@ -124,8 +128,7 @@ int acoustic(Core& c, double timestep, int n_map) {
 int tracer_advection(Core& c) {
   const double cmax_max_all_ranks = 2.0;  // hard-coded in the reference in place of an allreduce (:337-364)
   const int n_split = (int)floor(1.0 + cmax_max_all_ranks);
-  Names q{};
-  for (int n = 0; n < 8; ++n) q.v[q.n++] = TRACERS[n];
+  const Names q(TRACERS, 8);
   RUN(tracer_flux_prep(c, n_split));
   RUN(halo(c, A3, q));
   for (int it = 0; it < n_split; ++it) {
