@@ -23,7 +23,7 @@ constexpr double A1 = 9.0 / 16.0, A2C = -1.0 / 16.0;                   // a2b_or
 constexpr double BIG_NUMBER = 1e30;                                    // d2a2c_vect.py:414
 }  // namespace
 
-int c_sw(Core& c, double dt2) {
+int c_sw_unfused(Core& c, double dt2) {
   const Geo g = c.g;
   cudaStream_t st = c.stream;
   if (c.cfg.grid_type != 0) {

@@ -1,6 +1,8 @@
 // pace_b200 — host-side state of one dycore instance (all subdomains resident on one GPU).
 #pragma once
 #include <map>
+#include <memory>
+#include <tuple>
 #include <string>
 #include <vector>
 
@@ -56,6 +58,9 @@ struct Core {
   void* halo_user = nullptr;
   stage_callback_t stage_cb = nullptr;
   void* stage_user = nullptr;
+  // tensor maps of the tiled kernels (tile.cu), keyed by (field pointer, box width, box height); storage is 64-byte
+  // aligned inside the allocation
+  std::map<std::tuple<const void*, int, int>, std::unique_ptr<unsigned char[]>> tmaps;
   SatCfg sat_store;
   const SatCfg* sat_cfg = nullptr;
 

@@ -3,6 +3,9 @@
 #include <cstdlib>
 #include <cstring>
 #include <cmath>
+#include <algorithm>
+using std::max;
+using std::min;
 #define __device__
 #define __host__
 #define __global__
