@@ -5,7 +5,7 @@
 //
 // Reference: pyFV3/stencils/c_sw.py:21-500 (stencils), :644-807 (__call__ order); d2a2c_vect.py:20-377, :588-699.
 // Every expression tree is the reference's, as in c_sw.cu; the phases and what they need from their neighbours
-// (x / y reach relative to the patch a CTA owns, apron = 3):
+// (x / y reach relative to the patch a CTA owns; 3 cells suffice, the apron along i is 4 for TMA alignment):
 //   A  utmp (reads u at j-1..j+2), vtmp (v at i-1..i+2), ua / va               needed on [-3,2] x [-1,1] (+ transposed)
 //   c1 corner fills utmp <- vtmp, ua <- va (x) and vtmp <- utmp, va <- ua (y)   corner patches only
 //   B  uc, ut (utmp at i-2..i+1) and vc, vt (vtmp at j-2..j+1)                  needed on [-1,1] x [-1,1]
@@ -22,8 +22,15 @@ constexpr double C1 = -2.0 / 14.0, C2 = 11.0 / 14.0, C3 = 5.0 / 14.0;  // d2a2c_
 constexpr double A1 = 9.0 / 16.0, A2C = -1.0 / 16.0;                   // a2b_ord4.py:32-33
 constexpr double BIG_NUMBER = 1e30;                                    // d2a2c_vect.py:414
 
-typedef TileCfg<42, 16, 3, 48, 6> CswCfg;
+#ifndef PACE_HOST_EMU
+typedef TileCfg<40, 16, 4, 3, 48, 11> CswCfg;
+#else
+// the host emulation runs small patches so that the C48 fixture has interior patches (no edge formulas), edge patches
+// and corner patches: every code path of the tiling is then checked against the reference on the CPU
+typedef TileCfg<16, 8, 4, 3, 24, 2> CswCfg;
+#endif
 constexpr int CSW_ARRAYS = 13;
+constexpr int CSW_CTAS_PER_SM = (2 * (CSW_ARRAYS * CswCfg::BYTES + 1152) <= 232448 && 2 * CswCfg::NT <= 2048) ? 2 : 1;
 
 struct CswArgs {
   TileField u, v, delp, pt, w;                                    // loaded
@@ -36,7 +43,8 @@ struct CswArgs {
 };
 
 // All phases of one patch.  S: CSW_ARRAYS tile arrays; the first five hold u, v, delp, pt, w.
-template <class C>
+// EDGES = false: no tile-edge formula can apply inside this patch's box (Tile::near_edge), every edge test folds away.
+template <class C, bool EDGES>
 __device__ __forceinline__ void c_sw_tile(const Tile<C>& T, const CswArgs& a, typename Tile<C>::Arr* S) {
   constexpr int W = C::W, H = C::H;
   auto &Su = S[0], &Sv = S[1], &Sdp = S[2], &Spt = S[3], &Sw = S[4];
@@ -44,51 +52,52 @@ __device__ __forceinline__ void c_sw_tile(const Tile<C>& T, const CswArgs& a, ty
   auto &Ske = S[5], &Svort = S[6];  // utmp / vtmp are dead after phase B
   const Geo& g = T.g;
   const int is = g.is, ie = g.ie, js = g.js, je = g.je;
-  const EdgeInfo& e = T.e;
+  const EdgeInfo e = EDGES ? T.e : EdgeInfo{is, ie, js, je, false, false, false, false};
   const double dt2 = a.dt2;
   const int npt = a.npt, avg_off = (npt == 0) ? -1 : 3;
   const int bi = T.bi, bj = T.bj;
 #define M2(f, i, j) (a.f[T.o2((i), (j))])
   auto owned = [&](int i, int j) { return i >= T.oi0 && i < T.oi1 && j >= T.oj0 && j < T.oj1; };
 
-  // ---- A: utmp, vtmp (set_tmps + lagrange_interpolation_{y,x}_p1 + avg_box, d2a2c_vect.py:28-95, 421-540) -------
-  auto avg_edge = [&](int i, int j) {
-    return (e.S && j < js + avg_off) || (e.N && j > je - avg_off) || (e.W && i < is + avg_off) || (e.E && i > ie - avg_off);
-  };
-  T.each(0, g.nx + 5, 0, g.ny + 5, 0, W - 1, 1, H - 3, [&](int i, int j, int li, int lj) {
-    double ut_ = BIG_NUMBER;
-    const int js1 = e.S ? npt + 2 : js - 1, je1 = e.N ? (je + 1) - npt : je + 1;
-    const int is1 = e.W ? npt + 2 : 0, ie1 = e.E ? (ie + 1) - npt : ie + 3;
-    if (i >= is1 && i <= ie1 && j >= js1 && j <= je1)
-      ut_ = A2C * (Su[lj - 1][li] + Su[lj + 2][li]) + A1 * (Su[lj][li] + Su[lj + 1][li]);
-    if (avg_edge(i, j)) ut_ = 0.5 * (Su[lj][li] + Su[lj + 1][li]);
-    Sutmp[lj][li] = ut_;
-  }, false);
-  T.each(0, g.nx + 5, 0, g.ny + 5, 1, W - 3, 0, H - 1, [&](int i, int j, int li, int lj) {
-    double vt_ = BIG_NUMBER;
-    const int is2 = e.W ? npt + 2 : is - 1, ie2 = e.E ? (ie + 1) - npt : ie + 1;
-    const int js2 = e.S ? npt + 2 : 0, je2 = e.N ? (je + 1) - npt : je + 3;
-    if (i >= is2 && i <= ie2 && j >= js2 && j <= je2)
-      vt_ = A2C * (Sv[lj][li - 1] + Sv[lj][li + 2]) + A1 * (Sv[lj][li] + Sv[lj][li + 1]);
-    if (avg_edge(i, j)) vt_ = 0.5 * (Sv[lj][li] + Sv[lj][li + 1]);
-    Svtmp[lj][li] = vt_;
-  });
-  // contravariant_components on compute(-2,-2)+(4,4)
-  T.each(is - 2, ie + 2, js - 2, je + 2, 1, W - 3, 1, H - 3, [&](int i, int j, int li, int lj) {
-    const double ut_ = Sutmp[lj][li], vt_ = Svtmp[lj][li];
-    const double cs = M2(cosa_s, i, j), rs = M2(rsin2, i, j);
-    const double uav = (ut_ - vt_ * cs) * rs, vav = (vt_ - ut_ * cs) * rs;
-    Sua[lj][li] = uav;
-    Sva[lj][li] = vav;
-    if (owned(i, j)) {
-      a.ua[T.o3(i, j)] = uav;
-      a.va[T.o3(i, j)] = vav;
+  // ---- A: utmp, vtmp (set_tmps + lagrange_interpolation_{y,x}_p1 + avg_box, d2a2c_vect.py:28-95, 421-540) and
+  //      ua, va (contravariant_components) in one pass over the box: utmp needs u at lj-1..lj+2, vtmp v at li-1..li+2
+  T.each(0, g.nx + 5, 0, g.ny + 5, 0, W - 1, 0, H - 1, [&](int i, int j, int li, int lj) {
+    const bool edge = (e.S && j < js + avg_off) || (e.N && j > je - avg_off) || (e.W && i < is + avg_off) ||
+                      (e.E && i > ie - avg_off);
+    const bool has_u = lj >= 1 && lj <= H - 3, has_v = li >= 1 && li <= W - 3;
+    double ut_ = BIG_NUMBER, vt_ = BIG_NUMBER;
+    if (has_u) {
+      const int js1 = e.S ? npt + 2 : js - 1, je1 = e.N ? (je + 1) - npt : je + 1;
+      const int is1 = e.W ? npt + 2 : 0, ie1 = e.E ? (ie + 1) - npt : ie + 3;
+      if (i >= is1 && i <= ie1 && j >= js1 && j <= je1)
+        ut_ = A2C * (Su[lj - 1][li] + Su[lj + 2][li]) + A1 * (Su[lj][li] + Su[lj + 1][li]);
+      if (edge) ut_ = 0.5 * (Su[lj][li] + Su[lj + 1][li]);
+      Sutmp[lj][li] = ut_;
+    }
+    if (has_v) {
+      const int is2 = e.W ? npt + 2 : is - 1, ie2 = e.E ? (ie + 1) - npt : ie + 1;
+      const int js2 = e.S ? npt + 2 : 0, je2 = e.N ? (je + 1) - npt : je + 3;
+      if (i >= is2 && i <= ie2 && j >= js2 && j <= je2)
+        vt_ = A2C * (Sv[lj][li - 1] + Sv[lj][li + 2]) + A1 * (Sv[lj][li] + Sv[lj][li + 1]);
+      if (edge) vt_ = 0.5 * (Sv[lj][li] + Sv[lj][li + 1]);
+      Svtmp[lj][li] = vt_;
+    }
+    // contravariant_components on compute(-2,-2)+(4,4)
+    if (has_u && has_v && i >= is - 2 && i <= ie + 2 && j >= js - 2 && j <= je + 2) {
+      const double cs = M2(cosa_s, i, j), rs = M2(rsin2, i, j);
+      const double uav = (ut_ - vt_ * cs) * rs, vav = (vt_ - ut_ * cs) * rs;
+      Sua[lj][li] = uav;
+      Sva[lj][li] = vav;
+      if (owned(i, j)) {
+        a.ua[T.o3(i, j)] = uav;
+        a.va[T.o3(i, j)] = vav;
+      }
     }
   });
 
   // ---- c1: fill_corners_x (utmp <- vtmp 3 cells, ua <- va 2 cells), fill_corners_y (vtmp <- utmp, va <- ua);
   //      multipliers sw -1, se 1, nw 1, ne -1 (corners.py:129-304, vector fills)
-  if (T.corner_tile) {
+  if (EDGES && T.corner_tile) {
     auto fill = [&](int id) {
       const int io = id / 12, c = (id % 12) / 3, n = id % 3 + 1;
       const int ncells = (io & 1) ? 2 : 3;
@@ -132,63 +141,64 @@ __device__ __forceinline__ void c_sw_tile(const Tile<C>& T, const CswArgs& a, ty
 #endif
   }
 
-  // ---- B: uc, ut on [is-1, ie+2] x [js-1, je+1]; vc, vt on [is-1, ie+1] x [js-1, je+2] --------------------------
-  T.each(is - 1, ie + 2, js - 1, je + 1, 2, W - 2, 1, H - 3, [&](int i, int j, int li, int lj) {
-    double ucv, utv;
-    auto contra = [&](double ucx) { return (ucx - Sv[lj][li] * M2(cosa_u, i, j)) * M2(rsin_u, i, j); };
-    if ((e.W && i == is - 1) || (e.E && i == ie)) {
-      ucv = C1 * Sutmp[lj][li - 2] + C2 * Sutmp[lj][li - 1] + C3 * Sutmp[lj][li];
-      utv = contra(ucv);
-    } else if ((e.W && i == is) || (e.E && i == ie + 1)) {  // edge_interpolate4_x (d2a2c_vect.py:360-366)
-      const double t1 = M2(dxa, i - 2, j) + M2(dxa, i - 1, j);
-      const double t2 = M2(dxa, i, j) + M2(dxa, i + 1, j);
-      const double n1 = (t1 + M2(dxa, i - 1, j)) * Sua[lj][li - 1] - M2(dxa, i - 1, j) * Sua[lj][li - 2];
-      const double n2 = (t1 + M2(dxa, i, j)) * Sua[lj][li] - M2(dxa, i, j) * Sua[lj][li + 1];
-      utv = 0.5 * (n1 / t1 + n2 / t2);
-      ucv = utv > 0 ? utv * M2(sin_sg3, i - 1, j) : utv * M2(sin_sg1, i, j);
-    } else if ((e.W && i == is + 1) || (e.E && i == ie + 2)) {
-      ucv = C1 * Sutmp[lj][li + 1] + C2 * Sutmp[lj][li] + C3 * Sutmp[lj][li - 1];
-      utv = contra(ucv);
-    } else {  // ut_main
-      ucv = A2C * (Sutmp[lj][li - 2] + Sutmp[lj][li + 1]) + A1 * (Sutmp[lj][li - 1] + Sutmp[lj][li]);
-      utv = contra(ucv);
+  // ---- B: uc, ut on [is-1, ie+2] x [js-1, je+1]; vc, vt on [is-1, ie+1] x [js-1, je+2];
+  //      C: divergence_corner (c_sw.py:33-175) on the corner (interface x interface) compute domain, own cells.
+  //      One pass: all three read only what phase A left.
+  const bool do_div = a.nord > 0;
+  T.each(is - 1, ie + 2, js - 1, je + 2, 1, W - 2, 1, H - 2, [&](int i, int j, int li, int lj) {
+    if (li >= 2 && lj <= H - 3 && j <= je + 1) {
+      double ucv, utv;
+      auto contra = [&](double ucx) { return (ucx - Sv[lj][li] * M2(cosa_u, i, j)) * M2(rsin_u, i, j); };
+      if ((e.W && i == is - 1) || (e.E && i == ie)) {
+        ucv = C1 * Sutmp[lj][li - 2] + C2 * Sutmp[lj][li - 1] + C3 * Sutmp[lj][li];
+        utv = contra(ucv);
+      } else if ((e.W && i == is) || (e.E && i == ie + 1)) {  // edge_interpolate4_x (d2a2c_vect.py:360-366)
+        const double t1 = M2(dxa, i - 2, j) + M2(dxa, i - 1, j);
+        const double t2 = M2(dxa, i, j) + M2(dxa, i + 1, j);
+        const double n1 = (t1 + M2(dxa, i - 1, j)) * Sua[lj][li - 1] - M2(dxa, i - 1, j) * Sua[lj][li - 2];
+        const double n2 = (t1 + M2(dxa, i, j)) * Sua[lj][li] - M2(dxa, i, j) * Sua[lj][li + 1];
+        utv = 0.5 * (n1 / t1 + n2 / t2);
+        ucv = utv > 0 ? utv * M2(sin_sg3, i - 1, j) : utv * M2(sin_sg1, i, j);
+      } else if ((e.W && i == is + 1) || (e.E && i == ie + 2)) {
+        ucv = C1 * Sutmp[lj][li + 1] + C2 * Sutmp[lj][li] + C3 * Sutmp[lj][li - 1];
+        utv = contra(ucv);
+      } else {  // ut_main
+        ucv = A2C * (Sutmp[lj][li - 2] + Sutmp[lj][li + 1]) + A1 * (Sutmp[lj][li - 1] + Sutmp[lj][li]);
+        utv = contra(ucv);
+      }
+      Suc[lj][li] = ucv;
+      // geoadjust_ut (c_sw.py:178-200)
+      const double utf = utv > 0 ? dt2 * utv * M2(dy, i, j) * M2(sin_sg3, i - 1, j) : dt2 * utv * M2(dy, i, j) * M2(sin_sg1, i, j);
+      Sut[lj][li] = utf;
+      if (owned(i, j)) a.ut[T.o3(i, j)] = utf;
     }
-    Suc[lj][li] = ucv;
-    // geoadjust_ut (c_sw.py:178-200)
-    const double utf = utv > 0 ? dt2 * utv * M2(dy, i, j) * M2(sin_sg3, i - 1, j) : dt2 * utv * M2(dy, i, j) * M2(sin_sg1, i, j);
-    Sut[lj][li] = utf;
-    if (owned(i, j)) a.ut[T.o3(i, j)] = utf;
-  }, false);
-  T.each(is - 1, ie + 1, js - 1, je + 2, 1, W - 3, 2, H - 2, [&](int i, int j, int li, int lj) {
-    double vcv, vtv;
-    auto contra = [&](double vcx) { return (vcx - Su[lj][li] * M2(cosa_v, i, j)) * M2(rsin_v, i, j); };
-    if ((e.S && j == js - 1) || (e.N && j == je)) {
-      vcv = C1 * Svtmp[lj - 2][li] + C2 * Svtmp[lj - 1][li] + C3 * Svtmp[lj][li];
-      vtv = contra(vcv);
-    } else if ((e.S && j == js) || (e.N && j == je + 1)) {  // edge_interpolate4_y
-      const double t1 = M2(dya, i, j - 2) + M2(dya, i, j - 1);
-      const double t2 = M2(dya, i, j) + M2(dya, i, j + 1);
-      const double n1 = (t1 + M2(dya, i, j - 1)) * Sva[lj - 1][li] - M2(dya, i, j - 1) * Sva[lj - 2][li];
-      const double n2 = (t1 + M2(dya, i, j)) * Sva[lj][li] - M2(dya, i, j) * Sva[lj + 1][li];
-      vtv = 0.5 * (n1 / t1 + n2 / t2);
-      vcv = vtv > 0 ? vtv * M2(sin_sg4, i, j - 1) : vtv * M2(sin_sg2, i, j);
-    } else if ((e.S && j == js + 1) || (e.N && j == je + 2)) {
-      vcv = C1 * Svtmp[lj + 1][li] + C2 * Svtmp[lj][li] + C3 * Svtmp[lj - 1][li];
-      vtv = contra(vcv);
-    } else {  // vt_main / first region of north_south_edges
-      vcv = A2C * (Svtmp[lj - 2][li] + Svtmp[lj + 1][li]) + A1 * (Svtmp[lj - 1][li] + Svtmp[lj][li]);
-      vtv = contra(vcv);
+    if (lj >= 2 && li <= W - 3 && i <= ie + 1) {
+      double vcv, vtv;
+      auto contra = [&](double vcx) { return (vcx - Su[lj][li] * M2(cosa_v, i, j)) * M2(rsin_v, i, j); };
+      if ((e.S && j == js - 1) || (e.N && j == je)) {
+        vcv = C1 * Svtmp[lj - 2][li] + C2 * Svtmp[lj - 1][li] + C3 * Svtmp[lj][li];
+        vtv = contra(vcv);
+      } else if ((e.S && j == js) || (e.N && j == je + 1)) {  // edge_interpolate4_y
+        const double t1 = M2(dya, i, j - 2) + M2(dya, i, j - 1);
+        const double t2 = M2(dya, i, j) + M2(dya, i, j + 1);
+        const double n1 = (t1 + M2(dya, i, j - 1)) * Sva[lj - 1][li] - M2(dya, i, j - 1) * Sva[lj - 2][li];
+        const double n2 = (t1 + M2(dya, i, j)) * Sva[lj][li] - M2(dya, i, j) * Sva[lj + 1][li];
+        vtv = 0.5 * (n1 / t1 + n2 / t2);
+        vcv = vtv > 0 ? vtv * M2(sin_sg4, i, j - 1) : vtv * M2(sin_sg2, i, j);
+      } else if ((e.S && j == js + 1) || (e.N && j == je + 2)) {
+        vcv = C1 * Svtmp[lj + 1][li] + C2 * Svtmp[lj][li] + C3 * Svtmp[lj - 1][li];
+        vtv = contra(vcv);
+      } else {  // vt_main / first region of north_south_edges
+        vcv = A2C * (Svtmp[lj - 2][li] + Svtmp[lj + 1][li]) + A1 * (Svtmp[lj - 1][li] + Svtmp[lj][li]);
+        vtv = contra(vcv);
+      }
+      Svc[lj][li] = vcv;
+      // geoadjust_vt (c_sw.py:203-222)
+      const double vtf = vtv > 0 ? dt2 * vtv * M2(dx, i, j) * M2(sin_sg4, i, j - 1) : dt2 * vtv * M2(dx, i, j) * M2(sin_sg2, i, j);
+      Svt[lj][li] = vtf;
+      if (owned(i, j)) a.vt[T.o3(i, j)] = vtf;
     }
-    Svc[lj][li] = vcv;
-    // geoadjust_vt (c_sw.py:203-222)
-    const double vtf = vtv > 0 ? dt2 * vtv * M2(dx, i, j) * M2(sin_sg4, i, j - 1) : dt2 * vtv * M2(dx, i, j) * M2(sin_sg2, i, j);
-    Svt[lj][li] = vtf;
-    if (owned(i, j)) a.vt[T.o3(i, j)] = vtf;
-  });
-
-  // ---- C: divergence_corner (c_sw.py:33-175) on the corner (interface x interface) compute domain, own cells ----
-  if (a.nord > 0) {
-    T.each_owned(is, ie + 1, js, je + 1, [&](int i, int j, int li, int lj) {
+    if (do_div && owned(i, j) && i >= is && j >= js && i <= ie + 1 && j <= je + 1) {
       auto uf_gen = [&](int di, int dj) {
         return (Su[lj + dj][li + di] - 0.25 * (Sva[lj + dj - 1][li + di] + Sva[lj + dj][li + di]) *
                                            (M2(cos_sg4, i + di, j + dj - 1) + M2(cos_sg2, i + di, j + dj))) *
@@ -222,14 +232,14 @@ __device__ __forceinline__ void c_sw_tile(const Tile<C>& T, const CswArgs& a, ty
         d = (vf_gen(0, -1) - vf_gen(0, 0) + uf_gen(-1, 0) - uf_gen(0, 0)) * M2(rarea_c, i, j);
       }
       a.divgd[T.o3(i, j)] = d;
-    }, false);
-  }
+    }
+  });
 
   // ---- E: transportdelp_update_vorticity_and_kineticenergy (c_sw.py:287-391) on compute + 1 halo.  delp / pt / w are
   // read "as filled" by fill_corners_2cells_x for the x fluxes and by fill_corners_2cells_y for the y fluxes and the
   // cell's own value (the reference fills in place, x first: c_sw.py:700-760); ke is kept for the patch and one row /
   // column below it, delpc / ptc / omga are stored for own cells; zero_delpc_ptc covers the rest of compute + 3 halo.
-  const bool ct = T.corner_tile;
+  const bool ct = EDGES && T.corner_tile;
   auto rdx = [&](double(*Sq)[W], int i, int j) {  // q(i, j) after fill_corners_2cells_x
     if (ct) xfill_src(e, 2, i, j);
     return Sq[j - bj][i - bi];
@@ -242,69 +252,67 @@ __device__ __forceinline__ void c_sw_tile(const Tile<C>& T, const CswArgs& a, ty
     }
     return Sq[j - bj][i - bi];
   };
-  T.each(is - 1, ie + 1, js - 1, je + 1, 2, W - 4, 2, H - 4, [&](int i, int j, int li, int lj) {
-    if (owned(i, j)) {
-      double fx1_[2], fx_[2], fx2_[2], fy1_[2], fy_[2], fy2_[2];
-      for (int d = 0; d < 2; ++d) {
-        // compute_nonhydrostatic_fluxes_x (c_sw.py:252-284) at i + d
-        const double utc = Sut[lj][li + d];
-        double f1 = utc > 0.0 ? rdx(Sdp, i + d - 1, j) : rdx(Sdp, i + d, j);
-        const double f = utc > 0.0 ? rdx(Spt, i + d - 1, j) : rdx(Spt, i + d, j);
-        const double f2 = utc > 0.0 ? rdx(Sw, i + d - 1, j) : rdx(Sw, i + d, j);
-        f1 = utc * f1;
-        fx1_[d] = f1;
-        fx_[d] = f1 * f;
-        fx2_[d] = f1 * f2;
+  // One pass with F (circulation_cgrid + absolute_vorticity, c_sw.py:394-436, on corners): both read phase B's uc, vc.
+  T.each(0, g.nx + 5, 0, g.ny + 5, 2, W - 3, 2, H - 3, [&](int i, int j, int li, int lj) {
+    const bool in_e = i >= is - 1 && i <= ie + 1 && j >= js - 1 && j <= je + 1;
+    if (in_e && li <= W - 4 && lj <= H - 4) {
+      if (owned(i, j)) {
+        double fx1_[2], fx_[2], fx2_[2], fy1_[2], fy_[2], fy2_[2];
+        for (int d = 0; d < 2; ++d) {
+          // compute_nonhydrostatic_fluxes_x (c_sw.py:252-284) at i + d
+          const double utc = Sut[lj][li + d];
+          double f1 = utc > 0.0 ? rdx(Sdp, i + d - 1, j) : rdx(Sdp, i + d, j);
+          const double f = utc > 0.0 ? rdx(Spt, i + d - 1, j) : rdx(Spt, i + d, j);
+          const double f2 = utc > 0.0 ? rdx(Sw, i + d - 1, j) : rdx(Sw, i + d, j);
+          f1 = utc * f1;
+          fx1_[d] = f1;
+          fx_[d] = f1 * f;
+          fx2_[d] = f1 * f2;
+        }
+        for (int d = 0; d < 2; ++d) {
+          const double vtc = Svt[lj + d][li];
+          double f1 = vtc > 0.0 ? rdy(Sdp, i, j + d - 1) : rdy(Sdp, i, j + d);
+          const double f = vtc > 0.0 ? rdy(Spt, i, j + d - 1) : rdy(Spt, i, j + d);
+          const double f2 = vtc > 0.0 ? rdy(Sw, i, j + d - 1) : rdy(Sw, i, j + d);
+          f1 = vtc * f1;
+          fy1_[d] = f1;
+          fy_[d] = f1 * f;
+          fy2_[d] = f1 * f2;
+        }
+        const double delp0 = rdy(Sdp, i, j), pt0 = rdy(Spt, i, j), w0 = rdy(Sw, i, j), ra = M2(rarea, i, j);
+        const double dpc = delp0 + (fx1_[0] - fx1_[1] + fy1_[0] - fy1_[1]) * ra;
+        const long long o = T.o3(i, j);
+        a.delpc[o] = dpc;
+        a.ptc[o] = (pt0 * delp0 + (fx_[0] - fx_[1] + fy_[0] - fy_[1]) * ra) / dpc;
+        a.omga[o] = (w0 * delp0 + (fx2_[0] - fx2_[1] + fy2_[0] - fy2_[1]) * ra) / dpc;
       }
-      for (int d = 0; d < 2; ++d) {
-        const double vtc = Svt[lj + d][li];
-        double f1 = vtc > 0.0 ? rdy(Sdp, i, j + d - 1) : rdy(Sdp, i, j + d);
-        const double f = vtc > 0.0 ? rdy(Spt, i, j + d - 1) : rdy(Spt, i, j + d);
-        const double f2 = vtc > 0.0 ? rdy(Sw, i, j + d - 1) : rdy(Sw, i, j + d);
-        f1 = vtc * f1;
-        fy1_[d] = f1;
-        fy_[d] = f1 * f;
-        fy2_[d] = f1 * f2;
-      }
-      const double delp0 = rdy(Sdp, i, j), pt0 = rdy(Spt, i, j), w0 = rdy(Sw, i, j), ra = M2(rarea, i, j);
-      const double dpc = delp0 + (fx1_[0] - fx1_[1] + fy1_[0] - fy1_[1]) * ra;
-      const long long o = T.o3(i, j);
-      a.delpc[o] = dpc;
-      a.ptc[o] = (pt0 * delp0 + (fx_[0] - fx_[1] + fy_[0] - fy_[1]) * ra) / dpc;
-      a.omga[o] = (w0 * delp0 + (fx2_[0] - fx2_[1] + fy2_[0] - fy2_[1]) * ra) / dpc;
-    }
-    // vorticity / kinetic energy with upstream bias
-    const double uav = Sua[lj][li], vav = Sva[lj][li];
-    double kev = uav > 0.0 ? Suc[lj][li] : Suc[lj][li + 1];
-    double vo = vav > 0.0 ? Svc[lj][li] : Svc[lj + 1][li];
-    if ((e.S && j == js - 1) || (e.N && j == je))
-      vo = (vav <= 0.0) ? vo * M2(sin_sg4, i, j) + Su[lj + 1][li] * M2(cos_sg4, i, j) : vo;
-    if ((e.S && j == js) || (e.N && j == je + 1))
-      vo = (vav > 0.0) ? vo * M2(sin_sg2, i, j) + Su[lj][li] * M2(cos_sg2, i, j) : vo;
-    if ((e.E && i == ie) || (e.W && i == is - 1))
-      kev = (uav <= 0.0) ? kev * M2(sin_sg3, i, j) + Sv[lj][li + 1] * M2(cos_sg3, i, j) : kev;
-    if ((e.E && i == ie + 1) || (e.W && i == is))
-      kev = (uav > 0.0) ? kev * M2(sin_sg1, i, j) + Sv[lj][li] * M2(cos_sg1, i, j) : kev;
-    Ske[lj][li] = 0.5 * dt2 * (uav * kev + vav * vo);
-  }, false);
-  // zero_delpc_ptc (c_sw.py:21-30) where the stencil above does not write
-  T.each_owned(0, g.nx + 5, 0, g.ny + 5, [&](int i, int j, int, int) {
-    if (i < is - 1 || i > ie + 1 || j < js - 1 || j > je + 1) {
+      // vorticity / kinetic energy with upstream bias
+      const double uav = Sua[lj][li], vav = Sva[lj][li];
+      double kev = uav > 0.0 ? Suc[lj][li] : Suc[lj][li + 1];
+      double vo = vav > 0.0 ? Svc[lj][li] : Svc[lj + 1][li];
+      if ((e.S && j == js - 1) || (e.N && j == je))
+        vo = (vav <= 0.0) ? vo * M2(sin_sg4, i, j) + Su[lj + 1][li] * M2(cos_sg4, i, j) : vo;
+      if ((e.S && j == js) || (e.N && j == je + 1))
+        vo = (vav > 0.0) ? vo * M2(sin_sg2, i, j) + Su[lj][li] * M2(cos_sg2, i, j) : vo;
+      if ((e.E && i == ie) || (e.W && i == is - 1))
+        kev = (uav <= 0.0) ? kev * M2(sin_sg3, i, j) + Sv[lj][li + 1] * M2(cos_sg3, i, j) : kev;
+      if ((e.E && i == ie + 1) || (e.W && i == is))
+        kev = (uav > 0.0) ? kev * M2(sin_sg1, i, j) + Sv[lj][li] * M2(cos_sg1, i, j) : kev;
+      Ske[lj][li] = 0.5 * dt2 * (uav * kev + vav * vo);
+    } else if (!in_e && owned(i, j)) {  // zero_delpc_ptc (c_sw.py:21-30) where the stencil above does not write
       a.delpc[T.o3(i, j)] = 0.0;
       a.ptc[T.o3(i, j)] = 0.0;
     }
-  });
-
-  // ---- F: circulation_cgrid + absolute_vorticity (c_sw.py:394-436) on corners ------------------------------------
-  T.each(is, ie + 1, js, je + 1, 3, W - 3, 3, H - 3, [&](int i, int j, int li, int lj) {
-    const double fxv = M2(dxc, i, j) * Suc[lj][li];
-    const double fyv = M2(dyc, i, j) * Svc[lj][li];
-    const double fx1v = M2(dxc, i, j - 1) * Suc[lj - 1][li];
-    const double fy1v = M2(dyc, i - 1, j) * Svc[lj][li - 1];
-    double vc_ = fx1v - fxv - fy1v + fyv;
-    if (e.W && i == is && ((e.S && j == js) || (e.N && j == je + 1))) vc_ = fx1v - fxv + fyv;
-    if (e.E && i == ie + 1 && ((e.S && j == js) || (e.N && j == je + 1))) vc_ = fx1v - fxv - fy1v;
-    Svort[lj][li] = M2(fC, i, j) + M2(rarea_c, i, j) * vc_;
+    if (li >= 3 && lj >= 3 && i >= is && i <= ie + 1 && j >= js && j <= je + 1) {
+      const double fxv = M2(dxc, i, j) * Suc[lj][li];
+      const double fyv = M2(dyc, i, j) * Svc[lj][li];
+      const double fx1v = M2(dxc, i, j - 1) * Suc[lj - 1][li];
+      const double fy1v = M2(dyc, i - 1, j) * Svc[lj][li - 1];
+      double vc_ = fx1v - fxv - fy1v + fyv;
+      if (e.W && i == is && ((e.S && j == js) || (e.N && j == je + 1))) vc_ = fx1v - fxv + fyv;
+      if (e.E && i == ie + 1 && ((e.S && j == js) || (e.N && j == je + 1))) vc_ = fx1v - fxv - fy1v;
+      Svort[lj][li] = M2(fC, i, j) + M2(rarea_c, i, j) * vc_;
+    }
   });
 
   // ---- G: update_y_velocity on [X, Y_INTERFACE], update_x_velocity on [X_INTERFACE, Y]; own cells ----------------
@@ -334,7 +342,7 @@ __device__ __forceinline__ void c_sw_tile(const Tile<C>& T, const CswArgs& a, ty
 }
 
 #ifndef PACE_HOST_EMU
-__global__ void __launch_bounds__(CswCfg::NT, 2) k_c_sw_fused(Geo g, CswArgs a, const __grid_constant__ CUtensorMap m_u,
+__global__ void __launch_bounds__(CswCfg::NT, CSW_CTAS_PER_SM) k_c_sw_fused(Geo g, CswArgs a, const __grid_constant__ CUtensorMap m_u,
                                                               const __grid_constant__ CUtensorMap m_v,
                                                               const __grid_constant__ CUtensorMap m_dp,
                                                               const __grid_constant__ CUtensorMap m_pt,
@@ -358,7 +366,8 @@ __global__ void __launch_bounds__(CswCfg::NT, 2) k_c_sw_fused(Geo g, CswArgs a, 
     tma::load_tile(&S[4], &m_w, &bar, T.bi, T.bj, k, t);
   }
   tma::mbar_wait(&bar, 0);
-  c_sw_tile<C>(T, a, S);
+  if (T.near_edge) c_sw_tile<C, true>(T, a, S);
+  else c_sw_tile<C, false>(T, a, S);
 }
 #endif
 
@@ -418,7 +427,8 @@ int c_sw(Core& c, double dt2) {
           host_load_tile<C>(T, S[2], a.delp.p);
           host_load_tile<C>(T, S[3], a.pt.p);
           host_load_tile<C>(T, S[4], a.w.p);
-          c_sw_tile<C>(T, a, S);
+          if (T.near_edge) c_sw_tile<C, true>(T, a, S);
+          else c_sw_tile<C, false>(T, a, S);
         }
 #endif
   // the reference leaves delp, pt, w with their corner cells filled (x fill, then y fill)

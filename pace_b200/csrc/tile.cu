@@ -31,7 +31,7 @@ std::set<std::pair<const void*, int>> g_attr_done;  // (kernel, device)
 const CUtensorMap* tile_tensor_map(Core& c, const double* field, int box_w, int box_h) {
   const auto key = std::make_tuple((const void*)field, box_w, box_h);
   auto it = c.tmaps.find(key);
-  if (it != c.tmaps.end()) return (const CUtensorMap*)it->second.get();
+  if (it != c.tmaps.end()) return (const CUtensorMap*)(((uintptr_t)it->second.get() + 63) & ~(uintptr_t)63);
   encode_fn_t enc = encoder();
   if (!enc) {
     c.err = "cuTensorMapEncodeTiled is not available from this driver";

@@ -1,5 +1,5 @@
 // Tiled phase kernels: one CTA owns a TXM x TYM patch of one level of one subdomain, stages the fields it reads —
-// patch plus an AP-cell apron — in shared memory with TMA (cp.async.bulk.tensor, one elected thread, an mbarrier counts
+// patch plus an apron of APX / APY cells — in shared memory with TMA (cp.async.bulk.tensor, one elected thread, an mbarrier counts
 // the bytes), runs a chain of stencil phases on the shared-memory tiles with a CTA barrier between phases, and writes
 // only final results to HBM.  This is how a halo-delimited phase of the acoustic substep (c_sw: 23 reference stencils)
 // becomes one kernel whose DRAM traffic is its inputs (x apron overlap) plus its outputs.
@@ -21,10 +21,14 @@
 
 namespace pace {
 
-template <int TXM_, int TYM_, int AP_, int NTX_, int NTY_>
+// APX must be even and the patch width is kept even: a TMA box has to start on a 16-byte boundary along i (an odd fp64
+// start coordinate raises an illegal-instruction fault; measured with tools/probe/tma_probe.cu), so the apron along i
+// is 4 cells where the stencils need 3.
+template <int TXM_, int TYM_, int APX_, int APY_, int NTX_, int NTY_>
 struct TileCfg {
-  static constexpr int TXM = TXM_, TYM = TYM_, AP = AP_, NTX = NTX_, NTY = NTY_;
-  static constexpr int W = TXM + 2 * AP, H = TYM + 2 * AP;
+  static constexpr int TXM = TXM_, TYM = TYM_, APX = APX_, APY = APY_, NTX = NTX_, NTY = NTY_;
+  static constexpr int W = TXM + 2 * APX, H = TYM + 2 * APY;
+  static_assert(APX % 2 == 0 && TXM % 2 == 0, "TMA: box start coordinates along i must be even");
   static constexpr int NT = NTX * NTY;
   static constexpr int BYTES = W * H * 8;
   static_assert(W % 2 == 0, "TMA: the inner box extent must be a multiple of 16 bytes");
@@ -85,10 +89,11 @@ struct Tile {
   typedef double Arr[C::H][C::W];
   Geo g;
   int t, k;
-  int bi, bj;              // global index of tile-local (0, 0)  (= first owned cell - AP)
+  int bi, bj;              // global index of tile-local (0, 0)  (= first owned cell - apron)
   int oi0, oi1, oj0, oj1;  // owned cells [oi0, oi1) x [oj0, oj1)
   EdgeInfo e;
   bool corner_tile;        // the tile's box holds cube-corner halo cells (corner fills apply)
+  bool near_edge;          // some cell of the box lies within 4 cells of a cube-tile edge (edge formulas may apply)
   long long base3;         // offset of (t, k, 0, 0) in 3-D fields
   int base2;               // offset of (t, 0, 0) in 2-D fields
 #ifndef PACE_HOST_EMU
@@ -132,7 +137,7 @@ inline TileGrid tile_grid(const Geo& g) {
   const int ni = g.nx + 2 * HALO + 1, nj = g.ny + 2 * HALO + 1;
   tg.ntx = (ni + C::TXM - 1) / C::TXM;
   tg.nty = (nj + C::TYM - 1) / C::TYM;
-  tg.tw = (ni + tg.ntx - 1) / tg.ntx;
+  tg.tw = ((ni + tg.ntx - 1) / tg.ntx + 1) & ~1;  // even: every patch starts at an even i
   tg.th = (nj + tg.nty - 1) / tg.nty;
   return tg;
 }
@@ -144,12 +149,14 @@ __device__ __forceinline__ Tile<C> make_tile(const Geo& g, const TileGrid& tg, i
   const int ni = g.nx + 2 * HALO + 1, nj = g.ny + 2 * HALO + 1;
   T.oi0 = bx * tg.tw; T.oi1 = min(T.oi0 + tg.tw, ni);
   T.oj0 = by * tg.th; T.oj1 = min(T.oj0 + tg.th, nj);
-  T.bi = T.oi0 - C::AP; T.bj = T.oj0 - C::AP;
+  T.bi = T.oi0 - C::APX; T.bj = T.oj0 - C::APY;
   const unsigned ed = edge_of(g, t);
   T.e = EdgeInfo{g.is, g.ie, g.js, g.je, (bool)(ed & EDGE_W), (bool)(ed & EDGE_E), (bool)(ed & EDGE_S), (bool)(ed & EDGE_N)};
   const bool nw = T.e.W && T.bi < g.is, ne = T.e.E && T.bi + C::W - 1 > g.ie;
   const bool ns = T.e.S && T.bj < g.js, nn = T.e.N && T.bj + C::H - 1 > g.je;
   T.corner_tile = (nw || ne) && (ns || nn);
+  T.near_edge = (T.e.W && T.bi <= g.is + 4) || (T.e.E && T.bi + C::W - 1 >= g.ie - 4) ||
+                (T.e.S && T.bj <= g.js + 4) || (T.e.N && T.bj + C::H - 1 >= g.je - 4);
   T.base3 = (long long)t * g.st3 + (long long)k * g.sk;
   T.base2 = t * g.sk;
   return T;

@@ -30,7 +30,7 @@ def test_fused_matches_three_kernel_version(tmp_path):
     res = {}
     modes = {"march": {"PACE_B200_FVTP2D": "march"},
              "march_chunks": {"PACE_B200_FVTP2D": "march", "PACE_B200_FVTP2D_ROWS": "16"},
-             "tile": {"PACE_B200_FVTP2D": "tile"}, "unfused": {"PACE_B200_FVTP2D": "unfused", "PACE_B200_DELNFLUX": "unfused", "PACE_B200_RIEM": "global", "PACE_B200_A2B": "unfused"}}
+             "tile": {"PACE_B200_FVTP2D": "tile"}, "unfused": {"PACE_B200_FVTP2D": "unfused", "PACE_B200_DELNFLUX": "unfused", "PACE_B200_RIEM": "global", "PACE_B200_A2B": "unfused", "PACE_B200_CSW": "unfused"}}
     for mode, extra in modes.items():
         env = dict(os.environ, **extra)
         path = str(tmp_path / (mode + ".npz"))
@@ -51,7 +51,7 @@ def test_production_kernels_match_unfused_at_c96(tmp_path):
     narrower), several row chunks, 3 x 3 DelnFlux / a2b tiles."""
     res = {}
     for mode, extra in {"production": {}, "unfused": {"PACE_B200_FVTP2D": "unfused", "PACE_B200_DELNFLUX": "unfused",
-                                                      "PACE_B200_RIEM": "global", "PACE_B200_A2B": "unfused"}}.items():
+                                                      "PACE_B200_RIEM": "global", "PACE_B200_A2B": "unfused", "PACE_B200_CSW": "unfused"}}.items():
         env = dict(os.environ, **extra)
         path = str(tmp_path / (mode + ".npz"))
         subprocess.run([sys.executable, "-c", SCRIPT % ROOT, path, "96"], check=True, env=env, timeout=900)
@@ -106,7 +106,7 @@ def test_zero_shortcuts_match_dense_on_patchy_tracers(tmp_path):
     modes = {"production": {},
              "dense": {"PACE_B200_ZERO_PATHS": "0"},
              "dense_unfused": {"PACE_B200_ZERO_PATHS": "0", "PACE_B200_FVTP2D": "unfused", "PACE_B200_DELNFLUX": "unfused",
-                               "PACE_B200_RIEM": "global", "PACE_B200_A2B": "unfused"}}
+                               "PACE_B200_RIEM": "global", "PACE_B200_A2B": "unfused", "PACE_B200_CSW": "unfused"}}
     for mode, extra in modes.items():
         env = dict(os.environ, **extra)
         path = str(tmp_path / (mode + ".npz"))
