@@ -28,6 +28,7 @@ struct DelnFusedArgs {
   double *fx, *fy, *d2out;
   const int* lvl;
   int nk, accumulate;
+  int corner_only;  // 1: only the tiles that see cube-corner cells on levels with nord > 0 run (the rest: k_delnflux_march)
 };
 
 constexpr int RG = 6, RPG = (H + RG - 1) / RG;  // fast path: thread = (column, row group), RPG rows per group
@@ -150,6 +151,10 @@ __global__ void __launch_bounds__(TX * NTY, 6) k_delnflux_fused(Geo g, DelnFused
   const unsigned ed = edge_of(g, t);
   const EdgeInfo e{is, ie, js, je, (bool)(ed & EDGE_W), (bool)(ed & EDGE_E), (bool)(ed & EDGE_S), (bool)(ed & EDGE_N)};
   const int N = (int)a.nord_col[k < 3 ? k : 3];
+  // do cube-corner cells (both a west/east and a south/north tile edge within the apron) enter this tile?
+  const bool near_w = e.W && i0 - AP < is, near_e = e.E && i0 + TX + AP - 1 > ie;
+  const bool near_s = e.S && j0 - AP < js, near_n = e.N && j0 + TY + AP - 1 > je;
+  if (a.corner_only && !(N > 0 && (near_w || near_e) && (near_s || near_n))) return;
   const bool has_mass = a.mass != nullptr;
   const long long base3 = (long long)t * g.st3 + (long long)k * g.sk;
   const int base2 = t * g.sk;
@@ -191,9 +196,6 @@ __global__ void __launch_bounds__(TX * NTY, 6) k_delnflux_fused(Geo g, DelnFused
     }
   }
 
-  // do cube-corner cells (both a west/east and a south/north tile edge within the apron) enter this tile?
-  const bool near_w = e.W && i0 - AP < is, near_e = e.E && i0 + TX + AP - 1 > ie;
-  const bool near_s = e.S && j0 - AP < js, near_n = e.N && j0 + TY + AP - 1 > je;
   if (N > 0 && (near_w || near_e) && (near_s || near_n))
     deln_tile_corner(g, a, d2, fx2, fy2, e, N, i0, j0, base2);
   else
@@ -241,6 +243,159 @@ __global__ void __launch_bounds__(TX * NTY, 6) k_delnflux_fused(Geo g, DelnFused
     }
   }
 }
+// ---- row-marching version --------------------------------------------------------------------------------------
+// The tile kernel above spends ~470 thread instructions per cell, nine tenths of them on tile addressing, range tests
+// and barriers (profiles/r02d_step_metrics_c384.summary.txt: issue slots 70 % busy, fp64 pipe 9 %).  Here a WARP owns
+// one level, a strip of 26 columns (lane <-> i, 3-column apron each side, values exchanged by shuffles) and a chunk of
+// rows, and marches over the rows: row R of q comes in, the three damping levels advance by one row each
+//   d_0(R)                         fx_0(R), fy_0(R)
+//   d_1(R-1) = div(fx_0, fy_0)     fx_1(R-1), fy_1(R-1)
+//   d_2(R-2) = div(fx_1, fy_1)     fx_2(R-2), fy_2(R-2)
+// with everything carried in registers: no shared memory, no barrier, every field read and written once.  The
+// expressions are those of the tile kernel (same bits).  Cube-corner copies concern only the tiles that hold corner
+// cells on levels with nord > 0: those tiles are left to the tile kernel (corner_only) and skipped here.
+constexpr int MSW = 26;
+constexpr unsigned MFULL = 0xffffffffu;
+
+struct DelnMarchArgs {
+  DelnFusedArgs f;
+  int nstrips, nchunks, rows;  // column strips, row chunks, rows per chunk
+  int ntx, nty;                // tiles of the tile kernel per subdomain (ownership of the corner tiles)
+  long long items;
+};
+
+__global__ void __launch_bounds__(128, 4) k_delnflux_march(Geo g, DelnMarchArgs m) {
+  const DelnFusedArgs& a = m.f;
+  const long long item = (long long)blockIdx.x * 4 + (threadIdx.x >> 5);
+  if (item >= m.items) return;
+  const int lane = threadIdx.x & 31;
+  // item -> (t, k, chunk, strip), strips fastest: neighbouring warps share their column aprons in L1 / L2
+  const int strip = (int)(item % m.nstrips);
+  long long r1 = item / m.nstrips;
+  const int chunk = (int)(r1 % m.nchunks);
+  r1 /= m.nchunks;
+  const int k = (int)(r1 % a.nk), t = (int)(r1 / a.nk);
+  if (a.lvl != nullptr && a.accumulate && a.lvl[t * a.nk + k] == 0) return;  // a level of zeros adds no damping flux
+  const int is = g.is, ie = g.ie, js = g.js, je = g.je, sj = g.sj;
+  const unsigned ed = edge_of(g, t);
+  const bool eW = ed & EDGE_W, eE = ed & EDGE_E, eS = ed & EDGE_S, eN = ed & EDGE_N;
+  const int N = (int)a.nord_col[k < 3 ? k : 3];
+  const double dampk = a.damp[k];
+  const bool has_mass = a.mass != nullptr;
+  const int i = is + strip * MSW - 3 + lane;
+  const int ic = min(i, sj - 1);  // lanes right of the arrays read a valid address; their values are never used
+  // rows this warp delivers: [j_lo, j_hi] within [js-1, je+1]
+  const int j_lo = js - 1 + chunk * m.rows, j_hi = min(j_lo + m.rows - 1, je + 1);
+  // 32-bit element offsets (pace_b200_create refuses fields of 2^31 or more points): the field pointers stay in the
+  // constant bank and an address costs one IMAD.WIDE, instead of ten 64-bit running pointers in registers
+  const int base3 = (int)((long long)t * g.st3 + (long long)k * g.sk);
+  const int c3 = base3 + ic, c2 = t * g.sk + ic;
+  const double* __restrict__ q = a.q;
+  const double* __restrict__ dv = a.del6_v;
+  const double* __restrict__ du = a.del6_u;
+  const double* __restrict__ ra = a.rarea;
+  // ownership / validity per lane
+  const bool own_f = lane >= 3 && lane <= 28;                        // flux columns of this strip
+  const bool own_d = own_f || (strip == 0 && lane == 2);             // d2out also covers i = is - 1
+  const bool st_fx = own_f && i >= is && i <= ie + 1, st_fy = own_f && i >= is && i <= ie;
+  const bool st_d = own_d && i >= is - 1 && i <= ie + 1;
+  // tile column of this lane in the tile kernel's grid (the corner tiles are not ours when N > 0)
+  const int tbx = min(max(i - is, 0) / TX, m.ntx - 1);
+  const int ti0 = is + tbx * TX;
+  const bool tnear_w = eW && ti0 - AP < is, tnear_e = eE && ti0 + TX + AP - 1 > ie;
+  const bool lane_corner_x = N > 0 && (tnear_w || tnear_e);
+
+  const int R0 = max(0, j_lo - 1 - N - 1), R1 = j_hi + N;
+  double d0p = 0.0, fx0p = 0.0, fy0p = 0.0;   // level 0 at row R-1
+  double d1p = 0.0, fx1p = 0.0, fy1p = 0.0;   // level 1 at row R-2
+  double d2p = 0.0;                            // level 2 at row R-3
+  double dv1 = 0.0, du1 = 0.0, ra1 = 0.0, dv2 = 0.0, du2 = 0.0, ra2 = 0.0;  // metric terms of rows R-1, R-2
+  // Every stream is read two rows ahead of its use (registers): q and the metric terms of the incoming row, and — when
+  // accumulating — the old fluxes and the mass of the outgoing row.  With 8 warps per scheduler that is enough distance
+  // to cover the DRAM latency.
+  const bool acc = a.accumulate != 0, accm = acc && has_mass;
+  const bool ld_fx = acc && st_fx, ld_fy = acc && st_fy;
+  const double* fxo_p = a.fx;
+  const double* fyo_p = a.fy;
+  const double* ms_p = has_mass ? a.mass : a.q;
+  auto row_in = [&](int R) { return min(R, R1) * sj; };
+  auto row_out = [&](int R) { return min(max(R - N, 0), je + 1) * sj; };
+  double q_a = q[c3 + row_in(R0)], q_b = q[c3 + row_in(R0 + 1)];
+  double dv_a = dv[c2 + row_in(R0)], dv_b = dv[c2 + row_in(R0 + 1)], du_a = du[c2 + row_in(R0)], du_b = du[c2 + row_in(R0 + 1)];
+  double ra_a = ra[c2 + row_in(R0)], ra_b = ra[c2 + row_in(R0 + 1)];
+  double ofx_a = 0.0, ofx_b = 0.0, ofy_a = 0.0, ofy_b = 0.0, ms_a = 0.0, ms_b = 0.0, ms_m = 0.0;  // ms_m: mass one row below
+  if (ld_fx) { ofx_a = fxo_p[c3 + row_out(R0)]; ofx_b = fxo_p[c3 + row_out(R0 + 1)]; }
+  if (ld_fy) { ofy_a = fyo_p[c3 + row_out(R0)]; ofy_b = fyo_p[c3 + row_out(R0 + 1)]; }
+  if (accm) { ms_m = ms_p[c3 + row_out(R0 - 1)]; ms_a = ms_p[c3 + row_out(R0)]; ms_b = ms_p[c3 + row_out(R0 + 1)]; }
+  for (int R = R0; R <= R1; ++R) {
+    const double qv = q_a, dv0 = dv_a, du0 = du_a, ra0 = ra_a;
+    const double ofx = ofx_a, ofy = ofy_a, m_0 = ms_a, m_b = ms_m;
+    q_a = q_b; dv_a = dv_b; du_a = du_b; ra_a = ra_b;
+    ofx_a = ofx_b; ofy_a = ofy_b; ms_m = ms_a; ms_a = ms_b;
+    {
+      const int rin = row_in(R + 2);
+      q_b = q[c3 + rin]; dv_b = dv[c2 + rin]; du_b = du[c2 + rin]; ra_b = ra[c2 + rin];
+      const int rout = row_out(R + 2);
+      if (ld_fx) ofx_b = fxo_p[c3 + rout];
+      if (ld_fy) ofy_b = fyo_p[c3 + rout];
+      if (accm) ms_b = ms_p[c3 + rout];
+    }
+    const double d0 = has_mass ? qv : dampk * qv;
+    const double fx0 = dv0 * (__shfl_up_sync(MFULL, d0, 1) - d0);
+    const double fy0 = du0 * (d0p - d0);
+    double fxo = fx0, fyo = fy0, dout = d0;  // what goes out at row R - N
+    double d1 = 0.0, fx1 = 0.0, fy1 = 0.0, d2 = 0.0;
+    if (N >= 1) {
+      d1 = (fx0p - __shfl_down_sync(MFULL, fx0p, 1) + fy0p - fy0) * ra1;
+      fx1 = -dv1 * (__shfl_up_sync(MFULL, d1, 1) - d1);
+      fy1 = -du1 * (d1p - d1);
+      fxo = fx1; fyo = fy1; dout = d1;
+      if (N >= 2) {
+        d2 = (fx1p - __shfl_down_sync(MFULL, fx1p, 1) + fy1p - fy1) * ra2;
+        fxo = -dv2 * (__shfl_up_sync(MFULL, d2, 1) - d2);
+        fyo = -du2 * (d2p - d2);
+        dout = d2;
+      }
+    }
+    const int jo = R - N;
+    if (jo >= j_lo && jo <= j_hi) {  // warp-uniform
+      double m_l = 0.0;
+      if (accm) m_l = __shfl_up_sync(MFULL, m_0, 1);  // mass of the column to the left
+      // does (i, jo) belong to a tile the tile kernel handles?
+      bool skip = false;
+      if (lane_corner_x) {
+        const int tby = min(max(jo - js, 0) / TY, m.nty - 1);
+        const int tj0 = js + tby * TY;
+        skip = (eS && tj0 - AP < js) || (eN && tj0 + TY + AP - 1 > je);
+      }
+      if (!skip) {
+        const int o = base3 + jo * sj + i;
+        if (st_fx && jo >= js && jo <= je) {
+          if (acc) {
+            if (has_mass) a.fx[o] = ofx + 0.5 * dampk * (m_l + m_0) * fxo;
+            else a.fx[o] = ofx + fxo;
+          } else {
+            a.fx[o] = fxo;
+          }
+        }
+        if (st_fy && jo >= js && jo <= je + 1) {
+          if (acc) {
+            if (has_mass) a.fy[o] = ofy + 0.5 * dampk * (m_b + m_0) * fyo;
+            else a.fy[o] = ofy + fyo;
+          } else {
+            a.fy[o] = fyo;
+          }
+        }
+        if (a.d2out && st_d) a.d2out[o] = dout;
+      }
+    }
+    d2p = d2;
+    d1p = d1; fx1p = fx1; fy1p = fy1;
+    d0p = d0; fx0p = fx0; fy0p = fy0;
+    dv2 = dv1; du2 = du1; ra2 = ra1;
+    dv1 = dv0; du1 = du0; ra1 = ra0;
+  }
+}
 }  // namespace
 
 int delnflux_fused_launch(Core& c, const DelnArgs& a) {
@@ -251,11 +406,38 @@ int delnflux_fused_launch(Core& c, const DelnArgs& a) {
   f.del6_u = c.F("damp.del6_u"); f.del6_v = c.F("damp.del6_v"); f.rarea = c.F("grid.rarea");
   f.fx = a.fx; f.fy = a.fy; f.d2out = a.d2; f.nk = a.nk; f.accumulate = a.accumulate ? (zero_paths_enabled() ? 1 : 2) : 0;  // 2: accumulate, no zero-tile shortcut
   f.lvl = a.level_nonzero;
+  f.corner_only = 0;
   if (!c.err.empty()) return 1;
   dim3 blk(TX, NTY, 1);
   dim3 grd((g.nx + TX - 1) / TX, (g.ny + TY - 1) / TY, a.nk * g.nt);
-  LaunchScope scope(c.stream, "delnflux_fused");
-  k_delnflux_fused<<<grd, blk, 0, c.stream>>>(g, f);
+  static const bool tile_only = [] { const char* v = getenv("PACE_B200_DELNFLUX"); return v && std::string(v) == "tile"; }();
+  static const int rows_env = [] { const char* v = getenv("PACE_B200_DELN_ROWS"); return v ? atoi(v) : 0; }();
+  if (tile_only) {
+    LaunchScope scope(c.stream, "delnflux_fused");
+    k_delnflux_fused<<<grd, blk, 0, c.stream>>>(g, f);
+    return 0;
+  }
+  DelnMarchArgs m;
+  m.f = f;
+  m.ntx = grd.x; m.nty = grd.y;
+  m.nstrips = (g.nx + 1 + MSW - 1) / MSW;
+  // row chunks: enough warps to fill the GPU a few times over, chunks long enough that the 3 - 4 warm-up rows stay cheap
+  const int nrows = g.ny + 3;  // js-1 .. je+1
+  int rows = rows_env > 0 ? rows_env : 48;
+  m.nchunks = (nrows + rows - 1) / rows;
+  m.rows = (nrows + m.nchunks - 1) / m.nchunks;
+  m.items = (long long)m.nstrips * m.nchunks * a.nk * g.nt;
+  {
+    LaunchScope scope(c.stream, "delnflux_march");
+    k_delnflux_march<<<(unsigned)((m.items + 3) / 4), 128, 0, c.stream>>>(g, m);
+  }
+  // the tiles that see cube-corner cells (levels with nord > 0)
+  const unsigned eb0 = (unsigned)(g.edge_bits[0] | g.edge_bits[1]), eb1 = (unsigned)((g.edge_bits[0] | g.edge_bits[1]) >> 32);
+  if (a.nmax > 0 && (eb0 | eb1)) {
+    f.corner_only = 1;
+    LaunchScope scope(c.stream, "delnflux_fused");
+    k_delnflux_fused<<<grd, blk, 0, c.stream>>>(g, f);
+  }
   return 0;
 }
 
