@@ -253,6 +253,24 @@ typedef int (*pace_b200_halo_callback)(void* user, int plan_id, const char* cons
                                        int n, int nk);
 int pace_b200_set_halo_callback(void* handle, pace_b200_halo_callback cb, void* user);
 
+/* Halo exchange with subdomains on other GPUs of the node WITHOUT leaving the stream (replaces the Isend / Irecv of
+ * NDSL/ndsl/halo/updater.py:217-303 and the mpi4py calls behind comm/communicator.py): every rank owns an "arena" of
+ * 2 * half_doubles doubles followed by n_ranks 8-byte flag slots, zero-initialised and mapped into every peer process
+ * (CUDA IPC / torch symmetric memory); arena_ptrs[r] is rank r's arena as mapped HERE.  For a plan id (0..15) the caller
+ * uploads, per peer GPU, a pack plan whose message offsets follow that peer's receive layout, and one unpack plan
+ * (pace_b200_halo_plan_set, ids >= 16).  The phase calls then run pack-into-peer-arena, local gather, a flag barrier
+ * across all ranks and unpack as kernels on the handle's stream; pace_b200_halo_peer_update does one such update on
+ * its own.  Every rank must issue the same sequence of updates.  A barrier that waits 30 s for a peer gives up and the
+ * next call reports it. */
+int pace_b200_halo_peer_arena(void* handle, int my_rank, int n_ranks, void* const* arena_ptrs, long long half_doubles);
+int pace_b200_halo_peer_plan(void* handle, int plan_id, int n_peers, const int* peer_ranks, const int* pack_plan_ids,
+                             int unpack_plan_id);
+int pace_b200_halo_peer_update(void* handle, int plan_id, const char* const* x_names, const char* const* y_names, int n,
+                               int nk);
+/* Waits for the stream's work, then: number of barriers executed, and the sequence number of a barrier that gave up
+ * waiting for a peer (0 = none). */
+int pace_b200_halo_peer_status(void* handle, unsigned long long* barriers_done, unsigned long long* timed_out);
+
 /* The reference's checkpointer hooks (dyn_core.py:641-701, 787-893; fv_dynamics.py:342-443, 457-606): the callback is
  * called with the savepoint name ("FVDynamics-In", "C_SW-In", "C_SW-Out", "D_SW-In", "D_SW-Out", "Tracer2D1L-In",
  * "Tracer2D1L-Out", "Remapping-In", "Remapping-Out", "FVDynamics-Out") at the same points of the sequence.  The work

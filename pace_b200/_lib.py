@@ -104,6 +104,10 @@ def bind(lib):
     lib.pace_b200_set_satadj_config.argtypes = [vp, ctypes.POINTER(SatAdjConfig)]
     lib.pace_b200_set_halo_callback.argtypes = [vp, HALO_CALLBACK, vp]
     lib.pace_b200_set_stage_callback.argtypes = [vp, STAGE_CALLBACK, vp]
+    lib.pace_b200_halo_peer_arena.argtypes = [vp, _I, _I, ctypes.POINTER(vp), ctypes.c_longlong]
+    lib.pace_b200_halo_peer_plan.argtypes = [vp, _I, _I, ctypes.POINTER(_I), ctypes.POINTER(_I), _I]
+    lib.pace_b200_halo_peer_status.argtypes = [vp, ctypes.POINTER(ctypes.c_ulonglong), ctypes.POINTER(ctypes.c_ulonglong)]
+    lib.pace_b200_halo_peer_update.argtypes = [vp, _I, ctypes.POINTER(_S), ctypes.POINTER(_S), _I, _I]
     for name, extra in MODULE_CALLS.items():
         fn = getattr(lib, "pace_b200_" + name)
         fn.argtypes = [vp] + extra
@@ -158,4 +162,5 @@ MODULE_CALLS = {
 EXPORTS = ["pace_b200_row_stride", "pace_b200_create", "pace_b200_destroy", "pace_b200_last_error",
            "pace_b200_set_stream", "pace_b200_set_field", "pace_b200_set_column", "pace_b200_halo_plan_set", "pace_b200_halo_update", "pace_b200_halo_pack", "pace_b200_halo_unpack", "pace_b200_math_eval", "pace_b200_sat_adjust", "pace_b200_map_single_f32", "pace_b200_launch_count", "pace_b200_profile_enable",
            "pace_b200_profile_report", "pace_b200_set_satadj_config", "pace_b200_set_halo_callback",
-           "pace_b200_set_stage_callback"] + ["pace_b200_" + n for n in MODULE_CALLS]
+           "pace_b200_set_stage_callback", "pace_b200_halo_peer_arena", "pace_b200_halo_peer_plan",
+           "pace_b200_halo_peer_update", "pace_b200_halo_peer_status"] + ["pace_b200_" + n for n in MODULE_CALLS]

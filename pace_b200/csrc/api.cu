@@ -268,6 +268,25 @@ int pace_b200_set_stage_callback(void* h, pace_b200_stage_callback cb, void* use
   c->stage_cb = cb; c->stage_user = user;
   return 0;
 }
+int pace_b200_halo_peer_arena(void* h, int my_rank, int n_ranks, void* const* arena_ptrs, long long half_doubles) {
+  ENTRY(peer_arena_set(*c, my_rank, n_ranks, arena_ptrs, half_doubles))
+}
+int pace_b200_halo_peer_plan(void* h, int plan_id, int n_peers, const int* peer_ranks, const int* pack_plan_ids,
+                             int unpack_plan_id) {
+  ENTRY(peer_plan_set(*c, plan_id, n_peers, peer_ranks, pack_plan_ids, unpack_plan_id))
+}
+int pace_b200_halo_peer_status(void* h, unsigned long long* barriers_done, unsigned long long* timed_out) {
+  ENTRY(peer_status(*c, barriers_done, timed_out))
+}
+int pace_b200_halo_peer_update(void* h, int plan_id, const char* const* x_names, const char* const* y_names, int n, int nk) {
+  Core* c = (Core*)h;
+  c->err.clear();
+  if (plan_id < 0 || plan_id >= 16 || !c->peer_plans[plan_id].set || c->arena_ptrs.empty()) {
+    c->err = "halo_peer_update: no peer plan / arena set for this plan id";
+    return 1;
+  }
+  return finish(c, peer_halo_update(*c, plan_id, x_names, y_names, n, nk));
+}
 int pace_b200_acoustic(void* h, double timestep, int n_map) { ENTRY(acoustic(*c, timestep, n_map)) }
 int pace_b200_tracer_advection(void* h) { ENTRY(tracer_advection(*c)) }
 int pace_b200_remap(void* h, int last_step, double mdt) { ENTRY(remapping(*c, last_step, mdt)) }

@@ -63,6 +63,20 @@ struct Core {
   std::map<std::tuple<const void*, int, int>, std::unique_ptr<unsigned char[]>> tmaps;
   SatCfg sat_store;
   const SatCfg* sat_cfg = nullptr;
+  // halo exchange with subdomains on other GPUs by stores into the peers' receive arenas (halo.cu, peer_*):
+  // arena_ptrs[r] = rank r's arena as mapped into this process (two message halves of half_doubles doubles, then one
+  // 8-byte flag slot per rank); a plan's messages: one pack plan per peer GPU, one unpack plan
+  struct PeerPlan {
+    std::vector<int> peer_ranks, pack_ids;
+    int unpack_id = -1;
+    bool set = false;
+  };
+  std::vector<char*> arena_ptrs;
+  int peer_rank = 0;
+  long long half_doubles = 0;
+  unsigned long long peer_updates = 0;    // halo updates issued so far: its parity selects the message half
+  void* peer_dev = nullptr;               // device block: barrier sequence number, error word, flag-slot pointers
+  PeerPlan peer_plans[16];
 
   double* F(const char* name);              // caller-registered field, error if missing
   double* S(const char* name);              // zero-initialised library scratch field [nt][nz+1][ny+7][sj]
@@ -85,6 +99,11 @@ int halo_update(Core& c, int plan_id, const char* const* x_names, const char* co
 int halo_pack(Core& c, int plan_id, const char* const* x_names, const char* const* y_names, int n, int nk, double* buf);
 int halo_unpack(Core& c, int plan_id, const char* const* x_names, const char* const* y_names, int n, int nk,
                 const double* buf);
+int peer_arena_set(Core& c, int my_rank, int n_ranks, void* const* arena_ptrs, long long half_doubles);
+int peer_plan_set(Core& c, int plan_id, int n_peers, const int* peer_ranks, const int* pack_plan_ids, int unpack_plan_id);
+int peer_halo_update(Core& c, int plan_id, const char* const* x_names, const char* const* y_names, int n, int nk);
+int peer_barrier(Core& c);
+int peer_status(Core& c, unsigned long long* seq, unsigned long long* error);
 int tracer_flux_prep(Core& c, int n_split);
 int tracer_substep(Core& c, int nq);
 int tracer_swap_dp(Core& c);

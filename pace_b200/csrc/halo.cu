@@ -7,6 +7,8 @@
 // halo/data_transformer.py:404-560, halo/cuda_kernels.py:5-236).  The plan (which source cell fills which
 // halo cell, with rotation folded into an affine index map, pace_b200/halo.py) is uploaded once; an update is
 // ONE kernel per field group: no index arrays, no staging buffers, rotations applied in flight.
+#include <cstring>
+
 #include "core.hpp"
 
 namespace pace {
@@ -129,6 +131,131 @@ int halo_unpack(Core& c, int plan_id, const char* const* x_names, const char* co
                 const double* buf) {
   if (!buf) { c.err = "halo_unpack: null message buffer"; return 1; }
   return halo_run(c, plan_id, x_names, y_names, n, nk, 2, const_cast<double*>(buf));
+}
+
+
+// ---- neighbours on other GPUs: peer stores + flag barrier, all on the handle's stream -----------------------------
+// One halo update = for every peer GPU a pack kernel that stores its message straight into the peer's arena (NVLink
+// peer stores: plain st.global on a peer-mapped address), the local gather for same-GPU neighbours, a barrier kernel
+// (every rank writes the update's sequence number into its slot of every peer's flag array with release semantics at
+// system scope, then waits until all slots of its own array carry that number), and the unpack kernel.  Two message
+// halves alternate so that update n+1 cannot overwrite what a peer still unpacks from update n: the barrier of update
+// n+1 separates them.  No host code runs between the kernels, so a step is a pure launch sequence on one stream.
+// The arenas are mapped by the caller (torch symmetric memory in pace_b200/distributed.py); no TMA is involved.
+#ifndef PACE_HOST_EMU
+namespace {
+struct PeerDev {
+  unsigned long long seq;        // barriers executed so far
+  unsigned long long error;      // set to the sequence number of a barrier that timed out
+  unsigned long long* slot[64];  // slot[r]: this rank's flag slot inside rank r's arena
+  unsigned long long* mine;      // this rank's own flag array
+  int n, me;
+};
+
+__global__ void k_peer_barrier(PeerDev* d) {
+  __shared__ unsigned long long seq_s;
+  if (threadIdx.x == 0) {
+    seq_s = d->seq + 1;
+    d->seq = seq_s;
+  }
+  __syncthreads();
+  const unsigned long long seq = seq_s;
+  const int r = threadIdx.x;
+  if (r < d->n && r != d->me) {
+    __threadfence_system();  // the pack kernels before this one have completed; order their peer stores before the flag
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(d->slot[r]), "l"(seq) : "memory");
+    unsigned long long t0, t1, v;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    const unsigned long long* p = d->mine + r;
+    for (;;) {
+      asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+      if (v >= seq) break;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+      if (t1 - t0 > 30000000000ull) {  // 30 s: a peer has failed; give up instead of hanging the GPU
+        d->error = seq;
+        break;
+      }
+    }
+  }
+}
+}  // namespace
+#endif
+
+int peer_arena_set(Core& c, int my_rank, int n_ranks, void* const* arena_ptrs, long long half_doubles) {
+#ifndef PACE_HOST_EMU
+  if (n_ranks < 2 || n_ranks > 64 || my_rank < 0 || my_rank >= n_ranks) { c.err = "peer_arena_set: bad rank / world size"; return 1; }
+  c.arena_ptrs.assign(n_ranks, nullptr);
+  for (int r = 0; r < n_ranks; ++r) c.arena_ptrs[r] = (char*)arena_ptrs[r];
+  c.peer_rank = my_rank;
+  c.half_doubles = half_doubles;
+  c.peer_updates = 0;
+  PeerDev h;
+  memset(&h, 0, sizeof h);
+  h.n = n_ranks; h.me = my_rank;
+  const size_t flag_off = (size_t)2 * half_doubles * sizeof(double);
+  for (int r = 0; r < n_ranks; ++r) h.slot[r] = (unsigned long long*)(c.arena_ptrs[r] + flag_off) + my_rank;
+  h.mine = (unsigned long long*)(c.arena_ptrs[my_rank] + flag_off);
+  if (!c.peer_dev) {
+    if (cudaMalloc(&c.peer_dev, sizeof(PeerDev)) != cudaSuccess) { c.err = "cudaMalloc failed for the peer barrier block"; return 1; }
+    c.owned.push_back(c.peer_dev);
+  }
+  CUDA_CHECK_RET(cudaMemcpy(c.peer_dev, &h, sizeof h, cudaMemcpyHostToDevice));
+  return 0;
+#else
+  (void)my_rank; (void)n_ranks; (void)arena_ptrs; (void)half_doubles;
+  c.err = "peer-store halo exchange exists only in the CUDA library";
+  return 1;
+#endif
+}
+
+int peer_status(Core& c, unsigned long long* seq, unsigned long long* error) {
+#ifndef PACE_HOST_EMU
+  if (!c.peer_dev) { c.err = "peer_status: no arena set"; return 1; }
+  unsigned long long v[2];
+  CUDA_CHECK_RET(cudaMemcpy(v, c.peer_dev, sizeof v, cudaMemcpyDeviceToHost));  // synchronises with the stream's work
+  if (seq) *seq = v[0];
+  if (error) *error = v[1];
+  return 0;
+#else
+  (void)seq; (void)error;
+  c.err = "peer-store halo exchange exists only in the CUDA library";
+  return 1;
+#endif
+}
+
+int peer_plan_set(Core& c, int plan_id, int n_peers, const int* peer_ranks, const int* pack_plan_ids, int unpack_plan_id) {
+  if (plan_id < 0 || plan_id >= 16) { c.err = "peer_plan_set: plan id out of range"; return 1; }
+  Core::PeerPlan& p = c.peer_plans[plan_id];
+  p.peer_ranks.assign(peer_ranks, peer_ranks + n_peers);
+  p.pack_ids.assign(pack_plan_ids, pack_plan_ids + n_peers);
+  p.unpack_id = unpack_plan_id;
+  p.set = true;
+  return 0;
+}
+
+int peer_barrier(Core& c) {
+#ifndef PACE_HOST_EMU
+  if (!c.peer_dev) { c.err = "peer_barrier: no arena set"; return 1; }
+  LaunchScope scope(c.stream, "halo_barrier");
+  k_peer_barrier<<<1, 64, 0, c.stream>>>((PeerDev*)c.peer_dev);
+  return 0;
+#else
+  c.err = "peer-store halo exchange exists only in the CUDA library";
+  return 1;
+#endif
+}
+
+int peer_halo_update(Core& c, int plan_id, const char* const* x_names, const char* const* y_names, int n, int nk) {
+  const Core::PeerPlan& p = c.peer_plans[plan_id];
+  const long long half = (long long)(c.peer_updates & 1) * c.half_doubles;
+  ++c.peer_updates;
+  for (size_t m = 0; m < p.peer_ranks.size(); ++m)
+    if (halo_pack(c, p.pack_ids[m], x_names, y_names, n, nk, (double*)c.arena_ptrs[p.peer_ranks[m]] + half)) return 1;
+  if (halo_update(c, plan_id, x_names, y_names, n, nk)) return 1;  // same-GPU neighbours meanwhile
+  if (peer_barrier(c)) return 1;
+  if (p.unpack_id >= 0 && halo_unpack(c, p.unpack_id, x_names, y_names, n, nk, (double*)c.arena_ptrs[c.peer_rank] + half))
+    return 1;
+  return 0;
 }
 
 }  // namespace pace

@@ -46,6 +46,8 @@ int nk_heat_dissipation(const Config& cfg) {
 // registered exchange callback (other GPUs / processes hold neighbours) takes the whole update instead.
 static int halo(Core& c, int plan, const Names& x, const Names* y = nullptr, int nk = -1) {
   if (nk < 0) nk = c.g.nz;
+  if (plan < 16 && c.peer_plans[plan].set && !c.arena_ptrs.empty())
+    return peer_halo_update(c, plan, x.v, y ? y->v : nullptr, x.n, nk);
   if (c.halo_cb) {
     if (c.halo_cb(c.halo_user, plan, x.v, y ? y->v : nullptr, x.n, nk) != 0) {
       if (c.err.empty()) c.err = "halo exchange callback failed";
@@ -194,6 +196,12 @@ int step(Core& c) {
   const Names u{"u"}, v{"v"};
   RUN(halo(c, D3, u, &v));
   RUN(c2l_ord4(c));
+  // keep the number of halo updates per step even, so that every step starts on the same message half (a captured
+  // launch sequence can then be replayed) — the extra barrier also keeps the two-half protocol valid across steps
+  if (!c.arena_ptrs.empty() && (c.peer_updates & 1)) {
+    ++c.peer_updates;
+    RUN(peer_barrier(c));
+  }
   RUN(stage(c, "FVDynamics-Out"));
   return 0;
 }

@@ -64,13 +64,27 @@ class PeerArena:
         import torch.distributed._symmetric_memory as symm_mem
 
         self.cap = int(cap_doubles)
-        self.buf = symm_mem.empty(2 * self.cap, dtype=torch.float64, device=device)
+        self.world = comm.world_size
+        # two message halves, then one 8-byte flag slot per rank (the library's own barrier, csrc/halo.cu)
+        self.buf = symm_mem.empty(2 * self.cap + 64, dtype=torch.float64, device=device)
         self.buf.zero_()
         self.hdl = symm_mem.rendezvous(self.buf, comm.dist.group.WORLD.group_name if comm.group is None else comm.group.group_name)
         self.ptrs = [int(p) for p in self.hdl.buffer_ptrs]
         self.rank = comm.rank
         self.count = 0
+        self.native = False
         self.hdl.barrier()
+
+    def attach(self, core):
+        """Hand the mapped arenas to the library: halo updates of the phase calls then run pack / barrier / unpack as
+        kernels on the stream, without coming back to Python (pace_b200_halo_peer_arena)."""
+        import ctypes
+
+        arr = (ctypes.c_void_p * self.world)(*self.ptrs)
+        rc = core.lib.pace_b200_halo_peer_arena(core.handle, self.rank, self.world, arr, self.cap)
+        if rc != 0:
+            raise RuntimeError("halo_peer_arena: %s" % core.lib.pace_b200_last_error(core.handle).decode())
+        self.native = True
 
     def next_half(self):
         self.count += 1
@@ -143,6 +157,16 @@ class HaloExchanger:
                 pid = 64 + plan_id * 16 + n_peer
                 core.set_halo_plan_raw(pid, rows)
                 self.peer_packs.append((p, pid))
+            if arena.native:
+                import ctypes
+
+                n = len(self.peer_packs)
+                ranks = (ctypes.c_int * max(1, n))(*[p for p, _ in self.peer_packs])
+                pids = (ctypes.c_int * max(1, n))(*[pid for _, pid in self.peer_packs])
+                rc = core.lib.pace_b200_halo_peer_plan(core.handle, plan_id, n, ranks, pids,
+                                                       self.unpack_id if self.remote else -1)
+                if rc != 0:
+                    raise RuntimeError("halo_peer_plan: %s" % core.lib.pace_b200_last_error(core.handle).decode())
 
     def _buffers(self, nq, nk):
         key = (nq, nk)
@@ -159,6 +183,15 @@ class HaloExchanger:
             core.halo_update(self.plan_id, x_names, y_names, nk)
             return
         nq = len(x_names)
+        if self.arena is not None and self.arena.native:
+            n = len(x_names)
+            import ctypes
+
+            xs = (ctypes.c_char_p * n)(*[s.encode() for s in x_names])
+            ys = (ctypes.c_char_p * n)(*[s.encode() for s in y_names]) if y_names else None
+            if core.lib.pace_b200_halo_peer_update(core.handle, self.plan_id, xs, ys, n, nk) != 0:
+                raise RuntimeError("halo_peer_update: %s" % core.lib.pace_b200_last_error(core.handle).decode())
+            return
         if self.arena is not None:
             # direct peer stores over NVLink: pack into the receivers' buffers, barrier, unpack the local buffer
             ar = self.arena

@@ -89,6 +89,8 @@ class DycoreEngine:
                 cap = max(HaloExchanger.max_recv_cells(ops, self.placement) for ops in plans.values())
                 try:
                     arena = PeerArena(comm, cap * HaloExchanger.NQ_MAX * (npz + 1), core.device)
+                    if os.environ.get("PACE_B200_HALO", "peer") != "peer_py":
+                        arena.attach(core)  # the library drives the exchange itself; "peer_py": from Python, torch barrier
                 except Exception as exc:  # no symmetric memory on this box: every rank falls back together
                     import warnings
 
@@ -167,7 +169,8 @@ class DycoreEngine:
                 self._cb_error = exc
                 return 1
 
-        remote = any(h.remote or h.arena is not None for h in self.halo.values())
+        native = self.arena is not None and self.arena.native
+        remote = (not native) and any(h.remote or h.arena is not None for h in self.halo.values())
         self._halo_cb = _lib.HALO_CALLBACK(on_halo) if remote else _lib.HALO_CALLBACK()
         core.lib.pace_b200_set_halo_callback(core.handle, self._halo_cb, None)
         sat = _lib.SatAdjConfig.make(**dict({k: (int(v) if isinstance(v, bool) else v) for k, v in self._sat_adjust.items()},
