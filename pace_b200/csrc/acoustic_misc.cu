@@ -131,18 +131,30 @@ int compute_geopotential(Core& c) {
 }
 
 // NonHydrostaticPressureGradient.__call__ (nh_p_grad.py:201-265)
-int nh_p_grad(Core& c, double dt) {
+// keep_agrid: the B-grid interpolations of pp, pk3 and gz go to work arrays instead of replacing the fields (saves the
+// three copy-back passes); AcousticDynamics (step.cu) does that on every substep but its last, after which the
+// reference's temporaries hold the B-grid values, as here.
+int nh_p_grad(Core& c, double dt, bool keep_agrid) {
   const Geo g = c.g;
   cudaStream_t st = c.stream;
-  double *u = c.F("u"), *v = c.F("v"), *pp = c.F("ad.pkc"), *gz = c.F("ad.gz"), *pk3 = c.F("ad.pk3");
+  double *u = c.F("u"), *v = c.F("v"), *pp_a = c.F("ad.pkc"), *gz_a = c.F("ad.gz"), *pk3_a = c.F("ad.pk3");
   const double *delp = c.F("delp"), *rdx = c.F("grid.rdx"), *rdy = c.F("grid.rdy");
   double *wk = c.FS("nh.tmp_wk"), *wk1 = c.FS("nh.tmp_wk1");
   if (!c.err.empty()) return 1;
   const int km = g.nz, ie = g.ie, je = g.je;
   const double top_value = std::pow(c.cfg.ptop, KAPPA);  // ptk = ptop ** akap
-  if (a2b_ord4(c, pp, wk1, 1, km, true)) return 1;
-  if (a2b_ord4(c, pk3, wk1, 1, km, true)) return 1;
-  if (a2b_ord4(c, gz, wk1, 0, km + 1, true)) return 1;
+  double *pp = pp_a, *pk3 = pk3_a, *gz = gz_a;
+  if (keep_agrid) {
+    pp = c.S("nh.pp_b"); pk3 = c.S("nh.pk3_b"); gz = c.S("nh.gz_b");
+    if (!c.err.empty()) return 1;
+    if (a2b_ord4(c, pp_a, pp, 1, km, false)) return 1;
+    if (a2b_ord4(c, pk3_a, pk3, 1, km, false)) return 1;
+    if (a2b_ord4(c, gz_a, gz, 0, km + 1, false)) return 1;
+  } else {
+    if (a2b_ord4(c, pp, wk1, 1, km, true)) return 1;
+    if (a2b_ord4(c, pk3, wk1, 1, km, true)) return 1;
+    if (a2b_ord4(c, gz, wk1, 0, km + 1, true)) return 1;
+  }
   if (a2b_ord4(c, delp, wk1, 0, km, false)) return 1;
   // set_k0_and_calc_wk on compute (+1,+1), npz levels
   launch_ijk(st, g, box_compute(g, 0, 0, 1, 1, 0), [=] __device__(const Pt& p) {

@@ -92,6 +92,7 @@ struct Core {
 int riem_solver_c(Core& c, double dt2);
 int c_sw(Core& c, double dt2);
 int update_dz_c(Core& c, double dt2);
+int update_dz_c_from_zh(Core& c, double dt2, bool gz_equals_zh);
 int p_grad_c(Core& c, double dt2);
 int set_column(Core& c, const char* name, const double* host_values, int n);
 int halo_plan_set(Core& c, int plan_id, const void* host_ops, int n_ops);
@@ -131,7 +132,7 @@ int copy_full(Core& c, const char* src_name, const char* dst_name);
 int edge_pe(Core& c);
 int pk3_halo(Core& c);
 int compute_geopotential(Core& c);
-int nh_p_grad(Core& c, double dt);
+int nh_p_grad(Core& c, double dt, bool keep_agrid = false);
 int ray_fast(Core& c, double dt);
 int del2cubed(Core& c, double* q, double cd, int nmax);
 int apply_diffusive_heating(Core& c, double delt_time_factor, int nk);

@@ -15,6 +15,13 @@ int update_dz_c(Core& c, double dt) {
   return update_dz_c_with(c, dt, gz0);
 }
 
+// The same inside AcousticDynamics.__call__ (step.cu), where zh holds the pre-update heights: see update_dz_c_with.
+int update_dz_c_from_zh(Core& c, double dt, bool gz_equals_zh) {
+  double* zh = c.F("ad.zh");
+  if (!c.err.empty()) return 1;
+  return update_dz_c_with(c, dt, zh, gz_equals_zh ? 1 : 2);
+}
+
 // p_grad_c_stencil (dyn_core.py:122-173), nonhydrostatic branch (wk = delpc)
 int p_grad_c(Core& c, double dt2) {
   const Geo g = c.g;

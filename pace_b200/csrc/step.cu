@@ -89,13 +89,13 @@ int acoustic(Core& c, double timestep, int n_map) {
     RUN(c_sw(c, dt2));
     RUN(stage(c, "C_SW-Out"));
     if (cfg.nord > 0) RUN(halo(c, B3, Names{"ad.divgd"}));
+    // the reference copies gz -> zh (first substep) or zh -> gz (later ones) and then updates gz from two corner-filled
+    // copies of it; zh IS that pre-update copy, so the update reads zh and (later substeps) writes all of gz
     if (it == 0) {
       RUN(halo(c, A3, Names{"ad.gz"}, nullptr, npz + 1));
       RUN(copy_full(c, "ad.gz", "ad.zh"));
-    } else {
-      RUN(copy_full(c, "ad.zh", "ad.gz"));
     }
-    RUN(update_dz_c(c, dt2));
+    RUN(update_dz_c_from_zh(c, dt2, it == 0));
     RUN(riem_solver_c(c, dt2));
     RUN(p_grad_c(c, dt2));
     RUN(halo(c, C3, uc, &vc));
@@ -110,7 +110,7 @@ int acoustic(Core& c, double timestep, int n_map) {
     if (remap_step) RUN(edge_pe(c));
     RUN(pk3_halo(c));
     RUN(compute_geopotential(c));
-    RUN(nh_p_grad(c, dt));
+    RUN(nh_p_grad(c, dt, /*keep_agrid=*/it != n_split - 1));
     if (cfg.rf_fast) RUN(ray_fast(c, dt));
     if (it == n_split - 1 && cfg.grid_type < 4) RUN(halo(c, SYNC, u, &v));
   }

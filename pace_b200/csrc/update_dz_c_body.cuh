@@ -9,7 +9,13 @@ namespace pace {
 
 // The reference makes two corner-filled copies of gz (gz_x, gz_y); here one plain copy (gz0, caller-provided work array
 // of field size) keeps the pre-update values and the corner fills are applied virtually at read time (corners.cuh).
-static int update_dz_c_with(Core& c, double dt, double* gz0) {
+// mode 0: gz0 is a work array; gz is copied into it first (the stand-alone entry points).
+// mode 1: gz0 already holds the pre-update heights on the whole array and equals gz (first acoustic substep: zh, just
+//         copied from gz): no copy.
+// mode 2: gz0 holds the pre-update heights and gz holds anything (later substeps: the reference copies zh to gz and
+//         then updates gz): gz is written everywhere — the update on the compute domain + 1, gz0 outside it — which
+//         saves the separate copy zh -> gz (one read and one write pass) and the copy gz -> work array (another two).
+static int update_dz_c_with(Core& c, double dt, double* gz0, int mode = 0) {
   const Geo g = c.g;
   cudaStream_t st = c.stream;
   const double *zs = c.F("ad.zs"), *ut = c.F("ad.ut"), *vt = c.F("ad.vt"), *area = c.F("grid.area"),
@@ -17,8 +23,13 @@ static int update_dz_c_with(Core& c, double dt, double* gz0) {
   double *gz = c.F("ad.gz"), *ws = c.F("ad.ws3");
   if (!c.err.empty() || !gz0) return 1;
   const int km = g.nz;
-  launch_ijk(st, g, box_full(g, 1), [=] __device__(const Pt& p) { A0(gz0) = A0(gz); });
-  launch_ijk(st, g, box_compute(g, -1, -1, 2, 2, 1), [=] __device__(const Pt& p) {
+  if (mode == 0) launch_ijk(st, g, box_full(g, 1), [=] __device__(const Pt& p) { A0(gz0) = A0(gz); });
+  const bool everywhere = mode == 2;
+  launch_ijk(st, g, everywhere ? box_full(g, 1) : box_compute(g, -1, -1, 2, 2, 1), [=] __device__(const Pt& p) {
+    if (everywhere && (p.i < g.is - 1 || p.i > g.ie + 1 || p.j < g.js - 1 || p.j > g.je + 1)) {
+      A0(gz) = A0(gz0);
+      return;
+    }
     const int k = p.k;
     const EdgeInfo e = edge_info(g, p);
     // xfx/yfx at horizontal offset (di,dj): pressure-weighted interface average of ut/vt.  The weight depends on the
