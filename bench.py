@@ -2,6 +2,7 @@
 """bench.py — FV3 dycore step throughput of the B200-native hot path (pace_b200) and of the CPU baseline.
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c384|c128|c48] [--impl reference]
+    python bench.py --workload tracer_c192 | mapsingle_c384_l91_f32     (BASELINE.json configs 4 and 5, one GPU)
 
 One "step" = one DynamicalCore.step_dynamics (k_split=1, n_split=6: 6 acoustic substeps + tracer advection +
 vertical remap) on synthetic inputs of the named shape (pace_b200/synthetic.py).  Metric: simulated-days/day =
@@ -155,6 +156,94 @@ def run_reference(args):
     print(json.dumps(line))
 
 
+def side_workload(args):
+    """BASELINE.json configs 4 and 5 as stand-alone bench lines (one GPU): `--workload tracer_c192` times
+    TracerAdvection.__call__ (pace_b200_tracer_advection: 3 sub-cycles, 8 DENSE tracers, C192 L79 fp64, six tiles);
+    `--workload mapsingle_c384_l91_f32` times MapSingle.__call__ in the reference's fp32 mode (pace_b200_map_single_f32,
+    kord 9, iv 1, C384 L91, six tiles).  A step = one call; CUDA events; inputs >> L2."""
+    import torch
+
+    from pace_b200.native import NativeCore
+
+    pk, pk_kind = peaks()
+    dev = "cuda:0"
+    torch.cuda.set_device(0)
+    if args.workload == "tracer_c192":
+        from pace_b200.synthetic import make_engine
+
+        n, nsub = 192, 6
+        eng = make_engine(n, 1, npz=NPZ, device=dev, n_split=N_SPLIT, k_split=1, dt_atmos=DT_ATMOS)
+        eng.step_dynamics()  # leaves mass fluxes / Courant numbers of a real acoustic loop in mfxd, mfyd, cxd, cyd
+        core = eng.core
+        qv = core.t["qvapor"]
+        for m, name in enumerate(eng_tracers()):
+            if name != "qvapor":  # every species dense: a scaled copy of the vapour field with its own offset
+                core.t[name].copy_(qv * (0.1 + 0.05 * m) + 1.0e-6 * (m + 1))
+        call = lambda: eng.tracer_advection()  # noqa: E731
+        cells = nsub * n * n * NPZ
+        bytes_per_cell, what, dtype = 656.0, "TracerAdvection.__call__, 8 dense tracers, C192 L79, six tiles", "f64"
+        metric, unit = "tracer advection calls per second", "calls / s"
+    else:
+        n, nsub, nz = 384, 6, 91
+        core = NativeCore(n, n, nz, n_tiles=nsub, device=dev)
+        g = torch.Generator(device="cpu").manual_seed(0)
+        shape2 = (nsub, core.nj, core.sj)
+        ps = (95000.0 + 8000.0 * torch.rand(shape2, generator=g)).to(dev)
+        thick = (0.2 + 1.6 * torch.rand((nsub, nz) + shape2[1:], generator=g)).to(dev)
+        thick = thick * ((ps - 300.0) / thick.sum(dim=1))[:, None]
+        pe1 = torch.zeros((nsub, nz + 1) + shape2[1:], dtype=torch.float64, device=dev)
+        pe1[:, 0] = 300.0
+        pe1[:, 1:] = 300.0 + torch.cumsum(thick.double(), dim=1)
+        eta = (torch.arange(nz + 1, dtype=torch.float64, device=dev) / nz) ** 1.3
+        pe2 = 300.0 + (pe1[:, nz] - 300.0)[:, None] * eta[None, :, None, None]
+        pe1, pe2 = pe1.float().contiguous(), pe2.float().contiguous()
+        pe2[:, nz] = pe1[:, nz]
+        zz = torch.linspace(0.0, 1.0, nz + 1, device=dev)[None, :, None, None]
+        q0 = (250.0 + 40.0 * zz + 1.5 * torch.randn(pe1.shape, generator=g).to(dev)).float().contiguous()
+        q = q0.clone()
+        del thick, ps
+
+        def call():
+            q.copy_(q0)  # the remap is in place: every call starts from the same field (the copy is inside the timing)
+            core.map_single_f32(q, pe1, pe2, None, iv=1, kord=9, qmin=0.0)
+
+        cells = nsub * n * n * nz
+        # q read + written, pe1 and pe2 read (fp32), + the restoring copy (read + write)
+        bytes_per_cell, what, dtype = 6 * 4.0, "MapSingle.__call__ fp32 (kord 9, iv 1), C384 L91, six tiles", "f32"
+        metric, unit = "MapSingle calls per second", "calls / s"
+    lib = core.lib
+    for _ in range(max(args.warmup, 3)):
+        call()
+    torch.cuda.synchronize()
+    sampler = ClockSampler(0)
+    sampler.start()
+    l0 = lib.pace_b200_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        call()
+    e1.record()
+    torch.cuda.synchronize()
+    sampler.stop_flag = True
+    sampler.join(timeout=2)
+    ms = e0.elapsed_time(e1) / args.steps
+    achieved = cells * bytes_per_cell / (ms / 1000.0) / 1e9
+    line = {
+        "metric": metric, "value": 1000.0 / ms, "unit": unit, "n_gpus": 1, "steps": args.steps, "warmup": max(args.warmup, 3),
+        "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": dtype,
+        "data": "synthetic", "config": {"workload": what, "cells": cells, "l2": "inputs >> L2, no flush needed"},
+        "gpu_launches": int((lib.pace_b200_launch_count() - l0) // args.steps), "clocks": sampler.summary(),
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": pk["hbm_gbs"], "peak_source": pk_kind, "unit": "GB/s",
+                     "frac": achieved / pk["hbm_gbs"], "traffic": None, "algorithmic_bytes_per_step": cells * bytes_per_cell,
+                     "bytes_per_cell": bytes_per_cell},
+    }
+    print(json.dumps(line))
+
+
+def eng_tracers():
+    return ["qvapor", "qliquid", "qrain", "qice", "qsnow", "qgraupel", "qo3mr", "qsgs_tke"]
+
+
 def state_hash(eng, dist, world):
     """SHA-256 over the prognostic fields (compute domain, subdomains in cube order) after the timed steps: the same
     number of steps from the same state gives the same hash at every GPU count when the partitioning changes nothing."""
@@ -191,6 +280,10 @@ def main():
     args = ap.parse_args()
     if args.workload is None:
         args.workload = "c384"
+    if args.workload in ("tracer_c192", "mapsingle_c384_l91_f32"):
+        if int(os.environ.get("RANK", "0")) == 0:
+            side_workload(args)
+        return
     if args.impl == "reference":
         if int(os.environ.get("RANK", "0")) != 0:
             return  # under torchrun rank 0 alone times the CPU implementation

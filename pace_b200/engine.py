@@ -5,6 +5,8 @@ The numerics AND the call order are behind the C ABI (include/pace_b200.h: pace_
 _remap / _step, csrc/step.cu); this file owns the buffers' registration, the halo plans and — when subdomains live on
 other GPUs — the exchange the library calls back for.
 """
+import ctypes
+
 import numpy as np
 
 from .halo import HaloPlanner
@@ -289,6 +291,12 @@ class HostPipeline:
         get_in = host_in if callable(host_in) else (lambda n: host_in)
         get_out = host_out if callable(host_out) else (lambda n: host_out)
         main = torch.cuda.current_stream(core.device)
+        # the library launches on the stream it was given (NativeCore: the stream current at construction); the events
+        # below order the copies against THAT stream, so it must be the current one here
+        core.lib.pace_b200_set_stream(core.handle, ctypes.c_void_p(main.cuda_stream))
+        # work already queued on the main stream (the constructor's copies, the caller's writes) precedes the copies
+        self.s_up.wait_stream(main)
+        self.s_down.wait_stream(main)
         up_done = [torch.cuda.Event(), torch.cuda.Event()]
         step_done = [torch.cuda.Event(), torch.cuda.Event()]
         down_done = [None, None]

@@ -6,7 +6,8 @@ Grid generation and the analytic initial state are out of the hot-path scope (SU
 reference) and the reference cannot run on the GPU box, so bench.py needs inputs of the right SHAPE that keep the
 dycore in its normal regime: every tile keeps its edge / corner metric structure (edge rows map to edge rows, per
 staggering), winds / temperature / pressure fields keep their magnitudes, upwind directions and limiter branches
-vary in space as in the real case.  Cell sizes stay those of C12, so Courant numbers are ~N/12 times smaller than
+vary in space as in the real case; cell-scale noise (NOISE below) keeps neighbouring cells from taking identical
+limiter branches.  Cell sizes stay those of C12, so Courant numbers are ~N/12 times smaller than
 the true C<N> case — the arithmetic executed per cell is the same.  Not used by any parity test.
 """
 import os
@@ -80,9 +81,31 @@ def _load(kind):
     return out
 
 
-def make_engine(n_tile, layout, npz=79, device="cuda:0", comm=None, **cfg):
+# Small-scale structure on top of the (piecewise-linear) resampled fields: amplitude per field, absolute or relative.
+# Without it neighbouring cells see identical slopes, so the PPM limiters and upwind selects of a whole warp take the
+# same branch, which flatters instruction-bound kernels.
+NOISE = {"u": (0.2, False), "v": (0.2, False), "w": (0.02, False), "pt": (0.05, False), "delp": (1.0e-4, True),
+         "qvapor": (1.0e-3, True)}
+
+
+def cell_noise(shape, tile, field_id, device):
+    """Deterministic values in [-1, 1) from the integer position (tile, k, j, i) in the TILE's array — independent of the
+    layout and of which GPU holds the cell, and bit-identical on every device (integer arithmetic only)."""
+    nk, nj, ni = shape
+    k = torch.arange(nk, device=device, dtype=torch.int64).view(-1, 1, 1)
+    j = torch.arange(nj, device=device, dtype=torch.int64).view(1, -1, 1)
+    i = torch.arange(ni, device=device, dtype=torch.int64).view(1, 1, -1)
+    h = (i * 73856093 + j * 19349663 + k * 83492791 + tile * 2654435761 + field_id * 40503) & 0x7FFFFFFF
+    for _ in range(2):
+        h = (h * 1103515245 + 12345) & 0x7FFFFFFF
+        h = h ^ (h >> 13)
+    return h.to(torch.float64) / float(1 << 30) - 1.0
+
+
+def make_engine(n_tile, layout, npz=79, device="cuda:0", comm=None, noise=True, **cfg):
     """A DycoreEngine for C<n_tile> with `layout` x `layout` subdomains per tile, filled with resampled inputs.
-    comm: pace_b200.distributed.TorchComm — this process then holds only its block of subdomains."""
+    comm: pace_b200.distributed.TorchComm — this process then holds only its block of subdomains.
+    noise: add cell-scale perturbations (NOISE) to the prognostic fields."""
     from .distributed import Placement
     from .engine import STATE_2D, STATE_3D, DycoreEngine
     from .hostprep import a2b_corner_coefficients
@@ -145,7 +168,12 @@ def make_engine(n_tile, layout, npz=79, device="cuda:0", comm=None, **cfg):
             a = s[name]
             if not np.any(a):
                 continue
-            scatter(name, resample_tile(a, n_tile, STAGGER.get(name, (0, 0)), dev), tile)
+            t = resample_tile(a, n_tile, STAGGER.get(name, (0, 0)), dev)
+            if noise and name in NOISE and t.shape[0] > 1:
+                amp, relative = NOISE[name]
+                r = cell_noise(tuple(t.shape), tile, sorted(NOISE).index(name), dev)
+                t = t * (1.0 + amp * r) if relative else t + amp * r
+            scatter(name, t, tile)
         scatter("ad.zs", resample_tile(np.asarray(s["phis"]) / 9.80665, n_tile, (0, 0), dev), tile)
     core.set_column("grid.a2b_corner_coef", coef.reshape(-1))
     return eng
