@@ -12,6 +12,14 @@ import pytest
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
+
+def comparable(name, a, n):
+    """uc / vc double as work arrays of the divergence damping: their halo holds results of its earlier, wider
+    iterations in the stencil-by-stencil version and is not written by the marching kernel (nothing reads it);
+    everything else is compared on the whole arrays.  Layout [t][k][j][i], n compute cells per side."""
+    return a[:, :, 3:3 + n + 1, 3:3 + n + 1] if name in ("uc", "vc") else a
+
+
 SCRIPT = r"""
 import sys, numpy as np, torch
 sys.path.insert(0, %r)
@@ -30,7 +38,7 @@ def test_fused_matches_three_kernel_version(tmp_path):
     res = {}
     modes = {"march": {"PACE_B200_FVTP2D": "march"},
              "march_chunks": {"PACE_B200_FVTP2D": "march", "PACE_B200_FVTP2D_ROWS": "16"},
-             "tile": {"PACE_B200_FVTP2D": "tile"}, "unfused": {"PACE_B200_FVTP2D": "unfused", "PACE_B200_DELNFLUX": "unfused", "PACE_B200_RIEM": "global", "PACE_B200_A2B": "unfused", "PACE_B200_CSW": "unfused"}}
+             "tile": {"PACE_B200_FVTP2D": "tile"}, "unfused": {"PACE_B200_FVTP2D": "unfused", "PACE_B200_DELNFLUX": "unfused", "PACE_B200_RIEM": "global", "PACE_B200_A2B": "unfused", "PACE_B200_CSW": "unfused", "PACE_B200_DD": "unfused"}}
     for mode, extra in modes.items():
         env = dict(os.environ, **extra)
         path = str(tmp_path / (mode + ".npz"))
@@ -40,7 +48,7 @@ def test_fused_matches_three_kernel_version(tmp_path):
         if mode == "unfused":
             continue
         for name in res[mode].files:
-            a, b = res[mode][name], res["unfused"][name]
+            a, b = comparable(name, res[mode][name], 48), comparable(name, res["unfused"][name], 48)
             assert np.all(np.isfinite(a)), (mode, name)
             assert np.array_equal(a, b), "%s: %s differs: max |d| = %g" % (mode, name, np.max(np.abs(a - b)))
 
@@ -51,13 +59,13 @@ def test_production_kernels_match_unfused_at_c96(tmp_path):
     narrower), several row chunks, 3 x 3 DelnFlux / a2b tiles."""
     res = {}
     for mode, extra in {"production": {}, "unfused": {"PACE_B200_FVTP2D": "unfused", "PACE_B200_DELNFLUX": "unfused",
-                                                      "PACE_B200_RIEM": "global", "PACE_B200_A2B": "unfused", "PACE_B200_CSW": "unfused"}}.items():
+                                                      "PACE_B200_RIEM": "global", "PACE_B200_A2B": "unfused", "PACE_B200_CSW": "unfused", "PACE_B200_DD": "unfused"}}.items():
         env = dict(os.environ, **extra)
         path = str(tmp_path / (mode + ".npz"))
         subprocess.run([sys.executable, "-c", SCRIPT % ROOT, path, "96"], check=True, env=env, timeout=900)
         res[mode] = np.load(path)
     for name in res["production"].files:
-        a, b = res["production"][name], res["unfused"][name]
+        a, b = comparable(name, res["production"][name], 96), comparable(name, res["unfused"][name], 96)
         assert np.all(np.isfinite(a)), name
         assert np.array_equal(a, b), "%s differs: max |d| = %g" % (name, np.max(np.abs(a - b)))
 
@@ -106,7 +114,7 @@ def test_zero_shortcuts_match_dense_on_patchy_tracers(tmp_path):
     modes = {"production": {},
              "dense": {"PACE_B200_ZERO_PATHS": "0"},
              "dense_unfused": {"PACE_B200_ZERO_PATHS": "0", "PACE_B200_FVTP2D": "unfused", "PACE_B200_DELNFLUX": "unfused",
-                               "PACE_B200_RIEM": "global", "PACE_B200_A2B": "unfused", "PACE_B200_CSW": "unfused"}}
+                               "PACE_B200_RIEM": "global", "PACE_B200_A2B": "unfused", "PACE_B200_CSW": "unfused", "PACE_B200_DD": "unfused"}}
     for mode, extra in modes.items():
         env = dict(os.environ, **extra)
         path = str(tmp_path / (mode + ".npz"))
@@ -114,10 +122,10 @@ def test_zero_shortcuts_match_dense_on_patchy_tracers(tmp_path):
         res[mode] = np.load(path)
     moved = 0
     for name in res["production"].files:
-        a = res["production"][name]
+        a = comparable(name, res["production"][name], 48)
         assert np.all(np.isfinite(a)), name
         for other in ("dense", "dense_unfused"):
-            b = res[other][name]
+            b = comparable(name, res[other][name], 48)
             assert np.array_equal(a, b), "%s vs %s differs: max |d| = %g" % (name, other, np.max(np.abs(a - b)))
     for name in ("qrain", "qsnow", "qice", "qliquid", "qgraupel"):
         moved += int(np.count_nonzero(res["production"][name]))
