@@ -258,13 +258,15 @@ int pace_b200_set_halo_callback(void* handle, pace_b200_halo_callback cb, void* 
  * 2 * half_doubles doubles followed by n_ranks 8-byte flag slots, zero-initialised and mapped into every peer process
  * (CUDA IPC / torch symmetric memory); arena_ptrs[r] is rank r's arena as mapped HERE.  For a plan id (0..15) the caller
  * uploads, per peer GPU, a pack plan whose message offsets follow that peer's receive layout, and one unpack plan
- * (pace_b200_halo_plan_set, ids >= 16).  The phase calls then run pack-into-peer-arena, local gather, a flag barrier
+ * (pace_b200_halo_plan_set, ids >= 16); max_recv_cells = the largest number of halo cells any rank receives in one
+ * update of the plan (the same number on every rank: updates that share a wait point — (u, v) with w, zh with pkc —
+ * travel as one exchange, the second message behind the largest first one).  The phase calls then run pack-into-peer-arena, local gather, a flag barrier
  * across all ranks and unpack as kernels on the handle's stream; pace_b200_halo_peer_update does one such update on
  * its own.  Every rank must issue the same sequence of updates.  A barrier that waits 30 s for a peer gives up and the
  * next call reports it. */
 int pace_b200_halo_peer_arena(void* handle, int my_rank, int n_ranks, void* const* arena_ptrs, long long half_doubles);
 int pace_b200_halo_peer_plan(void* handle, int plan_id, int n_peers, const int* peer_ranks, const int* pack_plan_ids,
-                             int unpack_plan_id);
+                             int unpack_plan_id, long long max_recv_cells);
 int pace_b200_halo_peer_update(void* handle, int plan_id, const char* const* x_names, const char* const* y_names, int n,
                                int nk);
 /* Waits for the stream's work, then: number of barriers executed, and the sequence number of a barrier that gave up

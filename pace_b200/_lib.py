@@ -105,7 +105,7 @@ def bind(lib):
     lib.pace_b200_set_halo_callback.argtypes = [vp, HALO_CALLBACK, vp]
     lib.pace_b200_set_stage_callback.argtypes = [vp, STAGE_CALLBACK, vp]
     lib.pace_b200_halo_peer_arena.argtypes = [vp, _I, _I, ctypes.POINTER(vp), ctypes.c_longlong]
-    lib.pace_b200_halo_peer_plan.argtypes = [vp, _I, _I, ctypes.POINTER(_I), ctypes.POINTER(_I), _I]
+    lib.pace_b200_halo_peer_plan.argtypes = [vp, _I, _I, ctypes.POINTER(_I), ctypes.POINTER(_I), _I, ctypes.c_longlong]
     lib.pace_b200_halo_peer_status.argtypes = [vp, ctypes.POINTER(ctypes.c_ulonglong), ctypes.POINTER(ctypes.c_ulonglong)]
     lib.pace_b200_halo_peer_update.argtypes = [vp, _I, ctypes.POINTER(_S), ctypes.POINTER(_S), _I, _I]
     for name, extra in MODULE_CALLS.items():

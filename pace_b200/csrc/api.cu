@@ -121,6 +121,11 @@ int set_column(Core& c, const char* name, const double* host_values, int n) {
 
 Core::~Core() {
   for (void* p : owned) cudaFree(p);
+#ifndef PACE_HOST_EMU
+  if (ev_fork) cudaEventDestroy((cudaEvent_t)ev_fork);
+  if (ev_join) cudaEventDestroy((cudaEvent_t)ev_join);
+  if (side_stream) cudaStreamDestroy(side_stream);
+#endif
 }
 
 static int finish(Core* c, int rc) {
@@ -272,8 +277,8 @@ int pace_b200_halo_peer_arena(void* h, int my_rank, int n_ranks, void* const* ar
   ENTRY(peer_arena_set(*c, my_rank, n_ranks, arena_ptrs, half_doubles))
 }
 int pace_b200_halo_peer_plan(void* h, int plan_id, int n_peers, const int* peer_ranks, const int* pack_plan_ids,
-                             int unpack_plan_id) {
-  ENTRY(peer_plan_set(*c, plan_id, n_peers, peer_ranks, pack_plan_ids, unpack_plan_id))
+                             int unpack_plan_id, long long max_recv_cells) {
+  ENTRY(peer_plan_set(*c, plan_id, n_peers, peer_ranks, pack_plan_ids, unpack_plan_id, max_recv_cells))
 }
 int pace_b200_halo_peer_status(void* h, unsigned long long* barriers_done, unsigned long long* timed_out) {
   ENTRY(peer_status(*c, barriers_done, timed_out))

@@ -69,13 +69,24 @@ struct Core {
   struct PeerPlan {
     std::vector<int> peer_ranks, pack_ids;
     int unpack_id = -1;
+    long long max_recv_cells = 0;   // largest number of cells any rank receives in one update of this plan
     bool set = false;
+    // all pack plans and the local gather plan in one device list (one launch per update): ops + the peer slot each op
+    // stores to (-1: same-GPU gather)
+    void* merged_ops = nullptr;
+    int* merged_slot = nullptr;
+    int n_merged = 0;
   };
   std::vector<char*> arena_ptrs;
   int peer_rank = 0;
   long long half_doubles = 0;
   unsigned long long peer_updates = 0;    // halo updates issued so far: its parity selects the message half
   void* peer_dev = nullptr;               // device block: barrier sequence number, error word, flag-slot pointers
+  // an exchange whose halos are not needed right away runs on a side stream while the main stream computes
+  // (step.cu: halo_begin / halo_end); at most one is open, and no other exchange is issued while it is
+  cudaStream_t side_stream = 0;
+  void *ev_fork = nullptr, *ev_join = nullptr;   // cudaEvent_t
+  bool async_open = false;
   PeerPlan peer_plans[16];
 
   double* F(const char* name);              // caller-registered field, error if missing
@@ -101,8 +112,12 @@ int halo_pack(Core& c, int plan_id, const char* const* x_names, const char* cons
 int halo_unpack(Core& c, int plan_id, const char* const* x_names, const char* const* y_names, int n, int nk,
                 const double* buf);
 int peer_arena_set(Core& c, int my_rank, int n_ranks, void* const* arena_ptrs, long long half_doubles);
-int peer_plan_set(Core& c, int plan_id, int n_peers, const int* peer_ranks, const int* pack_plan_ids, int unpack_plan_id);
+int peer_plan_set(Core& c, int plan_id, int n_peers, const int* peer_ranks, const int* pack_plan_ids, int unpack_plan_id,
+                  long long max_recv_cells);
 int peer_halo_update(Core& c, int plan_id, const char* const* x_names, const char* const* y_names, int n, int nk);
+// two updates that share a wait point as one exchange (one barrier): plan A's message first, plan B's behind it
+int peer_halo_update2(Core& c, int plan_a, const char* const* xa, const char* const* ya, int na, int nka, int plan_b,
+                      const char* const* xb, const char* const* yb, int nb, int nkb);
 int peer_barrier(Core& c);
 int peer_status(Core& c, unsigned long long* seq, unsigned long long* error);
 int tracer_flux_prep(Core& c, int n_split);

@@ -255,6 +255,10 @@ __global__ void __launch_bounds__(TX * NTY, 6) k_delnflux_fused(Geo g, DelnFused
 // expressions are those of the tile kernel (same bits).  Cube-corner copies concern only the tiles that hold corner
 // cells on levels with nord > 0: those tiles are left to the tile kernel (corner_only) and skipped here.
 constexpr int MSW = 26;
+#ifndef PACE_DELN_PF_ROWS
+#define PACE_DELN_PF_ROWS 6
+#endif
+constexpr int PF_ROWS = PACE_DELN_PF_ROWS;  // L2 prefetch distance in rows beyond the register prefetch
 constexpr unsigned MFULL = 0xffffffffu;
 
 struct DelnMarchArgs {
@@ -339,6 +343,15 @@ __global__ void __launch_bounds__(128, 4) k_delnflux_march(Geo g, DelnMarchArgs 
       if (ld_fx) ofx_b = fxo_p[c3 + rout];
       if (ld_fy) ofy_b = fyo_p[c3 + rout];
       if (accm) ms_b = ms_p[c3 + rout];
+      // ask L2 for the rows a few steps further ahead (no register is tied up; one request per 32-byte sector), so that
+      // the two-row register prefetch above finds its data in L2 instead of DRAM
+      if (PF_ROWS > 0 && (lane & 3) == 0) {
+        const int pin = row_in(R + 2 + PF_ROWS), pout = row_out(R + 2 + PF_ROWS);
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(q + c3 + pin));
+        if (ld_fx) asm volatile("prefetch.global.L2 [%0];" ::"l"(fxo_p + c3 + pout));
+        if (ld_fy) asm volatile("prefetch.global.L2 [%0];" ::"l"(fyo_p + c3 + pout));
+        if (accm) asm volatile("prefetch.global.L2 [%0];" ::"l"(ms_p + c3 + pout));
+      }
     }
     const double d0 = has_mass ? qv : dampk * qv;
     const double fx0 = dv0 * (__shfl_up_sync(MFULL, d0, 1) - d0);

@@ -75,6 +75,23 @@ __global__ void k_halo(Geo g, const HaloOpDev* ops, HaloFields f, int nk, int mo
 }
 #endif
 
+#ifndef PACE_HOST_EMU
+// One launch for the sending half of an update: the ops of every peer's pack plan (slot >= 0: stored into that peer's
+// arena) and of the same-GPU gather plan (slot -1).
+struct PeerBufs { double* b[16]; };
+__global__ void k_halo_send(Geo g, const HaloOpDev* ops, const int* slot, HaloFields f, int nk, PeerBufs bufs) {
+  const HaloOpDev o = ops[blockIdx.x];
+  const int s = slot[blockIdx.x];
+  const int k = blockIdx.y;
+  const int cells = o.ni * o.nj;
+  for (int q = 0; q < f.n; ++q)
+    for (int c = threadIdx.x; c < cells; c += blockDim.x) {
+      if (s < 0) halo_cell(g, o, f, q, k, c);
+      else halo_pack_cell(g, o, f, bufs.b[s], nk, q, k, c);
+    }
+}
+#endif
+
 int halo_plan_set(Core& c, int plan_id, const void* host_ops, int n_ops) {
   if (plan_id < 0 || plan_id >= 256) { c.err = "halo plan id out of range"; return 1; }
   static_assert(sizeof(HaloOpDev) == 64, "HaloOpDev layout is part of the C ABI (pace_b200_halo_op)");
@@ -223,13 +240,44 @@ int peer_status(Core& c, unsigned long long* seq, unsigned long long* error) {
 #endif
 }
 
-int peer_plan_set(Core& c, int plan_id, int n_peers, const int* peer_ranks, const int* pack_plan_ids, int unpack_plan_id) {
+int peer_plan_set(Core& c, int plan_id, int n_peers, const int* peer_ranks, const int* pack_plan_ids, int unpack_plan_id,
+                  long long max_recv_cells) {
   if (plan_id < 0 || plan_id >= 16) { c.err = "peer_plan_set: plan id out of range"; return 1; }
   Core::PeerPlan& p = c.peer_plans[plan_id];
   p.peer_ranks.assign(peer_ranks, peer_ranks + n_peers);
   p.pack_ids.assign(pack_plan_ids, pack_plan_ids + n_peers);
   p.unpack_id = unpack_plan_id;
+  p.max_recv_cells = max_recv_cells;
   p.set = true;
+#ifndef PACE_HOST_EMU
+  // merged send list: the pack plans (in peer order) followed by the local gather plan
+  if (n_peers > 16) { c.err = "peer_plan_set: more than 16 peer GPUs"; return 1; }
+  int total = c.halo_nops[plan_id];
+  for (int m = 0; m < n_peers; ++m) total += c.halo_nops[pack_plan_ids[m]];
+  p.n_merged = total;
+  if (total > 0) {
+    void *ops = nullptr, *slots = nullptr;
+    if (cudaMalloc(&ops, sizeof(HaloOpDev) * total) != cudaSuccess || cudaMalloc(&slots, sizeof(int) * total) != cudaSuccess) {
+      c.err = "cudaMalloc failed for the merged halo plan";
+      return 1;
+    }
+    c.owned.push_back(ops);
+    c.owned.push_back(slots);
+    std::vector<int> hs(total);
+    int at = 0;
+    for (int m = 0; m <= n_peers; ++m) {
+      const int id = m < n_peers ? pack_plan_ids[m] : plan_id;
+      const int n = c.halo_nops[id];
+      if (n > 0)
+        CUDA_CHECK_RET(cudaMemcpy((HaloOpDev*)ops + at, c.halo_ops[id], sizeof(HaloOpDev) * n, cudaMemcpyDeviceToDevice));
+      for (int q = 0; q < n; ++q) hs[at + q] = m < n_peers ? m : -1;
+      at += n;
+    }
+    CUDA_CHECK_RET(cudaMemcpy(slots, hs.data(), sizeof(int) * total, cudaMemcpyHostToDevice));
+    p.merged_ops = ops;
+    p.merged_slot = (int*)slots;
+  }
+#endif
   return 0;
 }
 
@@ -245,16 +293,58 @@ int peer_barrier(Core& c) {
 #endif
 }
 
+// the sending half of one update of `plan_id`: pack into every peer's arena at byte offset `off`, gather locally
+static int peer_send(Core& c, int plan_id, const char* const* x_names, const char* const* y_names, int n, int nk,
+                     long long off_doubles) {
+#ifndef PACE_HOST_EMU
+  const Core::PeerPlan& p = c.peer_plans[plan_id];
+  if (n < 1 || n > 8) { c.err = "halo_update: 1..8 fields per call"; return 1; }
+  if (p.n_merged == 0) return 0;
+  HaloFields f;
+  f.n = n;
+  for (int q = 0; q < n; ++q) {
+    f.x[q] = c.F(x_names[q]);
+    f.y[q] = y_names ? c.F(y_names[q]) : nullptr;
+  }
+  if (!c.err.empty()) return 1;
+  PeerBufs bufs;
+  for (size_t m = 0; m < p.peer_ranks.size(); ++m) bufs.b[m] = (double*)c.arena_ptrs[p.peer_ranks[m]] + off_doubles;
+  LaunchScope scope(c.stream, "halo_send");
+  k_halo_send<<<dim3(p.n_merged, nk), 128, 0, c.stream>>>(c.g, (const HaloOpDev*)p.merged_ops, p.merged_slot, f, nk, bufs);
+  return 0;
+#else
+  (void)plan_id; (void)x_names; (void)y_names; (void)n; (void)nk; (void)off_doubles;
+  c.err = "peer-store halo exchange exists only in the CUDA library";
+  return 1;
+#endif
+}
+
 int peer_halo_update(Core& c, int plan_id, const char* const* x_names, const char* const* y_names, int n, int nk) {
   const Core::PeerPlan& p = c.peer_plans[plan_id];
   const long long half = (long long)(c.peer_updates & 1) * c.half_doubles;
   ++c.peer_updates;
-  for (size_t m = 0; m < p.peer_ranks.size(); ++m)
-    if (halo_pack(c, p.pack_ids[m], x_names, y_names, n, nk, (double*)c.arena_ptrs[p.peer_ranks[m]] + half)) return 1;
-  if (halo_update(c, plan_id, x_names, y_names, n, nk)) return 1;  // same-GPU neighbours meanwhile
+  if (p.max_recv_cells * n * nk > c.half_doubles) { c.err = "halo update larger than the peer arena"; return 1; }
+  if (peer_send(c, plan_id, x_names, y_names, n, nk, half)) return 1;
   if (peer_barrier(c)) return 1;
   if (p.unpack_id >= 0 && halo_unpack(c, p.unpack_id, x_names, y_names, n, nk, (double*)c.arena_ptrs[c.peer_rank] + half))
     return 1;
+  return 0;
+}
+
+int peer_halo_update2(Core& c, int plan_a, const char* const* xa, const char* const* ya, int na, int nka, int plan_b,
+                      const char* const* xb, const char* const* yb, int nb, int nkb) {
+  const Core::PeerPlan &pa = c.peer_plans[plan_a], &pb = c.peer_plans[plan_b];
+  const long long half = (long long)(c.peer_updates & 1) * c.half_doubles;
+  ++c.peer_updates;
+  // every rank places B's message behind the largest A message any rank receives: the same offset everywhere
+  const long long off_b = pa.max_recv_cells * na * nka;
+  if (off_b + pb.max_recv_cells * nb * nkb > c.half_doubles) { c.err = "merged halo update larger than the peer arena"; return 1; }
+  if (peer_send(c, plan_a, xa, ya, na, nka, half)) return 1;
+  if (peer_send(c, plan_b, xb, yb, nb, nkb, half + off_b)) return 1;
+  if (peer_barrier(c)) return 1;
+  double* mine = (double*)c.arena_ptrs[c.peer_rank] + half;
+  if (pa.unpack_id >= 0 && halo_unpack(c, pa.unpack_id, xa, ya, na, nka, mine)) return 1;
+  if (pb.unpack_id >= 0 && halo_unpack(c, pb.unpack_id, xb, yb, nb, nkb, mine + off_b)) return 1;
   return 0;
 }
 

@@ -6,6 +6,8 @@
 // _compute (fv_dynamics.py:445-655).  Where the reference starts a halo update early and waits later
 // (HaloUpdater.start / wait) the fields are not modified in between, so the update is issued at the wait point.
 // Host code only: it orders module calls (each a few kernel launches on the handle's stream) and halo updates.
+#include <cstdlib>
+
 #include "../../include/pace_b200.h"
 #include "core.hpp"
 
@@ -58,6 +60,61 @@ static int halo(Core& c, int plan, const Names& x, const Names* y = nullptr, int
   return halo_update(c, plan, x.v, y ? y->v : nullptr, x.n, nk);
 }
 
+// two updates the reference waits for at the same point
+static int halo2(Core& c, int plan_a, const Names& xa, const Names* ya, int nka, int plan_b, const Names& xb, const Names* yb,
+                 int nkb) {
+  if (nka < 0) nka = c.g.nz;
+  if (nkb < 0) nkb = c.g.nz;
+  if (plan_a < 16 && plan_b < 16 && c.peer_plans[plan_a].set && c.peer_plans[plan_b].set && !c.arena_ptrs.empty())
+    return peer_halo_update2(c, plan_a, xa.v, ya ? ya->v : nullptr, xa.n, nka, plan_b, xb.v, yb ? yb->v : nullptr, xb.n, nkb);
+  if (halo(c, plan_a, xa, ya, nka)) return 1;
+  return halo(c, plan_b, xb, yb, nkb);
+}
+
+// HaloUpdater.start() ... wait() with compute in between (dyn_core.py:763/810: divgd across update_dz_c / riem_solver_c /
+// p_grad_c; the delp / pt / q_con update is not needed before pk3_halo either): with peer arenas the whole exchange is
+// queued on a side stream behind an event, the main stream goes on with kernels that touch neither the halos being
+// filled nor the arenas, and halo_end makes the main stream wait for it.  Every rank opens and closes the same
+// exchanges in the same order, and none is issued in between, so the barriers stay in step across the GPUs.
+static int halo_begin(Core& c, int plan, const Names& x, const Names* y = nullptr, int nk = -1) {
+#ifndef PACE_HOST_EMU
+  static const bool no_overlap = [] { const char* v = getenv("PACE_B200_HALO_OVERLAP"); return v && v[0] == '0'; }();
+  const bool peer = plan < 16 && c.peer_plans[plan].set && !c.arena_ptrs.empty();
+  if (peer && !no_overlap && !c.async_open) {
+    if (!c.side_stream) {
+      cudaEvent_t a, b;
+      if (cudaStreamCreateWithFlags(&c.side_stream, cudaStreamNonBlocking) != cudaSuccess ||
+          cudaEventCreateWithFlags(&a, cudaEventDisableTiming) != cudaSuccess ||
+          cudaEventCreateWithFlags(&b, cudaEventDisableTiming) != cudaSuccess) {
+        c.err = "cannot create the halo side stream";
+        return 1;
+      }
+      c.ev_fork = a; c.ev_join = b;
+    }
+    cudaEventRecord((cudaEvent_t)c.ev_fork, c.stream);
+    cudaStreamWaitEvent(c.side_stream, (cudaEvent_t)c.ev_fork, 0);
+    cudaStream_t main_stream = c.stream;
+    c.stream = c.side_stream;
+    const int rc = halo(c, plan, x, y, nk);
+    c.stream = main_stream;
+    if (rc) return 1;
+    cudaEventRecord((cudaEvent_t)c.ev_join, c.side_stream);
+    c.async_open = true;
+    return 0;
+  }
+#endif
+  return halo(c, plan, x, y, nk);
+}
+static int halo_end(Core& c) {
+#ifndef PACE_HOST_EMU
+  if (c.async_open) {
+    cudaStreamWaitEvent(c.stream, (cudaEvent_t)c.ev_join, 0);
+    c.async_open = false;
+  }
+#endif
+  return 0;
+}
+
 static int stage(Core& c, const char* savepoint) {
   if (!c.stage_cb) return 0;
   if (c.stage_cb(c.stage_user, savepoint) != 0) {
@@ -83,12 +140,16 @@ int acoustic(Core& c, double timestep, int n_map) {
       RUN(halo(c, A3, Names{"delp", "pt"}));
     }
     if (it == n_split - 1 && end_step && cfg.use_old_omega) RUN(pem_from_delp(c));
-    RUN(halo(c, D3, u, &v));
-    RUN(halo(c, A3, Names{"w"}));
+    RUN(halo2(c, D3, u, &v, -1, A3, Names{"w"}, nullptr, -1));
     RUN(stage(c, "C_SW-In"));
     RUN(c_sw(c, dt2));
     RUN(stage(c, "C_SW-Out"));
-    if (cfg.nord > 0) RUN(halo(c, B3, Names{"ad.divgd"}));
+    // divgd is next read by d_sw: its exchange overlaps the C-grid height update, Riemann solver and pressure gradient
+    // (first substep: the gz update follows at once, so it is done in line)
+    if (cfg.nord > 0) {
+      if (it == 0) RUN(halo(c, B3, Names{"ad.divgd"}));
+      else RUN(halo_begin(c, B3, Names{"ad.divgd"}));
+    }
     // the reference copies gz -> zh (first substep) or zh -> gz (later ones) and then updates gz from two corner-filled
     // copies of it; zh IS that pre-update copy, so the update reads zh and (later substeps) writes all of gz
     if (it == 0) {
@@ -98,15 +159,17 @@ int acoustic(Core& c, double timestep, int n_map) {
     RUN(update_dz_c_from_zh(c, dt2, it == 0));
     RUN(riem_solver_c(c, dt2));
     RUN(p_grad_c(c, dt2));
+    RUN(halo_end(c));
     RUN(halo(c, C3, uc, &vc));
     RUN(stage(c, "D_SW-In"));
     RUN(d_sw(c, dt));
     RUN(stage(c, "D_SW-Out"));
-    RUN(halo(c, A3, Names{"delp", "pt", "q_con"}));
+    // update_dz_d and riem_solver3 read delp, pt, q_con on the compute domain only: their halo update overlaps both
+    RUN(halo_begin(c, A3, Names{"delp", "pt", "q_con"}));
     RUN(update_dz_d(c, dt));
     RUN(riem_solver3(c, dt, remap_step));
-    RUN(halo(c, A3, Names{"ad.zh"}, nullptr, npz + 1));
-    RUN(halo(c, A2, Names{"ad.pkc"}, nullptr, npz + 1));
+    RUN(halo_end(c));
+    RUN(halo2(c, A3, Names{"ad.zh"}, nullptr, npz + 1, A2, Names{"ad.pkc"}, nullptr, npz + 1));
     if (remap_step) RUN(edge_pe(c));
     RUN(pk3_halo(c));
     RUN(compute_geopotential(c));

@@ -164,7 +164,8 @@ class HaloExchanger:
                 ranks = (ctypes.c_int * max(1, n))(*[p for p, _ in self.peer_packs])
                 pids = (ctypes.c_int * max(1, n))(*[pid for _, pid in self.peer_packs])
                 rc = core.lib.pace_b200_halo_peer_plan(core.handle, plan_id, n, ranks, pids,
-                                                       self.unpack_id if self.remote else -1)
+                                                       self.unpack_id if self.remote else -1,
+                                                       self.max_recv_cells(global_ops, placement))
                 if rc != 0:
                     raise RuntimeError("halo_peer_plan: %s" % core.lib.pace_b200_last_error(core.handle).decode())
 
