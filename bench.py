@@ -387,7 +387,13 @@ def main():
         bytes_per_cell = {"fvtp2d_inner_ppm": 5 * 8, "fvtp2d_qi_qj": 7 * 8, "fvtp2d_outer_ppm": 10 * 8,
                           "fvtp2d_fused": 8.4 * 8,
                           # dense launches of a step: delp, vorticity, zh (7 passes), w, pt (9 passes) per substep -> 7.8
-                          "fvtp2d_march": 7.8 * 8, "fvtp2d_march_sparse": 9 * 8, "riem_solver_c": 8 * 8, "riem_solver3": 15 * 8, "remap_scalars_column": 40 * 8}.get(top, 8 * 8)
+                          "fvtp2d_march": 7.8 * 8, "fvtp2d_march_sparse": 9 * 8, "riem_solver_c": 8 * 8, "riem_solver3": 15 * 8, "remap_scalars_column": 40 * 8,
+                          # c_sw: u, v, delp, pt, w read; uc, vc, ua, va, ut, vt, divgd, omga, delpc, ptc written
+                          "c_sw_fused": 15 * 8,
+                          # DelnFlux: q (+ mass) read, fx / fy read-modify-written or fx2 / fy2 / d2 written
+                          "delnflux_march": 5.5 * 8, "delnflux_fused": 5.5 * 8,
+                          # divergence damping loop: divg_d read; delpc, d_N, uc, vc written
+                          "dd_march": 5 * 8}.get(top, 8 * 8)
         alg_bytes = cells / world * bytes_per_cell  # this GPU's share of the cells
         achieved = alg_bytes / (per_launch_ms / 1000.0) / 1e9
         # measured DRAM bytes per launch of that kernel from the committed ncu capture (profiles/traffic_r01.json),
@@ -445,7 +451,7 @@ def main():
         hin, hout = pipe.pinned_like(), pipe.pinned_like()
         for k in pipe.names:
             hin[k].copy_(core.t[k])
-        k_e2e = min(max(args.steps, 3), 6)
+        k_e2e = min(max(args.steps, 3), 12)  # pipeline fill (one upload) and drain (one download) are inside the timing
         fence()
         t0 = time.time()
         pipe.run(k_e2e, hin, hout)
@@ -454,7 +460,9 @@ def main():
         nbytes = pipe.bytes_per_step
         e2e = {"value": DT_ATMOS / (e2e_ms / 1000.0), "unit": "simulated days / day", "ms_per_step": e2e_ms,
                "h2d_bytes_per_step": pipe.upload_bytes_per_step * world, "d2h_bytes_per_step": nbytes * world,
-               "steps": k_e2e, "fields": len(pipe.names), "fields_uploaded": len(pipe.upload_names), "overlap": "upload(n+1) / download(n-1) on side streams during step n"}
+               "steps": k_e2e, "fields": len(pipe.names), "fields_uploaded": len(pipe.upload_names),
+               "h2d_gbs": pipe.upload_bytes_per_step / (e2e_ms / 1000.0) / 1e9, "d2h_gbs": nbytes / (e2e_ms / 1000.0) / 1e9,
+               "overlap": "upload(n+1) / download(n-1) on side streams during step n"}
         del hin, hout, pipe
 
     cpu = None

@@ -115,13 +115,16 @@ int d_sw(Core& c, double dt) {
     A0(mfy) = A0(mfy) + A0(tfy);
   });
   // 4. delnflux_nosg_w(w)
+  DelnHeat heat;
+  heat.dw = dw; heat.heat_s = heat_s; heat.col_damp_w = col_damp_w; heat.col_ke_bg = col_ke_bg; heat.absdt = fabs(dt);
   {
     DelnArgs d;
     d.q = w; d.fx = fx2; d.fy = fy2; d.nord_col = col_nord_w; d.damp = damp_w_c; d.d2 = wk; d.nmax = nmax_w; d.nk = nz;
+    d.heat = &heat;
     if (delnflux(c, d)) return 1;
   }
-  // 5. heat_diss
-  launch_ijk(st, g, box_dims(g, 0, 0, 0), [=] __device__(const Pt& p) {
+  // 5. heat_diss (evaluated inside the DelnFlux kernels when they ran: heat.done)
+  if (!heat.done) launch_ijk(st, g, box_dims(g, 0, 0, 0), [=] __device__(const Pt& p) {
     double hs = 0.0;
     if (col_damp_w[p.k] > 1e-5) {
       double dd8 = col_ke_bg[p.k] * fabs(dt);

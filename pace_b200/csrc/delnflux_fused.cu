@@ -29,6 +29,13 @@ struct DelnFusedArgs {
   const int* lvl;
   int nk, accumulate;
   int corner_only;  // 1: only the tiles that see cube-corner cells on levels with nord > 0 run (the rest: k_delnflux_march)
+  // heat != 0 (d_sw's call for w, not accumulating): instead of storing fx2 / fy2 / d2, the kernels apply heat_diss
+  // (d_sw.py:87-125) to them right away: dw = div(fx2, fy2) * rarea and heat_s = dd8 - dw * (w + 0.5 dw) on the compute
+  // domain (w = q).  Saves three written and three re-read field passes and a launch.
+  int heat;
+  double *hdw, *hheat;
+  const double *col_damp_w, *col_ke_bg;
+  double absdt;
 };
 
 constexpr int RG = 6, RPG = (H + RG - 1) / RG;  // fast path: thread = (column, row group), RPG rows per group
@@ -215,7 +222,7 @@ __global__ void __launch_bounds__(TX * NTY, 6) k_delnflux_fused(Geo g, DelnFused
         if (a.accumulate) {
           if (has_mass) a.fx[o] = a.fx[o] + 0.5 * dampk * (a.mass[o - 1] + a.mass[o]) * f;
           else a.fx[o] = a.fx[o] + f;
-        } else {
+        } else if (!a.heat) {
           a.fx[o] = f;
         }
       }
@@ -224,9 +231,20 @@ __global__ void __launch_bounds__(TX * NTY, 6) k_delnflux_fused(Geo g, DelnFused
         if (a.accumulate) {
           if (has_mass) a.fy[o] = a.fy[o] + 0.5 * dampk * (a.mass[o - sj] + a.mass[o]) * f;
           else a.fy[o] = a.fy[o] + f;
-        } else {
+        } else if (!a.heat) {
           a.fy[o] = f;
         }
+      }
+      if (a.heat && li < TX && lj < TY && i <= ie && j <= je) {
+        double hs = 0.0;
+        if (a.col_damp_w[k] > 1e-5) {
+          const double dd8 = a.col_ke_bg[k] * a.absdt;
+          const double dwv = (fx2[lj + AP][li + AP] - fx2[lj + AP][li + AP + 1] + fy2[lj + AP][li + AP] - fy2[lj + AP + 1][li + AP]) *
+                             a.rarea[base2 + j * sj + i];
+          a.hdw[o] = dwv;
+          hs = dd8 - dwv * (a.q[o] + 0.5 * dwv);
+        }
+        a.hheat[o] = hs;
       }
     }
   }
@@ -309,7 +327,10 @@ __global__ void __launch_bounds__(128, 4) k_delnflux_march(Geo g, DelnMarchArgs 
   const bool tnear_w = eW && ti0 - AP < is, tnear_e = eE && ti0 + TX + AP - 1 > ie;
   const bool lane_corner_x = N > 0 && (tnear_w || tnear_e);
 
-  const int R0 = max(0, j_lo - 1 - N - 1), R1 = j_hi + N;
+  // with the heat_diss epilogue one more row is needed: dw of row j uses fy2 of row j + 1
+  const int R0 = max(0, j_lo - 1 - N - 1), R1 = min(j_hi + N + (a.heat ? 1 : 0), g.ny + 6);
+  double hfx_p = 0.0, hfy_p = 0.0;             // delivered fluxes of the previous step (row jo - 1)
+  double qh1 = 0.0, qh2 = 0.0, qh3 = 0.0, ra3 = 0.0;  // q at rows R-1 .. R-3, rarea at row R-3
   double d0p = 0.0, fx0p = 0.0, fy0p = 0.0;   // level 0 at row R-1
   double d1p = 0.0, fx1p = 0.0, fy1p = 0.0;   // level 1 at row R-2
   double d2p = 0.0;                            // level 2 at row R-3
@@ -371,7 +392,33 @@ __global__ void __launch_bounds__(128, 4) k_delnflux_march(Geo g, DelnMarchArgs 
       }
     }
     const int jo = R - N;
-    if (jo >= j_lo && jo <= j_hi) {  // warp-uniform
+    if (a.heat) {  // warp-uniform: heat_diss of row jo - 1, now that fy2 of row jo is known
+      const int jh = jo - 1;
+      const double fx_r = __shfl_down_sync(MFULL, hfx_p, 1);
+      if (jh >= max(j_lo, js) && jh <= min(j_hi, je) && own_f && i >= is && i <= ie) {
+        bool skip = false;
+        if (lane_corner_x) {
+          const int tby = min(max(jh - js, 0) / TY, m.nty - 1);
+          const int tj0 = js + tby * TY;
+          skip = (eS && tj0 - AP < js) || (eN && tj0 + TY + AP - 1 > je);
+        }
+        if (!skip) {
+          const int o = base3 + jh * sj + i;
+          double hs = 0.0;
+          if (a.col_damp_w[k] > 1e-5) {
+            const double dd8 = a.col_ke_bg[k] * a.absdt;
+            const double ra_h = N == 2 ? ra3 : N == 1 ? ra2 : ra1;   // rarea of row jh = R - N - 1
+            const double w_h = N == 2 ? qh3 : N == 1 ? qh2 : qh1;    // w of row jh
+            const double dwv = (hfx_p - fx_r + hfy_p - fyo) * ra_h;
+            a.hdw[o] = dwv;
+            hs = dd8 - dwv * (w_h + 0.5 * dwv);
+          }
+          a.hheat[o] = hs;
+        }
+      }
+      hfx_p = fxo; hfy_p = fyo;
+    }
+    if (!a.heat && jo >= j_lo && jo <= j_hi) {  // warp-uniform
       double m_l = 0.0;
       if (accm) m_l = __shfl_up_sync(MFULL, m_0, 1);  // mass of the column to the left
       // does (i, jo) belong to a tile the tile kernel handles?
@@ -405,8 +452,10 @@ __global__ void __launch_bounds__(128, 4) k_delnflux_march(Geo g, DelnMarchArgs 
     d2p = d2;
     d1p = d1; fx1p = fx1; fy1p = fy1;
     d0p = d0; fx0p = fx0; fy0p = fy0;
+    ra3 = ra2;
     dv2 = dv1; du2 = du1; ra2 = ra1;
     dv1 = dv0; du1 = du0; ra1 = ra0;
+    qh3 = qh2; qh2 = qh1; qh1 = qv;
   }
 }
 }  // namespace
@@ -420,6 +469,12 @@ int delnflux_fused_launch(Core& c, const DelnArgs& a) {
   f.fx = a.fx; f.fy = a.fy; f.d2out = a.d2; f.nk = a.nk; f.accumulate = a.accumulate ? (zero_paths_enabled() ? 1 : 2) : 0;  // 2: accumulate, no zero-tile shortcut
   f.lvl = a.level_nonzero;
   f.corner_only = 0;
+  f.heat = 0; f.hdw = nullptr; f.hheat = nullptr; f.col_damp_w = nullptr; f.col_ke_bg = nullptr; f.absdt = 0.0;
+  if (a.heat && !a.accumulate) {
+    f.heat = 1; f.hdw = a.heat->dw; f.hheat = a.heat->heat_s; f.col_damp_w = a.heat->col_damp_w;
+    f.col_ke_bg = a.heat->col_ke_bg; f.absdt = a.heat->absdt; f.d2out = nullptr;
+    a.heat->done = true;
+  }
   if (!c.err.empty()) return 1;
   dim3 blk(TX, NTY, 1);
   dim3 grd((g.nx + TX - 1) / TX, (g.ny + TY - 1) / TY, a.nk * g.nt);

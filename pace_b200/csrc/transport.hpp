@@ -24,6 +24,14 @@ int fvtp2d(Core& c, const Fvtp2dArgs& a);
 // when the build has no such kernel (host emulation: everything is computed)
 const int* level_nonzero_flags(Core& c, const double* q, int nk);
 
+// heat_diss (d_sw.py:87-125) applied to the damping fluxes of w inside the DelnFlux kernels (optional)
+struct DelnHeat {
+  double *dw, *heat_s;
+  const double *col_damp_w, *col_ke_bg;
+  double absdt;
+  bool done = false;   // set by delnflux when its kernels evaluated heat_diss (the fluxes are then not stored)
+};
+
 // DelnFluxNoSG.__call__ (+ DelnFlux accumulation when accumulate=true)
 struct DelnArgs {
   const double* q = nullptr;
@@ -34,6 +42,7 @@ struct DelnArgs {
   int nmax = 0, nk = 0;
   bool accumulate = false;
   const int* level_nonzero = nullptr;        // accumulate only: levels of zeros (see Fvtp2dArgs) add nothing
+  DelnHeat* heat = nullptr;                  // not accumulating: see DelnHeat
 };
 int delnflux(Core& c, const DelnArgs& a);
 

@@ -41,7 +41,9 @@ CASES = {
                          "ad.divgd": (0, 1), "uc": (0, 1), "vc": (0, 1)},
                  # private work fields of the reference class that the kernels no longer materialise: the differences
                  # of the damped vorticity are formed in registers by the heat-source kernel (its outputs are compared)
-                 skip=("dsw.vort_x_delta", "dsw.vort_y_delta")),
+                 # ... and the damping fluxes of w (tmp_fx2 / tmp_fy2 / tmp_wk), consumed by heat_diss inside the DelnFlux
+                 # kernels on the GPU (its outputs tmp_dw / tmp_heat_s are compared)
+                 skip=("dsw.vort_x_delta", "dsw.vort_y_delta", "dsw.tmp_fx2", "dsw.tmp_fy2", "dsw.tmp_wk")),
     "d_sw_module": dict(stage="d_sw", call="d_sw", args=(DT,), tol=0.0,
                         region={"ad.divgd": (0, 1), "uc": (0, 1), "vc": (0, 1)}),
     "c_sw": dict(stage="c_sw", call="c_sw", args=(DT2,), tol=0.0),
