@@ -286,6 +286,9 @@ struct DelnMarchArgs {
   long long items;
 };
 
+// ACC: accumulate into existing fluxes (their old values and the mass are extra input streams); HEAT: heat_diss epilogue.
+// Separate instantiations keep the registers of the streams / epilogue a call does not use out of the others.
+template <bool ACC, bool HEAT>
 __global__ void __launch_bounds__(128, 4) k_delnflux_march(Geo g, DelnMarchArgs m) {
   const DelnFusedArgs& a = m.f;
   const long long item = (long long)blockIdx.x * 4 + (threadIdx.x >> 5);
@@ -297,7 +300,7 @@ __global__ void __launch_bounds__(128, 4) k_delnflux_march(Geo g, DelnMarchArgs 
   const int chunk = (int)(r1 % m.nchunks);
   r1 /= m.nchunks;
   const int k = (int)(r1 % a.nk), t = (int)(r1 / a.nk);
-  if (a.lvl != nullptr && a.accumulate && a.lvl[t * a.nk + k] == 0) return;  // a level of zeros adds no damping flux
+  if (ACC && a.lvl != nullptr && a.lvl[t * a.nk + k] == 0) return;  // a level of zeros adds no damping flux
   const int is = g.is, ie = g.ie, js = g.js, je = g.je, sj = g.sj;
   const unsigned ed = edge_of(g, t);
   const bool eW = ed & EDGE_W, eE = ed & EDGE_E, eS = ed & EDGE_S, eN = ed & EDGE_N;
@@ -328,7 +331,7 @@ __global__ void __launch_bounds__(128, 4) k_delnflux_march(Geo g, DelnMarchArgs 
   const bool lane_corner_x = N > 0 && (tnear_w || tnear_e);
 
   // with the heat_diss epilogue one more row is needed: dw of row j uses fy2 of row j + 1
-  const int R0 = max(0, j_lo - 1 - N - 1), R1 = min(j_hi + N + (a.heat ? 1 : 0), g.ny + 6);
+  const int R0 = max(0, j_lo - 1 - N - 1), R1 = min(j_hi + N + (HEAT ? 1 : 0), g.ny + 6);
   double hfx_p = 0.0, hfy_p = 0.0;             // delivered fluxes of the previous step (row jo - 1)
   double qh1 = 0.0, qh2 = 0.0, qh3 = 0.0, ra3 = 0.0;  // q at rows R-1 .. R-3, rarea at row R-3
   double d0p = 0.0, fx0p = 0.0, fy0p = 0.0;   // level 0 at row R-1
@@ -338,7 +341,8 @@ __global__ void __launch_bounds__(128, 4) k_delnflux_march(Geo g, DelnMarchArgs 
   // Every stream is read two rows ahead of its use (registers): q and the metric terms of the incoming row, and — when
   // accumulating — the old fluxes and the mass of the outgoing row.  With 8 warps per scheduler that is enough distance
   // to cover the DRAM latency.
-  const bool acc = a.accumulate != 0, accm = acc && has_mass;
+  constexpr bool acc = ACC;
+  const bool accm = acc && has_mass;
   const bool ld_fx = acc && st_fx, ld_fy = acc && st_fy;
   const double* fxo_p = a.fx;
   const double* fyo_p = a.fy;
@@ -392,7 +396,7 @@ __global__ void __launch_bounds__(128, 4) k_delnflux_march(Geo g, DelnMarchArgs 
       }
     }
     const int jo = R - N;
-    if (a.heat) {  // warp-uniform: heat_diss of row jo - 1, now that fy2 of row jo is known
+    if (HEAT) {  // heat_diss of row jo - 1, now that fy2 of row jo is known
       const int jh = jo - 1;
       const double fx_r = __shfl_down_sync(MFULL, hfx_p, 1);
       if (jh >= max(j_lo, js) && jh <= min(j_hi, je) && own_f && i >= is && i <= ie) {
@@ -418,7 +422,7 @@ __global__ void __launch_bounds__(128, 4) k_delnflux_march(Geo g, DelnMarchArgs 
       }
       hfx_p = fxo; hfy_p = fyo;
     }
-    if (!a.heat && jo >= j_lo && jo <= j_hi) {  // warp-uniform
+    if (!HEAT && jo >= j_lo && jo <= j_hi) {  // warp-uniform
       double m_l = 0.0;
       if (accm) m_l = __shfl_up_sync(MFULL, m_0, 1);  // mass of the column to the left
       // does (i, jo) belong to a tile the tile kernel handles?
@@ -497,7 +501,10 @@ int delnflux_fused_launch(Core& c, const DelnArgs& a) {
   m.items = (long long)m.nstrips * m.nchunks * a.nk * g.nt;
   {
     LaunchScope scope(c.stream, "delnflux_march");
-    k_delnflux_march<<<(unsigned)((m.items + 3) / 4), 128, 0, c.stream>>>(g, m);
+    const unsigned nb = (unsigned)((m.items + 3) / 4);
+    if (f.heat) k_delnflux_march<false, true><<<nb, 128, 0, c.stream>>>(g, m);
+    else if (f.accumulate) k_delnflux_march<true, false><<<nb, 128, 0, c.stream>>>(g, m);
+    else k_delnflux_march<false, false><<<nb, 128, 0, c.stream>>>(g, m);
   }
   // the tiles that see cube-corner cells (levels with nord > 0)
   const unsigned eb0 = (unsigned)(g.edge_bits[0] | g.edge_bits[1]), eb1 = (unsigned)((g.edge_bits[0] | g.edge_bits[1]) >> 32);

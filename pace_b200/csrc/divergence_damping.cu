@@ -219,6 +219,7 @@ __global__ void __launch_bounds__(128, 4) k_dd_march(Geo g, DdMarchArgs a) {
     {
       const int rin = row(R + 2);
       d_b = a.divg[c3 + rin]; u_b = a.divg_u[c2 + rin]; v_b = a.divg_v[c2 + rin]; r_b = a.rarea_c[c2 + rin];
+      if ((lane & 3) == 0) asm volatile("prefetch.global.L2 [%0];" ::"l"(a.divg + c3 + row(R + 8)));  // see delnflux_fused.cu
     }
     // iteration n works on d_n at row R - n; its results: vc_n(R-n), uc_n(R-n-1), d_{n+1}(R-n-1)
     double dn = d0;

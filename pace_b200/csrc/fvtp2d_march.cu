@@ -106,6 +106,10 @@ __device__ __forceinline__ double cells_flux(double c, double qm, double blm, do
   return q0 + (1.0 + c) * (bl + c * b0) * 1.0;
 }
 
+#ifndef PACE_MARCH_PF_ROWS
+#define PACE_MARCH_PF_ROWS 6
+#endif
+constexpr int PF_ROWS = PACE_MARCH_PF_ROWS;  // L2 prefetch distance (rows) beyond the two-row cp.async staging
 constexpr int NSLOT = 3, NSTREAM = 10;
 constexpr int SW = 26;         // cells per warp strip (32 lanes - 2 x 3 apron)
 constexpr int WPB = 1;         // warps per CTA (independent work items)
@@ -243,6 +247,20 @@ __global__ void __launch_bounds__(WPB * 32, 20) k_fvtp2d_march(Geo g, MarchArgs 
         cp_async8(ring(7, slot) + L, area + o3);
         cp_async8(ring(8, slot) + L, crx + o3);
         cp_async8(ring(9, slot) + L, xunit + o3);
+      }
+    }
+    // ask L2 for the rows a few steps further ahead (one request per 32-byte sector, no register or shared-memory slot
+    // tied up): the cp.async of those rows then finds them in L2 instead of waiting on DRAM
+    if (PF_ROWS > 0 && col_ok && (L & 3) == 0 && Rn + PF_ROWS <= j_hi + 3) {
+      const int op = (Rn + PF_ROWS) * sj + i;
+      asm volatile("prefetch.global.L2 [%0];" ::"l"(q + op));
+      asm volatile("prefetch.global.L2 [%0];" ::"l"(crx + op));
+      asm volatile("prefetch.global.L2 [%0];" ::"l"(xfx + op));
+      asm volatile("prefetch.global.L2 [%0];" ::"l"(cry + op - 2 * sj));
+      asm volatile("prefetch.global.L2 [%0];" ::"l"(yfx + op - 2 * sj));
+      if (yunit != yfx) {  // mass fluxes given: two more streams
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(yunit + op - 2 * sj));
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(xunit + op - 3 * sj));
       }
     }
     asm volatile("cp.async.commit_group;\n" ::: "memory");
