@@ -7,7 +7,7 @@
 // subdomains that lie on a tile edge) take a branch-free path; the others evaluate the same case analysis as
 // a2b_ord4.cu on shared-memory operands.  Expressions and their order are those of a2b_ord4.cu / the reference
 // (pyFV3/stencils/a2b_ord4.py:36-526), so results are bit-identical.
-#include "core.hpp"
+#include "tile.cuh"
 
 namespace pace {
 
@@ -26,8 +26,11 @@ struct A2bArgs {
   int k0, nk;
 };
 
-__global__ void __launch_bounds__(TX * NTY, 6) k_a2b_fused(Geo g, A2bArgs a) {
-  __shared__ double sq[QH][QW];           // qin(i0-3+li, j0-3+lj)
+// The qin tile arrives by TMA (one elected thread, an mbarrier counts the bytes): its box starts at column i0 - 3 = 32 bx,
+// an even index as the 16-byte alignment rule of the TMA unit demands (tile.cuh), and cells outside the array come as zeros.
+__global__ void __launch_bounds__(TX * NTY, 6) k_a2b_fused(Geo g, A2bArgs a, const __grid_constant__ CUtensorMap m_qin) {
+  __shared__ __align__(128) double sq[QH][QW];           // qin(i0-3+li, j0-3+lj)
+  __shared__ __align__(8) unsigned long long bar;
   __shared__ double sqx[QH][TX + 1];      // qx(i0+li, j0-3+lj)
   __shared__ double sqy[TY + 1][QW];      // qy(i0-3+li, j0+lj)
   const int k = a.k0 + blockIdx.z % a.nk, t = blockIdx.z / a.nk;
@@ -44,12 +47,13 @@ __global__ void __launch_bounds__(TX * NTY, 6) k_a2b_fused(Geo g, A2bArgs a) {
   // flat element loops: the tile widths (TX+6, TX+1) are not multiples of the warp size
   const int tid = ty * TX + tx;
   constexpr int NTHR = TX * NTY;
-  for (int n = tid; n < QH * QW; n += NTHR) {
-    const int lj = n / QW, li = n % QW;
-    const int i = i0 - 3 + li, j = j0 - 3 + lj;
-    sq[lj][li] = (i <= imax && j <= jmax) ? a.qin[base3 + j * sj + i] : 0.0;
-  }
+  if (tid == 0) tma::mbar_init(&bar, 1);
   __syncthreads();
+  if (tid == 0) {
+    tma::mbar_expect_tx(&bar, (unsigned)sizeof(sq));
+    tma::load_tile(&sq[0][0], &m_qin, &bar, i0 - 3, j0 - 3, k, t);
+  }
+  tma::mbar_wait(&bar, 0);
   auto Q = [&](int i, int j) { return sq[j - j0 + 3][i - i0 + 3]; };
   auto DXA = [&](int i, int j) { return a.dxa[base2 + j * sj + i]; };
   auto DYA = [&](int i, int j) { return a.dya[base2 + j * sj + i]; };
@@ -285,10 +289,13 @@ int a2b_ord4_fused_launch(Core& c, const double* qin, double* qout, int k0, int 
   a.dxa = c.F("grid.dxa"); a.dya = c.F("grid.dya"); a.edge_w = c.F("grid.edge_w"); a.edge_e = c.F("grid.edge_e");
   a.edge_s = c.F("grid.edge_s"); a.edge_n = c.F("grid.edge_n"); a.coef = c.F("grid.a2b_corner_coef");
   if (!c.err.empty()) return 1;
+  static_assert(QW % 2 == 0 && (TX % 2) == 0 && HALO == 3, "TMA box start i0 - 3 = 32 bx must be even");
+  const CUtensorMap* mq = tile_tensor_map(c, qin, QW, QH);
+  if (!mq) return 1;
   dim3 blk(TX, NTY, 1);
   dim3 grd((g.nx + TX - 1) / TX, (g.ny + TY - 1) / TY, nk * g.nt);
   LaunchScope scope(c.stream, "a2b_ord4_fused");
-  k_a2b_fused<<<grd, blk, 0, c.stream>>>(g, a);
+  k_a2b_fused<<<grd, blk, 0, c.stream>>>(g, a, *mq);
   return 0;
 }
 

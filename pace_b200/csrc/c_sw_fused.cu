@@ -44,8 +44,9 @@ struct CswArgs {
 
 // All phases of one patch.  S: CSW_ARRAYS tile arrays; the first five hold u, v, delp, pt, w.
 // EDGES = false: no tile-edge formula can apply inside this patch's box (Tile::near_edge), every edge test folds away.
-template <class C, bool EDGES>
-__device__ __forceinline__ void c_sw_tile(const Tile<C>& T, const CswArgs& a, typename Tile<C>::Arr* S) {
+// wait_dpw: called once before the first read of the delp / pt / w tiles (their TMA loads run under phases A - C)
+template <class C, bool EDGES, class WaitF>
+__device__ __forceinline__ void c_sw_tile(const Tile<C>& T, const CswArgs& a, typename Tile<C>::Arr* S, WaitF wait_dpw) {
   constexpr int W = C::W, H = C::H;
   auto &Su = S[0], &Sv = S[1], &Sdp = S[2], &Spt = S[3], &Sw = S[4];
   auto &Sutmp = S[5], &Svtmp = S[6], &Sua = S[7], &Sva = S[8], &Suc = S[9], &Svc = S[10], &Sut = S[11], &Svt = S[12];
@@ -239,6 +240,7 @@ __device__ __forceinline__ void c_sw_tile(const Tile<C>& T, const CswArgs& a, ty
   // read "as filled" by fill_corners_2cells_x for the x fluxes and by fill_corners_2cells_y for the y fluxes and the
   // cell's own value (the reference fills in place, x first: c_sw.py:700-760); ke is kept for the patch and one row /
   // column below it, delpc / ptc / omga are stored for own cells; zero_delpc_ptc covers the rest of compute + 3 halo.
+  wait_dpw();
   const bool ct = EDGES && T.corner_tile;
   auto rdx = [&](double(*Sq)[W], int i, int j) {  // q(i, j) after fill_corners_2cells_x
     if (ct) xfill_src(e, 2, i, j);
@@ -349,25 +351,30 @@ __global__ void __launch_bounds__(CswCfg::NT, CSW_CTAS_PER_SM) k_c_sw_fused(Geo 
                                                               const __grid_constant__ CUtensorMap m_w) {
   typedef CswCfg C;
   extern __shared__ __align__(128) unsigned char smem_raw[];
-  __shared__ __align__(8) unsigned long long bar;
+  __shared__ __align__(8) unsigned long long bar, bar2;   // u, v | delp, pt, w
   typename Tile<C>::Arr* S = reinterpret_cast<typename Tile<C>::Arr*>(smem_raw);
   const int k = blockIdx.z % g.nz, t = blockIdx.z / g.nz;
   Tile<C> T = make_tile<C>(g, a.tg, blockIdx.x, blockIdx.y, k, t);
   T.tx = threadIdx.x; T.ty = threadIdx.y;
   const bool leader = threadIdx.x == 0 && threadIdx.y == 0;
-  if (leader) tma::mbar_init(&bar, 1);
+  if (leader) {
+    tma::mbar_init(&bar, 1);
+    tma::mbar_init(&bar2, 1);
+  }
   __syncthreads();
   if (leader) {
-    tma::mbar_expect_tx(&bar, 5u * C::BYTES);
+    tma::mbar_expect_tx(&bar, 2u * C::BYTES);
     tma::load_tile(&S[0], &m_u, &bar, T.bi, T.bj, k, t);
     tma::load_tile(&S[1], &m_v, &bar, T.bi, T.bj, k, t);
-    tma::load_tile(&S[2], &m_dp, &bar, T.bi, T.bj, k, t);
-    tma::load_tile(&S[3], &m_pt, &bar, T.bi, T.bj, k, t);
-    tma::load_tile(&S[4], &m_w, &bar, T.bi, T.bj, k, t);
+    tma::mbar_expect_tx(&bar2, 3u * C::BYTES);
+    tma::load_tile(&S[2], &m_dp, &bar2, T.bi, T.bj, k, t);
+    tma::load_tile(&S[3], &m_pt, &bar2, T.bi, T.bj, k, t);
+    tma::load_tile(&S[4], &m_w, &bar2, T.bi, T.bj, k, t);
   }
   tma::mbar_wait(&bar, 0);
-  if (T.near_edge) c_sw_tile<C, true>(T, a, S);
-  else c_sw_tile<C, false>(T, a, S);
+  auto wait_dpw = [&]() { tma::mbar_wait(&bar2, 0); };
+  if (T.near_edge) c_sw_tile<C, true>(T, a, S, wait_dpw);
+  else c_sw_tile<C, false>(T, a, S, wait_dpw);
 }
 #endif
 
@@ -427,8 +434,8 @@ int c_sw(Core& c, double dt2) {
           host_load_tile<C>(T, S[2], a.delp.p);
           host_load_tile<C>(T, S[3], a.pt.p);
           host_load_tile<C>(T, S[4], a.w.p);
-          if (T.near_edge) c_sw_tile<C, true>(T, a, S);
-          else c_sw_tile<C, false>(T, a, S);
+          if (T.near_edge) c_sw_tile<C, true>(T, a, S, [] {});
+          else c_sw_tile<C, false>(T, a, S, [] {});
         }
 #endif
   // the reference leaves delp, pt, w with their corner cells filled (x fill, then y fill)
