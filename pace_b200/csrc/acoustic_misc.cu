@@ -139,7 +139,7 @@ int nh_p_grad(Core& c, double dt, bool keep_agrid) {
   cudaStream_t st = c.stream;
   double *u = c.F("u"), *v = c.F("v"), *pp_a = c.F("ad.pkc"), *gz_a = c.F("ad.gz"), *pk3_a = c.F("ad.pk3");
   const double *delp = c.F("delp"), *rdx = c.F("grid.rdx"), *rdy = c.F("grid.rdy");
-  double *wk = c.FS("nh.tmp_wk"), *wk1 = c.FS("nh.tmp_wk1");
+  double* wk1 = c.FS("nh.tmp_wk1");
   if (!c.err.empty()) return 1;
   const int km = g.nz, ie = g.ie, je = g.je;
   const double top_value = std::pow(c.cfg.ptop, KAPPA);  // ptk = ptop ** akap
@@ -156,36 +156,38 @@ int nh_p_grad(Core& c, double dt, bool keep_agrid) {
     if (a2b_ord4(c, gz, wk1, 0, km + 1, true)) return 1;
   }
   if (a2b_ord4(c, delp, wk1, 0, km, false)) return 1;
-  // set_k0_and_calc_wk on compute (+1,+1), npz levels
+  // set_k0_and_calc_wk + calc_u + calc_v (nh_p_grad.py:12-113) in one kernel on compute (+1,+1), npz levels: the
+  // reference first sets pp = 0 and pk3 = ptk on level 0 and forms wk = pk3(k+1) - pk3(k) in a work field; here the
+  // level-0 values are substituted at read time and wk is formed in registers for the three points that need it (same
+  // expression), which saves the work field's write and reads and a launch.  Level 0 of pp / pk3 is still stored.
   launch_ijk(st, g, box_compute(g, 0, 0, 1, 1, 0), [=] __device__(const Pt& p) {
-    double lo = A0(pk3);
-    if (p.k == 0) {
+    const bool top = p.k == 0;
+    auto PK = [&](int di, int dj) { return top ? top_value : A(pk3, di, dj, 0); };   // pk3 at this level
+    auto PP = [&](int di, int dj) { return top ? 0.0 : A(pp, di, dj, 0); };          // pp at this level
+    auto WK = [&](int di, int dj) { return A(pk3, di, dj, 1) - PK(di, dj); };
+    if (top) {
       A0(pp) = 0.0;
       A0(pk3) = top_value;
-      lo = top_value;
     }
-    A0(wk) = A(pk3, 0, 0, 1) - lo;
-  });
-  // calc_u on (nx, ny+1), calc_v on (nx+1, ny)
-  launch_ijk(st, g, box_compute(g, 0, 0, 1, 1, 0), [=] __device__(const Pt& p) {
+    const double wk0 = WK(0, 0);
     if (p.i <= ie) {
-      double du = dt / (A0(wk) + A(wk, 1, 0, 0)) *
-                  ((A(gz, 0, 0, 1) - A(gz, 1, 0, 0)) * (A(pk3, 1, 0, 1) - A0(pk3)) +
-                   (A0(gz) - A(gz, 1, 0, 1)) * (A(pk3, 0, 0, 1) - A(pk3, 1, 0, 0)));
+      double du = dt / (wk0 + WK(1, 0)) *
+                  ((A(gz, 0, 0, 1) - A(gz, 1, 0, 0)) * (A(pk3, 1, 0, 1) - PK(0, 0)) +
+                   (A0(gz) - A(gz, 1, 0, 1)) * (A(pk3, 0, 0, 1) - PK(1, 0)));
       A0(u) = (A0(u) + du +
                dt / (A0(wk1) + A(wk1, 1, 0, 0)) *
-                   ((A(gz, 0, 0, 1) - A(gz, 1, 0, 0)) * (A(pp, 1, 0, 1) - A0(pp)) +
-                    (A0(gz) - A(gz, 1, 0, 1)) * (A(pp, 0, 0, 1) - A(pp, 1, 0, 0)))) *
+                   ((A(gz, 0, 0, 1) - A(gz, 1, 0, 0)) * (A(pp, 1, 0, 1) - PP(0, 0)) +
+                    (A0(gz) - A(gz, 1, 0, 1)) * (A(pp, 0, 0, 1) - PP(1, 0)))) *
               A20(rdx);
     }
     if (p.j <= je) {
-      double dv = dt / (A0(wk) + A(wk, 0, 1, 0)) *
-                  ((A(gz, 0, 0, 1) - A(gz, 0, 1, 0)) * (A(pk3, 0, 1, 1) - A0(pk3)) +
-                   (A0(gz) - A(gz, 0, 1, 1)) * (A(pk3, 0, 0, 1) - A(pk3, 0, 1, 0)));
+      double dv = dt / (wk0 + WK(0, 1)) *
+                  ((A(gz, 0, 0, 1) - A(gz, 0, 1, 0)) * (A(pk3, 0, 1, 1) - PK(0, 0)) +
+                   (A0(gz) - A(gz, 0, 1, 1)) * (A(pk3, 0, 0, 1) - PK(0, 1)));
       A0(v) = (A0(v) + dv +
                dt / (A0(wk1) + A(wk1, 0, 1, 0)) *
-                   ((A(gz, 0, 0, 1) - A(gz, 0, 1, 0)) * (A(pp, 0, 1, 1) - A0(pp)) +
-                    (A0(gz) - A(gz, 0, 1, 1)) * (A(pp, 0, 0, 1) - A(pp, 0, 1, 0)))) *
+                   ((A(gz, 0, 0, 1) - A(gz, 0, 1, 0)) * (A(pp, 0, 1, 1) - PP(0, 0)) +
+                    (A0(gz) - A(gz, 0, 1, 1)) * (A(pp, 0, 0, 1) - PP(0, 1)))) *
               A20(rdy);
     }
   });
