@@ -137,7 +137,7 @@ int fv_setup(Core& c);
 int pt_to_potential_density_pt(Core& c);
 int omega_from_w(Core& c);
 int copy_levels(Core& c, const char* src_name, const char* dst_name);
-int fv_prep(Core& c, double dt);
+int fv_prep(Core& c, double dt, bool accumulate_courant = false);
 int riem_solver3(Core& c, double dt, int last_call);
 int update_dz_d(Core& c, double dt);
 int zero_data(Core& c, int first_timestep);

@@ -11,7 +11,6 @@
 namespace pace {
 
 int divergence_damping(Core& c, double* vort_b, double* delpc, double* ke, const double* vort_a, double dt);
-int fv_prep(Core& c, double dt);
 
 namespace {
 // bl/br of xtp_u.get_bl_br / ytp_v.get_bl_br for iord < 8, cell offset d along the sweep direction.
@@ -100,20 +99,19 @@ int d_sw(Core& c, double dt) {
   const int nmax_v = c.col_max("col.nord_v"), nmax_w = c.col_max("col.nord_w"), nmax_t = c.col_max("col.nord_t");
   if (!c.err.empty()) return 1;
 
-  // 1. fv_prep
-  if (fv_prep(c, dt)) return 1;
+  // 1. fv_prep; its last kernel also does the Courant-number half of flux_capacitor (3.): cx += crx, cy += cry.
+  // Outside the columns / rows fv_prep writes, crx / cry are zero for good (nothing else writes them), so adding them
+  // there, as the reference's full-box stencil does, changes nothing.
+  if (fv_prep(c, dt, true)) return 1;
   // 2. fvtp2d_dp(delp) with delnflux(nord_v, damp_vt)
   Fvtp2dArgs a;
   a.crx = crx; a.cry = cry; a.xfx = xfx; a.yfx = yfx; a.nk = nz;
   a.q = delp; a.fx = tfx; a.fy = tfy; a.hord = cf.hord_dp; a.nord_col = col_nord_v; a.damp = damp_vt_fv; a.nmax = nmax_v;
   if (fvtp2d(c, a)) return 1;
-  // 3. flux_capacitor (compute + 3 halo)
-  launch_ijk(st, g, box_dims(g, 0, 0, 0, 3, 3), [=] __device__(const Pt& p) {
-    A0(cx) = A0(cx) + A0(crx);
-    A0(cy) = A0(cy) + A0(cry);
-    A0(mfx) = A0(mfx) + A0(tfx);
-    A0(mfy) = A0(mfy) + A0(tfy);
-  });
+  // 3. flux_capacitor, mass-flux half: mfx += tfx, mfy += tfy are done by the kernel of steps 11./12., which reads the
+  // same fluxes anyway (tfx / tfy are zero outside the boxes fvtp2d writes, so the reference's additions on the rest of
+  // its compute + 3 halo box change nothing: same argument as for crx / cry)
+  (void)cx; (void)cy;
   // 4. delnflux_nosg_w(w)
   DelnHeat heat;
   heat.dw = dw; heat.heat_s = heat_s; heat.col_damp_w = col_damp_w; heat.col_ke_bg = col_ke_bg; heat.absdt = fabs(dt);
@@ -159,8 +157,13 @@ int d_sw(Core& c, double dt) {
   // 10. fvtp2d_tm(pt, mass=delp)
   a.q = pt; a.hord = cf.hord_tm; a.nord_col = col_nord_v; a.damp = damp_vt_fv; a.nmax = nmax_v;
   if (fvtp2d(c, a)) return 1;
-  // 11./12. apply_pt_delp_fluxes ; adjust_w_and_qcon
-  launch_ijk(st, g, box_dims(g, 0, 0, 0), [=] __device__(const Pt& p) {
+  // 11./12. apply_pt_delp_fluxes ; adjust_w_and_qcon on the compute domain; 3. mfx += tfx on [is, ie+1] x [js, je],
+  // mfy += tfy on [is, ie] x [js, je+1] (the boxes fvtp2d writes tfx / tfy on)
+  launch_ijk(st, g, box_dims(g, 1, 1, 0), [=] __device__(const Pt& p) {
+    const bool in_i = p.i <= ie, in_j = p.j <= je;
+    if (in_j) A0(mfx) = A0(mfx) + A0(tfx);
+    if (in_i) A0(mfy) = A0(mfy) + A0(tfy);
+    if (!(in_i && in_j)) return;
     const double delp0 = A0(delp);  // delp before this step: the weight of pt and w
     double ptv = A0(pt) * delp0 + (A0(gx) - A(gx, 1, 0, 0) + A0(gy) - A(gy, 0, 1, 0)) * A20(rarea);
     double dp = delp0 + (A0(tfx) - A(tfx, 1, 0, 0) + A0(tfy) - A(tfy, 0, 1, 0)) * A20(rarea);

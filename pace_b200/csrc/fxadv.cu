@@ -13,7 +13,9 @@
 
 namespace pace {
 
-int fv_prep(Core& c, double dt) {
+// accumulate_courant: also add the new Courant numbers to cxd / cyd (the first half of flux_capacitor, d_sw.py:34-60),
+// which d_sw otherwise does in a separate pass over crx / cry
+int fv_prep(Core& c, double dt, bool accumulate_courant) {
   const Geo g = c.g;
   cudaStream_t st = c.stream;
   const double *uc = c.F("uc"), *vc = c.F("vc");
@@ -166,26 +168,39 @@ int fv_prep(Core& c, double dt) {
   });
 
   // K8: fxadv_fluxes_stencil (fxadv.py:373-408) on the full domain
+  double *cx = nullptr, *cy = nullptr;
+  if (accumulate_courant) {
+    cx = c.F("cxd"); cy = c.F("cyd");
+    if (!c.err.empty()) return 1;
+  }
+  const int icap = g.nx + 5, jcap = g.ny + 5;  // flux_capacitor runs on the compute domain + 3 halo cells
   launch_ijk(st, g, box_full(g), [=] __device__(const Pt& p) {
+    const bool cap = cx != nullptr && p.i <= icap && p.j <= jcap;
     if (p.i >= is && p.i <= ie + 1) {
       double u = A0(ucc);
+      double cr;
       if (u > 0) {
-        A0(crx) = dt * u * A2(rdxa, -1, 0);
+        cr = dt * u * A2(rdxa, -1, 0);
         A0(xfx) = A20(dy) * dt * u * A2(sin_sg3, -1, 0);
       } else {
-        A0(crx) = dt * u * A20(rdxa);
+        cr = dt * u * A20(rdxa);
         A0(xfx) = A20(dy) * dt * u * A20(sin_sg1);
       }
+      A0(crx) = cr;
+      if (cap) A0(cx) = A0(cx) + cr;
     }
     if (p.j >= js && p.j <= je + 1) {
       double v = A0(vcc);
+      double cr;
       if (v > 0) {
-        A0(cry) = dt * v * A2(rdya, 0, -1);
+        cr = dt * v * A2(rdya, 0, -1);
         A0(yfx) = A20(dx) * dt * v * A2(sin_sg4, 0, -1);
       } else {
-        A0(cry) = dt * v * A20(rdya);
+        cr = dt * v * A20(rdya);
         A0(yfx) = A20(dx) * dt * v * A20(sin_sg2);
       }
+      A0(cry) = cr;
+      if (cap) A0(cy) = A0(cy) + cr;
     }
   });
   return 0;
