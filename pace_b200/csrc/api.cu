@@ -2,6 +2,7 @@
 #include <cstdarg>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 
 #include "../../include/pace_b200.h"
 #include "core.hpp"
@@ -12,6 +13,9 @@ namespace pace {
 static thread_local std::string g_err;
 
 // ---- launch accounting ------------------------------------------------------------------------------------
+// Process-wide by design (pace_b200_launch_count / pace_b200_profile_* take no handle: bench.py reads the totals of
+// everything the library launched); the event record is guarded so that handles driven from several host threads
+// cannot corrupt it, and the counter is per thread-of-execution exact only when one thread launches at a time.
 static long long g_launches = 0;
 long long& launch_counter() { return g_launches; }
 #ifndef PACE_HOST_EMU
@@ -19,6 +23,8 @@ struct ProfEntry { const char* label; cudaEvent_t a, b; };
 static bool g_prof_on = false;
 static std::vector<ProfEntry> g_prof;
 static std::vector<cudaEvent_t> g_event_pool;
+static std::mutex g_prof_mutex;
+static thread_local cudaEvent_t t_open_end = nullptr;   // end event of the scope this thread has open
 static cudaEvent_t get_event() {
   if (!g_event_pool.empty()) { cudaEvent_t e = g_event_pool.back(); g_event_pool.pop_back(); return e; }
   cudaEvent_t e;
@@ -27,11 +33,16 @@ static cudaEvent_t get_event() {
 }
 bool prof_enabled() { return g_prof_on; }
 void prof_begin(cudaStream_t s, const char* label) {
+  std::lock_guard<std::mutex> lock(g_prof_mutex);
   ProfEntry p{label, get_event(), get_event()};
   cudaEventRecord(p.a, s);
   g_prof.push_back(p);
+  t_open_end = p.b;
 }
-void prof_end(cudaStream_t s) { cudaEventRecord(g_prof.back().b, s); }
+void prof_end(cudaStream_t s) {
+  if (t_open_end) cudaEventRecord(t_open_end, s);
+  t_open_end = nullptr;
+}
 #else
 bool prof_enabled() { return false; }
 void prof_begin(cudaStream_t, const char*) {}
@@ -215,6 +226,7 @@ int pace_b200_profile_report(char* buf, int n) {
   std::string out;
 #ifndef PACE_HOST_EMU
   cudaDeviceSynchronize();
+  std::lock_guard<std::mutex> lock(g_prof_mutex);
   std::map<std::string, std::pair<long long, double>> acc;
   for (auto& p : g_prof) {
     float ms = 0;

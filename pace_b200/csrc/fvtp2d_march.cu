@@ -15,6 +15,7 @@
 #include "corners.cuh"
 #include "ppm.cuh"
 #include "transport.hpp"
+#include "tile.cuh"
 
 namespace pace {
 
@@ -368,15 +369,25 @@ __global__ void __launch_bounds__(WPB * 32, 20) k_fvtp2d_march(Geo g, MarchArgs 
 }
 
 template <int OIN, int OOUT>
-void launch(int blocks, size_t smem, cudaStream_t st, const Geo& g, const MarchArgs& f) {
-  static bool attr_set = false;  // opt in to > 48 KB of dynamic shared memory once per instantiation
-  if (!attr_set) {
-    cudaFuncSetAttribute(k_fvtp2d_march<OIN, OOUT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    attr_set = true;
-  }
+void launch(Core& c, int blocks, size_t smem, cudaStream_t st, const Geo& g, const MarchArgs& f) {
+  // opt in to the dynamic shared memory once per instantiation AND device (tile.cu)
+  if (func_attr_once(c, (const void*)k_fvtp2d_march<OIN, OOUT>, (int)smem)) return;
   k_fvtp2d_march<OIN, OOUT><<<blocks, WPB * 32, smem, st>>>(g, f);
 }
 }  // namespace
+
+// SMs of the current device (queried once per device)
+static int sm_count() {
+  static int cached[64] = {0};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+  if (!cached[dev]) {
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+    cached[dev] = n;
+  }
+  return cached[dev];
+}
 
 int fvtp2d_march_launch(Core& c, const Fvtp2dArgs& a) {
   const Geo g = c.g;
@@ -394,14 +405,15 @@ int fvtp2d_march_launch(Core& c, const Fvtp2dArgs& a) {
   const int oi = oo == 10 ? 8 : oo;
   static const int rows_env = [] { const char* v = getenv("PACE_B200_FVTP2D_ROWS"); return v ? atoi(v) : 0; }();
   f.nstrips = (g.nx + SW - 1) / SW;
-  // rows per chunk: 64 (6 warm-up rows = 9 % extra work) unless that leaves fewer than ~6 waves of warps on the
-  // GPU (148 SMs x 16 resident warps), then 32 or 16 — small per-GPU domains (multi-GPU runs) need the parallelism
+  // rows per chunk: 64 (6 warm-up rows = 9 % extra work) unless that leaves fewer than ~4 waves of warps on the
+  // GPU (SMs x 16 resident warps), then 32 (19 % extra) or 16 (37 %) — small per-GPU domains (multi-GPU runs) need the
+  // parallelism, but at 3 subdomains per GPU the warm-up rows of 16-row chunks cost more than a shorter last wave
   f.rows = 64;
   if (rows_env > 0) {
     f.rows = rows_env;
   } else {
-    const long long slots = 148LL * 16;
-    while (f.rows > 16 && (long long)f.nstrips * ((g.ny + f.rows - 1) / f.rows) * a.nk * g.nt < 6 * slots) f.rows /= 2;
+    const long long slots = (long long)sm_count() * 16;
+    while (f.rows > 16 && (long long)f.nstrips * ((g.ny + f.rows - 1) / f.rows) * a.nk * g.nt < 4 * slots) f.rows /= 2;
   }
   if (f.rows > g.ny) f.rows = g.ny;
   f.nchunks = (g.ny + f.rows - 1) / f.rows;
@@ -411,11 +423,11 @@ int fvtp2d_march_launch(Core& c, const Fvtp2dArgs& a) {
   // launches that carry level flags (tracer species, q_con) are timed apart: their duration depends on how many levels
   // hold anything, so they would blur the per-launch figure of the dense launches the roofline is quoted on
   LaunchScope scope(c.stream, a.level_nonzero ? "fvtp2d_march_sparse" : "fvtp2d_march");
-  if (oi == 5 && oo == 5) launch<5, 5>(blocks, smem, c.stream, g, f);
-  else if (oi == 6 && oo == 6) launch<6, 6>(blocks, smem, c.stream, g, f);
-  else if (oi == 7 && oo == 7) launch<7, 7>(blocks, smem, c.stream, g, f);
-  else if (oi == 8 && oo == 8) launch<8, 8>(blocks, smem, c.stream, g, f);
-  else if (oi == 8 && oo == 10) launch<8, 10>(blocks, smem, c.stream, g, f);
+  if (oi == 5 && oo == 5) launch<5, 5>(c, blocks, smem, c.stream, g, f);
+  else if (oi == 6 && oo == 6) launch<6, 6>(c, blocks, smem, c.stream, g, f);
+  else if (oi == 7 && oo == 7) launch<7, 7>(c, blocks, smem, c.stream, g, f);
+  else if (oi == 8 && oo == 8) launch<8, 8>(c, blocks, smem, c.stream, g, f);
+  else if (oi == 8 && oo == 10) launch<8, 10>(c, blocks, smem, c.stream, g, f);
   else return -1;  // not instantiated: the caller falls back to the tiled kernel
   return 0;
 }

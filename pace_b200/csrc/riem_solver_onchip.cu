@@ -16,7 +16,7 @@
 // registers; pem, pm, X and the intermediate w (S) are the only global work arrays.
 // Statement order and expression trees per level are those of riem_solver.cu / the reference (sim1_solver.py:20-141,
 // riem_solver_c.py:21-123, riem_solver3.py:26-146), so results are bit-identical.
-#include "core.hpp"
+#include "tile.cuh"
 
 namespace pace {
 
@@ -450,11 +450,7 @@ int launch_riem(Core& c, RiemArgs& a, const char* label) {
   a.pem = c.S("sim1.pem"); a.pm = c.S("sim1.pm"); a.wtmp = c.S("sim1.w"); a.xwork = c.S("sim1.x");
   if (!c.err.empty()) return 1;
   const size_t smem = (size_t)(a.km + 1) * 32 * sizeof(double);
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaFuncSetAttribute(k_riem<D3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
-    attr_set = true;
-  }
+  if (func_attr_once(c, (const void*)k_riem<D3>, 96 * 1024)) return 1;  // once per instantiation and device (tile.cu)
   if (smem > 96 * 1024) { c.err = "riem_solver: too many levels for the on-chip kernel"; return 1; }
   dim3 grd((a.b.ni * a.b.nj + 31) / 32, g.nt, 1);
   LaunchScope scope(c.stream, label);
