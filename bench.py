@@ -396,14 +396,15 @@ def main():
                           "dd_march": 5 * 8}.get(top, 8 * 8)
         alg_bytes = cells / world * bytes_per_cell  # this GPU's share of the cells
         achieved = alg_bytes / (per_launch_ms / 1000.0) / 1e9
-        # measured DRAM bytes per launch of that kernel from the committed ncu capture (profiles/traffic_r01.json),
+        # measured DRAM bytes per launch of that kernel from the committed ncu capture (profiles/traffic_r0*.json),
         # scaled by this GPU's share of the cells; null when no capture exists for this workload / kernel
         traffic = None
-        tpath = os.path.join(ROOT, "profiles", "traffic_r01.json")
-        if os.path.exists(tpath):
-            rec = json.load(open(tpath)).get(args.workload, {}).get(top)
+        for tname in ("traffic_r02.json", "traffic_r01.json"):  # the newest capture that has this kernel
+            tpath = os.path.join(ROOT, "profiles", tname)
+            rec = json.load(open(tpath)).get(args.workload, {}).get(top) if os.path.exists(tpath) else None
             if rec:
                 traffic = rec["dram_bytes_per_launch"] / world
+                break
         roof = {"kernel": top, "bound": "hbm", "achieved": achieved, "peak": pk["hbm_gbs"], "peak_source": pk_kind,
                 "unit": "GB/s", "frac": achieved / pk["hbm_gbs"], "traffic": traffic,
                 "algorithmic_bytes_per_launch": alg_bytes, "launches_timed": cnt,
