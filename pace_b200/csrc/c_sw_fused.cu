@@ -39,6 +39,7 @@ struct CswArgs {
       *rdxc, *rdyc, *sin_sg1, *sin_sg2, *sin_sg3, *sin_sg4, *cos_sg1, *cos_sg2, *cos_sg3, *cos_sg4, *rarea, *rarea_c, *fC;
   double dt2;
   int nord, npt;
+  int part;   // 0: every patch; 1: patches whose box lies inside the compute domain; 2: the others
   TileGrid tg;
 };
 
@@ -356,6 +357,10 @@ __global__ void __launch_bounds__(CswCfg::NT, CSW_CTAS_PER_SM) k_c_sw_fused(Geo 
   const int k = blockIdx.z % g.nz, t = blockIdx.z / g.nz;
   Tile<C> T = make_tile<C>(g, a.tg, blockIdx.x, blockIdx.y, k, t);
   T.tx = threadIdx.x; T.ty = threadIdx.y;
+  if (a.part != 0) {
+    const bool inside = T.bi >= g.is && T.bi + C::W - 1 <= g.ie && T.bj >= g.js && T.bj + C::H - 1 <= g.je;
+    if (inside != (a.part == 1)) return;
+  }
   const bool leader = threadIdx.x == 0 && threadIdx.y == 0;
   if (leader) {
     tma::mbar_init(&bar, 1);
@@ -382,11 +387,25 @@ __global__ void __launch_bounds__(CswCfg::NT, CSW_CTAS_PER_SM) k_c_sw_fused(Geo 
 
 int c_sw_unfused(Core& c, double dt2);
 
-int c_sw(Core& c, double dt2) {
+static bool csw_unfused_env() {
   static const bool unfused = [] { const char* v = getenv("PACE_B200_CSW"); return v && v[0] == 'u'; }();
+  return unfused;
+}
+// the interior / rim split needs the tiled kernel (device build, patches wide enough)
+bool c_sw_can_split(const Core& c) {
+#ifndef PACE_HOST_EMU
+  const TileGrid tg = tile_grid<CswCfg>(c.g);
+  return !csw_unfused_env() && c.cfg.grid_type == 0 && !((tg.ntx > 1 && tg.tw < 10) || (tg.nty > 1 && tg.th < 10));
+#else
+  (void)c;
+  return false;
+#endif
+}
+
+int c_sw(Core& c, double dt2, int part) {
   typedef CswCfg C;
   const Geo g = c.g;
-  if (unfused) return c_sw_unfused(c, dt2);
+  if (csw_unfused_env()) return c_sw_unfused(c, dt2);
   if (c.cfg.grid_type != 0) {
     c.err = "unimplemented grid_type (only 0)";  // d2a2c_vect.py:394 allows 0 and 4
     return 1;
@@ -404,6 +423,7 @@ int c_sw(Core& c, double dt2) {
   a.cos_sg4 = c.F("grid.cos_sg4"); a.rarea = c.F("grid.rarea"); a.rarea_c = c.F("grid.rarea_c"); a.fC = c.F("grid.fC");
   if (!c.err.empty()) return 1;
   a.dt2 = dt2;
+  a.part = part;
   a.nord = c.cfg.nord;
   a.npt = (4 > g.nx - 1 || 4 > g.ny - 1) ? 0 : 4;
   a.tg = tile_grid<C>(g);
@@ -439,6 +459,7 @@ int c_sw(Core& c, double dt2) {
         }
 #endif
   // the reference leaves delp, pt, w with their corner cells filled (x fill, then y fill)
+  if (part == 1) return 0;
   for (int ydir = 0; ydir < 2; ++ydir) {
     CornerOps ops;
     ops.n = 3; ops.nk = g.nz;

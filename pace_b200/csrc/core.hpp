@@ -101,7 +101,9 @@ struct Core {
 
 // ---- module entry points (one per reference class / stencil group) -------------------------------
 int riem_solver_c(Core& c, double dt2);
-int c_sw(Core& c, double dt2);
+// part 0: the whole call; 1: only the patches that lie inside the compute domain (they read no halo cell); 2: the rest
+int c_sw(Core& c, double dt2, int part = 0);
+bool c_sw_can_split(const Core& c);
 int update_dz_c(Core& c, double dt2);
 int update_dz_c_from_zh(Core& c, double dt2, bool gz_equals_zh);
 int p_grad_c(Core& c, double dt2);

@@ -76,10 +76,10 @@ static int halo2(Core& c, int plan_a, const Names& xa, const Names* ya, int nka,
 // queued on a side stream behind an event, the main stream goes on with kernels that touch neither the halos being
 // filled nor the arenas, and halo_end makes the main stream wait for it.  Every rank opens and closes the same
 // exchanges in the same order, and none is issued in between, so the barriers stay in step across the GPUs.
-static int halo_begin(Core& c, int plan, const Names& x, const Names* y = nullptr, int nk = -1) {
+template <class Issue>
+static int halo_async(Core& c, bool peer, Issue issue) {
 #ifndef PACE_HOST_EMU
   static const bool no_overlap = [] { const char* v = getenv("PACE_B200_HALO_OVERLAP"); return v && v[0] == '0'; }();
-  const bool peer = plan < 16 && c.peer_plans[plan].set && !c.arena_ptrs.empty();
   if (peer && !no_overlap && !c.async_open) {
     if (!c.side_stream) {
       cudaEvent_t a, b;
@@ -95,7 +95,7 @@ static int halo_begin(Core& c, int plan, const Names& x, const Names* y = nullpt
     cudaStreamWaitEvent(c.side_stream, (cudaEvent_t)c.ev_fork, 0);
     cudaStream_t main_stream = c.stream;
     c.stream = c.side_stream;
-    const int rc = halo(c, plan, x, y, nk);
+    const int rc = issue();
     c.stream = main_stream;
     if (rc) return 1;
     cudaEventRecord((cudaEvent_t)c.ev_join, c.side_stream);
@@ -103,7 +103,17 @@ static int halo_begin(Core& c, int plan, const Names& x, const Names* y = nullpt
     return 0;
   }
 #endif
-  return halo(c, plan, x, y, nk);
+  (void)peer;
+  return issue();
+}
+static bool peer_plan(const Core& c, int plan) { return plan < 16 && c.peer_plans[plan].set && !c.arena_ptrs.empty(); }
+static int halo_begin(Core& c, int plan, const Names& x, const Names* y = nullptr, int nk = -1) {
+  return halo_async(c, peer_plan(c, plan), [&] { return halo(c, plan, x, y, nk); });
+}
+static int halo2_begin(Core& c, int plan_a, const Names& xa, const Names* ya, int nka, int plan_b, const Names& xb,
+                       const Names* yb, int nkb) {
+  return halo_async(c, peer_plan(c, plan_a) && peer_plan(c, plan_b),
+                    [&] { return halo2(c, plan_a, xa, ya, nka, plan_b, xb, yb, nkb); });
 }
 static int halo_end(Core& c) {
 #ifndef PACE_HOST_EMU
@@ -140,10 +150,20 @@ int acoustic(Core& c, double timestep, int n_map) {
       RUN(halo(c, A3, Names{"delp", "pt"}));
     }
     if (it == n_split - 1 && end_step && cfg.use_old_omega) RUN(pem_from_delp(c));
-    RUN(halo2(c, D3, u, &v, -1, A3, Names{"w"}, nullptr, -1));
-    RUN(stage(c, "C_SW-In"));
-    RUN(c_sw(c, dt2));
-    RUN(stage(c, "C_SW-Out"));
+    // c_sw needs the halos of u, v, w only in the patches on the rim of a subdomain: with peer arenas (and no
+    // savepoint callback, which expects the halos before C_SW-In) the exchange runs on the side stream under the
+    // interior patches, and the rim patches follow it
+    if (!c.stage_cb && peer_plan(c, D3) && peer_plan(c, A3) && c_sw_can_split(c)) {
+      RUN(halo2_begin(c, D3, u, &v, -1, A3, Names{"w"}, nullptr, -1));
+      RUN(c_sw(c, dt2, 1));
+      RUN(halo_end(c));
+      RUN(c_sw(c, dt2, 2));
+    } else {
+      RUN(halo2(c, D3, u, &v, -1, A3, Names{"w"}, nullptr, -1));
+      RUN(stage(c, "C_SW-In"));
+      RUN(c_sw(c, dt2));
+      RUN(stage(c, "C_SW-Out"));
+    }
     // divgd is next read by d_sw: its exchange overlaps the C-grid height update, Riemann solver and pressure gradient
     // (first substep: the gz update follows at once, so it is done in line)
     if (cfg.nord > 0) {
