@@ -143,7 +143,7 @@ def test_full_step_six_tiles_gpu():
     run_step("cuda", 0.0)
 
 
-def run_two_steps(backend, tol):
+def run_two_steps(backend, tol, poison=False):
     """Two dycore steps with k_split=2, n_split=2 (all branches of the acoustic loop that depend on the substep and
     remap-step counters; non-zero w, q_con and condensates in the second step) against the reference's final state
     (tests/golden/c12_6rank_final_ns2_ks2_s2.npz, oracle/gen_golden.py --n-split 2 --k-split 2 --steps 2 --final-only)."""
@@ -156,7 +156,19 @@ def run_two_steps(backend, tol):
         kw = dict(device="cpu", _lib_handle=hostemu.load())
     eng = DycoreEngine(12, 1, 79, load_six("grid"), n_split=2, k_split=2, **kw)
     eng.set_state(load_six("init"))
+    if poison:
+        # engine.STEP_INPUTS under k_split = 2, n_split = 2 as well: everything a step does not read is NaN beforehand
+        from pace_b200.engine import STATE_2D, STATE_3D, STEP_INPUTS
+
+        for name in STATE_3D + STATE_2D:
+            if name not in STEP_INPUTS:
+                eng.core.t[name].fill_(float("nan"))
     eng.step_dynamics()
+    if poison:
+        # a host-resident driver re-uploads only the inputs before the second step too
+        for name in STATE_3D + STATE_2D:
+            if name not in STEP_INPUTS:
+                eng.core.t[name].fill_(float("nan"))
     eng.step_dynamics()
     eng.core.sync()
     z = np.load(os.path.join(GOLDEN, "c12_6rank_final_ns2_ks2_s2.npz"))
@@ -180,6 +192,10 @@ def run_two_steps(backend, tol):
 
 def test_two_steps_ksplit2_nsplit2_hostemu():
     run_two_steps("hostemu", 0.0)
+
+
+def test_step_inputs_ksplit2_nsplit2_hostemu():
+    run_two_steps("hostemu", 0.0, poison=True)
 
 
 @pytest.mark.gpu
