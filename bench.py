@@ -276,6 +276,7 @@ def main():
     ap.add_argument("--impl", default="pace_b200")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--e2e-full-state", action="store_true", help="e2e downloads all 32 DycoreState fields every step")
     ap.add_argument("--no-dense", action="store_true", help="skip the extra run with PACE_B200_ZERO_PATHS=0")
     args = ap.parse_args()
     if args.workload is None:
@@ -446,9 +447,11 @@ def main():
     # neighbouring steps overlap the compute on their own streams.  Pipeline fill and drain are inside the timing.
     e2e = None
     if not args.no_e2e:
-        from pace_b200.engine import HostPipeline
+        from pace_b200.engine import PHYSICS_FIELDS, HostPipeline
 
-        pipe = HostPipeline(eng)
+        # uploads the fields a step reads, downloads what the reference's driver reads back after a step
+        # (engine.PHYSICS_FIELDS: prognostics, A-grid winds, pe / peln, omga, ps, tracers); --e2e-full-state: all 32
+        pipe = HostPipeline(eng, download_names=None if args.e2e_full_state else PHYSICS_FIELDS)
         hin, hout = pipe.pinned_like(), pipe.pinned_like()
         for k in pipe.names:
             hin[k].copy_(core.t[k])
@@ -462,6 +465,8 @@ def main():
         e2e = {"value": DT_ATMOS / (e2e_ms / 1000.0), "unit": "simulated days / day", "ms_per_step": e2e_ms,
                "h2d_bytes_per_step": pipe.upload_bytes_per_step * world, "d2h_bytes_per_step": nbytes * world,
                "steps": k_e2e, "fields": len(pipe.names), "fields_uploaded": len(pipe.upload_names),
+               "fields_downloaded": len(pipe.download_names),
+               "downloaded": "engine.PHYSICS_FIELDS (what the reference's driver and physics hand-over read after a step)" if not args.e2e_full_state else "the whole DycoreState",
                "h2d_gbs": pipe.upload_bytes_per_step / (e2e_ms / 1000.0) / 1e9, "d2h_gbs": nbytes / (e2e_ms / 1000.0) / 1e9,
                "overlap": "upload(n+1) / download(n-1) on side streams during step n"}
         del hin, hout, pipe

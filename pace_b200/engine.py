@@ -31,6 +31,11 @@ STATE_2D = ["ps", "phis"]
 # them in the initial state leaves the result bit-identical (tools/find_step_inputs.py; tests/test_engine_acoustic.py).
 STEP_INPUTS = ["u", "v", "w", "delp", "delz", "pt", "qvapor", "qliquid", "qice", "qrain", "qsnow", "qgraupel", "qo3mr",
                "qsgs_tke", "qcld", "phis"]
+# What the reference's driver reads back from the dycore after a step (driver/pace/driver/driver.py and the physics
+# hand-over pySHiELD/update: delp, pt, delz, w, ua, va, pe, peln, omga, phis and the tracers) plus the prognostic winds
+# and ps: the default download set of a host-resident model that does not ask for the whole DycoreState.
+PHYSICS_FIELDS = ["u", "v", "w", "ua", "va", "delp", "delz", "pt", "pe", "peln", "omga", "ps", "qvapor", "qliquid", "qice",
+                  "qrain", "qsnow", "qgraupel", "qo3mr", "qsgs_tke", "qcld"]
 ACOUSTIC_TEMPORARIES = ["ad.ut", "ad.vt", "ad.gz", "ad.zh", "ad.pem", "ad.pkc", "ad.pk3", "ad.heat_source", "ad.cappa",
                         "ad.divgd", "ad.crx", "ad.cry", "ad.xfx", "ad.yfx", "csw.delpc", "csw.ptc", "dyn.dp1", "dyn.cvm"]
 TEMPORARIES_2D = ["ad.ws3", "ad.wsd", "ad.zs"]
@@ -265,19 +270,21 @@ class HostPipeline:
     step tends to max(compute, upload, download) instead of their sum.  phis (static) is expected to stay unchanged
     (ad.zs is derived from it once in set_state)."""
 
-    def __init__(self, eng, names=None, upload_names=STEP_INPUTS):
+    def __init__(self, eng, names=None, upload_names=STEP_INPUTS, download_names=None):
         import torch
 
         self.torch = torch
         self.eng = eng
         self.names = list(names) if names is not None else STATE_3D + STATE_2D
         self.upload_names = [n for n in self.names if upload_names is None or n in upload_names]
+        # download_names: the fields the caller wants back every step (default: all of `names`)
+        self.download_names = [n for n in self.names if download_names is None or n in download_names]
         core = eng.core
         self.sets = [{n: core.t[n] for n in self.names}, {n: torch.empty_like(core.t[n]) for n in self.names}]
         for n in self.names:
             self.sets[1][n].copy_(core.t[n])
         self.s_up, self.s_down = torch.cuda.Stream(core.device), torch.cuda.Stream(core.device)
-        self.bytes_per_step = sum(t.numel() * t.element_size() for t in self.sets[0].values())  # downloaded
+        self.bytes_per_step = sum(self.sets[0][n].numel() * self.sets[0][n].element_size() for n in self.download_names)
         self.upload_bytes_per_step = sum(self.sets[0][n].numel() * self.sets[0][n].element_size() for n in self.upload_names)
 
     def pinned_like(self):
@@ -326,7 +333,7 @@ class HostPipeline:
             with torch.cuda.stream(self.s_down):
                 self.s_down.wait_event(step_done[n % 2])
                 dst = get_out(n)
-                for name in self.names:
+                for name in self.download_names:
                     dst[name].copy_(cur[name], non_blocking=True)
                 ev = torch.cuda.Event()
                 ev.record(self.s_down)
