@@ -102,8 +102,9 @@ def cpu_port_step_seconds(n_tile, layout, threads, steps=1, warmup=1):
 
 
 def host_sample_for(n_tile, layout):
-    """The largest configuration of the CPU port that fits the host's free memory with a wide margin: the workload
-    itself when it does (~140 work fields in the unfused host build), else a quarter / sixteenth of its cells."""
+    """The largest configuration of the CPU port that fits the host's free memory with a margin (x1.8 of an estimate
+    that counts 150 fields; the unfused host build allocates ~140): the workload itself when it does — 92 GB at C384,
+    i.e. a box with 166 GB free — else a quarter / sixteenth of its cells."""
     try:
         import psutil
 
@@ -113,7 +114,7 @@ def host_sample_for(n_tile, layout):
     for tile, lay in ((n_tile, layout), (n_tile // 2, 1), (n_tile // 4, 1), (48, 1)):
         n = tile // lay
         need = 150 * 6 * lay * lay * (NPZ + 1) * (n + 7) * (n + 8) * 8
-        if tile >= 48 and need * 2.5 < avail:
+        if tile >= 48 and need * 1.8 < avail:
             return tile, lay
     return 48, 1
 
