@@ -6,6 +6,10 @@
 
 namespace pace {
 
+// levels ahead of the sweeps for which L2 is asked (one request per 32-byte sector); measured per update_dz_d call at
+// C384: 6.58 ms without, 6.12 ms with 6 levels, 6.43 ms with 12
+constexpr int DZD_PF = 6;
+
 int update_dz_d(Core& c, double dt) {
   const Geo g = c.g;
   cudaStream_t st = c.stream;
@@ -42,6 +46,14 @@ int update_dz_d(Core& c, double dt) {
     double m0 = A(crx, 0, 0, 0), m1 = A(xfx, 0, 0, 0), m2 = A(cry, 0, 0, 0), m3 = A(yfx, 0, 0, 0);  // level k-1
     for (int k = 1; k < km; ++k) {
       const double g_k = gk[k], b_k = beta[k];
+#ifndef PACE_HOST_EMU
+      if (DZD_PF > 0 && (p.i & 3) == 0 && k + DZD_PF < km) {  // L2 prefetch of the rows a few levels ahead (one per sector)
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(&A(crx, 0, 0, k + DZD_PF)));
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(&A(xfx, 0, 0, k + DZD_PF)));
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(&A(cry, 0, 0, k + DZD_PF)));
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(&A(yfx, 0, 0, k + DZD_PF)));
+      }
+#endif
       const double c0 = A(crx, 0, 0, k), c1 = A(xfx, 0, 0, k), c2 = A(cry, 0, 0, k), c3 = A(yfx, 0, 0, k);
       p0 = fv_div(3.0 * (m0 + g_k * c0) - p0, b_k);
       p1 = fv_div(3.0 * (m1 + g_k * c1) - p1, b_k);
@@ -64,6 +76,14 @@ int update_dz_d(Core& c, double dt) {
     }
     for (int k = km - 1; k >= 0; --k) {
       const double gm = gamma[k];
+#ifndef PACE_HOST_EMU
+      if (DZD_PF > 0 && (p.i & 3) == 0 && k - DZD_PF >= 0) {
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(&A(crx_i, 0, 0, k - DZD_PF)));
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(&A(xfx_i, 0, 0, k - DZD_PF)));
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(&A(cry_i, 0, 0, k - DZD_PF)));
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(&A(yfx_i, 0, 0, k - DZD_PF)));
+      }
+#endif
       p0 = A(crx_i, 0, 0, k) - gm * p0;
       p1 = A(xfx_i, 0, 0, k) - gm * p1;
       p2 = A(cry_i, 0, 0, k) - gm * p2;
