@@ -85,6 +85,7 @@ class PeerArena:
         if rc != 0:
             raise RuntimeError("halo_peer_arena: %s" % core.lib.pace_b200_last_error(core.handle).decode())
         self.native = True
+        core.peer_exchange = True   # NativeCore.sync() then also checks the barriers' time-out word
 
     def next_half(self):
         self.count += 1

@@ -165,7 +165,7 @@ class _Bridge:
     (reference layout (i, j, k), numpy or cupy storage) and the device buffers, and the checkpointer hook."""
 
     def _build(self, comm, grid_data, damping_coefficients, config, phis, n_tile, layout, npz, dt_atmos, checkpointer,
-               device, _lib_handle):
+               device, _lib_handle, **cfg_over):
         many = isinstance(grid_data, (list, tuple))
         grids = [grid_arrays(g, d) for g, d in zip(grid_data, damping_coefficients)] if many else [
             grid_arrays(grid_data, damping_coefficients)]
@@ -176,6 +176,7 @@ class _Bridge:
         cfg["ks"] = int(getattr(grid_data[0] if many else grid_data, "ks", 0))
         if dt_atmos is not None:
             cfg["dt_atmos"] = dt_atmos
+        cfg.update(cfg_over)
         transport = None
         if many:
             if len(grids) != total:
@@ -257,8 +258,7 @@ class AcousticDynamics(_Bridge):
             layout = tuple(part.layout)
         npz = int(getattr(getattr(quantity_factory, "sizer", None), "nz", 0)) or _arr(g0.ak).shape[0] - 1
         self._build(comm, grid_data, damping_coefficients, config, phis, nx * layout[0], layout, npz, None,
-                    checkpointer, device, _lib_handle)
-        self.engine.cfg["grid_type"] = grid_type
+                    checkpointer, device, _lib_handle, grid_type=int(grid_type))
 
     @property
     def cappa(self):

@@ -246,3 +246,15 @@ class NativeCore:
     def sync(self):
         if self.device.type == "cuda":
             torch.cuda.synchronize(self.device)
+            if getattr(self, "peer_exchange", False):
+                self.check_peers()
+
+    def check_peers(self):
+        """Raises if a flag barrier of the library-driven halo exchange gave up waiting for a peer GPU (a rank that
+        failed or fell out of step): the halos of that update are then not valid."""
+        done, bad = ctypes.c_ulonglong(0), ctypes.c_ulonglong(0)
+        rc = self.lib.pace_b200_halo_peer_status(self.handle, ctypes.byref(done), ctypes.byref(bad))
+        if rc != 0:
+            raise NativeError("halo_peer_status: %s" % self.lib.pace_b200_last_error(self.handle).decode())
+        if bad.value:
+            raise NativeError("halo exchange: barrier %d of %d timed out waiting for a peer GPU" % (bad.value, done.value))
