@@ -123,7 +123,7 @@ int peer_halo_update2(Core& c, int plan_a, const char* const* xa, const char* co
 int peer_barrier(Core& c);
 int peer_status(Core& c, unsigned long long* seq, unsigned long long* error);
 int tracer_flux_prep(Core& c, int n_split);
-int tracer_substep(Core& c, int nq);
+int tracer_substep(Core& c, int nq, bool first_subcycle = true);
 int tracer_swap_dp(Core& c);
 int math_eval(Core& c, int op, int n, const double* x, const double* y, double* out);
 int map_single(Core& c, double* q, const double* pe1, const double* pe2, const double* qs, int iv, int kord, bool xi,

@@ -217,7 +217,7 @@ int tracer_advection(Core& c) {
   RUN(tracer_flux_prep(c, n_split));
   RUN(halo(c, A3, q));
   for (int it = 0; it < n_split; ++it) {
-    RUN(tracer_substep(c, 8));
+    RUN(tracer_substep(c, 8, it == 0));
     if (it != n_split - 1) {
       RUN(halo(c, A3, q));
       RUN(tracer_swap_dp(c));

@@ -57,20 +57,51 @@ __global__ void __launch_bounds__(256) k_level_nonzero(Geo g, const double* q, i
   nz = __syncthreads_or(nz);
   if (threadIdx.x == 0) flags[t * nk + k] = nz ? 1 : 0;
 }
+// Later sub-cycles of TracerAdvection: a level that was zero on the whole padded array before a sub-cycle is still zero
+// on its compute cells afterwards (transport of zeros; the kernels skip it), so only the halo update in between can
+// have brought something in: flag |= "the 3-cell frame of the level holds a non-zero value".  Levels already flagged
+// stay flagged (a flag only permits skipping).  Reads 6 % of a level instead of all of it.
+__global__ void __launch_bounds__(256) k_level_frame_or(Geo g, const double* q, int nk, int* flags) {
+  const int k = blockIdx.x, t = blockIdx.y;
+  if (flags[t * nk + k] != 0) return;
+  const double* lev = q + (long long)t * g.st3 + (long long)k * g.sk;
+  const int nj = g.ny + 2 * HALO + 1, sj = g.sj;
+  bool nz = false;
+  // rows below / above the compute rows: whole rows; compute rows: the columns left / right of the compute cells
+  const int nrow_full = 2 * HALO + 1;                    // rows 0..2 and ny+3..ny+6
+  for (int n = threadIdx.x; n < nrow_full * sj; n += blockDim.x) {
+    const int r = n / sj, i = n - r * sj;
+    const int j = r < HALO ? r : g.ny + r;               // r = 3.. -> ny+3..
+    nz = nz || lev[j * sj + i] != 0.0;
+  }
+  const int nside = sj - g.nx;                            // columns 0..2 and nx+3..sj-1
+  for (int n = threadIdx.x; n < g.ny * nside; n += blockDim.x) {
+    const int r = n / nside, c = n - r * nside;
+    const int i = c < HALO ? c : g.nx + c;
+    nz = nz || lev[(HALO + r) * sj + i] != 0.0;
+  }
+  (void)nj;
+  nz = __syncthreads_or(nz);
+  if (threadIdx.x == 0 && nz) flags[t * nk + k] = 1;
+}
 }  // namespace
 #endif
 
 // Condensate species are zero on whole levels (above the clouds; everywhere in a dry test case).  One read pass finds
 // those levels; their transport (fvtp2d + apply_tracer_flux) is skipped: a level of zeros stays a level of zeros.
-const int* level_nonzero_flags(Core& c, const double* q, int nk) {
+// slot: one of 10 flag arrays (0 - 7: the tracers of TracerAdvection, 9: any other field); frame_only: update the
+// slot's flags from the halo frame alone (see k_level_frame_or; the slot must hold the flags of the same field from
+// before the last transport + halo update)
+const int* level_nonzero_flags(Core& c, const double* q, int nk, int slot, bool frame_only) {
 #ifndef PACE_HOST_EMU
   if (!zero_paths_enabled()) return nullptr;
   const Geo g = c.g;
   auto it = c.scratch.find("tr.level_nonzero");
   int* flags;
+  const size_t per_slot = (size_t)g.nt * (g.nz + 1);
   if (it == c.scratch.end()) {
     void* ptr = nullptr;
-    if (cudaMalloc(&ptr, sizeof(int) * (size_t)g.nt * (g.nz + 1)) != cudaSuccess) {
+    if (cudaMalloc(&ptr, sizeof(int) * per_slot * 10) != cudaSuccess) {
       c.err = "cudaMalloc failed for tr.level_nonzero";
       return nullptr;
     }
@@ -80,17 +111,20 @@ const int* level_nonzero_flags(Core& c, const double* q, int nk) {
   } else {
     flags = (int*)it->second;
   }
+  flags += per_slot * (size_t)slot;
   ++launch_counter();
-  k_level_nonzero<<<dim3(nk, g.nt), 256, 0, c.stream>>>(g, q, nk, flags);
+  if (frame_only) k_level_frame_or<<<dim3(nk, g.nt), 256, 0, c.stream>>>(g, q, nk, flags);
+  else k_level_nonzero<<<dim3(nk, g.nt), 256, 0, c.stream>>>(g, q, nk, flags);
   return flags;
 #else
-  (void)c; (void)q; (void)nk;
+  (void)c; (void)q; (void)nk; (void)slot; (void)frame_only;
   return nullptr;
 #endif
 }
 
 // one sub-cycle: apply_mass_flux, then fvtp2d + apply_tracer_flux for each tracer (tracer_2d_1l.py:381-411)
-int tracer_substep(Core& c, int nq) {
+// first_subcycle = false: the level flags of the previous sub-cycle are brought up to date from the halo frame
+int tracer_substep(Core& c, int nq, bool first_subcycle) {
   const Geo g = c.g;
   cudaStream_t st = c.stream;
   double *dp1 = c.F("dyn.dp1"), *dp2 = c.FS("tr.tmp_dp");
@@ -106,7 +140,7 @@ int tracer_substep(Core& c, int nq) {
     Fvtp2dArgs a;
     a.q = q; a.crx = cx; a.cry = cy; a.xfx = xfx; a.yfx = yfx; a.fx = fx; a.fy = fy;
     a.x_mass_flux = mfx; a.y_mass_flux = mfy; a.hord = c.cfg.hord_tr; a.nk = g.nz;
-    const int* lvl = level_nonzero_flags(c, q, g.nz);
+    const int* lvl = level_nonzero_flags(c, q, g.nz, n < 9 ? n : 9, !first_subcycle && n < 9);
     if (!c.err.empty()) return 1;
     a.level_nonzero = lvl;
     if (fvtp2d(c, a)) return 1;

@@ -82,6 +82,7 @@ g = torch.Generator().manual_seed(7)
 jj = torch.arange(nj).view(1, 1, nj, 1).double()
 ii = torch.arange(sj).view(1, 1, 1, sj).double()
 kk = torch.arange(nk).view(1, nk, 1, 1)
+tt = torch.arange(nt).view(nt, 1, 1, 1)
 dev = t["qvapor"].device
 def put(name, mask, amp):
     noise = (0.5 + torch.rand(t[name].shape, generator=g, dtype=torch.float64)).to(dev)
@@ -94,6 +95,9 @@ put("qsnow", (((ii == 11) & (jj == 12)) | (jj == 40)) & ((kk == 30) | (kk == 31)
 put("qice", (kk >= 10) & (kk < 20) & (ii >= 0), 1.0e-5)
 # cloud water: only in the first columns / rows next to a tile edge (aprons of the first strip and chunk)
 put("qliquid", ((ii < 6) | (jj < 5)) & (kk > 60), 3.0e-5)
+# ozone: on one level of ONE subdomain only, next to its east edge: the neighbours' copies of that level are zero until
+# a halo update brings it in (the level flags of the later sub-cycles are updated from the halo frame alone)
+put("qo3mr", (tt == 0) & (ii > 40) & (ii < 51) & (kk == 25), 1.0e-6)
 # graupel: rows of zeros interrupted every 9th row
 put("qgraupel", (jj %% 9 == 0) & (kk > 40), 1.0e-5)
 eng.step_dynamics()
@@ -127,6 +131,6 @@ def test_zero_shortcuts_match_dense_on_patchy_tracers(tmp_path):
         for other in ("dense", "dense_unfused"):
             b = comparable(name, res[other][name], 48)
             assert np.array_equal(a, b), "%s vs %s differs: max |d| = %g" % (name, other, np.max(np.abs(a - b)))
-    for name in ("qrain", "qsnow", "qice", "qliquid", "qgraupel"):
+    for name in ("qrain", "qsnow", "qice", "qliquid", "qgraupel", "qo3mr"):
         moved += int(np.count_nonzero(res["production"][name]))
     assert moved > 0
