@@ -87,6 +87,9 @@ struct Core {
   cudaStream_t side_stream = 0;
   void *ev_fork = nullptr, *ev_join = nullptr;   // cudaEvent_t
   bool async_open = false;
+  // inside AcousticDynamics q_con only changes by transport between two d_sw calls: after the first substep its level
+  // flags are kept up to date from the halo frame (tracer.cu: level_nonzero_flags)
+  bool in_acoustic = false, qcon_flags_fresh = false;
   PeerPlan peer_plans[16];
 
   double* F(const char* name);              // caller-registered field, error if missing

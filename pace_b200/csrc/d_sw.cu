@@ -144,7 +144,8 @@ int d_sw(Core& c, double dt) {
   a.fx = gx; a.fy = gy;
   // 8./9. fvtp2d_dp_t(q_con, mass=delp) ; apply_fluxes(q_con)
   // levels without condensate (all of them in dry air): q_con stays zero there, its transport is skipped
-  const int* qcon_levels = level_nonzero_flags(c, q_con, nz);
+  const int* qcon_levels = level_nonzero_flags(c, q_con, nz, 8, c.in_acoustic && c.qcon_flags_fresh);
+  c.qcon_flags_fresh = c.in_acoustic;
   if (!c.err.empty()) return 1;
   a.q = q_con; a.hord = cf.hord_dp; a.mass = delp; a.nord_col = col_nord_t; a.damp = damp_t_fv; a.nmax = nmax_t;
   a.level_nonzero = qcon_levels;

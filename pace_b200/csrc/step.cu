@@ -141,6 +141,11 @@ int acoustic(Core& c, double timestep, int n_map) {
   const bool end_step = n_map == cfg.k_split;
   const double dt = timestep / n_split, dt2 = 0.5 * dt;
   const Names u{"u"}, v{"v"}, uc{"uc"}, vc{"vc"};
+  struct InAcoustic {   // d_sw may reuse q_con's level flags between the substeps of this call only
+    Core& c;
+    explicit InAcoustic(Core& c_) : c(c_) { c.in_acoustic = true; c.qcon_flags_fresh = false; }
+    ~InAcoustic() { c.in_acoustic = false; c.qcon_flags_fresh = false; }
+  } in_acoustic(c);
   RUN(halo(c, A3, Names{"q_con", "ad.cappa"}));
   RUN(zero_data(c, n_map == 1));
   for (int it = 0; it < n_split; ++it) {

@@ -89,7 +89,7 @@ __global__ void __launch_bounds__(256) k_level_frame_or(Geo g, const double* q, 
 
 // Condensate species are zero on whole levels (above the clouds; everywhere in a dry test case).  One read pass finds
 // those levels; their transport (fvtp2d + apply_tracer_flux) is skipped: a level of zeros stays a level of zeros.
-// slot: one of 10 flag arrays (0 - 7: the tracers of TracerAdvection, 9: any other field); frame_only: update the
+// slot: one of 10 flag arrays (0 - 7: the tracers of TracerAdvection, 8: q_con inside AcousticDynamics, 9: any other); frame_only: update the
 // slot's flags from the halo frame alone (see k_level_frame_or; the slot must hold the flags of the same field from
 // before the last transport + halo update)
 const int* level_nonzero_flags(Core& c, const double* q, int nk, int slot, bool frame_only) {
@@ -140,7 +140,7 @@ int tracer_substep(Core& c, int nq, bool first_subcycle) {
     Fvtp2dArgs a;
     a.q = q; a.crx = cx; a.cry = cy; a.xfx = xfx; a.yfx = yfx; a.fx = fx; a.fy = fy;
     a.x_mass_flux = mfx; a.y_mass_flux = mfy; a.hord = c.cfg.hord_tr; a.nk = g.nz;
-    const int* lvl = level_nonzero_flags(c, q, g.nz, n < 9 ? n : 9, !first_subcycle && n < 9);
+    const int* lvl = level_nonzero_flags(c, q, g.nz, n < 8 ? n : 9, !first_subcycle && n < 8);
     if (!c.err.empty()) return 1;
     a.level_nonzero = lvl;
     if (fvtp2d(c, a)) return 1;
