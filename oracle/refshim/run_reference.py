@@ -5,6 +5,7 @@ quoted in profiles/ and BASELINE.md).  Needs /root/reference, so it never runs o
 Constructor sequence follows the reference's own test tests/main/fv3core/test_dycore_call.py:28-136,
 with NullComm replaced by ProcComm so halos are real.
 """
+import os
 import time
 from datetime import timedelta
 
@@ -42,7 +43,8 @@ def build_dycore(mpi_comm, cfg_kwargs, backend="numpy"):
     communicator = CubedSphereCommunicator(mpi_comm, partitioner)
     dace_config = DaceConfig(communicator=communicator, backend=backend)
     stencil_config = ndsl.dsl.stencil.StencilConfig(
-        compilation_config=ndsl.dsl.stencil.CompilationConfig(backend=backend, rebuild=False, validate_args=True),
+        compilation_config=ndsl.dsl.stencil.CompilationConfig(
+            backend=backend, rebuild=False, validate_args=os.environ.get("PACE_REF_VALIDATE_ARGS", "1") != "0"),
         dace_config=dace_config,
     )
     sizer = SubtileGridSizer.from_tile_params(
