@@ -265,12 +265,12 @@ class DycoreEngine:
 class HostPipeline:
     """Steps a HOST-resident model state through a DycoreEngine: the call a coupled driver makes when the rest of the
     model lives in host memory.  Every step uploads the fields the step reads (STEP_INPUTS; upload_names=None uploads
-    the full DycoreState) from pinned host buffers and downloads the whole updated state (STATE_3D + STATE_2D); with two device copies of the state the upload of step n+1 and the
+    the full DycoreState) from pinned host buffers and downloads the whole updated state (STATE_3D + STATE_2D); with nsets device copies of the state (default three) the upload of step n+1 and the
     download of step n-1 run on their own CUDA streams while step n computes (PCIe is full duplex), so the cost per
     step tends to max(compute, upload, download) instead of their sum.  phis (static) is expected to stay unchanged
     (ad.zs is derived from it once in set_state)."""
 
-    def __init__(self, eng, names=None, upload_names=STEP_INPUTS, download_names=None):
+    def __init__(self, eng, names=None, upload_names=STEP_INPUTS, download_names=None, nsets=3):
         import torch
 
         self.torch = torch
@@ -280,12 +280,22 @@ class HostPipeline:
         # download_names: the fields the caller wants back every step (default: all of `names`)
         self.download_names = [n for n in self.names if download_names is None or n in download_names]
         core = eng.core
-        self.sets = [{n: core.t[n] for n in self.names}, {n: torch.empty_like(core.t[n]) for n in self.names}]
-        for n in self.names:
-            self.sets[1][n].copy_(core.t[n])
+        # nsets device copies of the state, used round robin.  With two, the upload of step n+1 has to wait for the
+        # download of step n-1 (same copy) and the two transfers of a step run one after the other; with three it
+        # only waits for the download of step n-2, which had a whole step to finish.
+        if nsets < 2:
+            raise ValueError("HostPipeline: nsets must be at least 2")
+        self.nsets = nsets
+        self.sets = [{n: core.t[n] for n in self.names}]
+        for _ in range(nsets - 1):
+            self.sets.append({n: torch.empty_like(core.t[n]) for n in self.names})
+        for extra in self.sets[1:]:
+            for n in self.names:
+                extra[n].copy_(core.t[n])
         self.s_up, self.s_down = torch.cuda.Stream(core.device), torch.cuda.Stream(core.device)
         self.bytes_per_step = sum(self.sets[0][n].numel() * self.sets[0][n].element_size() for n in self.download_names)
         self.upload_bytes_per_step = sum(self.sets[0][n].numel() * self.sets[0][n].element_size() for n in self.upload_names)
+        self.copy_ms = None   # (upload, download) durations of the last step of the last run(), on the device
 
     def pinned_like(self):
         """A dict of pinned host tensors shaped like the state (one upload or download buffer)."""
@@ -304,45 +314,59 @@ class HostPipeline:
         # work already queued on the main stream (the constructor's copies, the caller's writes) precedes the copies
         self.s_up.wait_stream(main)
         self.s_down.wait_stream(main)
-        up_done = [torch.cuda.Event(), torch.cuda.Event()]
-        step_done = [torch.cuda.Event(), torch.cuda.Event()]
-        down_done = [None, None]
+        S = self.nsets
+        up_done = [torch.cuda.Event() for _ in range(S)]
+        step_done = [torch.cuda.Event() for _ in range(S)]
+        down_done = [None] * S
+        t_up = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+        t_down = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
 
         def upload(n):
-            tgt = self.sets[n % 2]
+            tgt = self.sets[n % S]
             with torch.cuda.stream(self.s_up):
-                if down_done[n % 2] is not None:
-                    self.s_up.wait_event(down_done[n % 2])   # the previous result must have left this copy
-                if n >= 2:
-                    self.s_up.wait_event(step_done[n % 2])
+                if down_done[n % S] is not None:
+                    self.s_up.wait_event(down_done[n % S])   # the previous result must have left this copy
+                if n >= S:
+                    self.s_up.wait_event(step_done[n % S])
                 src = get_in(n)
+                if n == steps - 1:
+                    t_up[0].record(self.s_up)
                 for name in self.upload_names:
                     tgt[name].copy_(src[name], non_blocking=True)
-                up_done[n % 2].record(self.s_up)
+                if n == steps - 1:
+                    t_up[1].record(self.s_up)
+                up_done[n % S].record(self.s_up)
 
         upload(0)
         for n in range(steps):
-            cur = self.sets[n % 2]
+            cur = self.sets[n % S]
             for name in self.names:
                 core._register(name, cur[name])
-            main.wait_event(up_done[n % 2])
+            main.wait_event(up_done[n % S])
             if n + 1 < steps:
                 upload(n + 1)
             eng.step_dynamics()
-            step_done[n % 2].record(main)
+            step_done[n % S].record(main)
             with torch.cuda.stream(self.s_down):
-                self.s_down.wait_event(step_done[n % 2])
+                self.s_down.wait_event(step_done[n % S])
                 dst = get_out(n)
+                if n == steps - 1:
+                    t_down[0].record(self.s_down)
                 for name in self.download_names:
                     dst[name].copy_(cur[name], non_blocking=True)
+                if n == steps - 1:
+                    t_down[1].record(self.s_down)
                 ev = torch.cuda.Event()
                 ev.record(self.s_down)
-                down_done[n % 2] = ev
+                down_done[n % S] = ev
         torch.cuda.synchronize(core.device)
+        if steps > 0:
+            self.copy_ms = (t_up[0].elapsed_time(t_up[1]), t_down[0].elapsed_time(t_down[1]))
         for name in self.names:  # leave the engine bound to its original tensors
             core._register(name, self.sets[0][name])
-        if steps % 2 == 0 and steps > 0:
-            # the last step ran on the second copy: bring its result home
+        last = (steps - 1) % S if steps > 0 else 0
+        if last != 0:
+            # the last step ran on another copy: bring its result home
             for name in self.names:
-                self.sets[0][name].copy_(self.sets[1][name])
+                self.sets[0][name].copy_(self.sets[last][name])
             torch.cuda.synchronize(core.device)

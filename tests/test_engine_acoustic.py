@@ -204,15 +204,17 @@ def test_two_steps_ksplit2_nsplit2_gpu():
 
 
 @pytest.mark.gpu
-def test_host_pipeline_matches_plain_steps_gpu():
-    """HostPipeline (state streamed from / to pinned host memory on side streams, two device copies): three steps
+@pytest.mark.parametrize("nsets,nsteps", [(3, 4), (2, 3)])
+def test_host_pipeline_matches_plain_steps_gpu(nsets, nsteps):
+    """HostPipeline (state streamed from / to pinned host memory on side streams, nsets device copies): steps
     that each start from the same host-resident initial state must each return the reference's one-step result."""
     import torch
 
     from pace_b200.engine import HostPipeline
 
     eng = make_engine("cuda")
-    pipe = HostPipeline(eng)
+    pipe = HostPipeline(eng, nsets=nsets)
+    assert len(pipe.sets) == nsets
     hin = pipe.pinned_like()
     for name in pipe.names:
         hin[name].copy_(eng.core.t[name])
@@ -222,10 +224,11 @@ def test_host_pipeline_matches_plain_steps_gpu():
             if name not in pipe.upload_names:
                 dev_set[name].fill_(float("nan"))
     assert len(pipe.upload_names) == 16
-    outs = [pipe.pinned_like() for _ in range(3)]
-    pipe.run(3, hin, lambda n: outs[n])
+    outs = [pipe.pinned_like() for _ in range(nsteps)]
+    pipe.run(nsteps, hin, lambda n: outs[n])
+    assert pipe.copy_ms[0] > 0.0 and pipe.copy_ms[1] > 0.0
     want = load_six("final")
-    for n in range(3):
+    for n in range(nsteps):
         for name in ("u", "v", "w", "delp", "pt", "delz", "qvapor", "pe", "pkz", "q_con"):
             t = outs[n][name].numpy()
             for r in range(6):
@@ -236,7 +239,7 @@ def test_host_pipeline_matches_plain_steps_gpu():
                 assert np.array_equal(got, w), "step %d %s rank %d differs" % (n, name, r)
     # the engine is bound to its own tensors again and holds the last result
     assert eng.core.t["u"].data_ptr() == pipe.sets[0]["u"].data_ptr()
-    assert torch.equal(eng.core.t["delp"].cpu(), outs[2]["delp"])
+    assert torch.equal(eng.core.t["delp"].cpu(), outs[nsteps - 1]["delp"])
 
 
 def test_step_inputs_hostemu():
