@@ -16,6 +16,9 @@
 // registers; pem, pm, X and the intermediate w (S) are the only global work arrays.
 // Statement order and expression trees per level are those of riem_solver.cu / the reference (sim1_solver.py:20-141,
 // riem_solver_c.py:21-123, riem_solver3.py:26-146), so results are bit-identical.
+#include <cstdlib>
+#include <string>
+
 #include "tile.cuh"
 
 namespace pace {
@@ -35,22 +38,56 @@ struct RiemArgs {
   Box b;
 };
 
-// D3 = false: riem_solver_c, true: riem_solver3
-template <bool D3>
-__global__ void __launch_bounds__(32) k_riem(Geo g, RiemArgs a) {
-  extern __shared__ double sm[];
-  const int lane = threadIdx.x;
+// ---- where Y lives -------------------------------------------------------------------------------------------------
+// TM = false: all km+1 levels in shared memory (20.7 KB per warp at L79: 10 warps per SM).
+// TM = true : levels 0 .. TMEM_LEVELS-1 in tensor memory, the rest in shared memory.  Tensor memory (512 columns x 128
+//   lanes x 32 bit per SM) is otherwise idle on this path; with the 32x32b access shape lane l of warp w of the CTA owns
+//   TMEM lane 32 (w % 4) + l, i.e. every thread has its own row of 32-bit words, and an fp64 level is two adjacent
+//   columns.  A CTA of four warps allocates 128 columns (64 levels); four CTAs fill the 512 columns = 16 warps per SM,
+//   1.6 x the residency of the shared-memory layout for these latency-bound sweeps.
+constexpr int TMEM_LEVELS = 64;
+constexpr int TMEM_COLS = 2 * TMEM_LEVELS;   // a power of two >= 32, as tcgen05.alloc requires
+
+template <bool TM>
+struct YAcc {
+  double* sm;        // this lane's first shared-memory level (stride 32 doubles)
+  uint32_t taddr;    // TMEM address of this warp's lanes, first allocated column
+  __device__ __forceinline__ double ld(int k) const {
+    if (TM && k < TMEM_LEVELS) {
+      uint32_t lo, hi;
+      asm volatile("tcgen05.ld.sync.aligned.32x32b.x2.b32 {%0, %1}, [%2];" : "=r"(lo), "=r"(hi) : "r"(taddr + 2 * k));
+      asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+      return __hiloint2double((int)hi, (int)lo);
+    }
+    return sm[(TM ? k - TMEM_LEVELS : k) * 32];
+  }
+  __device__ __forceinline__ void st(int k, double v) const {
+    if (TM && k < TMEM_LEVELS) {
+      asm volatile("tcgen05.st.sync.aligned.32x32b.x2.b32 [%0], {%1, %2};"
+                   :: "r"(taddr + 2 * k), "r"((uint32_t)__double2loint(v)), "r"((uint32_t)__double2hiint(v)) : "memory");
+    } else {
+      sm[(TM ? k - TMEM_LEVELS : k) * 32] = v;
+    }
+  }
+  // all earlier st() of this thread have landed (needed before a later ld() of the same level)
+  __device__ __forceinline__ void fence_st() const {
+    if (TM) asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+  }
+};
+
+// The six sweeps of one column per lane.  `active` = this lane's column exists; a lane without one (tail of the last
+// warp) works on a copy of the last column and stores nothing, because the tensor-memory accesses are warp-collective.
+template <bool D3, bool TM>
+__device__ __forceinline__ void riem_column(const Geo& g, const RiemArgs& a, const YAcc<TM>& Y, int col, int t, bool active) {
   const int km = a.km;
-  double* Y = sm + lane;                 // Y[k] -> Y[k * 32]
-#define YS(k) Y[(k) * 32]
-  // columns of the box are numbered row by row and dealt to lanes in that order (no idle lanes at row ends)
-  const int col = blockIdx.x * 32 + lane;
-  if (col >= a.b.ni * a.b.nj) return;  // no barrier is used anywhere below
-  const int i = a.b.i0 + col % a.b.ni, j = a.b.j0 + col / a.b.ni, t = blockIdx.y;
+#define yld(k) Y.ld(k)
+#define yst(k, v) Y.st((k), (v))
+  const int i = a.b.i0 + col % a.b.ni, j = a.b.j0 + col / a.b.ni;
   const long long o0 = (long long)t * g.st3 + j * g.sj + i;  // level 0
   const int o2 = t * g.sk + j * g.sj + i;
   const long long sk = g.sk;
 #define G(f, k) (f)[o0 + (long long)(k) * sk]
+#define GST(f, k, v) do { const double gst_v_ = (v); if (active) G(f, k) = gst_v_; } while (0)
   // all arrays are distinct (w_in == w_out in the D-grid solver: neither is restrict-qualified), so loads of the
   // following levels may be hoisted above the stores of the current one
   const double* __restrict__ delp = a.delp;
@@ -82,15 +119,15 @@ __global__ void __launch_bounds__(32) k_riem(Geo g, RiemArgs a) {
 #ifdef PACE_RIEM_U
   constexpr int U = PACE_RIEM_U;
 #else
-  constexpr int U = D3 ? 4 : 2;
+  constexpr int U = (D3 && !TM) ? 4 : 2;   // TM: 128 registers per thread (16 warps per SM), which U = 4 does not fit
 #endif
   // ---- A: forward ---------------------------------------------------------------------------------------------
   {
     double pem_k = ptop, peg_k = ptop, logpg_k = a.peln1;
-    G(pem, 0) = ptop;
+    GST(pem, 0, ptop);
     if (D3) {
-      G(pk3, 0) = a.ptk;
-      if (a.last_call) { G(peln, 0) = a.peln1; G(pk, 0) = a.ptk; G(pe, 0) = ptop; }
+      GST(pk3, 0, a.ptk);
+      if (a.last_call) { GST(peln, 0, a.peln1); GST(pk, 0, a.ptk); GST(pe, 0, ptop); }
     }
     double zh_k = G(zh, 0);
     double dm_j = 0.0, pe0_j = 0.0;            // level k-1
@@ -145,8 +182,8 @@ __global__ void __launch_bounds__(32) k_riem(Geo g, RiemArgs a) {
           logpg_k = lg[u];
           const int k = k0 + u;
           if (k < km) {
-            G(pk3, k + 1) = pk3n[u];
-            if (a.last_call) { G(peln, k + 1) = lp[u]; G(pk, k + 1) = pk3n[u]; G(pe, k + 1) = pemn[u]; }
+            GST(pk3, k + 1, pk3n[u]);
+            if (a.last_call) { GST(peln, k + 1, lp[u]); GST(pk, k + 1, pk3n[u]); GST(pe, k + 1, pemn[u]); }
           }
         }
       } else {
@@ -172,8 +209,8 @@ __global__ void __launch_bounds__(32) k_riem(Geo g, RiemArgs a) {
       for (int u = 0; u < U; ++u) {
         const int k = k0 + u;
         if (k < km) {
-          G(pem, k + 1) = pemn[u];
-          G(pm, k) = pmv[u];
+          GST(pem, k + 1, pemn[u]);
+          GST(pm, k, pmv[u]);
           const double dm_k = dmv[u];
           const double pe0_k = pe0v[u];
           if (k >= 1) {  // elimination step of level j = k-1
@@ -182,16 +219,16 @@ __global__ void __launch_bounds__(32) k_riem(Geo g, RiemArgs a) {
             const double bb = 2.0 * (1.0 + gr);
             const double dd = 3.0 * (pe0_j + gr * pe0_k);
             if (jl == 0) {
-              YS(0) = 0.0;
+              yst(0, 0.0);
               pp_prev = dd / bb;
-              YS(1) = pp_prev;
+              yst(1, pp_prev);
               bet_prev = bb;
             } else {
               const double gam = grat_prev / bet_prev;
               const double bet = bb - gam;
-              G(xg, jl) = gam;
+              GST(xg, jl, gam);
               pp_prev = (dd - pp_prev) / bet;
-              YS(jl + 1) = pp_prev;
+              yst(jl + 1, pp_prev);
               bet_prev = bet;
             }
             grat_prev = gr;
@@ -207,13 +244,14 @@ __global__ void __launch_bounds__(32) k_riem(Geo g, RiemArgs a) {
       const double dd = 3.0 * pe0_j;
       const double gam = grat_prev / bet_prev;
       const double bet = bb - gam;
-      G(xg, jl) = gam;
-      YS(jl + 1) = (dd - pp_prev) / bet;
+      GST(xg, jl, gam);
+      yst(jl + 1, (dd - pp_prev) / bet);
     }
+    Y.fence_st();
   }
   // ---- B: backward, pp and aa (k = km-1 .. 1) -----------------------------------------------------------------
   {
-    double pp_next = YS(km);
+    double pp_next = yld(km);
     double zh_k = G(zh, km - 1);
     double dz_k = G(zh, km) - zh_k;      // dz(km-1)
     double gm_k = GM(km - 1);
@@ -238,25 +276,26 @@ __global__ void __launch_bounds__(32) k_riem(Geo g, RiemArgs a) {
       for (int u = 0; u < U; ++u) {
         const int k = k0 - u;
         if (k >= 1) {
-          const double ppk = YS(k) - c_x[u] * pp_next;
-          YS(k) = ppk;
+          const double ppk = yld(k) - c_x[u] * pp_next;
+          yst(k, ppk);
           const double zh_m = c_zh[u];
           const double dz_m = zh_k - zh_m;  // dz(k-1)
           const double gm_m = 1.0 / (1.0 - c_cap[u]);
-          G(xg, k) = t1g * 0.5 * (gm_m + gm_k) / (dz_m + dz_k) * (c_pem[u] + ppk);
+          GST(xg, k, t1g * 0.5 * (gm_m + gm_k) / (dz_m + dz_k) * (c_pem[u] + ppk));
           pp_next = ppk;
           zh_k = zh_m; dz_k = dz_m; gm_k = gm_m;
         }
       }
     }
+    Y.fence_st();
   }
   // ---- C: forward, w elimination ------------------------------------------------------------------------------
   {
     const double dm0 = DM(0);
     double betk = dm0 - G(xg, 1);
-    double wprev = (dm0 * G(w_in, 0) + dt * YS(1)) / betk;
-    G(wtmp, 0) = wprev;
-    double pp_k = YS(1);
+    double wprev = (dm0 * G(w_in, 0) + dt * yld(1)) / betk;
+    GST(wtmp, 0, wprev);
+    double pp_k = yld(1);
     double n_delp[U], n_w[U], n_x[U + 1];  // n_x: aa(k0 .. k0+U)
 #pragma unroll
     for (int u = 0; u < U; ++u) {
@@ -286,12 +325,12 @@ __global__ void __launch_bounds__(32) k_riem(Geo g, RiemArgs a) {
         if (k < km - 1) {
           const double aak = c_x[u];
           const double gm = aak / betk;
-          G(xg, k) = gm;
+          GST(xg, k, gm);
           const double dm_k = D3 ? c_delp[u] * RGRAV : c_delp[u] / GRAV;
           betk = dm_k - (aak + c_x[u + 1] + aak * gm);
-          const double pp_n = YS(k + 1);
+          const double pp_n = yld(k + 1);
           wprev = (dm_k * c_w[u] + dt * (pp_n - pp_k) - aak * wprev) / betk;
-          G(wtmp, k) = wprev;
+          GST(wtmp, k, wprev);
           pp_k = pp_n;
         }
       }
@@ -300,14 +339,14 @@ __global__ void __launch_bounds__(32) k_riem(Geo g, RiemArgs a) {
       const int k = km - 1;
       const double aak = G(xg, k);
       const double dz_k = G(zh, k + 1) - G(zh, k);
-      const double pp_n = YS(k + 1);
+      const double pp_n = yld(k + 1);
       const double p1 = t1g * GM(k) / dz_k * (G(pem, k + 1) + pp_n);
       const double gm = aak / betk;
-      G(xg, k) = gm;
+      GST(xg, k, gm);
       const double dm_k = DM(k);
       betk = dm_k - (aak + p1 + aak * gm);
       wprev = (dm_k * G(w_in, k) + dt * (pp_n - pp_k) - p1 * ws - aak * wprev) / betk;
-      G(wtmp, k) = wprev;
+      GST(wtmp, k, wprev);
     }
   }
   // ---- D: backward, w back substitution; the corrected w goes to shared memory (Y is free until E) ------------
@@ -329,7 +368,7 @@ __global__ void __launch_bounds__(32) k_riem(Geo g, RiemArgs a) {
         const int k = k0 - u;
         if (k >= 0) {
           wn = c_w[u] - c_x[u] * wn;
-          G(wtmp, k) = wn;
+          GST(wtmp, k, wn);
         }
       }
     }
@@ -337,7 +376,7 @@ __global__ void __launch_bounds__(32) k_riem(Geo g, RiemArgs a) {
   // ---- E: forward, pe; the D-grid solver publishes w here (its old value is needed up to this point) ---------
   {
     double pe_k = 0.0;
-    YS(0) = 0.0;
+    yst(0, 0.0);
     double n_w[U], n_delp[U], n_w1[U];
 #pragma unroll
     for (int u = 0; u < U; ++u) {
@@ -362,18 +401,20 @@ __global__ void __launch_bounds__(32) k_riem(Geo g, RiemArgs a) {
           const double wk = c_w[u];
           const double dm_m = D3 ? c_delp[u] * RGRAV : c_delp[u] / GRAV;
           pe_k = pe_k + dm_m * (wk - c_w1[u]) * rdt;
-          YS(k) = pe_k;
-          if (D3) G(w_out, k - 1) = wk;
+          yst(k, pe_k);
+          if (D3) GST(w_out, k - 1, wk);
         }
       }
     }
+    Y.fence_st();
   }
   // ---- F: backward, p1, new dz, heights, output pressures ----------------------------------------------------
   {
     double zcur = a.zsurf[o2];
-    G(zh, km) = zcur;
+    GST(zh, km, zcur);
     double p1_next = 0.0;
     double dm_n = 0.0;  // dm(k+1)
+    double y_p1 = yld(km), y_p2 = 0.0;  // Y[k+1], Y[k+2] of the level in work: every level of Y is read once
     double n_delp[U], n_pm[U], n_ptv[U], n_cap[U], n_pem[U];
 #pragma unroll
     for (int u = 0; u < U; ++u) {
@@ -396,19 +437,23 @@ __global__ void __launch_bounds__(32) k_riem(Geo g, RiemArgs a) {
         }
       }
       // sequential p1 recurrence of the U levels, then their exp / log as independent chains, then the stores
-      double dmv[U], maxp[U], lm[U], earg[U], ev[U];
+      double dmv[U], maxp[U], lm[U], earg[U], ev[U], ypk[U];
 #pragma unroll
       for (int u = 0; u < U; ++u) {
         const int k = max(k0 - u, 0);
         const double dm_k = D3 ? c_delp[u] * RGRAV : c_delp[u] / GRAV;
+        const double y_k = yld(k);
+        ypk[u] = y_p1;
         double p1;
         if (k == km - 1) {
-          p1 = (YS(k) + 2.0 * YS(k + 1)) * 1.0 / 3.0;
+          p1 = (y_k + 2.0 * y_p1) * 1.0 / 3.0;
         } else {
           const double gr = dm_k / dm_n;
           const double bb = 2.0 * (1.0 + gr);
-          p1 = (YS(k) + bb * YS(k + 1) + gr * YS(k + 2)) * 1.0 / 3.0 - gr * p1_next;
+          p1 = (y_k + bb * y_p1 + gr * y_p2) * 1.0 / 3.0 - gr * p1_next;
         }
+        y_p2 = y_p1;
+        y_p1 = y_k;
         const double pm_k = c_pm[u];
         const double aa = p1 + pm_k;
         maxp[u] = (p_fac * dm_k > aa) ? p_fac * pm_k : aa;
@@ -426,22 +471,74 @@ __global__ void __launch_bounds__(32) k_riem(Geo g, RiemArgs a) {
         if (k >= 0) {
           const double dzn = (-dmv[u]) * RDGAS * c_ptv[u] * ev[u];
           if (D3) {
-            G(delz, k) = dzn;
+            GST(delz, k, dzn);
             zcur = zcur - dzn;
-            G(pef, k + 1) = a.beta_neg ? YS(k + 1) + c_pem[u] : YS(k + 1);
+            GST(pef, k + 1, a.beta_neg ? ypk[u] + c_pem[u] : ypk[u]);
           } else {
             zcur = zcur - dzn * GRAV;
-            G(pef, k + 1) = YS(k + 1) + c_pem[u];
+            GST(pef, k + 1, ypk[u] + c_pem[u]);
           }
-          G(zh, k) = zcur;
+          GST(zh, k, zcur);
         }
       }
     }
-    if (D3) G(pef, 0) = a.beta_neg ? YS(0) + G(pem, 0) : YS(0);
-    else G(pef, 0) = ptop;
+    if (D3) GST(pef, 0, a.beta_neg ? yld(0) + G(pem, 0) : yld(0));
+    else GST(pef, 0, ptop);
   }
 #undef G
-#undef YS
+#undef GST
+#undef yld
+#undef yst
+}
+
+// D3 = false: riem_solver_c, true: riem_solver3.  One warp per CTA, Y in shared memory.
+template <bool D3>
+__global__ void __launch_bounds__(32) k_riem(Geo g, RiemArgs a) {
+  extern __shared__ double sm[];
+  const int col = blockIdx.x * 32 + threadIdx.x;
+  // columns of the box are numbered row by row and dealt to lanes in that order (no idle lanes at row ends)
+  if (col >= a.b.ni * a.b.nj) return;  // no barrier is used anywhere below
+  YAcc<false> Y{sm + threadIdx.x, 0u};
+  riem_column<D3, false>(g, a, Y, col, blockIdx.y, true);
+}
+
+// Four warps per CTA, the first 64 levels of Y in tensor memory.
+template <bool D3>
+__global__ void __launch_bounds__(128, 4) k_riem_tmem(Geo g, RiemArgs a) {
+  extern __shared__ double sm[];
+  __shared__ uint32_t tmem_base;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (warp == 0) {
+    const uint32_t slot = (uint32_t)__cvta_generic_to_shared(&tmem_base);
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" :: "r"(slot), "r"((uint32_t)TMEM_COLS) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t base = tmem_base;
+  const int ncol = a.b.ni * a.b.nj;
+  const int col0 = blockIdx.x * 128 + warp * 32;       // first column of this warp
+  if (col0 < ncol) {                                   // warp-uniform: the TMEM accesses below are warp-collective
+    const int nsm = a.km + 1 > TMEM_LEVELS ? a.km + 1 - TMEM_LEVELS : 0;   // levels kept in shared memory
+    YAcc<true> Y{sm + (size_t)warp * nsm * 32 + lane, base + ((uint32_t)(warp * 32) << 16)};
+    const int col = col0 + lane;
+    riem_column<D3, true>(g, a, Y, col < ncol ? col : ncol - 1, blockIdx.y, col < ncol);
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == 0) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(base), "r"((uint32_t)TMEM_COLS) : "memory");
+  }
+}
+
+// PACE_B200_RIEM=smem selects the shared-memory layout (A/B runs)
+bool riem_use_tmem() {
+  static const bool v = [] {
+    const char* e = std::getenv("PACE_B200_RIEM");
+    return !(e != nullptr && std::string(e) == "smem");
+  }();
+  return v;
 }
 
 template <bool D3>
@@ -449,11 +546,20 @@ int launch_riem(Core& c, RiemArgs& a, const char* label) {
   const Geo g = c.g;
   a.pem = c.S("sim1.pem"); a.pm = c.S("sim1.pm"); a.wtmp = c.S("sim1.w"); a.xwork = c.S("sim1.x");
   if (!c.err.empty()) return 1;
+  const int ncol = a.b.ni * a.b.nj;
+  LaunchScope scope(c.stream, label);
+  if (riem_use_tmem()) {
+    const int nsm = a.km + 1 > TMEM_LEVELS ? a.km + 1 - TMEM_LEVELS : 0;
+    const size_t smem = (size_t)nsm * 32 * 4 * sizeof(double);
+    if (smem > 48 * 1024) { c.err = "riem_solver: too many levels for the on-chip kernel"; return 1; }
+    dim3 grd((ncol + 127) / 128, g.nt, 1);
+    k_riem_tmem<D3><<<grd, 128, smem, c.stream>>>(g, a);
+    return 0;
+  }
   const size_t smem = (size_t)(a.km + 1) * 32 * sizeof(double);
   if (func_attr_once(c, (const void*)k_riem<D3>, 96 * 1024)) return 1;  // once per instantiation and device (tile.cu)
   if (smem > 96 * 1024) { c.err = "riem_solver: too many levels for the on-chip kernel"; return 1; }
-  dim3 grd((a.b.ni * a.b.nj + 31) / 32, g.nt, 1);
-  LaunchScope scope(c.stream, label);
+  dim3 grd((ncol + 31) / 32, g.nt, 1);
   k_riem<D3><<<grd, 32, smem, c.stream>>>(g, a);
   return 0;
 }
