@@ -7,13 +7,13 @@
 // memory and X in one global work array that every sweep prefetches a chunk ahead (two shared arrays would cap the
 // SM at 5 warps; these sweeps are chains of dependent fp64 divisions / exp / log and need the occupancy):
 //   A  forward : pressures (pem, peg cumulative sums), pm, first guess pe, tridiagonal elimination   X=gam  Y=pp
-//   B  backward: back substitution, aa                                                               X=aa   Y=pp
-//   C  forward : w elimination                                                                        X=gam' S=w
+//   B  backward: back substitution                                                                    Y=pp
+//   C  forward : aa (pem summed again), w elimination                                                 X=gam' S=w
 //   D  backward: w back substitution                                                                  S=w
-//   E  forward : pe cumulative sum                                                                    Y=pe
-//   F  backward: p1 recurrence, new dz, heights, output pressures
+//   E  forward : pe cumulative sum, output pressures (pem summed again)                               Y=pe
+//   F  backward: p1 recurrence, new dz, heights
 // Everything else is recomputed from the inputs (identical expressions give identical bits) or carried in
-// registers; pem, pm, X and the intermediate w (S) are the only global work arrays.
+// registers; pm, X and the intermediate w (S) are the only global work arrays.
 // Statement order and expression trees per level are those of riem_solver.cu / the reference (sim1_solver.py:20-141,
 // riem_solver_c.py:21-123, riem_solver3.py:26-146), so results are bit-identical.
 #include <cstdlib>
@@ -30,7 +30,7 @@ namespace {
 struct RiemArgs {
   const double *delp, *cappa, *ptv, *q_con, *w_in, *zsurf, *ws;
   double* zh;                       // heights: ad.gz (C) / ad.zh (D), read then rewritten
-  double *pem, *pm, *wtmp, *xwork;  // global work arrays
+  double *pm, *wtmp, *xwork;  // global work arrays
   double *pef;                      // ad.pkc
   double *w_out, *delz, *pk3, *peln, *pk, *pe;  // D-grid solver only
   double ptop, p_fac, dt, t1g, rdt, peln1, ptk;
@@ -77,7 +77,7 @@ struct YAcc {
 
 // The six sweeps of one column per lane.  `active` = this lane's column exists; a lane without one (tail of the last
 // warp) works on a copy of the last column and stores nothing, because the tensor-memory accesses are warp-collective.
-template <bool D3, bool TM>
+template <bool D3, bool TM, int UU>
 __device__ __forceinline__ void riem_column(const Geo& g, const RiemArgs& a, const YAcc<TM>& Y, int col, int t, bool active) {
   const int km = a.km;
 #define yld(k) Y.ld(k)
@@ -97,7 +97,6 @@ __device__ __forceinline__ void riem_column(const Geo& g, const RiemArgs& a, con
   const double* w_in = a.w_in;
   double* w_out = a.w_out;
   double* __restrict__ zh = a.zh;
-  double* __restrict__ pem = a.pem;
   double* __restrict__ pm = a.pm;
   double* __restrict__ wtmp = a.wtmp;
   double* __restrict__ xg = a.xwork;
@@ -116,15 +115,10 @@ __device__ __forceinline__ void riem_column(const Geo& g, const RiemArgs& a, con
   // Every sweep walks the column in chunks of U levels: the global inputs of the next chunk are requested before the
   // current chunk is computed, so that ~5 x U loads per warp are in flight behind the (latency-bound) recurrences.
   // Measured at C384 (ms per step, U = 2 / 3 / 4): riem_solver_c 32.5 / 35.5 / 37.5, riem_solver3 37.2 / 36.8 / 31.8.
-#ifdef PACE_RIEM_U
-  constexpr int U = PACE_RIEM_U;
-#else
-  constexpr int U = (D3 && !TM) ? 4 : 2;   // TM: 128 registers per thread (16 warps per SM), which U = 4 does not fit
-#endif
+  constexpr int U = UU;
   // ---- A: forward ---------------------------------------------------------------------------------------------
   {
     double pem_k = ptop, peg_k = ptop, logpg_k = a.peln1;
-    GST(pem, 0, ptop);
     if (D3) {
       GST(pk3, 0, a.ptk);
       if (a.last_call) { GST(peln, 0, a.peln1); GST(pk, 0, a.ptk); GST(pe, 0, ptop); }
@@ -209,7 +203,6 @@ __device__ __forceinline__ void riem_column(const Geo& g, const RiemArgs& a, con
       for (int u = 0; u < U; ++u) {
         const int k = k0 + u;
         if (k < km) {
-          GST(pem, k + 1, pemn[u]);
           GST(pm, k, pmv[u]);
           const double dm_k = dmv[u];
           const double pe0_k = pe0v[u];
@@ -249,28 +242,20 @@ __device__ __forceinline__ void riem_column(const Geo& g, const RiemArgs& a, con
     }
     Y.fence_st();
   }
-  // ---- B: backward, pp and aa (k = km-1 .. 1) -----------------------------------------------------------------
+  // ---- B: backward, pp (k = km-1 .. 1).  aa, which the reference forms here, only needs the final pp of its own
+  // level: it is formed in sweep C, where the pressure sum runs forward again (no aa / pem arrays in global memory)
   {
     double pp_next = yld(km);
-    double zh_k = G(zh, km - 1);
-    double dz_k = G(zh, km) - zh_k;      // dz(km-1)
-    double gm_k = GM(km - 1);
-    double n_zh[U], n_cap[U], n_pem[U], n_x[U];
+    double n_x[U];
 #pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const int kk = max(km - 1 - u, 1);
-      n_zh[u] = G(zh, kk - 1); n_cap[u] = G(cappa, kk - 1); n_pem[u] = G(pem, kk); n_x[u] = G(xg, kk);
-    }
+    for (int u = 0; u < U; ++u) n_x[u] = G(xg, max(km - 1 - u, 1));
     for (int k0 = km - 1; k0 >= 1; k0 -= U) {
-      double c_zh[U], c_cap[U], c_pem[U], c_x[U];
+      double c_x[U];
 #pragma unroll
-      for (int u = 0; u < U; ++u) { c_zh[u] = n_zh[u]; c_cap[u] = n_cap[u]; c_pem[u] = n_pem[u]; c_x[u] = n_x[u]; }
+      for (int u = 0; u < U; ++u) c_x[u] = n_x[u];
       if (k0 - U >= 1) {
 #pragma unroll
-        for (int u = 0; u < U; ++u) {
-          const int kk = max(k0 - U - u, 1);
-          n_zh[u] = G(zh, kk - 1); n_cap[u] = G(cappa, kk - 1); n_pem[u] = G(pem, kk); n_x[u] = G(xg, kk);
-        }
+        for (int u = 0; u < U; ++u) n_x[u] = G(xg, max(k0 - U - u, 1));
       }
 #pragma unroll
       for (int u = 0; u < U; ++u) {
@@ -278,72 +263,85 @@ __device__ __forceinline__ void riem_column(const Geo& g, const RiemArgs& a, con
         if (k >= 1) {
           const double ppk = yld(k) - c_x[u] * pp_next;
           yst(k, ppk);
-          const double zh_m = c_zh[u];
-          const double dz_m = zh_k - zh_m;  // dz(k-1)
-          const double gm_m = 1.0 / (1.0 - c_cap[u]);
-          GST(xg, k, t1g * 0.5 * (gm_m + gm_k) / (dz_m + dz_k) * (c_pem[u] + ppk));
           pp_next = ppk;
-          zh_k = zh_m; dz_k = dz_m; gm_k = gm_m;
         }
       }
     }
     Y.fence_st();
   }
-  // ---- C: forward, w elimination ------------------------------------------------------------------------------
+  // ---- C: forward, aa and the w elimination ---------------------------------------------------------------------
+  // aa(k) = t1g * 0.5 * (gm(k-1) + gm(k)) / (dz(k-1) + dz(k)) * (pem(k) + pp(k)), 1 <= k <= km-1 (sim1_solver.py), with
+  // pem(k) = pem(k-1) + delp(k-1) summed in the order of sweep A, gm = 1 / (1 - cappa), dz(k) = zh(k+1) - zh(k)
   {
-    const double dm0 = DM(0);
-    double betk = dm0 - G(xg, 1);
-    double wprev = (dm0 * G(w_in, 0) + dt * yld(1)) / betk;
-    GST(wtmp, 0, wprev);
+    const double delp0 = G(delp, 0);
+    const double dm0 = D3 ? delp0 * RGRAV : delp0 / GRAV;
+    double pem_k = ptop + delp0;                       // pem(1)
+    double zh_lo = G(zh, 1);
+    double dz_m = zh_lo - G(zh, 0);                    // dz(0)
+    double gm_m = GM(0);
     double pp_k = yld(1);
-    double n_delp[U], n_w[U], n_x[U + 1];  // n_x: aa(k0 .. k0+U)
+    double aa_k;                                       // aa(k) of the level in work
+    {
+      const double zh_hi = G(zh, 2);
+      const double dz_k = zh_hi - zh_lo;               // dz(1)
+      const double gm_k = GM(1);
+      aa_k = t1g * 0.5 * (gm_m + gm_k) / (dz_m + dz_k) * (pem_k + pp_k);
+      zh_lo = zh_hi; dz_m = dz_k; gm_m = gm_k;         // now dz(1), gm(1), zh(2)
+    }
+    double betk = dm0 - aa_k;
+    double wprev = (dm0 * G(w_in, 0) + dt * pp_k) / betk;
+    GST(wtmp, 0, wprev);
+    double n_delp[U], n_w[U], n_cap[U], n_zh[U];       // delp(k), w(k), cappa(k+1), zh(k+2)
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       const int kk = min(1 + u, km - 1);
-      n_delp[u] = G(delp, kk); n_w[u] = G(w_in, kk);
+      n_delp[u] = G(delp, kk); n_w[u] = G(w_in, kk); n_cap[u] = G(cappa, min(kk + 1, km - 1)); n_zh[u] = G(zh, min(kk + 2, km));
     }
-#pragma unroll
-    for (int u = 0; u <= U; ++u) n_x[u] = G(xg, min(1 + u, km - 1));
     for (int k0 = 1; k0 < km - 1; k0 += U) {
-      double c_delp[U], c_w[U], c_x[U + 1];
+      double c_delp[U], c_w[U], c_cap[U], c_zh[U];
 #pragma unroll
-      for (int u = 0; u < U; ++u) { c_delp[u] = n_delp[u]; c_w[u] = n_w[u]; }
-#pragma unroll
-      for (int u = 0; u <= U; ++u) c_x[u] = n_x[u];
+      for (int u = 0; u < U; ++u) { c_delp[u] = n_delp[u]; c_w[u] = n_w[u]; c_cap[u] = n_cap[u]; c_zh[u] = n_zh[u]; }
       if (k0 + U < km - 1) {
 #pragma unroll
         for (int u = 0; u < U; ++u) {
           const int kk = min(k0 + U + u, km - 1);
-          n_delp[u] = G(delp, kk); n_w[u] = G(w_in, kk);
+          n_delp[u] = G(delp, kk); n_w[u] = G(w_in, kk); n_cap[u] = G(cappa, min(kk + 1, km - 1)); n_zh[u] = G(zh, min(kk + 2, km));
         }
-#pragma unroll
-        for (int u = 0; u <= U; ++u) n_x[u] = G(xg, min(k0 + U + u, km - 1));
       }
 #pragma unroll
       for (int u = 0; u < U; ++u) {
         const int k = k0 + u;
         if (k < km - 1) {
-          const double aak = c_x[u];
+          // aa(k + 1)
+          const double pp_n = yld(k + 1);
+          pem_k = pem_k + c_delp[u];                   // pem(k + 1)
+          const double dz_k = c_zh[u] - zh_lo;         // dz(k + 1)
+          const double gm_k = 1.0 / (1.0 - c_cap[u]);  // gm(k + 1)
+          const double aa_n = t1g * 0.5 * (gm_m + gm_k) / (dz_m + dz_k) * (pem_k + pp_n);
+          zh_lo = c_zh[u]; dz_m = dz_k; gm_m = gm_k;
+          // elimination step of level k
+          const double aak = aa_k;
           const double gm = aak / betk;
           GST(xg, k, gm);
           const double dm_k = D3 ? c_delp[u] * RGRAV : c_delp[u] / GRAV;
-          betk = dm_k - (aak + c_x[u + 1] + aak * gm);
-          const double pp_n = yld(k + 1);
+          betk = dm_k - (aak + aa_n + aak * gm);
           wprev = (dm_k * c_w[u] + dt * (pp_n - pp_k) - aak * wprev) / betk;
           GST(wtmp, k, wprev);
           pp_k = pp_n;
+          aa_k = aa_n;
         }
       }
     }
     {
+      // level km-1: dz_m = dz(km-1), gm_m = gm(km-1), pem_k = pem(km-1) at this point
       const int k = km - 1;
-      const double aak = G(xg, k);
-      const double dz_k = G(zh, k + 1) - G(zh, k);
+      const double aak = aa_k;
+      const double delp_k = G(delp, k);
       const double pp_n = yld(k + 1);
-      const double p1 = t1g * GM(k) / dz_k * (G(pem, k + 1) + pp_n);
+      const double p1 = t1g * gm_m / dz_m * ((pem_k + delp_k) + pp_n);
       const double gm = aak / betk;
       GST(xg, k, gm);
-      const double dm_k = DM(k);
+      const double dm_k = D3 ? delp_k * RGRAV : delp_k / GRAV;
       betk = dm_k - (aak + p1 + aak * gm);
       wprev = (dm_k * G(w_in, k) + dt * (pp_n - pp_k) - p1 * ws - aak * wprev) / betk;
       GST(wtmp, k, wprev);
@@ -373,10 +371,14 @@ __device__ __forceinline__ void riem_column(const Geo& g, const RiemArgs& a, con
       }
     }
   }
-  // ---- E: forward, pe; the D-grid solver publishes w here (its old value is needed up to this point) ---------
+  // ---- E: forward, pe and the output pressure (pe, or pe + pem with the pressure sum of sweep A run again); the
+  // D-grid solver publishes w here (its old value is needed up to this point)
   {
     double pe_k = 0.0;
+    double pem_k = ptop;
     yst(0, 0.0);
+    if (D3) GST(pef, 0, a.beta_neg ? 0.0 + ptop : 0.0);   // pe(0) = 0, pem(0) = ptop
+    else GST(pef, 0, ptop);
     double n_w[U], n_delp[U], n_w1[U];
 #pragma unroll
     for (int u = 0; u < U; ++u) {
@@ -402,7 +404,13 @@ __device__ __forceinline__ void riem_column(const Geo& g, const RiemArgs& a, con
           const double dm_m = D3 ? c_delp[u] * RGRAV : c_delp[u] / GRAV;
           pe_k = pe_k + dm_m * (wk - c_w1[u]) * rdt;
           yst(k, pe_k);
-          if (D3) GST(w_out, k - 1, wk);
+          pem_k = pem_k + c_delp[u];                   // pem(k)
+          if (D3) {
+            GST(w_out, k - 1, wk);
+            GST(pef, k, a.beta_neg ? pe_k + pem_k : pe_k);
+          } else {
+            GST(pef, k, pe_k + pem_k);
+          }
         }
       }
     }
@@ -415,35 +423,32 @@ __device__ __forceinline__ void riem_column(const Geo& g, const RiemArgs& a, con
     double p1_next = 0.0;
     double dm_n = 0.0;  // dm(k+1)
     double y_p1 = yld(km), y_p2 = 0.0;  // Y[k+1], Y[k+2] of the level in work: every level of Y is read once
-    double n_delp[U], n_pm[U], n_ptv[U], n_cap[U], n_pem[U];
+    double n_delp[U], n_pm[U], n_ptv[U], n_cap[U];
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       const int kk = max(km - 1 - u, 0);
       n_delp[u] = G(delp, kk); n_pm[u] = G(pm, kk); n_ptv[u] = G(ptv, kk); n_cap[u] = G(cappa, kk);
-      n_pem[u] = G(pem, kk + 1);
     }
     for (int k0 = km - 1; k0 >= 0; k0 -= U) {
-      double c_delp[U], c_pm[U], c_ptv[U], c_cap[U], c_pem[U];
+      double c_delp[U], c_pm[U], c_ptv[U], c_cap[U];
 #pragma unroll
       for (int u = 0; u < U; ++u) {
-        c_delp[u] = n_delp[u]; c_pm[u] = n_pm[u]; c_ptv[u] = n_ptv[u]; c_cap[u] = n_cap[u]; c_pem[u] = n_pem[u];
+        c_delp[u] = n_delp[u]; c_pm[u] = n_pm[u]; c_ptv[u] = n_ptv[u]; c_cap[u] = n_cap[u];
       }
       if (k0 - U >= 0) {
 #pragma unroll
         for (int u = 0; u < U; ++u) {
           const int kk = max(k0 - U - u, 0);
           n_delp[u] = G(delp, kk); n_pm[u] = G(pm, kk); n_ptv[u] = G(ptv, kk); n_cap[u] = G(cappa, kk);
-          n_pem[u] = G(pem, kk + 1);
         }
       }
       // sequential p1 recurrence of the U levels, then their exp / log as independent chains, then the stores
-      double dmv[U], maxp[U], lm[U], earg[U], ev[U], ypk[U];
+      double dmv[U], maxp[U], lm[U], earg[U], ev[U];
 #pragma unroll
       for (int u = 0; u < U; ++u) {
         const int k = max(k0 - u, 0);
         const double dm_k = D3 ? c_delp[u] * RGRAV : c_delp[u] / GRAV;
         const double y_k = yld(k);
-        ypk[u] = y_p1;
         double p1;
         if (k == km - 1) {
           p1 = (y_k + 2.0 * y_p1) * 1.0 / 3.0;
@@ -473,17 +478,13 @@ __device__ __forceinline__ void riem_column(const Geo& g, const RiemArgs& a, con
           if (D3) {
             GST(delz, k, dzn);
             zcur = zcur - dzn;
-            GST(pef, k + 1, a.beta_neg ? ypk[u] + c_pem[u] : ypk[u]);
           } else {
             zcur = zcur - dzn * GRAV;
-            GST(pef, k + 1, ypk[u] + c_pem[u]);
           }
           GST(zh, k, zcur);
         }
       }
     }
-    if (D3) GST(pef, 0, a.beta_neg ? yld(0) + G(pem, 0) : yld(0));
-    else GST(pef, 0, ptop);
   }
 #undef G
 #undef GST
@@ -499,11 +500,11 @@ __global__ void __launch_bounds__(32) k_riem(Geo g, RiemArgs a) {
   // columns of the box are numbered row by row and dealt to lanes in that order (no idle lanes at row ends)
   if (col >= a.b.ni * a.b.nj) return;  // no barrier is used anywhere below
   YAcc<false> Y{sm + threadIdx.x, 0u};
-  riem_column<D3, false>(g, a, Y, col, blockIdx.y, true);
+  riem_column<D3, false, D3 ? 4 : 2>(g, a, Y, col, blockIdx.y, true);
 }
 
 // Four warps per CTA, the first 64 levels of Y in tensor memory.
-template <bool D3>
+template <bool D3, int UU>
 __global__ void __launch_bounds__(128, 4) k_riem_tmem(Geo g, RiemArgs a) {
   extern __shared__ double sm[];
   __shared__ uint32_t tmem_base;
@@ -523,7 +524,7 @@ __global__ void __launch_bounds__(128, 4) k_riem_tmem(Geo g, RiemArgs a) {
     const int nsm = a.km + 1 > TMEM_LEVELS ? a.km + 1 - TMEM_LEVELS : 0;   // levels kept in shared memory
     YAcc<true> Y{sm + (size_t)warp * nsm * 32 + lane, base + ((uint32_t)(warp * 32) << 16)};
     const int col = col0 + lane;
-    riem_column<D3, true>(g, a, Y, col < ncol ? col : ncol - 1, blockIdx.y, col < ncol);
+    riem_column<D3, true, UU>(g, a, Y, col < ncol ? col : ncol - 1, blockIdx.y, col < ncol);
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
@@ -544,7 +545,7 @@ bool riem_use_tmem() {
 template <bool D3>
 int launch_riem(Core& c, RiemArgs& a, const char* label) {
   const Geo g = c.g;
-  a.pem = c.S("sim1.pem"); a.pm = c.S("sim1.pm"); a.wtmp = c.S("sim1.w"); a.xwork = c.S("sim1.x");
+  a.pm = c.S("sim1.pm"); a.wtmp = c.S("sim1.w"); a.xwork = c.S("sim1.x");
   if (!c.err.empty()) return 1;
   const int ncol = a.b.ni * a.b.nj;
   LaunchScope scope(c.stream, label);
@@ -553,7 +554,11 @@ int launch_riem(Core& c, RiemArgs& a, const char* label) {
     const size_t smem = (size_t)nsm * 32 * 4 * sizeof(double);
     if (smem > 48 * 1024) { c.err = "riem_solver: too many levels for the on-chip kernel"; return 1; }
     dim3 grd((ncol + 127) / 128, g.nt, 1);
-    k_riem_tmem<D3><<<grd, 128, smem, c.stream>>>(g, a);
+    // levels per chunk (PACE_B200_RIEM_U = 2 / 3): at C384 riem_solver_c 21.6 / 20.8, riem_solver3 24.9 / 24.7 ms per step
+    // (three levels of exp / log chains spill 8 / 80 bytes at the 128 registers that 16 warps per SM allow)
+    static const int u = [] { const char* e = std::getenv("PACE_B200_RIEM_U"); return e ? std::atoi(e) : 3; }();
+    if (u == 3) k_riem_tmem<D3, 3><<<grd, 128, smem, c.stream>>>(g, a);
+    else k_riem_tmem<D3, 2><<<grd, 128, smem, c.stream>>>(g, a);
     return 0;
   }
   const size_t smem = (size_t)(a.km + 1) * 32 * sizeof(double);
