@@ -160,6 +160,48 @@ int nh_p_grad(Core& c, double dt, bool keep_agrid) {
   // reference first sets pp = 0 and pk3 = ptk on level 0 and forms wk = pk3(k+1) - pk3(k) in a work field; here the
   // level-0 values are substituted at read time and wk is formed in registers for the three points that need it (same
   // expression), which saves the work field's write and reads and a launch.  Level 0 of pp / pk3 is still stored.
+#ifndef PACE_HOST_EMU
+  // Device build: one thread per column, marching down the levels.  Every level of pk3 / pp / gz is then read once per
+  // point (the values of interface k+1 become those of interface k of the next level) instead of twice by two CTAs.
+  // PACE_B200_NHPG=levels selects the level-parallel kernel below (A/B runs; the host emulation always uses it).
+  static const bool by_levels = [] { const char* e = getenv("PACE_B200_NHPG"); return e != nullptr && e[0] == 'l'; }();
+  if (!by_levels) {
+    launch_ij_occ<5>(st, g, box_compute(g, 0, 0, 1, 1, 0), [=] __device__(const Pt& p) {
+      const bool has_u = p.i <= ie, has_v = p.j <= je;
+      // interface k: pk3 and pp of level 0 are the prescribed top values, stored here as the reference does
+      double pk00 = top_value, pk10 = top_value, pk01 = top_value;
+      double pp00 = 0.0, pp10 = 0.0, pp01 = 0.0;
+      double gz00 = A(gz, 0, 0, 0), gz10 = A(gz, 1, 0, 0), gz01 = A(gz, 0, 1, 0);
+      A(pp, 0, 0, 0) = 0.0;
+      A(pk3, 0, 0, 0) = top_value;
+      const double rdx0 = A20(rdx), rdy0 = A20(rdy);
+#pragma unroll 1
+      for (int k = 0; k < km; ++k) {
+        const double npk00 = A(pk3, 0, 0, k + 1), npk10 = A(pk3, 1, 0, k + 1), npk01 = A(pk3, 0, 1, k + 1);
+        const double npp00 = A(pp, 0, 0, k + 1), npp10 = A(pp, 1, 0, k + 1), npp01 = A(pp, 0, 1, k + 1);
+        const double ngz00 = A(gz, 0, 0, k + 1), ngz10 = A(gz, 1, 0, k + 1), ngz01 = A(gz, 0, 1, k + 1);
+        const double w00 = A(wk1, 0, 0, k), w10 = A(wk1, 1, 0, k), w01 = A(wk1, 0, 1, k);
+        const double wk0 = npk00 - pk00;
+        if (has_u) {
+          double du = dt / (wk0 + (npk10 - pk10)) * ((ngz00 - gz10) * (npk10 - pk00) + (gz00 - ngz10) * (npk00 - pk10));
+          A(u, 0, 0, k) = (A(u, 0, 0, k) + du +
+                           dt / (w00 + w10) * ((ngz00 - gz10) * (npp10 - pp00) + (gz00 - ngz10) * (npp00 - pp10))) *
+                          rdx0;
+        }
+        if (has_v) {
+          double dv = dt / (wk0 + (npk01 - pk01)) * ((ngz00 - gz01) * (npk01 - pk00) + (gz00 - ngz01) * (npk00 - pk01));
+          A(v, 0, 0, k) = (A(v, 0, 0, k) + dv +
+                           dt / (w00 + w01) * ((ngz00 - gz01) * (npp01 - pp00) + (gz00 - ngz01) * (npp00 - pp01))) *
+                          rdy0;
+        }
+        pk00 = npk00; pk10 = npk10; pk01 = npk01;
+        pp00 = npp00; pp10 = npp10; pp01 = npp01;
+        gz00 = ngz00; gz10 = ngz10; gz01 = ngz01;
+      }
+    }, "nh_p_grad_winds");
+    return 0;
+  }
+#endif
   launch_ijk(st, g, box_compute(g, 0, 0, 1, 1, 0), [=] __device__(const Pt& p) {
     const bool top = p.k == 0;
     auto PK = [&](int di, int dj) { return top ? top_value : A(pk3, di, dj, 0); };   // pk3 at this level

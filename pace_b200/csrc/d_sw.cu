@@ -5,6 +5,8 @@
 // 178 reference launches; the transport operators are in transport.cu, the flux prep in fxadv.cu, the
 // divergence damping in divergence_damping.cu, the rest is grouped here (comments name the reference
 // stencil each kernel covers).
+#include <cstdlib>
+
 #include "ppm.cuh"
 #include "transport.hpp"
 
@@ -240,10 +242,19 @@ int d_sw(Core& c, double dt) {
   a.crx = crx; a.cry = cry; a.xfx = xfx; a.yfx = yfx; a.nk = nz;
   a.q = abs_vort; a.fx = tfx; a.fy = tfy; a.hord = cf.hord_vt;
   if (fvtp2d(c, a)) return 1;
-  // 18. u_and_v_from_ke
+  // 18. u_and_v_from_ke.  The winds of this stage go to two work fields (us, vs) unless PACE_B200_DSW_UV=split: the
+  // heat-source kernel below reads them at neighbouring points, so it can only write the final winds (23.) in the
+  // same pass if its inputs live elsewhere.
+  static const bool uv_split_env = [] { const char* e = getenv("PACE_B200_DSW_UV"); return e != nullptr && e[0] == 's'; }();
+  const bool uv_split = uv_split_env;
+  double *us = u, *vs = v;
+  if (!uv_split) {
+    us = c.S("dsw.u_from_ke"); vs = c.S("dsw.v_from_ke");
+    if (!c.err.empty()) return 1;
+  }
   launch_ijk(st, g, box_dims(g, 1, 1, 0), [=] __device__(const Pt& p) {
-    if (p.i <= ie) A0(u) = A0(u) * A20(dx) + A0(ke) - A(ke, 1, 0, 0) + A0(tfy);
-    if (p.j <= je) A0(v) = A0(v) * A20(dy) + A0(ke) - A(ke, 0, 1, 0) - A0(tfx);
+    if (p.i <= ie) A0(us) = A0(u) * A20(dx) + A0(ke) - A(ke, 1, 0, 0) + A0(tfy);
+    if (p.j <= je) A0(vs) = A0(v) * A20(dy) + A0(ke) - A(ke, 0, 1, 0) - A0(tfx);
   });
   // 19. delnflux_nosg_v(vorticity_agrid) -> tmp_ut, tmp_vt
   {
@@ -255,34 +266,43 @@ int d_sw(Core& c, double dt) {
   // (compute domain).  vort_x_delta / vort_y_delta are differences of the damped B-grid vorticity and only enter here:
   // they are formed in registers (same expression) instead of two scratch fields.
   const bool do_accum = cf.d_con > 1.0e-5;
-  launch_ijk(st, g, box_dims(g, 0, 0, 0), [=] __device__(const Pt& p) {
-    const double hs0 = A0(heat_s);
-    double hs = hs0;
-    const double frac = col_d_con[p.k];
-    if (frac > 1e-5) {
-      auto vxdf = [&](int dj) { return A(vort_b, 0, dj, 0) - A(vort_b, 1, dj, 0); };   // vort_x_delta(i, j+dj)
-      auto vydf = [&](int di) { return A(vort_b, di, 0, 0) - A(vort_b, di, 1, 0); };   // vort_y_delta(i+di, j)
-      auto ubt = [&](int dj) { return (vxdf(dj) + A(tvt, 0, dj, 0)) * A2(rdx, 0, dj); };
-      auto fyf = [&](int dj) { return A(u, 0, dj, 0) * A2(rdx, 0, dj); };
-      auto vbt = [&](int di) { return (vydf(di) - A(tut, di, 0, 0)) * A2(rdy, di, 0); };
-      auto fxf = [&](int di) { return A(v, di, 0, 0) * A2(rdy, di, 0); };
-      double ub0 = ubt(0), ub1 = ubt(1), fy0 = fyf(0), fy1 = fyf(1);
-      double vb0 = vbt(0), vb1 = vbt(1), fx0 = fxf(0), fx1 = fxf(1);
-      double gy0 = fy0 * ub0, gy1 = fy1 * ub1, gx0 = fx0 * vb0, gx1 = fx1 * vb1;
-      double u2 = fy0 + fy1, du2 = ub0 + ub1, v2 = fx0 + fx1, dv2 = vb0 + vb1;
-      double dampterm = A20(rsin2) * 0.25 *
-                        ((ub0 * ub0 + ub1 * ub1 + vb0 * vb0 + vb1 * vb1) + 2.0 * (gy0 + gy1 + gx0 + gx1) -
-                         A20(cosa_s) * (u2 * dv2 + v2 * du2 + du2 * dv2));
-      hs = A0(delp) * (hs - frac * dampterm);
-      A0(heat_s) = hs;
+  launch_ijk(st, g, uv_split ? box_dims(g, 0, 0, 0) : box_dims(g, 1, 1, 0), [=] __device__(const Pt& p) {
+    const bool in_i = p.i <= ie, in_j = p.j <= je;
+    if (in_i && in_j) {
+      const double hs0 = A0(heat_s);
+      double hs = hs0;
+      const double frac = col_d_con[p.k];
+      if (frac > 1e-5) {
+        auto vxdf = [&](int dj) { return A(vort_b, 0, dj, 0) - A(vort_b, 1, dj, 0); };   // vort_x_delta(i, j+dj)
+        auto vydf = [&](int di) { return A(vort_b, di, 0, 0) - A(vort_b, di, 1, 0); };   // vort_y_delta(i+di, j)
+        auto ubt = [&](int dj) { return (vxdf(dj) + A(tvt, 0, dj, 0)) * A2(rdx, 0, dj); };
+        auto fyf = [&](int dj) { return A(us, 0, dj, 0) * A2(rdx, 0, dj); };
+        auto vbt = [&](int di) { return (vydf(di) - A(tut, di, 0, 0)) * A2(rdy, di, 0); };
+        auto fxf = [&](int di) { return A(vs, di, 0, 0) * A2(rdy, di, 0); };
+        double ub0 = ubt(0), ub1 = ubt(1), fy0 = fyf(0), fy1 = fyf(1);
+        double vb0 = vbt(0), vb1 = vbt(1), fx0 = fxf(0), fx1 = fxf(1);
+        double gy0 = fy0 * ub0, gy1 = fy1 * ub1, gx0 = fx0 * vb0, gx1 = fx1 * vb1;
+        double u2 = fy0 + fy1, du2 = ub0 + ub1, v2 = fx0 + fx1, dv2 = vb0 + vb1;
+        double dampterm = A20(rsin2) * 0.25 *
+                          ((ub0 * ub0 + ub1 * ub1 + vb0 * vb0 + vb1 * vb1) + 2.0 * (gy0 + gy1 + gx0 + gx1) -
+                           A20(cosa_s) * (u2 * dv2 + v2 * du2 + du2 * dv2));
+        hs = A0(delp) * (hs - frac * dampterm);
+        A0(heat_s) = hs;
+      }
+      if (do_accum) {
+        A0(heat_source) = A0(heat_source) + hs;
+        A0(diss_est) = A0(diss_est) + hs0;
+      }
     }
-    if (do_accum) {
-      A0(heat_source) = A0(heat_source) + hs;
-      A0(diss_est) = A0(diss_est) + hs0;
+    if (!uv_split) {
+      // 23. update_u_and_v, from the winds of stage 18 in the work fields
+      const bool damp = col_damp_vt[p.k] > 1e-5;
+      if (in_i) A0(u) = damp ? A0(us) + A0(tvt) : A0(us);
+      if (in_j) A0(v) = damp ? A0(vs) - A0(tut) : A0(vs);
     }
   });
   // 23. update_u_and_v
-  launch_ijk(st, g, box_dims(g, 1, 1, 0), [=] __device__(const Pt& p) {
+  if (uv_split) launch_ijk(st, g, box_dims(g, 1, 1, 0), [=] __device__(const Pt& p) {
     if (col_damp_vt[p.k] > 1e-5) {
       if (p.i <= ie) A0(u) = A0(u) + A0(tvt);
       if (p.j <= je) A0(v) = A0(v) - A0(tut);
