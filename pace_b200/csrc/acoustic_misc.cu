@@ -165,6 +165,7 @@ int nh_p_grad(Core& c, double dt, bool keep_agrid) {
   // point (the values of interface k+1 become those of interface k of the next level) instead of twice by two CTAs.
   // PACE_B200_NHPG=levels selects the level-parallel kernel below (A/B runs; the host emulation always uses it).
   static const bool by_levels = [] { const char* e = getenv("PACE_B200_NHPG"); return e != nullptr && e[0] == 'l'; }();
+  constexpr int NHPG_PF = 6;
   if (!by_levels) {
     launch_ij_occ<5>(st, g, box_compute(g, 0, 0, 1, 1, 0), [=] __device__(const Pt& p) {
       const bool has_u = p.i <= ie, has_v = p.j <= je;
@@ -177,6 +178,14 @@ int nh_p_grad(Core& c, double dt, bool keep_agrid) {
       const double rdx0 = A20(rdx), rdy0 = A20(rdy);
 #pragma unroll 1
       for (int k = 0; k < km; ++k) {
+        if ((p.i & 3) == 0 && k + NHPG_PF < km) {   // ask L2 for the rows a few levels ahead, one request per sector
+          asm volatile("prefetch.global.L2 [%0];" ::"l"(&A(pk3, 0, 0, k + 1 + NHPG_PF)));
+          asm volatile("prefetch.global.L2 [%0];" ::"l"(&A(pp, 0, 0, k + 1 + NHPG_PF)));
+          asm volatile("prefetch.global.L2 [%0];" ::"l"(&A(gz, 0, 0, k + 1 + NHPG_PF)));
+          asm volatile("prefetch.global.L2 [%0];" ::"l"(&A(wk1, 0, 0, k + NHPG_PF)));
+          asm volatile("prefetch.global.L2 [%0];" ::"l"(&A(u, 0, 0, k + NHPG_PF)));
+          asm volatile("prefetch.global.L2 [%0];" ::"l"(&A(v, 0, 0, k + NHPG_PF)));
+        }
         const double npk00 = A(pk3, 0, 0, k + 1), npk10 = A(pk3, 1, 0, k + 1), npk01 = A(pk3, 0, 1, k + 1);
         const double npp00 = A(pp, 0, 0, k + 1), npp10 = A(pp, 1, 0, k + 1), npp01 = A(pp, 0, 1, k + 1);
         const double ngz00 = A(gz, 0, 0, k + 1), ngz10 = A(gz, 1, 0, k + 1), ngz01 = A(gz, 0, 1, k + 1);
