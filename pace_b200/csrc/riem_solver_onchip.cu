@@ -20,6 +20,7 @@
 #include <string>
 
 #include "tile.cuh"
+#include "tmem.cuh"
 
 namespace pace {
 
@@ -38,42 +39,8 @@ struct RiemArgs {
   Box b;
 };
 
-// ---- where Y lives -------------------------------------------------------------------------------------------------
-// TM = false: all km+1 levels in shared memory (20.7 KB per warp at L79: 10 warps per SM).
-// TM = true : levels 0 .. TMEM_LEVELS-1 in tensor memory, the rest in shared memory.  Tensor memory (512 columns x 128
-//   lanes x 32 bit per SM) is otherwise idle on this path; with the 32x32b access shape lane l of warp w of the CTA owns
-//   TMEM lane 32 (w % 4) + l, i.e. every thread has its own row of 32-bit words, and an fp64 level is two adjacent
-//   columns.  A CTA of four warps allocates 128 columns (64 levels); four CTAs fill the 512 columns = 16 warps per SM,
-//   1.6 x the residency of the shared-memory layout for these latency-bound sweeps.
-constexpr int TMEM_LEVELS = 64;
-constexpr int TMEM_COLS = 2 * TMEM_LEVELS;   // a power of two >= 32, as tcgen05.alloc requires
-
-template <bool TM>
-struct YAcc {
-  double* sm;        // this lane's first shared-memory level (stride 32 doubles)
-  uint32_t taddr;    // TMEM address of this warp's lanes, first allocated column
-  __device__ __forceinline__ double ld(int k) const {
-    if (TM && k < TMEM_LEVELS) {
-      uint32_t lo, hi;
-      asm volatile("tcgen05.ld.sync.aligned.32x32b.x2.b32 {%0, %1}, [%2];" : "=r"(lo), "=r"(hi) : "r"(taddr + 2 * k));
-      asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-      return __hiloint2double((int)hi, (int)lo);
-    }
-    return sm[(TM ? k - TMEM_LEVELS : k) * 32];
-  }
-  __device__ __forceinline__ void st(int k, double v) const {
-    if (TM && k < TMEM_LEVELS) {
-      asm volatile("tcgen05.st.sync.aligned.32x32b.x2.b32 [%0], {%1, %2};"
-                   :: "r"(taddr + 2 * k), "r"((uint32_t)__double2loint(v)), "r"((uint32_t)__double2hiint(v)) : "memory");
-    } else {
-      sm[(TM ? k - TMEM_LEVELS : k) * 32] = v;
-    }
-  }
-  // all earlier st() of this thread have landed (needed before a later ld() of the same level)
-  __device__ __forceinline__ void fence_st() const {
-    if (TM) asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
-  }
-};
+// Y lives in shared memory (k_riem, 20.7 KB per warp at L79: 10 warps per SM) or, for its first 64 levels, in tensor
+// memory (k_riem_tmem: 16 warps per SM, 1.6 x the residency for these latency-bound sweeps): tmem.cuh.
 
 // The six sweeps of one column per lane.  `active` = this lane's column exists; a lane without one (tail of the last
 // warp) works on a copy of the last column and stores nothing, because the tensor-memory accesses are warp-collective.
@@ -507,30 +474,18 @@ __global__ void __launch_bounds__(32) k_riem(Geo g, RiemArgs a) {
 template <bool D3, int UU>
 __global__ void __launch_bounds__(128, 4) k_riem_tmem(Geo g, RiemArgs a) {
   extern __shared__ double sm[];
-  __shared__ uint32_t tmem_base;
+  __shared__ uint32_t tmem_slot;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  if (warp == 0) {
-    const uint32_t slot = (uint32_t)__cvta_generic_to_shared(&tmem_base);
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" :: "r"(slot), "r"((uint32_t)TMEM_COLS) : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
-  }
-  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-  __syncthreads();
-  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-  const uint32_t base = tmem_base;
+  const uint32_t base = tmem_alloc_cta(&tmem_slot);
   const int ncol = a.b.ni * a.b.nj;
   const int col0 = blockIdx.x * 128 + warp * 32;       // first column of this warp
   if (col0 < ncol) {                                   // warp-uniform: the TMEM accesses below are warp-collective
     const int nsm = a.km + 1 > TMEM_LEVELS ? a.km + 1 - TMEM_LEVELS : 0;   // levels kept in shared memory
-    YAcc<true> Y{sm + (size_t)warp * nsm * 32 + lane, base + ((uint32_t)(warp * 32) << 16)};
+    YAcc<true> Y{sm + (size_t)warp * nsm * 32 + lane, tmem_warp_addr(base)};
     const int col = col0 + lane;
     riem_column<D3, true, UU>(g, a, Y, col < ncol ? col : ncol - 1, blockIdx.y, col < ncol);
   }
-  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-  __syncthreads();
-  if (warp == 0) {
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(base), "r"((uint32_t)TMEM_COLS) : "memory");
-  }
+  tmem_free_cta(base);
 }
 
 // PACE_B200_RIEM=smem selects the shared-memory layout (A/B runs)

@@ -2,9 +2,95 @@
 //
 // Reference: pyFV3/stencils/updatedzd.py:28-109 (apply_height_fluxes), :130-209 (cubic spline),
 //            :316-389 (__call__ order).  29 reference launches -> 1 + fvtp2d(4) + delnflux(5) + 2.
+#include <cstdlib>
+
+#include "tmem.cuh"
 #include "transport.hpp"
 
 namespace pace {
+
+#ifndef PACE_HOST_EMU
+namespace {
+// cubic_spline_interpolation_from_layer_center_to_interfaces (updatedzd.py:130-209) with the forward sweep's values in
+// tensor memory (tmem.cuh) instead of the output field: a thread owns one column of ONE of the four fields, reads its
+// km levels once and writes its km+1 interface values once (8 field passes for the four fields instead of 16: the
+// kernel is bound by DRAM bandwidth).  Same expressions, level by level, as the four-field kernel in update_dz_d.
+struct SplineArgs {
+  const double* in[4];
+  double* out[4];
+  const double *gk, *beta, *gamma;
+  int km, ni, nj, i0, j0;
+};
+constexpr int SPL_U = 8;   // levels requested ahead of the forward recurrence
+
+__global__ void __launch_bounds__(128, 4) k_dzd_spline_tmem(Geo g, SplineArgs a) {
+  extern __shared__ double sm[];          // [3][km] level constants, then the levels >= TMEM_LEVELS of Y per warp
+  __shared__ uint32_t tmem_slot;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int km = a.km;
+  double *s_gk = sm, *s_beta = sm + km, *s_gamma = sm + 2 * km;
+  for (int k = threadIdx.x; k < km; k += blockDim.x) {
+    s_gk[k] = a.gk[k]; s_beta[k] = a.beta[k]; s_gamma[k] = a.gamma[k];
+  }
+  const uint32_t base = tmem_alloc_cta(&tmem_slot);   // contains the CTA barrier that publishes the constants
+  const int ncol = a.ni * a.nj;
+  const int col0 = blockIdx.x * 128 + warp * 32;
+  if (col0 < ncol) {   // warp-uniform: the TMEM accesses are warp-collective
+    const int nsm = km > TMEM_LEVELS ? km - TMEM_LEVELS : 0;
+    const YAcc<true> Y{sm + 3 * km + (size_t)warp * nsm * 32 + lane, tmem_warp_addr(base)};
+    const bool active = col0 + lane < ncol;           // lanes past the end work on a copy of the last column, store nothing
+    const int col = active ? col0 + lane : ncol - 1;
+    const int i = a.i0 + col % a.ni, j = a.j0 + col / a.ni, t = blockIdx.y, f = blockIdx.z;
+    const long long o0 = (long long)t * g.st3 + j * g.sj + i;
+    const long long sk = g.sk;
+    const double* __restrict__ in = (f == 0 ? a.in[0] : f == 1 ? a.in[1] : f == 2 ? a.in[2] : a.in[3]) + o0;
+    double* __restrict__ out = (f == 0 ? a.out[0] : f == 1 ? a.out[1] : f == 2 ? a.out[2] : a.out[3]) + o0;
+    // forward sweep
+    double nxt[SPL_U];
+#pragma unroll
+    for (int u = 0; u < SPL_U; ++u) nxt[u] = in[(long long)min(1 + u, km - 1) * sk];
+    const double c_top = in[0];
+    double p = fv_div(2.0 * s_gk[0] * (s_gk[0] + 1.0) * c_top + nxt[0], s_beta[0]);
+    Y.st(0, p);
+    double m = c_top, m2 = c_top;                     // levels k-1, k-2
+    for (int k0 = 1; k0 < km; k0 += SPL_U) {
+      double cur[SPL_U];
+#pragma unroll
+      for (int u = 0; u < SPL_U; ++u) cur[u] = nxt[u];
+      if (k0 + SPL_U < km) {
+#pragma unroll
+        for (int u = 0; u < SPL_U; ++u) nxt[u] = in[(long long)min(k0 + SPL_U + u, km - 1) * sk];
+      }
+#pragma unroll
+      for (int u = 0; u < SPL_U; ++u) {
+        const int k = k0 + u;
+        if (k < km) {
+          p = fv_div(3.0 * (m + s_gk[k] * cur[u]) - p, s_beta[k]);
+          Y.st(k, p);
+          m2 = m;
+          m = cur[u];
+        }
+      }
+    }
+    {
+      const double gl = s_gk[km - 1];
+      const double a_bot = 1.0 + gl * (gl + 1.5);
+      const double xt1b = 2.0 * gl * (gl + 1.0);
+      const double xt2 = gl * (gl + 0.5) - a_bot * s_gamma[km - 1];
+      p = (xt1b * m + m2 - a_bot * p) / xt2;          // m: level km-1, m2: level km-2
+      if (active) out[(long long)km * sk] = p;
+    }
+    Y.fence_st();
+    // backward sweep
+    for (int k = km - 1; k >= 0; --k) {
+      p = Y.ld(k) - s_gamma[k] * p;
+      if (active) out[(long long)k * sk] = p;
+    }
+  }
+  tmem_free_cta(base);
+}
+}  // namespace
+#endif
 
 // levels ahead of the sweeps for which L2 is asked (one request per 32-byte sector); measured per update_dz_d call at
 // C384: 6.58 ms without, 6.12 ms with 6 levels, 6.43 ms with 12
@@ -30,10 +116,16 @@ int update_dz_d(Core& c, double dt) {
       if ((*dv)[k] <= 1e-5) { c.err = "damp <= 1e-5 in column_namelist is untested"; return 1; }
   }
 
+#ifndef PACE_HOST_EMU
+  // PACE_B200_DZD_SPLINE=field selects the four-field kernel below (A/B runs; the host emulation always uses it)
+  static const bool spline_tmem = [] { const char* e = getenv("PACE_B200_DZD_SPLINE"); return !(e != nullptr && e[0] == 'f'); }();
+#else
+  const bool spline_tmem = false;
+#endif
   // cubic_spline_interpolation_from_layer_center_to_interfaces x4, full horizontal domain
   // The four fields are independent: their recurrences advance together, level by level, so that four division
   // chains are in flight per thread instead of one (the kernel is bound by the latency of the dependent divisions).
-  launch_ij(st, g, box_full(g), [=] __device__(const Pt& p) {
+  if (!spline_tmem) launch_ij(st, g, box_full(g), [=] __device__(const Pt& p) {
     double p0, p1, p2, p3;  // crx, xfx, cry, yfx
     {
       const double xt1 = 2.0 * gk[0] * (gk[0] + 1.0), b0 = beta[0];
@@ -91,6 +183,20 @@ int update_dz_d(Core& c, double dt) {
       A(crx_i, 0, 0, k) = p0; A(xfx_i, 0, 0, k) = p1; A(cry_i, 0, 0, k) = p2; A(yfx_i, 0, 0, k) = p3;
     }
   }, "dzd_spline");
+#ifndef PACE_HOST_EMU
+  if (spline_tmem) {
+    const Box b = box_full(g);
+    SplineArgs sa;
+    sa.in[0] = crx; sa.in[1] = xfx; sa.in[2] = cry; sa.in[3] = yfx;
+    sa.out[0] = crx_i; sa.out[1] = xfx_i; sa.out[2] = cry_i; sa.out[3] = yfx_i;
+    sa.gk = gk; sa.beta = beta; sa.gamma = gamma; sa.km = km; sa.ni = b.ni; sa.nj = b.nj; sa.i0 = b.i0; sa.j0 = b.j0;
+    const int nsm = km > TMEM_LEVELS ? km - TMEM_LEVELS : 0;
+    const size_t smem = ((size_t)3 * km + (size_t)nsm * 32 * 4) * sizeof(double);
+    if (km < 3 || smem > 48 * 1024) { c.err = "update_dz_d: level count outside the range of the spline kernel"; return 1; }
+    LaunchScope scope(st, "dzd_spline");
+    k_dzd_spline_tmem<<<dim3((b.ni * b.nj + 127) / 128, g.nt, 4), 128, smem, st>>>(g, sa);
+  }
+#endif
   Fvtp2dArgs a;
   a.q = zh; a.crx = crx_i; a.cry = cry_i; a.xfx = xfx_i; a.yfx = yfx_i; a.fx = fx; a.fy = fy; a.hord = c.cfg.hord_tm; a.nk = km + 1;
   if (fvtp2d(c, a)) return 1;
