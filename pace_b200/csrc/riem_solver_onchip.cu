@@ -8,12 +8,12 @@
 // SM at 5 warps; these sweeps are chains of dependent fp64 divisions / exp / log and need the occupancy):
 //   A  forward : pressures (pem, peg cumulative sums), pm, first guess pe, tridiagonal elimination   X=gam  Y=pp
 //   B  backward: back substitution                                                                    Y=pp
-//   C  forward : aa (pem summed again), w elimination                                                 X=gam' S=w
-//   D  backward: w back substitution                                                                  S=w
-//   E  forward : pe cumulative sum, output pressures (pem summed again)                               Y=pe
+//   C  forward : aa (pem summed again), w elimination                                                 X=gam' Y=w behind the sweep
+//   D  backward: w back substitution                                                                  Y=w
+//   E  forward : pe cumulative sum, output pressures (pem summed again)                               Y=pe behind the sweep
 //   F  backward: p1 recurrence, new dz, heights
 // Everything else is recomputed from the inputs (identical expressions give identical bits) or carried in
-// registers; pm, X and the intermediate w (S) are the only global work arrays.
+// registers; pm and X are the only global work arrays.
 // Statement order and expression trees per level are those of riem_solver.cu / the reference (sim1_solver.py:20-141,
 // riem_solver_c.py:21-123, riem_solver3.py:26-146), so results are bit-identical.
 #include <cstdlib>
@@ -31,7 +31,7 @@ namespace {
 struct RiemArgs {
   const double *delp, *cappa, *ptv, *q_con, *w_in, *zsurf, *ws;
   double* zh;                       // heights: ad.gz (C) / ad.zh (D), read then rewritten
-  double *pm, *wtmp, *xwork;  // global work arrays
+  double *pm, *xwork;  // global work arrays
   double *pef;                      // ad.pkc
   double *w_out, *delz, *pk3, *peln, *pk, *pe;  // D-grid solver only
   double ptop, p_fac, dt, t1g, rdt, peln1, ptk;
@@ -65,7 +65,6 @@ __device__ __forceinline__ void riem_column(const Geo& g, const RiemArgs& a, con
   double* w_out = a.w_out;
   double* __restrict__ zh = a.zh;
   double* __restrict__ pm = a.pm;
-  double* __restrict__ wtmp = a.wtmp;
   double* __restrict__ xg = a.xwork;
   double* __restrict__ pef = a.pef;
   double* __restrict__ delz = a.delz;
@@ -257,7 +256,7 @@ __device__ __forceinline__ void riem_column(const Geo& g, const RiemArgs& a, con
     }
     double betk = dm0 - aa_k;
     double wprev = (dm0 * G(w_in, 0) + dt * pp_k) / betk;
-    GST(wtmp, 0, wprev);
+    yst(0, wprev);   // pp(0) is not read: from here on Y(k) holds the eliminated w of the levels this sweep has passed
     double n_delp[U], n_w[U], n_cap[U], n_zh[U];       // delp(k), w(k), cappa(k+1), zh(k+2)
 #pragma unroll
     for (int u = 0; u < U; ++u) {
@@ -293,7 +292,7 @@ __device__ __forceinline__ void riem_column(const Geo& g, const RiemArgs& a, con
           const double dm_k = D3 ? c_delp[u] * RGRAV : c_delp[u] / GRAV;
           betk = dm_k - (aak + aa_n + aak * gm);
           wprev = (dm_k * c_w[u] + dt * (pp_n - pp_k) - aak * wprev) / betk;
-          GST(wtmp, k, wprev);
+          yst(k, wprev);
           pp_k = pp_n;
           aa_k = aa_n;
         }
@@ -311,63 +310,67 @@ __device__ __forceinline__ void riem_column(const Geo& g, const RiemArgs& a, con
       const double dm_k = D3 ? delp_k * RGRAV : delp_k / GRAV;
       betk = dm_k - (aak + p1 + aak * gm);
       wprev = (dm_k * G(w_in, k) + dt * (pp_n - pp_k) - p1 * ws - aak * wprev) / betk;
-      GST(wtmp, k, wprev);
+      yst(k, wprev);
     }
+    Y.fence_st();
   }
-  // ---- D: backward, w back substitution; the corrected w goes to shared memory (Y is free until E) ------------
+  // ---- D: backward, w back substitution, in place in Y (pp is dead once sweep C has passed a level) ---------------
   {
-    double wn = G(wtmp, km - 1);
-    double n_w[U], n_x[U];
+    double wn = yld(km - 1);
+    double n_x[U];
 #pragma unroll
-    for (int u = 0; u < U; ++u) { n_w[u] = G(wtmp, max(km - 2 - u, 0)); n_x[u] = G(xg, max(km - 2 - u, 0) + 1); }
+    for (int u = 0; u < U; ++u) n_x[u] = G(xg, max(km - 2 - u, 0) + 1);
     for (int k0 = km - 2; k0 >= 0; k0 -= U) {
-      double c_w[U], c_x[U];
+      double c_x[U];
 #pragma unroll
-      for (int u = 0; u < U; ++u) { c_w[u] = n_w[u]; c_x[u] = n_x[u]; }
+      for (int u = 0; u < U; ++u) c_x[u] = n_x[u];
       if (k0 - U >= 0) {
 #pragma unroll
-        for (int u = 0; u < U; ++u) { n_w[u] = G(wtmp, max(k0 - U - u, 0)); n_x[u] = G(xg, max(k0 - U - u, 0) + 1); }
+        for (int u = 0; u < U; ++u) n_x[u] = G(xg, max(k0 - U - u, 0) + 1);
       }
 #pragma unroll
       for (int u = 0; u < U; ++u) {
         const int k = k0 - u;
         if (k >= 0) {
-          wn = c_w[u] - c_x[u] * wn;
-          GST(wtmp, k, wn);
+          wn = yld(k) - c_x[u] * wn;
+          yst(k, wn);
         }
       }
     }
+    Y.fence_st();
   }
   // ---- E: forward, pe and the output pressure (pe, or pe + pem with the pressure sum of sweep A run again); the
   // D-grid solver publishes w here (its old value is needed up to this point)
   {
     double pe_k = 0.0;
     double pem_k = ptop;
+    double w_cur = yld(0);   // Y(k) holds the new w of level k until this sweep replaces it by pe(k): read one level ahead
     yst(0, 0.0);
     if (D3) GST(pef, 0, a.beta_neg ? 0.0 + ptop : 0.0);   // pe(0) = 0, pem(0) = ptop
     else GST(pef, 0, ptop);
-    double n_w[U], n_delp[U], n_w1[U];
+    double n_delp[U], n_w1[U];
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       const int kk = min(u, km - 1);
-      n_w[u] = G(wtmp, kk); n_delp[u] = G(delp, kk); n_w1[u] = G(w_in, kk);
+      n_delp[u] = G(delp, kk); n_w1[u] = G(w_in, kk);
     }
     for (int k0 = 1; k0 <= km; k0 += U) {
-      double c_w[U], c_delp[U], c_w1[U];
+      double c_delp[U], c_w1[U];
 #pragma unroll
-      for (int u = 0; u < U; ++u) { c_w[u] = n_w[u]; c_delp[u] = n_delp[u]; c_w1[u] = n_w1[u]; }
+      for (int u = 0; u < U; ++u) { c_delp[u] = n_delp[u]; c_w1[u] = n_w1[u]; }
       if (k0 + U <= km) {
 #pragma unroll
         for (int u = 0; u < U; ++u) {
           const int kk = min(k0 + U + u - 1, km - 1);
-          n_w[u] = G(wtmp, kk); n_delp[u] = G(delp, kk); n_w1[u] = G(w_in, kk);
+          n_delp[u] = G(delp, kk); n_w1[u] = G(w_in, kk);
         }
       }
 #pragma unroll
       for (int u = 0; u < U; ++u) {
         const int k = k0 + u;
         if (k <= km) {
-          const double wk = c_w[u];
+          const double wk = w_cur;                     // w(k-1)
+          if (k < km) w_cur = yld(k);                  // w(k), before pe(k) takes its place
           const double dm_m = D3 ? c_delp[u] * RGRAV : c_delp[u] / GRAV;
           pe_k = pe_k + dm_m * (wk - c_w1[u]) * rdt;
           yst(k, pe_k);
@@ -500,7 +503,7 @@ bool riem_use_tmem() {
 template <bool D3>
 int launch_riem(Core& c, RiemArgs& a, const char* label) {
   const Geo g = c.g;
-  a.pm = c.S("sim1.pm"); a.wtmp = c.S("sim1.w"); a.xwork = c.S("sim1.x");
+  a.pm = c.S("sim1.pm"); a.xwork = c.S("sim1.x");
   if (!c.err.empty()) return 1;
   const int ncol = a.b.ni * a.b.nj;
   LaunchScope scope(c.stream, label);
@@ -509,9 +512,9 @@ int launch_riem(Core& c, RiemArgs& a, const char* label) {
     const size_t smem = (size_t)nsm * 32 * 4 * sizeof(double);
     if (smem > 48 * 1024) { c.err = "riem_solver: too many levels for the on-chip kernel"; return 1; }
     dim3 grd((ncol + 127) / 128, g.nt, 1);
-    // levels per chunk (PACE_B200_RIEM_U = 2 / 3): at C384 riem_solver_c 21.6 / 20.8, riem_solver3 24.9 / 24.7 ms per step
+    // levels per chunk (PACE_B200_RIEM_U = 2 / 3): at C384 riem_solver_c 20.5 / 21.2, riem_solver3 23.3 / 24.7 ms per step
     // (three levels of exp / log chains spill 8 / 80 bytes at the 128 registers that 16 warps per SM allow)
-    static const int u = [] { const char* e = std::getenv("PACE_B200_RIEM_U"); return e ? std::atoi(e) : 3; }();
+    static const int u = [] { const char* e = std::getenv("PACE_B200_RIEM_U"); return e ? std::atoi(e) : 2; }();
     if (u == 3) k_riem_tmem<D3, 3><<<grd, 128, smem, c.stream>>>(g, a);
     else k_riem_tmem<D3, 2><<<grd, 128, smem, c.stream>>>(g, a);
     return 0;
