@@ -176,7 +176,8 @@ int d_sw(Core& c, double dt) {
     double wv = wdp / dp;
     wv = col_damp_w[p.k] > 1e-5 ? wv + A0(dw) : wv;
     A0(w) = wv;
-    A0(q_con) = fv_div(A0(q_con), dp);  // zero wherever there is no condensate
+    // zero wherever there is no condensate: levels flagged all-zero keep their zeros (0 / dp), no read, no write
+    if (qcon_levels == nullptr || qcon_levels[p.t * nz + p.k] != 0) A0(q_con) = fv_div(A0(q_con), dp);
   });
   // 13. compute_kinetic_energy on the corner compute domain
   const int mord_mt = cf.hord_mt < 0 ? -cf.hord_mt : cf.hord_mt;
