@@ -20,6 +20,10 @@ def comparable(name, a, n):
     return a[:, :, 3:3 + n + 1, 3:3 + n + 1] if name in ("uc", "vc") else a
 
 
+# the other kernels that have a simpler counterpart kept for A/B runs: level-parallel nh_p_grad winds and update_dz_c, the
+# separate update_u_and_v pass of d_sw, the four-field interface spline of update_dz_d
+ALT = {"PACE_B200_NHPG": "levels", "PACE_B200_DZC": "levels", "PACE_B200_DSW_UV": "split", "PACE_B200_DZD_SPLINE": "field"}
+
 SCRIPT = r"""
 import sys, numpy as np, torch
 sys.path.insert(0, %r)
@@ -38,7 +42,7 @@ def test_fused_matches_three_kernel_version(tmp_path):
     res = {}
     modes = {"march": {"PACE_B200_FVTP2D": "march"},
              "march_chunks": {"PACE_B200_FVTP2D": "march", "PACE_B200_FVTP2D_ROWS": "16"},
-             "tile": {"PACE_B200_FVTP2D": "tile"}, "unfused": {"PACE_B200_FVTP2D": "unfused", "PACE_B200_DELNFLUX": "unfused", "PACE_B200_RIEM": "global", "PACE_B200_A2B": "unfused", "PACE_B200_CSW": "unfused", "PACE_B200_DD": "unfused"}}
+             "tile": {"PACE_B200_FVTP2D": "tile"}, "riem_smem": {"PACE_B200_RIEM": "smem"}, "unfused": {"PACE_B200_FVTP2D": "unfused", "PACE_B200_DELNFLUX": "unfused", "PACE_B200_RIEM": "global", "PACE_B200_A2B": "unfused", "PACE_B200_CSW": "unfused", "PACE_B200_DD": "unfused", **ALT}}
     for mode, extra in modes.items():
         env = dict(os.environ, **extra)
         path = str(tmp_path / (mode + ".npz"))
@@ -59,7 +63,7 @@ def test_production_kernels_match_unfused_at_c96(tmp_path):
     narrower), several row chunks, 3 x 3 DelnFlux / a2b tiles."""
     res = {}
     for mode, extra in {"production": {}, "unfused": {"PACE_B200_FVTP2D": "unfused", "PACE_B200_DELNFLUX": "unfused",
-                                                      "PACE_B200_RIEM": "global", "PACE_B200_A2B": "unfused", "PACE_B200_CSW": "unfused", "PACE_B200_DD": "unfused"}}.items():
+                                                      "PACE_B200_RIEM": "global", "PACE_B200_A2B": "unfused", "PACE_B200_CSW": "unfused", "PACE_B200_DD": "unfused", **ALT}}.items():
         env = dict(os.environ, **extra)
         path = str(tmp_path / (mode + ".npz"))
         subprocess.run([sys.executable, "-c", SCRIPT % ROOT, path, "96"], check=True, env=env, timeout=900)
@@ -118,7 +122,7 @@ def test_zero_shortcuts_match_dense_on_patchy_tracers(tmp_path):
     modes = {"production": {},
              "dense": {"PACE_B200_ZERO_PATHS": "0"},
              "dense_unfused": {"PACE_B200_ZERO_PATHS": "0", "PACE_B200_FVTP2D": "unfused", "PACE_B200_DELNFLUX": "unfused",
-                               "PACE_B200_RIEM": "global", "PACE_B200_A2B": "unfused", "PACE_B200_CSW": "unfused", "PACE_B200_DD": "unfused"}}
+                               "PACE_B200_RIEM": "global", "PACE_B200_A2B": "unfused", "PACE_B200_CSW": "unfused", "PACE_B200_DD": "unfused", **ALT}}
     for mode, extra in modes.items():
         env = dict(os.environ, **extra)
         path = str(tmp_path / (mode + ".npz"))
