@@ -3,9 +3,10 @@
 // The straightforward column kernels (riem_solver.cu) keep ~20 per-level work arrays in global scratch: measured
 // 4.9 GB of DRAM traffic per riem_solver_c launch at C128 against 0.5 GB of compulsory traffic, 35 long-scoreboard
 // stall cycles per issued instruction (profiles/r01_columns_c128.txt).  Here a warp owns 32 adjacent columns (lane
-// <-> column, coalesced rows); of the two arrays that must survive between the k-sweeps, Y[k][lane] lives in shared
-// memory and X in one global work array that every sweep prefetches a chunk ahead (two shared arrays would cap the
-// SM at 5 warps; these sweeps are chains of dependent fp64 divisions / exp / log and need the occupancy):
+// <-> column, coalesced rows); of the two arrays that must survive between the k-sweeps, Y[k] lives on chip - in
+// tensor memory for its first 64 levels and in shared memory for the rest (tmem.cuh; 16 warps per SM), or wholly in
+// shared memory (10 warps per SM) - and X in one global work array that every sweep prefetches a chunk ahead (these
+// sweeps are chains of dependent fp64 divisions / exp / log and need the occupancy):
 //   A  forward : pressures (pem, peg cumulative sums), pm, first guess pe, tridiagonal elimination   X=gam  Y=pp
 //   B  backward: back substitution                                                                    Y=pp
 //   C  forward : aa (pem summed again), w elimination                                                 X=gam' Y=w behind the sweep
