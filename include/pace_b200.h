@@ -293,6 +293,22 @@ int pace_b200_remap(void* handle, int last_step, double mdt);
 /* DynamicalCore.step_dynamics (pyFV3/stencils/fv_dynamics.py:445-655): one dycore step of dt_atmos. */
 int pace_b200_step(void* handle);
 
+/* ---- dycore <-> physics coupling of the driver's time loop (driver/pace/driver/driver.py:645-661) -------------------
+ * Fields, registered like all others: "phy.<name>" = PhysicsState.<name> (the 16 copied fields qvapor ... omga, prsi and
+ * physics_updated_{ua,va,pt,specific_humidity,qliquid,qrain,qsnow,qice,qgraupel}), "tend.u_dt / v_dt / pt_dt" =
+ * TendencyState, "dgrid.<name>" = DriverGridData (vlon1-3, vlat1-3, edge_vect_w/e/s/n, es1_1-3, ew2_1-3; the two
+ * edge vectors that are 1-D along i in the reference as 2-D fields constant along j).  The physics parameterisations
+ * are the caller's: it fills phy.prsi and phy.physics_updated_* between the two calls. */
+/* DycoreToPhysics.__call__ with do_dry_convective_adjust = false (pySHiELD/update/update_atmos_state.py:184-231). */
+int pace_b200_dycore_to_physics(void* handle);
+/* UpdateAtmosphereState.__call__(dycore_state, phy_state, u_dt, v_dt, pt_dt, dt) (update_atmos_state.py:296-349) incl.
+ * ApplyPhysicsToDycore (fv_update_phys.py:152-195), AGrid2DGridPhysics (update_dwind_phys.py:490-701), the halo updates
+ * of the tendencies and of the winds, and CubedToLatLon.  dycore_only / apply_tendencies: the constructor arguments of
+ * the reference class.  origin_i / origin_j (one int per subdomain of the handle): subtile_index * subtile_width, what
+ * the reference adds to a local index to get its position on the tile (local_to_global_1d); npx, npy: namelist. */
+int pace_b200_update_atmos_state(void* handle, double dt, int dycore_only, int apply_tendencies, const int* origin_i,
+                                 const int* origin_j, int npx, int npy);
+
 #ifdef __cplusplus
 }
 #endif

@@ -134,6 +134,7 @@ def bootstrap(gt_cache_root=None):
         os.path.join(REF, "NDSL/external/gt4py/src"),
         os.path.join(REF, "NDSL"),
         os.path.join(REF, "pyFV3"),
+        os.path.join(REF, "pySHiELD"),   # physics package: only its update/ (dycore <-> physics coupling) is used
     ):
         if p not in sys.path:
             sys.path.insert(0, p)

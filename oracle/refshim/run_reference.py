@@ -66,6 +66,8 @@ def build_dycore(mpi_comm, cfg_kwargs, backend="numpy"):
         damping_coefficients=damping, config=config, timestep=timedelta(seconds=config.dt_atmos), phis=state.phis,
         state=state,
     )
+    # the factories, for callers that build further reference objects on the same grid (oracle/gen_coupling_golden.py)
+    build_dycore.extras = {"stencil_factory": stencil_factory, "quantity_factory": quantity_factory}
     return dycore, state, grid_data, damping, metric_terms, config, communicator
 
 

@@ -157,6 +157,8 @@ MODULE_CALLS = {
     "tracer_advection": [],
     "remap": [_I, _D],
     "step": [],
+    "dycore_to_physics": [],
+    "update_atmos_state": [_D, _I, _I, ctypes.POINTER(_I), ctypes.POINTER(_I), _I, _I],
 }
 
 EXPORTS = ["pace_b200_row_stride", "pace_b200_create", "pace_b200_destroy", "pace_b200_last_error",

@@ -308,6 +308,11 @@ int pace_b200_acoustic(void* h, double timestep, int n_map) { ENTRY(acoustic(*c,
 int pace_b200_tracer_advection(void* h) { ENTRY(tracer_advection(*c)) }
 int pace_b200_remap(void* h, int last_step, double mdt) { ENTRY(remapping(*c, last_step, mdt)) }
 int pace_b200_step(void* h) { ENTRY(step(*c)) }
+int pace_b200_dycore_to_physics(void* h) { ENTRY(dycore_to_physics(*c)) }
+int pace_b200_update_atmos_state(void* h, double dt, int dycore_only, int apply_tendencies, const int* origin_i,
+                                 const int* origin_j, int npx, int npy) {
+  ENTRY(update_atmos_state(*c, dt, dycore_only, apply_tendencies, origin_i, origin_j, npx, npy))
+}
 int pace_b200_remap_main(void* h, int nq) { ENTRY(remap_main(*c, nq)) }
 int pace_b200_remap_finish(void* h, int last_step) { ENTRY(remap_finish(*c, last_step)) }
 int pace_b200_map_single(void* h, const char* q, const char* pe1, const char* pe2, const char* qs, int iv, int kord,

@@ -162,6 +162,13 @@ int acoustic(Core& c, double timestep, int n_map);
 int tracer_advection(Core& c);
 int remapping(Core& c, int last_step, double mdt);
 int step(Core& c);
+// dycore <-> physics coupling (coupling.cu; sequencing with the halo updates in step.cu)
+int dycore_to_physics(Core& c);
+int coupling_tendencies(Core& c, double dt_atmos, int dycore_only);
+int coupling_thermo(Core& c, double dt);
+int update_dwind_phys(Core& c, double dt_atmos, const int* origin_i, const int* origin_j, int npx, int npy);
+int update_atmos_state(Core& c, double dt, int dycore_only, int apply_tendencies, const int* origin_i,
+                       const int* origin_j, int npx, int npy);
 int divergence_damping(Core& c, double* vort_b, double* delpc, double* ke, const double* vort_a, double dt);
 
 }  // namespace pace

@@ -294,4 +294,21 @@ int step(Core& c) {
   return 0;
 }
 
+// ---- UpdateAtmosphereState.__call__ (pySHiELD/update/update_atmos_state.py:296-349) ---------------------------
+// with ApplyPhysicsToDycore.__call__ (fv_update_phys.py:152-195): fill and tracer update, moist_cv, pressures, the halo
+// update of the wind tendencies, their transfer to the D-grid winds, and the A-grid winds of the new state.  The two
+// halo updates (the reference's three: u_dt and v_dt travel together here) keep the number of updates per step even.
+int update_atmos_state(Core& c, double dt, int dycore_only, int apply_tendencies, const int* origin_i,
+                       const int* origin_j, int npx, int npy) {
+  RUN(coupling_tendencies(c, c.cfg.dt_atmos, dycore_only));
+  if (!apply_tendencies) return 0;
+  RUN(coupling_thermo(c, dt));
+  RUN(halo(c, A3, Names{"tend.u_dt", "tend.v_dt"}));
+  RUN(update_dwind_phys(c, c.cfg.dt_atmos, origin_i, origin_j, npx, npy));
+  const Names u{"u"}, v{"v"};
+  RUN(halo(c, D3, u, &v));
+  RUN(c2l_ord4(c));
+  return 0;
+}
+
 }  // namespace pace

@@ -36,6 +36,15 @@ STEP_INPUTS = ["u", "v", "w", "delp", "delz", "pt", "qvapor", "qliquid", "qice",
 # and ps: the default download set of a host-resident model that does not ask for the whole DycoreState.
 PHYSICS_FIELDS = ["u", "v", "w", "ua", "va", "delp", "delz", "pt", "pe", "peln", "omga", "ps", "qvapor", "qliquid", "qice",
                   "qrain", "qsnow", "qgraupel", "qo3mr", "qsgs_tke", "qcld"]
+# dycore <-> physics coupling (pySHiELD/update/update_atmos_state.py): the fields DycoreToPhysics copies into the
+# PhysicsState, what the physics hands back, and the DriverGridData arrays AGrid2DGridPhysics reads
+COUPLING_COPIED = ["qvapor", "qliquid", "qrain", "qsnow", "qice", "qgraupel", "qo3mr", "qsgs_tke", "qcld", "pt", "delp",
+                   "delz", "ua", "va", "w", "omga"]
+COUPLING_PHYSICS_OUT = ["prsi", "physics_updated_ua", "physics_updated_va", "physics_updated_pt",
+                        "physics_updated_specific_humidity", "physics_updated_qliquid", "physics_updated_qrain",
+                        "physics_updated_qsnow", "physics_updated_qice", "physics_updated_qgraupel"]
+DRIVER_GRID = ["vlon1", "vlon2", "vlon3", "vlat1", "vlat2", "vlat3", "edge_vect_w", "edge_vect_e", "edge_vect_s",
+               "edge_vect_n", "es1_1", "es1_2", "es1_3", "ew2_1", "ew2_2", "ew2_3"]
 ACOUSTIC_TEMPORARIES = ["ad.ut", "ad.vt", "ad.gz", "ad.zh", "ad.pem", "ad.pkc", "ad.pk3", "ad.heat_source", "ad.cappa",
                         "ad.divgd", "ad.crx", "ad.cry", "ad.xfx", "ad.yfx", "csw.delpc", "csw.ptc", "dyn.dp1", "dyn.cvm"]
 TEMPORARIES_2D = ["ad.ws3", "ad.wsd", "ad.zs"]
@@ -220,6 +229,47 @@ class DycoreEngine:
     def remapping(self, last_step, mdt):
         """LagrangianToEulerian.__call__ (remapping.py:522-731) -> pace_b200_remap."""
         self._call("remap", int(last_step), float(mdt))
+
+    # -- dycore <-> physics coupling of the driver's time loop (driver/pace/driver/driver.py:645-661) -------------
+    def setup_coupling(self, driver_grids):
+        """Allocates the PhysicsState / TendencyState fields of the coupling ("phy.*", "tend.*") and registers the
+        DriverGridData arrays.  driver_grids: list over resident subdomains of dict name -> reference-layout array with
+        the names of engine.DRIVER_GRID (edge_vect_s / edge_vect_n are 1-D along i, as in the reference)."""
+        core = self.core
+        n_sub = self.planner.n
+        ni, nj = n_sub + 7, n_sub + 7
+        for name in DRIVER_GRID:
+            arrs = []
+            for gdict in driver_grids:
+                a = np.asarray(gdict[name], dtype=np.float64)
+                if a.ndim == 1:   # FloatFieldI: constant along j
+                    a = np.repeat(a[:ni, None], nj, axis=1)
+                arrs.append(a)
+            core.put("dgrid." + name, arrs)
+        for name in COUPLING_COPIED + COUPLING_PHYSICS_OUT:
+            if "phy." + name not in core.t:
+                core.alloc3("phy." + name)
+        for name in ("u_dt", "v_dt", "pt_dt"):
+            if "tend." + name not in core.t:
+                core.alloc3("tend." + name)
+        # what the reference adds to a local index to get the position on the tile (update_dwind_phys.py:488-499)
+        pos = [self.planner.position(r) for r in self.ranks]
+        self._origin_i = (ctypes.c_int * len(pos))(*[p[1] * n_sub for p in pos])
+        self._origin_j = (ctypes.c_int * len(pos))(*[p[2] * n_sub for p in pos])
+
+    def dycore_to_physics(self):
+        """DycoreToPhysics.__call__ (update_atmos_state.py:184-231, no dry convective adjustment) ->
+        pace_b200_dycore_to_physics: the dycore state is copied into the "phy.*" fields on the device."""
+        self._call("dycore_to_physics")
+
+    def update_atmos_state(self, dt=None, dycore_only=False, apply_tendencies=True):
+        """UpdateAtmosphereState.__call__ (update_atmos_state.py:296-349) -> pace_b200_update_atmos_state: applies what
+        the physics left in "phy.prsi" / "phy.physics_updated_*" (and "tend.*") to the dycore state."""
+        if not hasattr(self, "_origin_i"):
+            raise RuntimeError("update_atmos_state: call setup_coupling(driver_grids) first")
+        c = self.cfg
+        self._call("update_atmos_state", float(c["dt_atmos"] if dt is None else dt), int(bool(dycore_only)),
+                   int(bool(apply_tendencies)), self._origin_i, self._origin_j, int(c["npx"]), int(c["npy"]))
 
     # -- DynamicalCore.step_dynamics / _compute (fv_dynamics.py:445-655) ----------------------------------------
     def step_dynamics(self, timer=None):

@@ -1,0 +1,166 @@
+"""Dycore <-> physics coupling: pace_b200_dycore_to_physics / pace_b200_update_atmos_state against the
+unmodified reference classes DycoreToPhysics and UpdateAtmosphereState run on 6 ranks at C12
+(oracle/gen_coupling_golden.py -> tests/golden/c12_6rank_coupling.npz).  Bit for bit, compute domain."""
+import os
+
+import numpy as np
+import pytest
+
+from tests.golden_util import GOLDEN
+from tests.test_engine_acoustic import load_six
+
+NX = 12
+
+
+def load_coupling():
+    z = np.load(os.path.join(GOLDEN, "c12_6rank_coupling.npz"))
+    out = [dict() for _ in range(6)]
+    for key in z.files:
+        r, kind, name = key.split(":", 2)
+        out[int(r[1:])].setdefault(kind, {})[name] = z[key]
+    return out
+
+
+def full(a):
+    """fixture arrays hold [is, ie+1] x [js, je+1]; back to the array with its 3-cell halo"""
+    f = np.zeros((19, 19) + a.shape[2:])
+    f[3:16, 3:16] = a
+    return f
+
+
+def run_coupling(backend):
+    from pace_b200.engine import COUPLING_COPIED, COUPLING_PHYSICS_OUT, DycoreEngine
+
+    kw = {}
+    if backend == "hostemu":
+        from tests import hostemu
+
+        kw = dict(device="cpu", _lib_handle=hostemu.load())
+    fx = load_coupling()
+    eng = DycoreEngine(NX, 1, 79, load_six("grid"), **kw)
+    init = load_six("init")
+    states = []
+    for r in range(6):
+        s = {"phis": init[r]["phis"]}
+        for name, a in fx[r]["in"].items():
+            s[name] = full(a)
+        states.append(s)
+    eng.set_state(states)
+    eng.setup_coupling([fx[r]["grid"] for r in range(6)])
+    core = eng.core
+
+    # DycoreToPhysics: plain copies on [is, ie+1] x [js, je+1] x [0, npz) (checked against the reference's output when
+    # the fixture was generated: oracle/gen_coupling_golden.py)
+    eng.dycore_to_physics()
+    for name in COUPLING_COPIED:
+        got = core.get("phy." + name)
+        for r in range(6):
+            want = full(fx[r]["in"][name])
+            assert np.array_equal(got[r][3:16, 3:16, :79], want[3:16, 3:16, :79]), (name, r)
+            assert not got[r][:, :, 79].any(), (name, r)
+    # the physics' part: prsi and the updated fields come from the fixture
+    for name in COUPLING_PHYSICS_OUT:
+        core.put("phy." + name, [full(fx[r]["phy"][name]) for r in range(6)])
+    eng.update_atmos_state()
+    core.sync()
+    bad = []
+    for r in range(6):
+        for name, want in fx[r]["out"].items():
+            got = core.get(name)[r]
+            if want.ndim == 3:
+                g, w = got[3:15, 3:15, :79], want[:12, :12, :79]
+                if name == "u":
+                    g, w = got[3:15, 3:16, :79], want[:12, :13, :79]
+                elif name == "v":
+                    g, w = got[3:16, 3:15, :79], want[:13, :12, :79]
+                elif name in ("pe", "peln", "pk"):
+                    g, w = got[3:15, 3:15, :80], want[:12, :12, :80]
+            else:
+                g, w = got[3:15, 3:15], want[:12, :12]
+            if not (np.isfinite(g).all() and np.array_equal(g, w)):
+                bad.append("%s rank %d: %d values differ, max |d| = %g" % (name, r, (g != w).sum(), np.nanmax(np.abs(g - w))))
+    assert not bad, "\n".join(bad)
+    # fields the coupling must not touch
+    for name in ("w", "delz", "omga", "qo3mr", "qcld"):
+        got = core.get(name)
+        for r in range(6):
+            assert np.array_equal(got[r][3:15, 3:15, :79], full(fx[r]["in"][name])[3:15, 3:15, :79]), (name, r)
+
+
+def test_coupling_hostemu():
+    run_coupling("hostemu")
+
+
+@pytest.mark.gpu
+def test_coupling_gpu():
+    run_coupling("cuda")
+
+
+def run_coupling_layout2(backend):
+    """The same coupling step on the 2x2 layout (24 subdomains of 6x6, the partitioning of the C384 configuration).  Given
+    the same state the coupling is a function of each point and its neighbours, with tile-edge formulas that depend on
+    the position on the TILE: the 24 blocks must reproduce the blocks of the 6-rank reference result bit for bit.  This
+    checks the tile positions handed to AGrid2DGridPhysics (which half of an edge a subdomain lies in) and the halo
+    updates of the tendencies between subdomains of one tile."""
+    from pace_b200.engine import COUPLING_PHYSICS_OUT, DycoreEngine
+    from tests.test_engine_layout2 import load24
+
+    kw = {}
+    if backend == "hostemu":
+        from tests import hostemu
+
+        kw = dict(device="cpu", _lib_handle=hostemu.load())
+    fx = load_coupling()
+    n = 6
+    init = load24("init")
+    eng = DycoreEngine(NX, 2, 79, load24("grid"), **kw)
+
+    def block(a, rank, halo):
+        """rank's block of a 6-rank array: with its 3-cell halo from a full array, else [is, ie+1] x [js, je+1]"""
+        _, ix, jy = eng.planner.position(rank)
+        if halo:
+            return a[ix * n: ix * n + n + 7] if a.ndim == 1 else a[ix * n: ix * n + n + 7, jy * n: jy * n + n + 7]
+        f = np.zeros((n + 7, n + 7) + a.shape[2:])
+        f[3:3 + n + 1, 3:3 + n + 1] = a[ix * n: ix * n + n + 1, jy * n: jy * n + n + 1]
+        return f
+
+    states, dgrids = [], []
+    for rank in range(24):
+        tile = rank // 4
+        s = {"phis": init[rank]["phis"]}
+        for name, a in fx[tile]["in"].items():
+            s[name] = block(a, rank, False)
+        states.append(s)
+        dgrids.append({name: block(a, rank, True) for name, a in fx[tile]["grid"].items()})
+    eng.set_state(states)
+    eng.setup_coupling(dgrids)
+    eng.dycore_to_physics()
+    for name in COUPLING_PHYSICS_OUT:
+        eng.core.put("phy." + name, [block(fx[r // 4]["phy"][name], r, False) for r in range(24)])
+    eng.update_atmos_state()
+    eng.core.sync()
+    bad = []
+    for rank in range(24):
+        tile = rank // 4
+        _, ix, jy = eng.planner.position(rank)
+        for name, want in fx[tile]["out"].items():
+            got = eng.core.get(name)[rank]
+            di = 1 if name == "v" else 0
+            dj = 1 if name == "u" else 0
+            nk = 80 if name in ("pe", "peln", "pk") else 79
+            w = want[ix * n: ix * n + n + di, jy * n: jy * n + n + dj]
+            g = got[3:3 + n + di, 3:3 + n + dj]
+            if want.ndim == 3:
+                g, w = g[:, :, :nk], w[:, :, :nk]
+            if not (np.isfinite(g).all() and np.array_equal(g, w)):
+                bad.append("%s rank %d: %d values differ" % (name, rank, (g != w).sum()))
+    assert not bad, "\n".join(bad)
+
+
+def test_coupling_layout2_hostemu():
+    run_coupling_layout2("hostemu")
+
+
+@pytest.mark.gpu
+def test_coupling_layout2_gpu():
+    run_coupling_layout2("cuda")
