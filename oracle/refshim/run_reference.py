@@ -67,7 +67,8 @@ def build_dycore(mpi_comm, cfg_kwargs, backend="numpy"):
         state=state,
     )
     # the factories, for callers that build further reference objects on the same grid (oracle/gen_coupling_golden.py)
-    build_dycore.extras = {"stencil_factory": stencil_factory, "quantity_factory": quantity_factory}
+    build_dycore.extras = {"stencil_factory": stencil_factory, "quantity_factory": quantity_factory,
+                           "metric_terms": metric_terms}
     return dycore, state, grid_data, damping, metric_terms, config, communicator
 
 

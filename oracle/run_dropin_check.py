@@ -40,8 +40,76 @@ def _rank(mpi_comm):
             a, b = got[name][3:15, 3:15], want[name][3:15, 3:15]
         if not np.array_equal(a, b):
             bad.append((name, float(np.max(np.abs(a - b)))))
+    bad += _coupling(mpi_comm, dycore, mine, state, mine_state, grid_data, config, communicator)
     return bad
 
+
+def _coupling(mpi_comm, dycore, mine, state, mine_state, grid_data, config, communicator):
+    """The coupling classes of pace_b200.dropin next to pySHiELD's (update_atmos_state.py), on the stepped states."""
+    import copy
+    import dataclasses
+
+    import pySHiELD
+    from ndsl.constants import X_DIM, Y_DIM, Z_DIM
+    from ndsl.grid import DriverGridData
+    from pySHiELD.update import update_atmos_state as ref
+
+    from oracle.gen_coupling_golden import PHY_IN, synthesize_physics
+    from oracle.refshim.run_reference import build_dycore, state_arrays
+    from pace_b200 import dropin
+
+    qf, sf = build_dycore.extras["quantity_factory"], build_dycore.extras["stencil_factory"]
+    driver_grid = DriverGridData.new_from_metric_terms(build_dycore.extras["metric_terms"])
+    schemes = [pySHiELD.PHYSICS_PACKAGES["GFS_microphysics"]]
+
+    @dataclasses.dataclass
+    class Tend:
+        u_dt: object
+        v_dt: object
+        pt_dt: object
+
+    def tend():
+        return Tend(*(qf.zeros([X_DIM, Y_DIM, Z_DIM], "unknown") for _ in range(3)))
+
+    phys_cfg = pySHiELD.PhysicsConfig(
+        dt_atmos=config.dt_atmos, hydrostatic=config.hydrostatic, npx=config.npx, npy=config.npy, npz=config.npz,
+        nwat=config.nwat, schemes=["GFS_microphysics"], do_qa=True, layout=config.layout, c2l_ord=config.c2l_ord)
+    t_ref, t_mine = tend(), tend()
+    p_ref = pySHiELD.PhysicsState.init_zeros(quantity_factory=qf, schemes=schemes)
+    p_mine = pySHiELD.PhysicsState.init_zeros(quantity_factory=qf, schemes=schemes)
+    d2p_ref = ref.DycoreToPhysics(stencil_factory=sf, quantity_factory=qf, dycore_config=config,
+                                  do_dry_convective_adjust=False, dycore_only=False)
+    upd_ref = ref.UpdateAtmosphereState(stencil_factory=sf, grid_data=grid_data, namelist=phys_cfg, comm=communicator,
+                                        grid_info=driver_grid, state=state, quantity_factory=qf, dycore_only=False,
+                                        apply_tendencies=True, tendency_state=t_ref)
+    upd_mine = dropin.UpdateAtmosphereState(sf, grid_data, phys_cfg, communicator, driver_grid, mine_state, qf, False,
+                                            True, t_mine, dycore=mine)
+    d2p_mine = dropin.DycoreToPhysics(sf, qf, config, False, False, dycore=mine)
+    dt = float(config.dt_atmos)
+    d2p_ref(dycore_state=state, physics_state=p_ref, tendency_state=t_ref, timestep=dt)
+    d2p_mine(mine_state, p_mine, t_mine, dt)
+    rank = mpi_comm.Get_rank()
+    synthesize_physics(p_ref, rank, config.npx - 1, float(grid_data.ptop))
+    for n in PHY_IN:   # the same "physics result" for both
+        np.asarray(getattr(p_mine, n))[...] = np.asarray(getattr(p_ref, n))
+    upd_ref(dycore_state=state, phy_state=p_ref, u_dt=t_ref.u_dt, v_dt=t_ref.v_dt, pt_dt=t_ref.pt_dt, dt=dt)
+    upd_mine(mine_state, p_mine, t_mine.u_dt, t_mine.v_dt, t_mine.pt_dt, dt)
+    want, got = state_arrays(state), state_arrays(mine_state)
+    bad = []
+    for name in ("u", "v", "delp", "pt", "qvapor", "qliquid", "qice", "qrain", "qsnow", "qgraupel", "pe", "pk", "peln",
+                 "ps", "ua", "va"):
+        a, b = got[name], want[name]
+        a, b = (a[3:15, 3:15], b[3:15, 3:15]) if name in ("pe", "pk", "peln", "ps") else (a[3:15, 3:15, :79], b[3:15, 3:15, :79])
+        if not np.array_equal(a, b):
+            bad.append(("coupling:" + name, float(np.max(np.abs(a - b)))))
+    for n in ("qvapor", "pt", "ua", "omga"):
+        if not np.array_equal(np.asarray(getattr(p_mine, n))[3:15, 3:15, :79], np.asarray(getattr(p_ref, n))[3:15, 3:15, :79]):
+            bad.append(("coupling:phy." + n, 0.0))
+    for n in ("u_dt", "v_dt", "pt_dt"):
+        a, b = np.asarray(getattr(t_mine, n).data)[3:15, 3:15, :79], np.asarray(getattr(t_ref, n).data)[3:15, 3:15, :79]
+        if not np.array_equal(a, b):
+            bad.append(("coupling:tend." + n, float(np.max(np.abs(a - b)))))
+    return bad
 
 
 if __name__ == "__main__":

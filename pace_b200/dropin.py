@@ -38,7 +38,7 @@ CONFIG_NAMES = [
 
 def _arr(x):
     """numpy view (numpy storage) or host copy (cupy storage) of a Quantity / gt4py storage / array-like."""
-    d = getattr(x, "data", x)
+    d = x if isinstance(x, np.ndarray) else getattr(x, "data", x)   # (ndarray.data is a memoryview)
     if hasattr(d, "get"):  # cupy
         d = d.get()
     return np.asarray(d)
@@ -47,7 +47,7 @@ def _arr(x):
 def _write_back(dst, a):
     """Store the result `a` into the caller's field object: in place for numpy storage, through a host-to-device copy
     for cupy storage; anything else is refused rather than silently dropped."""
-    d = getattr(dst, "data", dst)
+    d = dst if isinstance(dst, np.ndarray) else getattr(dst, "data", dst)
     if isinstance(d, np.ndarray):
         if d.ndim == 3 and d.shape[2] != a.shape[2]:
             a = a[:, :, :d.shape[2]]
@@ -314,3 +314,81 @@ class DynamicalCore(_Bridge):
 
     def __call__(self, *args, **kwargs):
         return self.step_dynamics(*args, **kwargs)
+
+
+# ---- dycore <-> physics coupling of the driver's time loop (driver/pace/driver/driver.py:519-537, 645-661) ----------
+def _driver_grid_arrays(grid_info):
+    from .engine import DRIVER_GRID
+
+    return {n: _arr(getattr(grid_info, n)) for n in DRIVER_GRID}
+
+
+class DycoreToPhysics:
+    """Drop-in for `pySHiELD.update.update_atmos_state.DycoreToPhysics` (update_atmos_state.py:148-231): the reference's
+    constructor arguments plus `dycore=` (the pace_b200.dropin.DynamicalCore whose device state is the source), and
+    `__call__(dycore_state, physics_state, tendency_state=None, timestep=None)`.  The sixteen fields are copied on the
+    device and written into `physics_state`; the dry convective adjustment (fv_subgridz) is not implemented."""
+
+    def __init__(self, stencil_factory, quantity_factory, dycore_config, do_dry_convective_adjust, dycore_only, *,
+                 dycore):
+        del stencil_factory, quantity_factory, dycore_config
+        if do_dry_convective_adjust:
+            raise NotImplementedError("pace_b200: do_dry_convective_adjust (fv_subgridz) is not implemented")
+        self._dycore_only = bool(dycore_only)
+        self._owner = dycore
+
+    def __call__(self, dycore_state, physics_state, tendency_state=None, timestep=None):
+        from .engine import COUPLING_COPIED
+
+        if self._dycore_only:
+            return
+        own, eng = self._owner, self._owner.engine
+        if not hasattr(eng, "_origin_i"):
+            raise RuntimeError("DycoreToPhysics: build the UpdateAtmosphereState of this dycore first (it registers the "
+                               "coupling fields)")
+        own._upload(dycore_state)
+        eng.dycore_to_physics()
+        eng.core.sync()
+        states = list(physics_state) if own._many else [physics_state]
+        for n in COUPLING_COPIED:
+            for s, a in zip(states, eng.core.get("phy." + n)):
+                _write_back(getattr(s, n), a)
+
+
+class UpdateAtmosphereState:
+    """Drop-in for `pySHiELD.update.update_atmos_state.UpdateAtmosphereState` (update_atmos_state.py:234-349): the
+    reference's constructor arguments plus `dycore=`, and `__call__(dycore_state, phy_state, u_dt, v_dt, pt_dt, dt)`.
+    `grid_info` is the reference's DriverGridData (a list over the cube ranks when the dycore holds the whole cube)."""
+
+    def __init__(self, stencil_factory, grid_data, namelist, comm, grid_info, state, quantity_factory, dycore_only,
+                 apply_tendencies, tendency_state, *, dycore):
+        del stencil_factory, grid_data, comm, state, quantity_factory, tendency_state
+        self.namelist = namelist
+        self._dycore_only, self._apply_tendencies = bool(dycore_only), bool(apply_tendencies)
+        self._owner = dycore
+        infos = list(grid_info) if dycore._many else [grid_info]
+        if int(getattr(infos[0], "grid_type", 0)) > 3:
+            raise NotImplementedError("pace_b200: doubly periodic grids (grid_type > 3) are not supported")
+        dycore.engine.setup_coupling([_driver_grid_arrays(g) for g in infos])
+
+    def __call__(self, dycore_state, phy_state, u_dt, v_dt, pt_dt, dt):
+        from .engine import COUPLING_PHYSICS_OUT
+
+        own, eng = self._owner, self._owner.engine
+        core = eng.core
+        fields, names = own._upload(dycore_state)
+        phys = list(phy_state) if own._many else [phy_state]
+        tend = {"u_dt": u_dt, "v_dt": v_dt, "pt_dt": pt_dt}
+        if not self._dycore_only:
+            for n in COUPLING_PHYSICS_OUT + ["ua", "va", "pt"]:
+                core.put("phy." + n, [_arr(getattr(s, n)) for s in phys])
+        for n, q in tend.items():
+            core.put("tend." + n, [_arr(x) for x in q] if own._many else [_arr(q)])
+        eng.update_atmos_state(float(dt), self._dycore_only, self._apply_tendencies)
+        own._download(fields, names)
+        for n, q in tend.items():
+            for dst, a in zip(list(q) if own._many else [q], core.get("tend." + n)):
+                _write_back(dst, a)
+        if not self._dycore_only:   # fill_gfs_delp adjusts the physics' specific humidity in place
+            for s, a in zip(phys, core.get("phy.physics_updated_specific_humidity")):
+                _write_back(s.physics_updated_specific_humidity, a)
