@@ -3,6 +3,7 @@
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c384|c128|c48] [--impl reference]
     python bench.py --workload tracer_c192 | mapsingle_c384_l91_f32     (BASELINE.json configs 4 and 5, one GPU)
+    python bench.py --workload coupling_c384                            (the driver's dycore <-> physics coupling calls)
 
 One "step" = one DynamicalCore.step_dynamics (k_split=1, n_split=6: 6 acoustic substeps + tracer advection +
 vertical remap) on synthetic inputs of the named shape (pace_b200/synthetic.py).  Metric: simulated-days/day =
@@ -169,7 +170,42 @@ def side_workload(args):
     pk, pk_kind = peaks()
     dev = "cuda:0"
     torch.cuda.set_device(0)
-    if args.workload == "tracer_c192":
+    if args.workload == "coupling_c384":
+        # the two coupling calls of the driver's time loop around its physics, C384 L79, 24 subdomains;
+        # what the physics hands back is set once (perturbed copies of the state), outside the timing
+        from pace_b200.engine import COUPLING_PHYSICS_OUT
+        from pace_b200.synthetic import make_engine, setup_coupling
+
+        n, nsub = 384, 6
+        eng = make_engine(n, 2, npz=NPZ, device=dev, n_split=N_SPLIT, k_split=1, dt_atmos=DT_ATMOS)
+        eng.step_dynamics()
+        setup_coupling(eng, n, 2)
+        core = eng.core
+        eng.dycore_to_physics()
+        t = core.t
+        t["phy.prsi"][:, 0] = float(eng.cfg["ptop"])
+        t["phy.prsi"][:, 1:] = float(eng.cfg["ptop"]) + torch.cumsum(t["delp"][:, :NPZ], dim=1)
+        g = torch.Generator(device="cpu").manual_seed(0)
+        for name in COUPLING_PHYSICS_OUT[1:]:
+            src = {"physics_updated_specific_humidity": "qvapor"}.get(name, name.replace("physics_updated_", ""))
+            r = torch.rand(t["phy." + src].shape[1:], generator=g, dtype=torch.float64).to(dev)
+            if src in ("ua", "va"):
+                t["phy." + name].copy_(t["phy." + src] + 1.5 * (r - 0.5))
+            elif src == "pt":
+                t["phy." + name].copy_(t["phy." + src] * (1.0 + 2.0e-3 * (r - 0.5)))
+            else:
+                t["phy." + name].copy_(t["phy." + src] * (1.0 + 0.05 * (r - 0.5)) + 1.0e-7 * r)
+
+        def call():
+            eng.dycore_to_physics()
+            eng.update_atmos_state()
+
+        cells = nsub * n * n * NPZ
+        # field passes: 16 R + 16 W (copies), 24 R + 10 W (tendencies, tracers, delp), 3 (fill), 10 (moist_cv), 4
+        # (pressures), 6 + 2 (D-grid winds, zeroing), 4 (A-grid winds) = 95
+        bytes_per_cell, what, dtype = 95 * 8.0, "DycoreToPhysics + UpdateAtmosphereState, C384 L79, 24 subdomains", "f64"
+        metric, unit = "coupling calls per second", "calls / s"
+    elif args.workload == "tracer_c192":
         from pace_b200.synthetic import make_engine
 
         n, nsub = 192, 6
@@ -282,7 +318,7 @@ def main():
     args = ap.parse_args()
     if args.workload is None:
         args.workload = "c384"
-    if args.workload in ("tracer_c192", "mapsingle_c384_l91_f32"):
+    if args.workload in ("tracer_c192", "mapsingle_c384_l91_f32", "coupling_c384"):
         if int(os.environ.get("RANK", "0")) == 0:
             side_workload(args)
         return

@@ -177,3 +177,30 @@ def make_engine(n_tile, layout, npz=79, device="cuda:0", comm=None, noise=True, 
         scatter("ad.zs", resample_tile(np.asarray(s["phis"]) / 9.80665, n_tile, (0, 0), dev), tile)
     core.set_column("grid.a2b_corner_coef", coef.reshape(-1))
     return eng
+
+
+def setup_coupling(eng, n_tile, layout):
+    """Registers the dycore <-> physics coupling fields of `eng` (DycoreEngine.setup_coupling) with DriverGridData arrays
+    resampled from the coupling fixture (tests/golden/c12_6rank_coupling.npz), for bench.py --workload coupling_c384."""
+    from .engine import DRIVER_GRID
+
+    z = np.load(os.path.join(GOLDEN, "c12_6rank_coupling.npz"))
+    n = n_tile // layout
+    core = eng.core
+    dev = core.device
+    eng.setup_coupling([{name: np.zeros((n + 7, n + 7)) for name in DRIVER_GRID}] * len(eng.ranks))
+    slot = {r: s for s, r in enumerate(eng.ranks)}
+    for tile in range(6):
+        if not any(r // (layout * layout) == tile for r in eng.ranks):
+            continue
+        for name in DRIVER_GRID:
+            a = np.nan_to_num(z["r%d:grid:%s" % (tile, name)])
+            if a.ndim == 1:
+                a = np.repeat(a[:, None], 19, axis=1)
+            t = resample_tile(a, n_tile, (0, 0), dev)
+            dst = core.t["dgrid." + name]
+            for jy in range(layout):
+                for ix in range(layout):
+                    r = slot.get(tile * layout * layout + jy * layout + ix)
+                    if r is not None:
+                        dst[r, :, :n + 7] = t[0, jy * n:jy * n + n + 7, ix * n:ix * n + n + 7]
