@@ -120,13 +120,19 @@ def rank_main(mpi_comm, cfg_kwargs, out_dir):
     nx = config.npx - 1
     out = {}
     pre = {k: v.copy() for k, v in state_arrays(state).items()}
+    import time
+
+    t0 = time.time()
     d2p(dycore_state=state, physics_state=phy, tendency_state=tend, timestep=float(config.dt_atmos))
+    t_d2p = time.time() - t0
     for n in COPIED:
         out["copy:" + n] = _a(getattr(phy, n)).copy()
     synthesize_physics(phy, rank, nx, float(grid_data.ptop))
     for n in PHY_IN:
         out["phy:" + n] = _a(getattr(phy, n)).copy()
+    t0 = time.time()
     upd(dycore_state=state, phy_state=phy, u_dt=tend.u_dt, v_dt=tend.v_dt, pt_dt=tend.pt_dt, dt=float(config.dt_atmos))
+    t_upd = time.time() - t0
     post = state_arrays(state)
     for k, v in pre.items():
         out["in:" + k] = v
@@ -139,12 +145,14 @@ def rank_main(mpi_comm, cfg_kwargs, out_dir):
         out["grid:" + n] = _a(getattr(driver_grid, n)).copy()
     os.makedirs(out_dir, exist_ok=True)
     np.savez(os.path.join(out_dir, "rank%d.npz" % rank), **out)
-    return {"rank": rank, "changed": sorted(k for k in out if k.startswith("out:"))}
+    return {"rank": rank, "changed": sorted(k for k in out if k.startswith("out:")), "dycore_to_physics_s": t_d2p,
+            "update_atmos_state_s": t_upd}
 
 
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--raw", default="/tmp/pace_golden_coupling")
+    ap.add_argument("--time-only", action="store_true", help="print the reference's call times, leave the fixture alone")
     ap.add_argument("--warm", action="store_true",
                     help="first compile every stencil in ONE process (NullComm), so that the six ranks read a warm GT4Py "
                          "cache instead of racing to write it")
@@ -157,6 +165,15 @@ def main():
     res = run_ranks(6, rank_main, (cfg, args.raw), timeout=3600)
     for r in res:
         print(r)
+    if args.time_only:
+        import json
+
+        print("REFERENCE_COUPLING " + json.dumps({
+            "what": "UNMODIFIED reference, numpy backend, C12 L79, 6 processes: first call of DycoreToPhysics and of "
+                    "UpdateAtmosphereState after one dycore step (max over ranks)",
+            "dycore_to_physics_s": max(r["dycore_to_physics_s"] for r in res),
+            "update_atmos_state_s": max(r["update_atmos_state_s"] for r in res)}))
+        return
     nx = 12
     merged = {}
     for r in range(6):
