@@ -309,6 +309,17 @@ int pace_b200_dycore_to_physics(void* handle);
 int pace_b200_update_atmos_state(void* handle, double dt, int dycore_only, int apply_tendencies, const int* origin_i,
                                  const int* origin_j, int npx, int npy);
 
+/* ---- diagnostics egress (driver/pace/driver/diagnostics.py:142-249) ------------------------------------------------
+ * What MonitorDiagnostics.store hands its monitor, produced on the device in the reference's own order.
+ * pace_b200_egress_pack: `quantity.view[:]` of a field as a dense [subdomain][i][j][k] array (k fastest) at the device
+ * address dst.  kind 0: 3-D field, levels [0, nk); kind 1: 2-D field; kind 2: level `level` of a 3-D field as a 2-D array
+ * (ZSelect.select_data, diagnostics.py:44-64).  x_interface / y_interface: the field has nx+1 / ny+1 points.
+ * pace_b200_column_integral: _compute_column_integral (diagnostics.py:226-249) into the registered 2-D field out2d,
+ * bit-identical to RGRAV * np.sum(q * delp, axis=2). */
+int pace_b200_egress_pack(void* handle, const char* name, int kind, int level, int x_interface, int y_interface, int nk,
+                          double* dst);
+int pace_b200_column_integral(void* handle, const char* q, const char* delp, const char* out2d);
+
 #ifdef __cplusplus
 }
 #endif

@@ -158,6 +158,8 @@ MODULE_CALLS = {
     "remap": [_I, _D],
     "step": [],
     "dycore_to_physics": [],
+    "egress_pack": [_S, _I, _I, _I, _I, _I, ctypes.c_void_p],
+    "column_integral": [_S, _S, _S],
     "update_atmos_state": [_D, _I, _I, ctypes.POINTER(_I), ctypes.POINTER(_I), _I, _I],
 }
 

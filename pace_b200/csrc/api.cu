@@ -309,6 +309,10 @@ int pace_b200_tracer_advection(void* h) { ENTRY(tracer_advection(*c)) }
 int pace_b200_remap(void* h, int last_step, double mdt) { ENTRY(remapping(*c, last_step, mdt)) }
 int pace_b200_step(void* h) { ENTRY(step(*c)) }
 int pace_b200_dycore_to_physics(void* h) { ENTRY(dycore_to_physics(*c)) }
+int pace_b200_egress_pack(void* h, const char* name, int kind, int level, int x_interface, int y_interface, int nk, double* dst) {
+  ENTRY(egress_pack(*c, name, kind, level, x_interface, y_interface, nk, dst))
+}
+int pace_b200_column_integral(void* h, const char* q, const char* delp, const char* out2d) { ENTRY(column_integral(*c, q, delp, out2d)) }
 int pace_b200_update_atmos_state(void* h, double dt, int dycore_only, int apply_tendencies, const int* origin_i,
                                  const int* origin_j, int npx, int npy) {
   ENTRY(update_atmos_state(*c, dt, dycore_only, apply_tendencies, origin_i, origin_j, npx, npy))

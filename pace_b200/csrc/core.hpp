@@ -162,6 +162,9 @@ int acoustic(Core& c, double timestep, int n_map);
 int tracer_advection(Core& c);
 int remapping(Core& c, int last_step, double mdt);
 int step(Core& c);
+// diagnostics egress (egress.cu)
+int egress_pack(Core& c, const char* name, int kind, int level, int x_interface, int y_interface, int nk, double* dst);
+int column_integral(Core& c, const char* q_name, const char* delp_name, const char* out_name);
 // dycore <-> physics coupling (coupling.cu; sequencing with the halo updates in step.cu)
 int dycore_to_physics(Core& c);
 int coupling_tendencies(Core& c, double dt_atmos, int dycore_only);
