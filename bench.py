@@ -4,6 +4,7 @@
     python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c384|c128|c48] [--impl reference]
     python bench.py --workload tracer_c192 | mapsingle_c384_l91_f32     (BASELINE.json configs 4 and 5, one GPU)
     python bench.py --workload coupling_c384                            (the driver's dycore <-> physics coupling calls)
+    python bench.py --workload egress_c384                              (diagnostics stored every step vs no output)
 
 One "step" = one DynamicalCore.step_dynamics (k_split=1, n_split=6: 6 acoustic substeps + tracer advection +
 vertical remap) on synthetic inputs of the named shape (pace_b200/synthetic.py).  Metric: simulated-days/day =
@@ -277,6 +278,91 @@ def side_workload(args):
     print(json.dumps(line))
 
 
+def egress_workload(args):
+    """the headline workload with diagnostics stored EVERY step (pace_b200.egress.MonitorDiagnostics: ten
+    3-D fields, two column integrals, three level selections) against the same steps without output: what an output
+    step costs the time loop.  The monitor only samples what it receives (a strided checksum per array): zarr / netCDF4
+    are not in this image, and the cost of a file writer is the writer's, not the egress path's; a sink that is slower
+    than the time loop shows up as back-pressure (wall time per step above the device time)."""
+    import numpy as np
+    import torch
+
+    from pace_b200.egress import MonitorDiagnostics
+    from pace_b200.synthetic import make_engine
+
+    dev = "cuda:0"
+    torch.cuda.set_device(0)
+    eng = make_engine(384, 2, npz=NPZ, device=dev, n_split=N_SPLIT, k_split=1, dt_atmos=DT_ATMOS)
+    names = ["u", "v", "w", "pt", "delp", "delz", "qvapor", "qliquid", "ua", "va"]
+
+    class Monitor:
+        def __init__(self):
+            self.checksum, self.n = 0.0, 0
+
+        def store(self, state):
+            for k, v in state.items():
+                if k == "time":
+                    continue
+                for q in v:
+                    self.checksum += float(np.sum(q.data[::7, ::7]))
+            self.n += 1
+
+        def store_constant(self, state):
+            pass
+
+        def cleanup(self):
+            pass
+
+    mon = Monitor()
+    diag = MonitorDiagnostics(mon, names, ["column_integrated_qvapor", "column_integrated_qliquid"],
+                              [(40, ["pt", "w"]), (78, ["ua"])], dycore=eng)
+    for _ in range(max(args.warmup, 3)):
+        eng.step_dynamics()
+        diag.store(0.0)
+    torch.cuda.synchronize()
+    sampler = ClockSampler(0)
+    sampler.start()
+
+    def timed(with_store):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        t0 = time.time()
+        e0.record()
+        for n in range(args.steps):
+            eng.step_dynamics()
+            if with_store:
+                diag.store(float(n))
+        e1.record()
+        torch.cuda.synchronize()
+        if with_store:
+            diag._egress.cleanup()   # every stored step has reached the monitor
+        return e0.elapsed_time(e1) / args.steps, (time.time() - t0) / args.steps * 1000.0
+
+    plain_ms, _ = timed(False)
+    l0 = eng.core.lib.pace_b200_launch_count()
+    dev_ms, wall_ms = timed(True)
+    launches = (eng.core.lib.pace_b200_launch_count() - l0) // args.steps
+    sampler.stop_flag = True
+    sampler.join(timeout=2)
+    nbytes = diag._egress.bytes_per_store
+    stored = mon.n
+    diag.cleanup()
+    line = {
+        "metric": "dycore simulated-days/day with diagnostics stored every step", "value": DT_ATMOS / (wall_ms / 1000.0),
+        "unit": "simulated days / day", "n_gpus": 1, "steps": args.steps, "warmup": max(args.warmup, 3),
+        "ms_per_step": wall_ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic",
+        "config": {"workload": "C384 L79 fp64, 24 subdomains, MonitorDiagnostics.store after every step: %d 3-D fields, "
+                               "2 column integrals, 3 level selections" % len(names)},
+        "gpu_launches": int(launches), "clocks": sampler.summary(),
+        "egress": {"ms_per_step_device": dev_ms, "ms_per_step_wall_until_the_monitor_has_everything": wall_ms,
+                   "ms_per_step_without_output": plain_ms, "cost_of_an_output_step_ms": dev_ms - plain_ms,
+                   "d2h_bytes_per_store": nbytes, "d2h_gbs_over_the_step": nbytes / (wall_ms / 1000.0) / 1e9,
+                   "stores_received_by_the_monitor": stored},
+    }
+    print(json.dumps(line))
+
+
 def eng_tracers():
     return ["qvapor", "qliquid", "qrain", "qice", "qsnow", "qgraupel", "qo3mr", "qsgs_tke"]
 
@@ -318,6 +404,8 @@ def main():
     args = ap.parse_args()
     if args.workload is None:
         args.workload = "c384"
+    if args.workload == "egress_c384":
+        return egress_workload(args)
     if args.workload in ("tracer_c192", "mapsingle_c384_l91_f32", "coupling_c384"):
         if int(os.environ.get("RANK", "0")) == 0:
             side_workload(args)
