@@ -28,7 +28,8 @@ def full(a):
     return f
 
 
-def run_coupling(backend):
+def run_coupling(backend, comm=None, mine=None):
+    """mine / comm: the cube ranks this process holds and its pace_b200.distributed.TorchComm (multi-process runs)"""
     from pace_b200.engine import COUPLING_COPIED, COUPLING_PHYSICS_OUT, DycoreEngine
 
     kw = {}
@@ -36,17 +37,21 @@ def run_coupling(backend):
         from tests import hostemu
 
         kw = dict(device="cpu", _lib_handle=hostemu.load())
-    fx = load_coupling()
-    eng = DycoreEngine(NX, 1, 79, load_six("grid"), **kw)
-    init = load_six("init")
+    elif backend != "cuda":
+        kw = dict(device=backend)
+    mine = list(range(6)) if mine is None else list(mine)
+    fx_all = load_coupling()
+    fx = [fx_all[r] for r in mine]
+    grids, init = load_six("grid"), load_six("init")
+    eng = DycoreEngine(NX, 1, 79, [grids[r] for r in mine], comm=comm, **kw)
     states = []
-    for r in range(6):
+    for slot, r in enumerate(mine):
         s = {"phis": init[r]["phis"]}
-        for name, a in fx[r]["in"].items():
+        for name, a in fx[slot]["in"].items():
             s[name] = full(a)
         states.append(s)
     eng.set_state(states)
-    eng.setup_coupling([fx[r]["grid"] for r in range(6)])
+    eng.setup_coupling([f["grid"] for f in fx])
     core = eng.core
 
     # DycoreToPhysics: plain copies on [is, ie+1] x [js, je+1] x [0, npz) (checked against the reference's output when
@@ -54,17 +59,17 @@ def run_coupling(backend):
     eng.dycore_to_physics()
     for name in COUPLING_COPIED:
         got = core.get("phy." + name)
-        for r in range(6):
+        for r in range(len(mine)):
             want = full(fx[r]["in"][name])
             assert np.array_equal(got[r][3:16, 3:16, :79], want[3:16, 3:16, :79]), (name, r)
             assert not got[r][:, :, 79].any(), (name, r)
     # the physics' part: prsi and the updated fields come from the fixture
     for name in COUPLING_PHYSICS_OUT:
-        core.put("phy." + name, [full(fx[r]["phy"][name]) for r in range(6)])
+        core.put("phy." + name, [full(fx[r]["phy"][name]) for r in range(len(mine))])
     eng.update_atmos_state()
     core.sync()
     bad = []
-    for r in range(6):
+    for r in range(len(mine)):
         for name, want in fx[r]["out"].items():
             got = core.get(name)[r]
             if want.ndim == 3:
@@ -83,7 +88,7 @@ def run_coupling(backend):
     # fields the coupling must not touch
     for name in ("w", "delz", "omga", "qo3mr", "qcld"):
         got = core.get(name)
-        for r in range(6):
+        for r in range(len(mine)):
             assert np.array_equal(got[r][3:15, 3:15, :79], full(fx[r]["in"][name])[3:15, 3:15, :79]), (name, r)
 
 
@@ -164,3 +169,45 @@ def test_coupling_layout2_hostemu():
 @pytest.mark.gpu
 def test_coupling_layout2_gpu():
     run_coupling_layout2("cuda")
+
+
+def _gloo_worker(rank, world, port, q):
+    try:
+        import sys
+
+        sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+        import torch.distributed as dist
+
+        from pace_b200.distributed import Placement, TorchComm
+
+        dist.init_process_group("gloo", init_method="tcp://127.0.0.1:%d" % port, rank=rank, world_size=world)
+        run_coupling("hostemu", comm=TorchComm(), mine=Placement(6, world).ranks_of(rank))
+        dist.barrier()
+        dist.destroy_process_group()
+        q.put((rank, None))
+    except BaseException as e:  # noqa: BLE001 — surfaced in the parent
+        import traceback
+
+        q.put((rank, "%s\n%s" % (e, traceback.format_exc())))
+
+
+def test_coupling_two_processes_gloo():
+    """The coupling on 2 processes holding 3 subdomains each: the halo updates of the tendencies and of the winds cross
+    the process boundary (pace_b200.distributed over gloo)."""
+    import torch.multiprocessing as mp
+
+    from tests import hostemu
+    from tests.test_distributed_gloo import _free_port
+
+    hostemu.load()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_gloo_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    results = [q.get(timeout=600) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    for rank, err in sorted(results):
+        assert err is None, "rank %d: %s" % (rank, err)
