@@ -143,6 +143,23 @@ def rank_main(mpi_comm, cfg_kwargs, out_dir):
         out["out:tend." + n] = _a(getattr(tend, n)).copy()
     for n in DRIVER_GRID:
         out["grid:" + n] = _a(getattr(driver_grid, n)).copy()
+    # second case: dycore_only=True, apply_tendencies=False (driver.py:160-165 with no dry convective adjustment): the
+    # call reduces to fill_gfs_delp on the dycore's own qvapor, given scattered values below the threshold and below zero
+    upd_only = update_atmos_state.UpdateAtmosphereState(
+        stencil_factory=stencil_factory, grid_data=grid_data, namelist=phys_cfg, comm=communicator,
+        grid_info=driver_grid, state=state, quantity_factory=qf, dycore_only=True, apply_tendencies=False,
+        tendency_state=tend)
+    rng = np.random.default_rng(4321 + rank)
+    qv = _a(state.qvapor)
+    c = (slice(3, 3 + nx), slice(3, 3 + nx), slice(0, config.npz))
+    pick = rng.random(qv[c].shape)
+    qv[c] = np.where(pick < 0.03, 1.0e-10 * rng.random(pick.shape), qv[c])
+    qv[c] = np.where((pick >= 0.03) & (pick < 0.05), -2.0e-6 * rng.random(pick.shape), qv[c])
+    out["in2:qvapor"] = qv.copy()
+    out["in2:delp"] = _a(state.delp).copy()
+    upd_only(dycore_state=state, phy_state=phy, u_dt=tend.u_dt, v_dt=tend.v_dt, pt_dt=tend.pt_dt, dt=float(config.dt_atmos))
+    out["out2:qvapor"] = _a(state.qvapor).copy()
+    assert np.array_equal(_a(state.delp), out["in2:delp"])
     os.makedirs(out_dir, exist_ok=True)
     np.savez(os.path.join(out_dir, "rank%d.npz" % rank), **out)
     return {"rank": rank, "changed": sorted(k for k in out if k.startswith("out:")), "dycore_to_physics_s": t_d2p,

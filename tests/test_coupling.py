@@ -211,3 +211,39 @@ def test_coupling_two_processes_gloo():
         p.join(timeout=60)
     for rank, err in sorted(results):
         assert err is None, "rank %d: %s" % (rank, err)
+
+
+def run_fill_only(backend):
+    """UpdateAtmosphereState(dycore_only=True, apply_tendencies=False): fill_gfs_delp on the dycore's own qvapor."""
+    from pace_b200.engine import DycoreEngine
+
+    kw = {}
+    if backend == "hostemu":
+        from tests import hostemu
+
+        kw = dict(device="cpu", _lib_handle=hostemu.load())
+    fx = load_coupling()
+    eng = DycoreEngine(NX, 1, 79, load_six("grid"), **kw)
+    init = load_six("init")
+    eng.set_state([{"phis": init[r]["phis"], "qvapor": full(fx[r]["in2"]["qvapor"]), "delp": full(fx[r]["in2"]["delp"])}
+                   for r in range(6)])
+    eng.setup_coupling([fx[r]["grid"] for r in range(6)])
+    eng.update_atmos_state(dycore_only=True, apply_tendencies=False)
+    eng.core.sync()
+    got_q, got_dp = eng.core.get("qvapor"), eng.core.get("delp")
+    changed = 0
+    for r in range(6):
+        want = fx[r]["out2"]["qvapor"][:12, :12, :79]
+        assert np.array_equal(got_q[r][3:15, 3:15, :79], want), r
+        assert np.array_equal(got_dp[r][3:15, 3:15, :79], fx[r]["in2"]["delp"][:12, :12, :79]), r
+        changed += int((want != fx[r]["in2"]["qvapor"][:12, :12, :79]).sum())
+    assert changed > 1000   # the fill had work to do
+
+
+def test_fill_only_hostemu():
+    run_fill_only("hostemu")
+
+
+@pytest.mark.gpu
+def test_fill_only_gpu():
+    run_fill_only("cuda")
