@@ -90,6 +90,9 @@ struct Core {
   // inside AcousticDynamics q_con only changes by transport between two d_sw calls: after the first substep its level
   // flags are kept up to date from the halo frame (tracer.cu: level_nonzero_flags)
   bool in_acoustic = false, qcon_flags_fresh = false;
+  // the level flags of the tracers (tracer.cu) are those of a TracerAdvection call that has just run: set by step()
+  // around its remapping call only, so that a caller who changes the tracers between the two phases is never affected
+  bool tracer_flags_fresh = false;
   PeerPlan peer_plans[16];
 
   double* F(const char* name);              // caller-registered field, error if missing

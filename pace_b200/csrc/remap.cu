@@ -407,6 +407,7 @@ struct TrPtrs { double* p[9]; };
 }  // namespace
 
 const char* tracer_name(int n);
+const int* tracer_zero_fields(Core& c, int nq);   // tracer.cu
 
 // Resident CTAs per SM the scalar column kernel is compiled for (8, 10 or 12; see launch_ij_occ).
 static int remap_occupancy() {
@@ -509,21 +510,28 @@ int remap_main(Core& c, int nq) {
   for (int n = 0; n < 9; ++n) trp.p[n] = n < nq ? tr[n] : nullptr;
   const bool fill = cf.fill != 0;
   const bool zero_paths = zero_paths_enabled();
+  // tracers that are zero on a whole subdomain (known from TracerAdvection's level flags inside step()): their columns
+  // would be read, found all zero and rewritten as zeros - they are left alone
+  const int* zero_field = tracer_zero_fields(c, nq);
+  if (!c.err.empty()) return 1;
   auto scalars_column = [=] __device__(const Pt& p) {
     COL_DECL;
     map_single_column(p, col, km, pt, peln, pn2, 1, kord_tm, 0.0, t_min);
     unsigned negative = 0;  // tracers whose remapped column holds a negative value
+    bool have_dp = false;   // col.dp holds the thicknesses of pe1 (the first tracer that is remapped fills it)
     for (int n = 0; n < nq; ++n) {
+      if (zero_field != nullptr && zero_field[p.t * 9 + n]) continue;
       // mapn_tracer.py:40-41: every tracer uses kord_tr, entry 5 is forced to 9
       int kord = n == 5 ? 9 : kord_tr;
-      if (map_single_column(p, col, km, trp.p[n], pe1, pe2, 0, kord, 0.0, 0.0, n > 0, zero_paths)) negative |= 1u << n;
+      if (map_single_column(p, col, km, trp.p[n], pe1, pe2, 0, kord, 0.0, 0.0, have_dp, zero_paths)) negative |= 1u << n;
+      have_dp = true;
     }
     // fillz leaves a column without negative values exactly as it is (no borrowing, zfix == 0): only the others
     // go through it.  It uses col.dp as scratch, so the thicknesses are rebuilt afterwards if it ran.
     if (fill)
       for (int n = 0; n < nq; ++n)
         if (negative & (1u << n)) fillz_column(p, col, km, trp.p[n], dp2);
-    map_single_column(p, col, km, w, pe1, pe2, -2, kord_wz, A20(wsd), 0.0, nq > 0 && !(fill && negative));
+    map_single_column(p, col, km, w, pe1, pe2, -2, kord_wz, A20(wsd), 0.0, have_dp && !(fill && negative));
     map_single_column(p, col, km, delz, pe1, pe2, 1, kord_wz, 0.0, 0.0, true);
     // undo_delz_adjust_and_copy_peln
     for (int k = 0; k < km; ++k) A(delz, 0, 0, k) = -A(delz, 0, 0, k) * A(delp, 0, 0, k);

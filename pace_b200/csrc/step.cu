@@ -267,7 +267,12 @@ int step(Core& c) {
     RUN(stage(c, "Tracer2D1L-Out"));
     if (c.g.nz > 4) {
       RUN(stage(c, "Remapping-In"));
-      RUN(remapping(c, last_step, cfg.dt_atmos / cfg.k_split));
+      // TracerAdvection has just run in this call and nothing but (optionally) the caller's savepoint hook came in
+      // between: without a hook its level flags describe the tracers the remap is about to read
+      c.tracer_flags_fresh = c.stage_cb == nullptr;
+      const int remap_rc = remapping(c, last_step, cfg.dt_atmos / cfg.k_split);
+      c.tracer_flags_fresh = false;
+      if (remap_rc) return remap_rc;
       RUN(stage(c, "Remapping-Out"));
       if (last_step) {
         RUN(omega_from_w(c));

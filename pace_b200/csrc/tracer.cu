@@ -122,6 +122,54 @@ const int* level_nonzero_flags(Core& c, const double* q, int nk, int slot, bool 
 #endif
 }
 
+#ifndef PACE_HOST_EMU
+namespace {
+// zero[t * 9 + n] = 1 when every level flag of tracer n on subdomain t is 0 (slots 0 - 7 of level_nonzero_flags)
+__global__ void k_fields_all_zero(const int* flags, int per_slot, int nk, int nq, int* zero) {
+  const int t = blockIdx.x, n = blockIdx.y;
+  bool any = false;
+  if (n < 8) {
+    const int* f = flags + (size_t)per_slot * n + t * nk;
+    for (int k = threadIdx.x; k < nk; k += blockDim.x) any = any || f[k] != 0;
+  } else {
+    any = true;   // no flags are kept for a ninth tracer
+  }
+  any = __syncthreads_or(any);
+  if (threadIdx.x == 0) zero[t * 9 + n] = any ? 0 : 1;
+}
+}  // namespace
+#endif
+
+// After TracerAdvection: which tracers are zero on a whole subdomain (all their level flags of the last sub-cycle are
+// 0: the levels, halo included, held no non-zero value before the last transport, so the compute cells hold none
+// after it).  The vertical remap leaves such a field as it is.  nullptr when the flags are not those of a
+// TracerAdvection call that has just run (Core::tracer_flags_fresh, set by step()) or the shortcuts are off.
+const int* tracer_zero_fields(Core& c, int nq) {
+#ifndef PACE_HOST_EMU
+  if (!zero_paths_enabled() || !c.tracer_flags_fresh) return nullptr;
+  auto it = c.scratch.find("tr.level_nonzero");
+  if (it == c.scratch.end()) return nullptr;
+  const Geo g = c.g;
+  int* zero;
+  auto iz = c.scratch.find("tr.field_zero");
+  if (iz == c.scratch.end()) {
+    void* ptr = nullptr;
+    if (cudaMalloc(&ptr, sizeof(int) * (size_t)g.nt * 9) != cudaSuccess) { c.err = "cudaMalloc failed for tr.field_zero"; return nullptr; }
+    c.owned.push_back(ptr);
+    c.scratch["tr.field_zero"] = (double*)ptr;
+    zero = (int*)ptr;
+  } else {
+    zero = (int*)iz->second;
+  }
+  ++launch_counter();
+  k_fields_all_zero<<<dim3(g.nt, 9), 128, 0, c.stream>>>((const int*)it->second, g.nt * (g.nz + 1), g.nz, nq, zero);
+  return zero;
+#else
+  (void)c; (void)nq;
+  return nullptr;
+#endif
+}
+
 // one sub-cycle: apply_mass_flux, then fvtp2d + apply_tracer_flux for each tracer (tracer_2d_1l.py:381-411)
 // first_subcycle = false: the level flags of the previous sub-cycle are brought up to date from the halo frame
 int tracer_substep(Core& c, int nq, bool first_subcycle) {

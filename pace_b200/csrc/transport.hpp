@@ -23,6 +23,7 @@ int fvtp2d(Core& c, const Fvtp2dArgs& a);
 // level_nonzero flags of a field (see Fvtp2dArgs); returns a library-owned device array of nt * nk ints, or nullptr
 // when the build has no such kernel (host emulation: everything is computed)
 const int* level_nonzero_flags(Core& c, const double* q, int nk, int slot = 9, bool frame_only = false);
+const int* tracer_zero_fields(Core& c, int nq);
 
 // heat_diss (d_sw.py:87-125) applied to the damping fluxes of w inside the DelnFlux kernels (optional)
 struct DelnHeat {
