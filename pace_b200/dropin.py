@@ -333,6 +333,8 @@ class DycoreToPhysics:
                  dycore):
         del stencil_factory, quantity_factory, dycore_config
         if do_dry_convective_adjust:
+            # the reference's own call path raises for this option (TypeError at fv_subgridz.py:874: DycoreState.pe is a
+            # Quantity and is indexed there; oracle/probe_reference_subgridz.py), so there is nothing to reproduce
             raise NotImplementedError("pace_b200: do_dry_convective_adjust (fv_subgridz) is not implemented")
         self._dycore_only = bool(dycore_only)
         self._owner = dycore
